@@ -1,0 +1,280 @@
+"""Run the UNMODIFIED reference ``point_foot.py`` behind ``sys.modules`` stubs.  ORACLE / TEST CODE.
+
+Only usable where /root/reference exists (the build container).  It pins ``oracle.pointfoot_ref``
+and generates ``tests/golden/*.npz`` (tests/golden/make_golden.py).  Nothing on the GPU box imports it.
+
+What is stubbed: ``isaacgym{,.gymapi,.gymutil,.gymtorch,.terrain_utils}`` = inert mocks,
+``isaacgym.torch_utils`` = oracle.isaacgym_torch_utils, ``rsl_rl*`` and ``matplotlib*`` = empty modules.
+``PointFoot`` is built with ``object.__new__`` and the fields its ctor / ``_create_envs`` would have filled
+from PhysX (point_foot.py:56-77, 900-968) are set from the URDF constants instead; then the reference's own
+``_parse_cfg`` / ``_init_buffers`` / ``_prepare_reward_function`` run.  Random draws are routed to the
+counter-based contract (oracle.rng) by wrapping the five methods that draw; ``torch.save``
+(point_foot.py:334) is neutralised.
+"""
+import os
+import sys
+import types
+import contextlib
+
+import numpy as np
+import torch
+
+from . import rng
+from . import isaacgym_torch_utils as _tu
+
+REFERENCE_ROOT = os.environ.get("POINTFOOT_REFERENCE_ROOT", "/root/reference")
+
+
+def reference_available():
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "legged_gym/envs/pointfoot/point_foot.py"))
+
+
+class _Anything:
+    """Inert object: any attribute / call returns another inert object."""
+    def __init__(self, *a, **k):
+        pass
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        return _Anything()
+
+    def __call__(self, *a, **k):
+        return _Anything()
+
+    def __iter__(self):
+        return iter(())
+
+
+class FakeGym:
+    """The 12 ``gym.*`` calls the hot path makes (point_foot.py:182-185, 200-202, 562-564, 586-588, 606-611)
+    are inert; the acquire_* calls hand out the synthetic state tensors."""
+    def __init__(self, tensors):
+        self.t = tensors
+        self.calls = []
+
+    def acquire_actor_root_state_tensor(self, sim): return self.t["root_states"]
+    def acquire_dof_state_tensor(self, sim): return self.t["dof_state"]
+    def acquire_net_contact_force_tensor(self, sim): return self.t["contact_forces"]
+    def acquire_rigid_body_state_tensor(self, sim): return self.t["rigid_body_states"]
+
+    def __getattr__(self, name):
+        def _inert(*a, **k):
+            self.calls.append(name)
+            return None
+        return _inert
+
+
+_installed = False
+
+
+def install_stubs():
+    global _installed
+    if _installed:
+        return
+    if not reference_available():
+        raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
+
+    def mod(name, **attrs):
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+        sys.modules[name] = m
+        return m
+
+    class _ModAny(types.ModuleType):
+        def __getattr__(self, name):
+            if name.startswith("__"):
+                raise AttributeError(name)
+            return _Anything
+
+    def anymod(name):
+        m = _ModAny(name)
+        sys.modules[name] = m
+        return m
+
+    ig = mod("isaacgym")
+    ig.gymapi = anymod("isaacgym.gymapi")
+    ig.gymutil = anymod("isaacgym.gymutil")
+    ig.terrain_utils = anymod("isaacgym.terrain_utils")
+    ig.gymtorch = mod("isaacgym.gymtorch", wrap_tensor=lambda t: t, unwrap_tensor=lambda t: t)
+    tu = mod("isaacgym.torch_utils")
+    for k in ("to_torch", "get_axis_params", "normalize", "quat_apply", "quat_rotate",
+              "quat_rotate_inverse", "torch_rand_float"):
+        setattr(tu, k, getattr(_tu, k))
+    tu.torch = torch
+    tu.np = np            # point_foot.py uses ``np`` via ``from isaacgym.torch_utils import *`` (:470, :991)
+    ig.torch_utils = tu
+    for name in ("rsl_rl", "rsl_rl.env", "rsl_rl.runners", "rsl_rl.modules", "rsl_rl.algorithms",
+                 "matplotlib", "matplotlib.pyplot", "onnxruntime"):
+        anymod(name)
+    sys.modules["rsl_rl.env"].VecEnv = object
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    _installed = True
+
+
+# --------------------------------------------------------------------------------------------
+# PF_P441A constants PhysX would have reported (resources/robots/PF_P441A/urdf/PF_P441A.urdf:148,191,234,
+# 390,433,476).  Body order after fixed-joint collapse: base, abad_L, hip_L, knee_L, foot_L, abad_R, hip_R,
+# knee_R, foot_R.
+DOF_NAMES = ["abad_L_Joint", "hip_L_Joint", "knee_L_Joint", "abad_R_Joint", "hip_R_Joint", "knee_R_Joint"]
+BODY_NAMES = ["base_Link", "abad_L_Link", "hip_L_Link", "knee_L_Link", "foot_L_Link",
+              "abad_R_Link", "hip_R_Link", "knee_R_Link", "foot_R_Link"]
+DOF_LOWER = [-0.38397, -1.012291, -0.872665, -1.39626, -1.518436, -1.396263]
+DOF_UPPER = [1.39626, 1.518436, 1.396263, 0.38397, 1.012291, 0.872665]
+DOF_VELOCITY = [20.0, 20.0, 20.0, 20.0, 20.0, 50.0]
+DOF_EFFORT = [80.0] * 6
+
+
+@contextlib.contextmanager
+def _patched(obj, name, value):
+    old = getattr(obj, name)
+    setattr(obj, name, value)
+    try:
+        yield
+    finally:
+        setattr(obj, name, old)
+
+
+def _make_class():
+    """Subclass of the reference PointFoot whose only additions route RNG draws to the contract."""
+    install_stubs()
+    from legged_gym.envs.pointfoot.point_foot import PointFoot
+
+    class RefPointFoot(PointFoot):
+        rng_seed = 1
+        env_id_offset = 0
+
+        def _ctx(self, purpose, env_ids, lane0=0):
+            ids = env_ids.cpu().numpy() if torch.is_tensor(env_ids) else np.asarray(env_ids)
+            return rng.draw(rng.DrawContext(self.rng_seed, int(self.common_step_counter), purpose, ids,
+                                            self.env_id_offset, lane0))
+
+        def _add_noise_to_obs(self):
+            def rand_like(t):
+                return rng.active_uniform(t.shape, t.device)
+            with self._ctx(rng.OBS_NOISE, np.arange(self.num_envs)), \
+                    _patched(torch, "rand_like", rand_like), _patched(torch, "save", lambda *a, **k: None):
+                super()._add_noise_to_obs()
+
+        def _reset_dofs(self, env_ids):
+            with self._ctx(rng.RESET_DOF, env_ids):
+                super()._reset_dofs(env_ids)
+
+        def _reset_root_states(self, env_ids):
+            with self._ctx(rng.RESET_ROOT, env_ids, 0 if self.custom_origins else 2):
+                super()._reset_root_states(env_ids)
+
+        def _push_robots(self):
+            with self._ctx(rng.PUSH, np.arange(self.num_envs)):
+                super()._push_robots()
+
+        def _update_terrain_curriculum(self, env_ids):
+            def randint_like(t, high):
+                return rng.active_randint(t.shape, high, t.device).to(t.dtype)
+            with self._ctx(rng.CURRICULUM, env_ids), _patched(torch, "randint_like", randint_like):
+                super()._update_terrain_curriculum(env_ids)
+
+    return RefPointFoot
+
+
+def make_cfg(task, num_envs, mutate=None):
+    install_stubs()
+    from legged_gym.envs.pointfoot.mixed_terrain.pointfoot_rough_config import PointFootRoughCfg
+    from legged_gym.envs.pointfoot.flat.pointfoot_flat_config import PointFootFlatCfg
+    cfg = {"pointfoot_rough": PointFootRoughCfg, "pointfoot_flat": PointFootFlatCfg}[task]()
+    cfg.env.num_envs = num_envs
+    if mutate is not None:
+        mutate(cfg)
+    return cfg
+
+
+def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0):
+    """Build the reference ``PointFoot`` over the synthetic tensors in ``state`` (a dict of CPU torch tensors,
+    see pointfoot_b200.synth.make_state).  The four PhysX-owned tensors are used in place (the reference
+    writes reset rows into them, point_foot.py:557-588)."""
+    cls = _make_class()
+    from types import SimpleNamespace
+    N = int(state["root_states"].shape[0])
+    cfg = make_cfg(task, N, mutate_cfg)
+    env = object.__new__(cls)
+    env.rng_seed, env.env_id_offset = seed, env_id_offset
+
+    # ---- what __init__ sets (point_foot.py:30-77) ----
+    env.terminate = None
+    env.cfg = cfg
+    env.sim_params = SimpleNamespace(dt=cfg.sim.dt, use_gpu_pipeline=False)
+    env.height_samples = None
+    env.debug_viz = False
+    env.init_done = False
+    env._parse_cfg()
+    env.gym = FakeGym(state)
+    env.sim = None
+    env.physics_engine = None
+    env.sim_device = env.device = 'cpu'
+    env.headless = True
+    env.num_envs = N
+    env.num_obs = cfg.env.num_propriceptive_obs
+    env.num_privileged_obs = cfg.env.num_privileged_obs
+    env.num_actions = cfg.env.num_actions
+    env.proprioceptive_obs_buf = torch.zeros(N, env.num_obs)
+    env.rew_buf = torch.zeros(N)
+    env.reset_buf = torch.ones(N, dtype=torch.long)
+    env.episode_length_buf = torch.zeros(N, dtype=torch.long)
+    env.time_out_buf = torch.zeros(N, dtype=torch.bool)
+    env.privileged_obs_buf = (torch.zeros(N, env.num_privileged_obs)
+                              if env.num_privileged_obs is not None else None)
+    env.extras = {}
+    env.enable_viewer_sync = True
+    env.viewer = None
+
+    # ---- what create_sim / _create_envs set from PhysX (point_foot.py:384-401, 870-968) ----
+    env.up_axis_idx = 2
+    env.num_dof = env.num_dofs = 6
+    env.num_bodies = 9
+    env.dof_names = list(DOF_NAMES)
+    props = np.zeros(6, dtype=[("lower", "f4"), ("upper", "f4"), ("velocity", "f4"), ("effort", "f4")])
+    props["lower"], props["upper"] = DOF_LOWER, DOF_UPPER
+    props["velocity"], props["effort"] = DOF_VELOCITY, DOF_EFFORT
+    env._process_dof_props(props, 0)                       # reference code: soft limits, point_foot.py:449-463
+
+    def idx(names):
+        out = []
+        for n in names:
+            out.extend(i for i, s in enumerate(BODY_NAMES) if n in s)
+        return torch.tensor(out, dtype=torch.long)
+    env.feet_indices = torch.tensor([i for i, s in enumerate(BODY_NAMES) if cfg.asset.foot_name in s])
+    env.penalised_contact_indices = idx(cfg.asset.penalize_contacts_on)
+    env.termination_contact_indices = idx(cfg.asset.terminate_after_contacts_on)
+    isl = cfg.init_state
+    env.base_init_state = _tu.to_torch(isl.pos + isl.rot + isl.lin_vel + isl.ang_vel)
+    env.base_mass = state["base_mass"].clone()
+    if cfg.terrain.mesh_type in ("heightfield", "trimesh"):
+        env.terrain = SimpleNamespace(cfg=cfg.terrain, env_length=cfg.terrain.terrain_length,
+                                      env_origins=state["terrain_origins"].numpy())
+        env.height_samples = state["height_samples"]
+    env._get_env_origins()                                   # reference code, point_foot.py:970-997
+    if env.custom_origins:
+        env.terrain_levels = state["terrain_levels"].clone()
+        env.terrain_types = state["terrain_types"].clone()
+        env.env_origins[:] = env.terrain_origins[env.terrain_levels, env.terrain_types]
+    env.envs, env.actor_handles = [None] * N, [None] * N
+
+    # ---- the reference's own buffer setup ----
+    env._include_feet_height_rewards = env._check_if_include_feet_height_rewards()
+    env._init_buffers()
+    env._prepare_reward_function()
+    env.init_done = True
+
+    # ---- internal state the synthetic generator randomises ----
+    env.commands[:] = state["commands"]
+    env.episode_length_buf[:] = state["episode_length_buf"]
+    for k in ("last_actions", "last_dof_vel", "feet_air_time", "last_feet_air_time", "contact_filt",
+              "first_contact", "last_contacts", "current_max_feet_height", "last_max_feet_height"):
+        if k in state:
+            getattr(env, k)[:] = state[k]
+    if "episode_sums" in state:
+        for i, name in enumerate(env.episode_sums.keys()):
+            env.episode_sums[name][:] = state["episode_sums"][i]
+    env.common_step_counter = int(state.get("common_step_counter", 0))
+    return env
