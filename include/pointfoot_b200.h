@@ -1,0 +1,186 @@
+/* pointfoot_b200 -- C ABI of the B200-native hot path of peachvegetable/pointfoot (legged_gym fork).
+ *
+ * Plain pointers and sizes only; every pointer is a DEVICE pointer into caller-owned memory (torch tensors,
+ * or PhysX tensors wrapped zero-copy) unless the name says host.  No allocation, no ownership transfer;
+ * the only retained state is the opaque pf_ctx (constants + small scratch).  Every entry point returns 0
+ * on success; on failure a non-zero code, with pf_last_error() giving the message.  All launches go to the
+ * cudaStream_t passed as `void* stream` (NULL = legacy default stream).  One ctx per device; thread-compatible.
+ *
+ * Citations: PF = legged_gym/envs/pointfoot/point_foot.py, LR = legged_gym/envs/base/legged_robot.py,
+ * rsl_rl = rsl_rl v1.0.2 (third-party).
+ */
+#ifndef POINTFOOT_B200_H
+#define POINTFOOT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PF_ABI_VERSION 1
+#define PF_MAX_DOF 6
+#define PF_MAX_BODIES 9
+#define PF_NUM_FEET 2
+#define PF_MAX_REWARD_TERMS 24
+#define PF_MAX_HEIGHT_POINTS 256
+#define PF_MAX_OBS 512
+
+/* reward term ids: the 24 _reward_* methods, PF:1132-1253 */
+enum pf_reward_id {
+    PF_REW_LIN_VEL_Z = 0, PF_REW_ANG_VEL_XY, PF_REW_ORIENTATION, PF_REW_BASE_HEIGHT, PF_REW_TORQUES,
+    PF_REW_DOF_VEL, PF_REW_DOF_ACC, PF_REW_ACTION_RATE, PF_REW_COLLISION, PF_REW_TERMINATION,
+    PF_REW_DOF_POS_LIMITS, PF_REW_DOF_VEL_LIMITS, PF_REW_TORQUE_LIMITS, PF_REW_TRACKING_LIN_VEL,
+    PF_REW_TRACKING_ANG_VEL, PF_REW_FEET_AIR_TIME, PF_REW_NO_FLY, PF_REW_UNBALANCE_FEET_AIR_TIME,
+    PF_REW_UNBALANCE_FEET_HEIGHT, PF_REW_STUMBLE, PF_REW_STAND_STILL, PF_REW_FEET_CONTACT_FORCES,
+    PF_REW_FEET_DISTANCE, PF_REW_SURVIVAL, PF_REW_COUNT
+};
+
+enum pf_control_type { PF_CONTROL_P = 0, PF_CONTROL_V = 1, PF_CONTROL_T = 2 };   /* PF:537-546 */
+enum pf_terrain_kind { PF_TERRAIN_PLANE = 0, PF_TERRAIN_HEIGHTFIELD = 1 };     /* 'plane' vs 'heightfield'/'trimesh' */
+/* (x / horizontal_scale).long() at PF:1102: CPU eager divides, CUDA eager multiplies by fp32 1/scale. */
+enum pf_index_div_mode { PF_DIV_TRUE = 0, PF_DIV_RECIPROCAL = 1 };
+
+/* Constants of one task, flattened from the nested cfg classes (pointfoot_rough_config.py, PF:999-1009,
+ * PF:698-820).  POD, copied into the ctx at pf_ctx_create. */
+typedef struct pf_params {
+    int32_t abi_version;              /* = PF_ABI_VERSION */
+    int32_t num_envs;                 /* envs on THIS device */
+    int64_t env_id_offset;            /* global id of local env 0 (multi-GPU block sharding) */
+    int32_t num_dof, num_bodies;      /* 6, 9 */
+    int32_t num_commands;             /* 3 flat / 4 rough */
+    int32_t num_obs, num_priv_obs;    /* 27, 27/148; num_priv_obs = 0 => no privileged buffer */
+    uint32_t seed;                    /* RNG contract seed (train cfg seed) */
+
+    /* control, PF:523-547 */
+    int32_t control_type, decimation;
+    float action_scale, sim_dt, dt;   /* dt = decimation * sim_dt, PF:1000 */
+    float clip_actions, clip_obs;     /* PF:176, 189 */
+    float p_gains[PF_MAX_DOF], d_gains[PF_MAX_DOF], torque_limits[PF_MAX_DOF];
+    float default_dof_pos[PF_MAX_DOF];
+    float dof_pos_limits[PF_MAX_DOF][2], dof_vel_limits[PF_MAX_DOF];   /* soft limits, PF:449-463 */
+
+    /* body index lists, PF:951-968 */
+    int32_t feet_indices[PF_NUM_FEET];
+    int32_t num_termination, termination_indices[PF_MAX_BODIES];
+    int32_t num_penalised, penalised_indices[PF_MAX_BODIES];
+
+    /* episode / commands, PF:479-493, 1006-1009 */
+    float max_episode_length;         /* np.ceil(episode_length_s/dt), compared as float: PF:246 */
+    float max_episode_length_s;
+    int32_t resample_period;          /* int(resampling_time/dt), PF:484 */
+    int32_t heading_command;          /* PF:487 */
+    int32_t resample_commands;        /* 0 = PF (no-op, PF:498-521), 1 = LR:337-351 */
+    float cmd_range[4][2];            /* lin_vel_x, lin_vel_y, ang_vel_yaw, heading */
+
+    /* observations, PF:320-382, 652-695 */
+    float obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel, obs_scale_height;
+    float commands_scale[3];
+    int32_t add_noise;
+    int32_t measure_heights_actor, measure_heights_critic;
+
+    /* terrain + height scan, PF:1032-1112 */
+    int32_t terrain_kind, index_div_mode;
+    int32_t hf_rows, hf_cols;         /* height_samples.shape */
+    float border_size, horizontal_scale, vertical_scale;
+    int32_t num_height_points;        /* P; 0 when nothing measures heights */
+
+    /* resets + curriculum, PF:249-299, 549-588, 613-636 */
+    int32_t custom_origins, terrain_curriculum;
+    int32_t max_terrain_level, num_terrain_types;    /* terrain_origins is [max_terrain_level][num_terrain_types][3] */
+    float terrain_env_length;
+    float base_init_state[13];
+    int32_t send_timeouts;
+
+    /* rewards, PF:301-318, 796-820: terms in summation order (alphabetical), scales already * dt */
+    int32_t num_reward_terms;                          /* excludes 'termination' */
+    int32_t reward_ids[PF_MAX_REWARD_TERMS];
+    float reward_scales[PF_MAX_REWARD_TERMS];
+    int32_t has_termination_term; float termination_scale;   /* added after the clip, PF:315-318 */
+    int32_t only_positive_rewards;
+    int32_t include_feet_height_rewards;               /* PF:232-237 */
+    float base_height_target, soft_dof_vel_limit, soft_torque_limit, tracking_sigma, max_contact_force;
+    float min_feet_air_time, max_feet_air_time, min_feet_distance;
+
+    /* push, PF:590-611 */
+    float max_push_vel_xy;
+} pf_params;
+
+/* Device pointers of one env instance.  Shapes in [] with N = num_envs, D = num_dof, B = num_bodies,
+ * F = 2 feet, C = num_commands, P = num_height_points, R = num_reward_terms (+1 if termination term). */
+typedef struct pf_env_buffers {
+    /* PhysX-owned, AoS, written in place for reset rows (PF:713-724) */
+    float* root_states;               /* [N,13] pos3 quat4(xyzw) linvel3 angvel3 */
+    float* dof_state;                 /* [N*D,2] (pos, vel) */
+    const float* contact_forces;      /* [N*B,3] */
+    const float* rigid_body_states;   /* [N*B,13] */
+    /* env-owned */
+    float* actions;                   /* [N,D] clipped actions (PF:177) */
+    float* torques;                   /* [N,D] */
+    float* commands;                  /* [N,C] */
+    int64_t* episode_length_buf;      /* [N] */
+    float* base_lin_vel; float* base_ang_vel; float* projected_gravity;   /* [N,3] each */
+    float* last_actions; float* last_dof_vel;    /* [N,D] */
+    float* last_root_vel;             /* [N,6] */
+    float* feet_air_time; float* last_feet_air_time;                    /* [N,F] */
+    float* current_max_feet_height; float* last_max_feet_height; float* feet_height;   /* [N,F] */
+    uint8_t* contact_filt; uint8_t* first_contact; uint8_t* last_contacts;      /* [N,F] torch.bool */
+    float* episode_sums;              /* [R,N] one row per term, rows in reward order (termination last) */
+    float* rew_buf;                   /* [N] */
+    uint8_t* reset_buf; uint8_t* time_out_buf; uint8_t* terminate;      /* [N] torch.bool */
+    float* obs_buf;                   /* [N,num_obs] */
+    float* priv_obs_buf;              /* [N,num_priv_obs] or NULL */
+    float* measured_heights;          /* [N,P] or NULL (not materialised) */
+    /* terrain (rough only, else NULL) */
+    const int16_t* height_samples;    /* [hf_rows,hf_cols] */
+    const float* terrain_origins;     /* [max_terrain_level,num_terrain_types,3] */
+    int64_t* terrain_levels;          /* [N] */
+    const int64_t* terrain_types;     /* [N] */
+    float* env_origins;               /* [N,3] */
+    /* per-step outputs for the caller / gym setters */
+    int32_t* reset_ids;               /* [N] ascending ids of reset envs (PF:221, 561, 585) */
+    int32_t* reset_count;             /* [1] device count */
+    float* episode_stats;             /* [R+2] extras["episode"]: R term means /max_episode_length_s,
+                                         terrain_level mean, reset count as float; rewritten only when >=1 reset (PF:259) */
+} pf_env_buffers;
+
+typedef struct pf_ctx pf_ctx;
+
+const char* pf_last_error(void);
+int pf_abi_version(void);
+int pf_sizeof_params(void);        /* layout checks for FFI bindings */
+int pf_sizeof_env_buffers(void);
+
+/* Create / destroy.  noise_scale_vec: HOST float[num_priv_obs or num_obs] (PF:652-695 output, obs part then
+ * privileged-extra part); height_points_xy: HOST float[P][2] grid in the base frame (PF:1032-1046). */
+int pf_ctx_create(const pf_params* params, const float* noise_scale_vec_host,
+                  const float* height_points_xy_host, pf_ctx** out);
+int pf_ctx_destroy(pf_ctx* ctx);
+
+/* PF:176-177 + PF:523-547 (LR:353-375).  If actions_in != NULL it is clipped to +-clip_actions into
+ * bufs->actions first (the step() prologue); torques written to bufs->torques. */
+int pf_pd_torques(pf_ctx* ctx, const pf_env_buffers* bufs, const float* actions_in, void* stream);
+
+/* PF:195-227 + the obs clip of PF:189-192: everything post_physics_step does between the gym refresh calls
+ * and the return of step(); `common_step_counter` is the value AFTER the increment at PF:205.  Also fills
+ * reset_ids / reset_count / episode_stats (PF:221, 276-288). */
+int pf_post_physics_step(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
+
+/* PF:590-611: random push forces into forces[N,B,3] (body 0 rows; everything else zeroed).
+ * max_push_force = base_mass.mean() * max_push_vel_xy / sim_dt, evaluated by the host in double (PF:592-596). */
+int pf_push_forces(pf_ctx* ctx, const pf_env_buffers* bufs, float* forces, float max_push_force,
+                   int64_t common_step_counter, void* stream);
+
+/* PF:137-139 reset(): reset_idx over ALL envs (before the zero-action step). */
+int pf_reset_all(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
+
+/* Convenience for hosts without a device runtime of their own (the cgo/ctypes drop-in): host-buffer step.
+ * actions_host[N,D] -> H2D, decimation x pd_torques, post_physics_step, obs/priv/rew/reset -> D2H, sync. */
+int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const float* actions_host, float* obs_host,
+                 float* priv_obs_host, float* rew_host, uint8_t* reset_host, int64_t common_step_counter,
+                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POINTFOOT_B200_H */

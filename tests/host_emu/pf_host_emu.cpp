@@ -1,0 +1,81 @@
+// Host emulation of the env kernels: the SAME pf_env_core.cuh the CUDA kernels use, driven by serial loops
+// over host memory.  TEST INFRASTRUCTURE ONLY (built by tests/host_emu/build.sh into tests/host_emu/_build/,
+// never linked into or loaded by the product).  It lets the per-env logic be checked against the oracle in a
+// container without a GPU; the GPU parity tests then only have to catch staging / indexing mistakes.
+#include "../../pointfoot_b200/csrc/pf_env_core.cuh"
+#include <vector>
+
+extern "C" int pf_emu_pd_torques(const pf_params* Pp, const pf_env_buffers* Bp, const float* actions_in) {
+    const pf_params& P = *Pp; const pf_env_buffers& B = *Bp;
+    const int D = P.num_dof;
+    for (int e = 0; e < P.num_envs; ++e)
+        for (int d = 0; d < D; ++d) {
+            if (actions_in) B.actions[e * D + d] = pf_clipf(actions_in[e * D + d], -P.clip_actions, P.clip_actions);
+            B.torques[e * D + d] = pf_pd_torque(P, d, B.actions[e * D + d], B.dof_state[(e * D + d) * 2],
+                                                B.dof_state[(e * D + d) * 2 + 1], B.last_dof_vel[e * D + d]);
+        }
+    return 0;
+}
+
+extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffers* Bp, const float* noise_vec,
+                                        const float* height_points_xy, long long common_step_counter) {
+    const pf_params& P = *Pp; const pf_env_buffers& B = *Bp;
+    const int D = P.num_dof, N = P.num_envs, Pn = P.num_height_points;
+    const uint32_t step = (uint32_t)common_step_counter;
+    const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
+    const int base_w = pf_obs_base_width(P);
+    std::vector<int16_t> raw(Pn > 0 ? Pn : 1);
+    std::vector<double> stat(R, 0.0);
+    int count = 0;
+    for (int e = 0; e < N; ++e) {
+        PfEnvIn in; PfEnvOut out;
+        float root_pre[13];
+        for (int i = 0; i < 13; ++i) root_pre[i] = B.root_states[e * 13 + i];
+        in.root = root_pre;
+        in.dof = B.dof_state + (size_t)e * D * 2;
+        in.cf = B.contact_forces + (size_t)e * P.num_bodies * 3;
+        for (int f = 0; f < PF_NUM_FEET; ++f)
+            in.feet_pos[f] = B.rigid_body_states + ((size_t)e * P.num_bodies + P.feet_indices[f]) * 13;
+        in.height_sum = 0.0f; in.have_heights = Pn > 0;
+        if (Pn > 0) {
+            float zn, wn; pf_yaw_quat(root_pre + 3, zn, wn);
+            for (int p = 0; p < Pn; ++p) {
+                raw[p] = pf_scan_point(P, B.height_samples, zn, wn, height_points_xy[2 * p],
+                                       height_points_xy[2 * p + 1], root_pre[0], root_pre[1]);
+                const float h = (float)raw[p] * P.vertical_scale;
+                if (B.measured_heights) B.measured_heights[(size_t)e * Pn + p] = h;
+                in.height_sum += root_pre[2] - h;
+            }
+        }
+        pf_env_step(P, B, e, in, step, nullptr, out);
+        if (out.reset) {
+            std::vector<float> sums(R);
+            pf_env_reset(P, B, e, root_pre, out.commands, step, true, sums.data(), out);
+            for (int k = 0; k < R; ++k) stat[k] += sums[k];
+            B.reset_ids[count++] = e;
+        }
+        // observations, PF:320-382 + clip PF:189-192
+        const uint32_t nk = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
+        const float* act = B.actions + e * D;
+        for (int j = 0; j < P.num_obs; ++j) {
+            const float v = j < base_w ? pf_obs_base_col(P, out, act, j) : pf_obs_height_col(P, out.root_z, raw[j - base_w]);
+            B.obs_buf[(size_t)e * P.num_obs + j] = pf_obs_finish(P, v, nk, j, noise_vec);
+        }
+        if (B.priv_obs_buf)
+            for (int j = 0; j < P.num_priv_obs; ++j) {
+                const float v = j < base_w ? pf_obs_base_col(P, out, act, j) : pf_obs_height_col(P, out.root_z, raw[j - base_w]);
+                B.priv_obs_buf[(size_t)e * P.num_priv_obs + j] = pf_obs_finish(P, v, nk, j, noise_vec);
+            }
+        // PF:225-227
+        for (int d = 0; d < D; ++d) { B.last_actions[e * D + d] = act[d]; B.last_dof_vel[e * D + d] = out.dof_vel[d]; }
+        for (int i = 0; i < 6; ++i) B.last_root_vel[e * 6 + i] = B.root_states[e * 13 + 7 + i];
+    }
+    *B.reset_count = count;
+    if (count > 0) {
+        for (int k = 0; k < R; ++k) B.episode_stats[k] = (float)(stat[k] / count) / P.max_episode_length_s;
+        double lv = 0; if (B.terrain_levels) for (int e = 0; e < N; ++e) lv += (double)B.terrain_levels[e];
+        B.episode_stats[R] = (float)(lv / N);
+        B.episode_stats[R + 1] = (float)count;
+    }
+    return 0;
+}
