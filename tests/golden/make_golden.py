@@ -1,0 +1,77 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference point_foot.py (oracle/ref_harness.py) on seeded
+synthetic states.  Only runs where /root/reference exists; the .npz files are committed and travel to the GPU box.
+
+    python tests/golden/make_golden.py
+
+Each file holds the inputs (every state tensor except the 5.5 MB heightfield, which is regenerated from its seed
+and pinned by a checksum) and, for each of STEPS chained steps, the outputs and the state the reference left.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import common                                     # noqa: E402
+from pointfoot_b200 import synth                  # noqa: E402
+from oracle import ref_harness                    # noqa: E402
+
+STEPS = 3
+N = 64
+FIELDS = ("root_states", "dof_state", "commands", "episode_length_buf", "last_actions", "last_dof_vel",
+          "last_root_vel", "feet_air_time", "last_feet_air_time", "current_max_feet_height", "last_max_feet_height",
+          "contact_filt", "first_contact", "last_contacts", "base_lin_vel", "base_ang_vel", "projected_gravity",
+          "torques", "terminate", "time_out_buf")
+
+
+def actions_for(task, seed, i):
+    return synth.make_state(N, task, seed=seed + 100 + i)["actions"] * (30.0 if i == 1 else 1.0)
+
+
+def hf_checksum(hf):
+    return hashlib.sha256(hf.numpy().tobytes()).hexdigest()
+
+
+def generate(task, seed=1, mutate=None, tag=""):
+    state = synth.make_state(N, task, seed=seed, adversarial=True)
+    out = {}
+    for k, v in state.items():
+        if k == "height_samples":
+            out["hf_sha256"] = np.frombuffer(hf_checksum(v).encode(), dtype=np.uint8)
+        elif torch.is_tensor(v):
+            out["in_" + k] = v.numpy().copy()
+    env = ref_harness.build_reference_env(task, common.clone_state(state), seed=seed, mutate_cfg=mutate)
+    names = list(env.episode_sums.keys())
+    out["reward_names"] = np.array(names)
+    for i in range(STEPS):
+        a = actions_for(task, seed, i)
+        obs, priv, rew, reset, extras = env.step(a.clone())
+        p = f"s{i}_"
+        out[p + "obs"], out[p + "rew"], out[p + "reset"] = obs.numpy().copy(), rew.numpy().copy(), reset.numpy().copy()
+        if priv is not None:
+            out[p + "priv"] = priv.numpy().copy()
+        for k in FIELDS:
+            out[p + k] = getattr(env, k).numpy().copy()
+        out[p + "episode_sums"] = torch.stack([env.episode_sums[n] for n in names]).numpy().copy()
+        out[p + "reset_ids"] = reset.nonzero().flatten().to(torch.int32).numpy()
+        if task == "pointfoot_rough":
+            out[p + "terrain_levels"] = env.terrain_levels.numpy().copy()
+            out[p + "env_origins"] = env.env_origins.numpy().copy()
+            out[p + "measured_heights"] = env.measured_heights.numpy().copy()
+        ep = extras.get("episode", {})
+        out[p + "extras_episode"] = np.array([float(ep["rew_" + n]) for n in names] if ep else [], np.float32)
+        out[p + "time_outs"] = extras["time_outs"].numpy().copy()
+    path = os.path.join(HERE, f"{task}{tag}_n{N}.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    if not ref_harness.reference_available():
+        raise SystemExit("reference not available here; golden files can only be regenerated in the build container")
+    generate("pointfoot_flat")
+    generate("pointfoot_rough")
+    generate("pointfoot_rough", mutate=common.grid187, tag="_p187")

@@ -1,0 +1,62 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/pointfoot_b200.h declares; the ctypes
+struct layouts match the header; compute entry points fail loudly (no CPU fallback) when there is no device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+import common
+from pointfoot_b200 import capi, synth
+
+HEADER = os.path.join(common.ROOT, "include", "pointfoot_b200.h")
+
+
+def declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pf_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.isfile(capi.lib_path()):
+        import __graft_entry__
+        __graft_entry__.build()
+    return capi.load()
+
+
+def test_exports_every_declared_symbol(lib):
+    names = declared_functions()
+    assert "pf_post_physics_step" in names and "pf_pd_torques" in names
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in the header but not exported"
+
+
+def test_struct_layouts_match(lib):
+    assert lib.pf_abi_version() == capi.PF_ABI_VERSION
+    assert lib.pf_sizeof_params() == C.sizeof(capi.PfParams)
+    assert lib.pf_sizeof_env_buffers() == C.sizeof(capi.PfEnvBuffers)
+
+
+def test_no_cpu_fallback(lib):
+    if torch.cuda.is_available():
+        pytest.skip("has a device")
+    st = synth.make_state(8, "pointfoot_flat")
+    cfg, P, noise, pts, names = common.make_params("pointfoot_flat", st)
+    ctx = C.c_void_p()
+    rc = lib.pf_ctx_create(C.byref(P), C.c_void_p(noise.data_ptr()), None, C.byref(ctx))
+    assert rc != 0 and b"no CUDA device" in lib.pf_last_error()
+
+
+def test_bad_params_are_rejected(lib):
+    st = synth.make_state(8, "pointfoot_flat")
+    cfg, P, noise, pts, names = common.make_params("pointfoot_flat", st)
+    P.abi_version = 99
+    ctx = C.c_void_p()
+    assert lib.pf_ctx_create(C.byref(P), C.c_void_p(noise.data_ptr()), None, C.byref(ctx)) != 0
+    cfg, P, noise, pts, names = common.make_params("pointfoot_flat", st)
+    P.num_obs = 30            # reference: RuntimeError at point_foot.py:363-365
+    rc = lib.pf_ctx_create(C.byref(P), C.c_void_p(noise.data_ptr()), None, C.byref(ctx))
+    assert rc == 3 and b"observation width" in lib.pf_last_error()
