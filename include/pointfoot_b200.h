@@ -142,6 +142,13 @@ typedef struct pf_env_buffers {
     int32_t* reset_count;             /* [1] device count */
     float* episode_stats;             /* [R+2] extras["episode"]: R term means /max_episode_length_s,
                                          terrain_level mean, reset count as float; rewritten only when >=1 reset (PF:259) */
+    uint8_t* extras_time_outs;        /* [N] or NULL: extras["time_outs"] -- a copy of time_out_buf taken only on
+                                         steps with >=1 reset (PF:259-260, 287-288: the dict entry is set inside
+                                         reset_idx, after its early return) */
+    int64_t* step_counter;            /* [1] or NULL: device copy of common_step_counter.  When non-NULL,
+                                         pf_post_physics_step / pf_reset_all ignore their host argument: the step
+                                         uses *step_counter + 1 and stores it back (PF:205), so that a whole step
+                                         can be replayed from a CUDA graph */
 } pf_env_buffers;
 
 typedef struct pf_ctx pf_ctx;
@@ -174,11 +181,21 @@ int pf_push_forces(pf_ctx* ctx, const pf_env_buffers* bufs, float* forces, float
 /* PF:137-139 reset(): reset_idx over ALL envs (before the zero-action step). */
 int pf_reset_all(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
 
-/* Convenience for hosts without a device runtime of their own (the cgo/ctypes drop-in): host-buffer step.
- * actions_host[N,D] -> H2D, decimation x pd_torques, post_physics_step, obs/priv/rew/reset -> D2H, sync. */
-int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const float* actions_host, float* obs_host,
-                 float* priv_obs_host, float* rew_host, uint8_t* reset_host, int64_t common_step_counter,
-                 void* stream);
+/* Host-buffer step: the call a host without a device runtime of its own binds (cgo / ctypes drop-in), and the
+ * reference's actual deployment (the fork runs PhysX on the CPU pipeline, PF:41,50: state tensors live in host
+ * memory).  If `state` != NULL its non-NULL members (HOST, same AoS layouts as pf_env_buffers) are copied into the
+ * device tensors first; then actions_host[N,D] -> H2D, decimation x pd_torques, post_physics_step,
+ * obs / priv / rew / reset (+ torques if torques_host != NULL) -> D2H, stream sync. */
+typedef struct pf_host_state {
+    const float* root_states;         /* [N,13] */
+    const float* dof_state;           /* [N*D,2] */
+    const float* contact_forces;      /* [N*B,3] */
+    const float* rigid_body_states;   /* [N*B,13] */
+} pf_host_state;
+
+int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* state, const float* actions_host,
+                 float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
+                 int64_t common_step_counter, void* stream);
 
 #ifdef __cplusplus
 }

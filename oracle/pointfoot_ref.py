@@ -116,6 +116,7 @@ class RefEnv:
         self.episode_stats = z(R + 2)
         self.reset_ids = torch.zeros(0, dtype=torch.int32)
         self.push_forces = z(N, B, 3)
+        self.extras_time_outs = z(N, dt=torch.bool)
 
     # -------------------------------------------------------------------------------- PF:523-547
     def compute_torques(self):
@@ -375,6 +376,8 @@ class RefEnv:
         if P.terrain_curriculum:
             self.episode_stats[R] = torch.mean(self.terrain_levels.float())
         self.episode_stats[R + 1] = float(len(env_ids))
+        if P.send_timeouts:     # PF:287-288: the dict entry is (re)bound only here, i.e. on steps with >= 1 reset
+            self.extras_time_outs = self.time_out_buf
 
     # -------------------------------------------------------------------------------- PF:320-382
     def compute_observations(self):

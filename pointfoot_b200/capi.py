@@ -67,7 +67,7 @@ ENV_BUFFER_FIELDS = (
     "episode_sums", "rew_buf", "reset_buf", "time_out_buf", "terminate",
     "obs_buf", "priv_obs_buf", "measured_heights",
     "height_samples", "terrain_origins", "terrain_levels", "terrain_types", "env_origins",
-    "reset_ids", "reset_count", "episode_stats",
+    "reset_ids", "reset_count", "episode_stats", "extras_time_outs", "step_counter",
 )
 
 
@@ -111,3 +111,7 @@ def check(rc, what=""):
 def ptr(t):
     """Raw device (or host) address of a torch tensor, NULL for None."""
     return C.c_void_p(None if t is None else t.data_ptr())
+
+
+class PfHostState(C.Structure):
+    _fields_ = [(n, _P) for n in ("root_states", "dof_state", "contact_forces", "rigid_body_states")]

@@ -123,12 +123,13 @@ __device__ __forceinline__ void pf_block_partials(const pf_params& P, const PfCt
 // Fused post_physics_step (PF:195-227) + obs clip (PF:189-192).  `epb` envs per CTA (32, 64 or 128).
 __global__ void __launch_bounds__(PF_THREADS) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                      const PfCtxScratch S, const int epb,
-                                                                     const uint32_t step) {
+                                                                     const uint32_t step_arg) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const PfSmem s = pf_carve(P, epb, smem_raw);
     const int tid = threadIdx.x;
     const int e0 = blockIdx.x * epb;
     const int nenv = min(epb, P.num_envs - e0);
+    const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     const int D = P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     const int base_w = pf_obs_base_width(P);
@@ -185,13 +186,13 @@ __global__ void __launch_bounds__(PF_THREADS) pf_post_physics_kernel(const pf_pa
         in.feet_pos[0] = s.feet + tid * 6;
         in.feet_pos[1] = s.feet + tid * 6 + 3;
         in.have_heights = Pn > 0;
-        float hs = 0.0f;
         {
             const float rz = in.root[2];
             const int16_t* raw = s.raw + tid * Pn;
-            for (int p = 0; p < Pn; ++p) hs += rz - (float)raw[p] * P.vertical_scale;
+            double hs = 0.0;          // terms in fp32 like the reference, summed in double (see pf_env_core.cuh)
+            for (int p = 0; p < Pn; ++p) hs += (double)(rz - (float)raw[p] * P.vertical_scale);
+            in.height_mean = Pn > 0 ? (float)(hs / (double)Pn) : 0.0f;
         }
-        in.height_sum = hs;
         pf_env_step(P, B, e, in, step, nullptr, out);
         is_reset = out.reset;
         if (is_reset) pf_env_reset(P, B, e, in.root, out.commands, step, true, s.sums + tid * R, out);
@@ -239,12 +240,13 @@ __global__ void __launch_bounds__(PF_THREADS) pf_post_physics_kernel(const pf_pa
 // reset_idx over ALL envs (PF:137-139 reset(), before the zero-action step).
 __global__ void __launch_bounds__(PF_THREADS) pf_reset_all_kernel(const pf_params P, const pf_env_buffers B,
                                                                   const PfCtxScratch S, const int epb,
-                                                                  const uint32_t step) {
+                                                                  const uint32_t step_arg) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const PfSmem s = pf_carve(P, epb, smem_raw);
     const int tid = threadIdx.x;
     const int e0 = blockIdx.x * epb;
     const int nenv = min(epb, P.num_envs - e0);
+    const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter) : step_arg;   // reset() does not count a step
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     long long lvl = 0;
     const bool active = tid < nenv;
@@ -268,7 +270,7 @@ __global__ void __launch_bounds__(PF_THREADS) pf_reset_all_kernel(const pf_param
 // before it.  CTA 0 additionally reduces the per-term partials (one warp per statistic, fixed order).
 __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, const pf_env_buffers B,
                                                            const PfCtxScratch S, const int epb,
-                                                           const int num_step_blocks) {
+                                                           const int num_step_blocks, const int count_step) {
     __shared__ int s_warp[32];
     __shared__ int s_base;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -290,7 +292,27 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int base = s_base;
     __syncthreads();
 
+    // total number of resets (every CTA needs it for extras["time_outs"])
+    __shared__ int s_total;
+    {
+        int tot = 0;
+        for (int i = tid; i < num_step_blocks; i += 1024) tot += S.blk_count[i];
+        tot = __reduce_add_sync(0xffffffffu, tot);
+        __syncthreads();
+        if (lane == 0) s_warp[warp] = tot;
+        __syncthreads();
+        if (tid == 0) {
+            int t = 0;
+            for (int w = 0; w < 32; ++w) t += s_warp[w];
+            s_total = t;
+        }
+        __syncthreads();
+    }
+    const int total = s_total;
+    __syncthreads();
+
     const int e = blockIdx.x * 1024 + tid;
+    if (B.extras_time_outs && total > 0 && e < P.num_envs) B.extras_time_outs[e] = B.time_out_buf[e];
     const bool flag = e < P.num_envs && B.reset_buf[e] != 0;
     const unsigned m = __ballot_sync(0xffffffffu, flag);
     if (lane == 0) s_warp[warp] = __popc(m);
@@ -300,11 +322,10 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     if (flag) B.reset_ids[off + __popc(m & ((1u << lane) - 1u))] = e;
 
     if (blockIdx.x == 0) {
-        // total count: every warp needs it
-        int total = 0;
-        for (int i = lane; i < num_step_blocks; i += 32) total += S.blk_count[i];
-        total = __reduce_add_sync(0xffffffffu, total);
-        if (tid == 0) *B.reset_count = total;
+        if (tid == 0) {
+            *B.reset_count = total;
+            if (B.step_counter && count_step) *B.step_counter += 1;
+        }
         if (total > 0 && warp < R + 1) {          // PF:259: extras rebuilt only when >= 1 env resets
             if (warp < R) {
                 double acc = 0.0;
@@ -462,9 +483,9 @@ extern "C" int pf_pd_torques(pf_ctx* c, const pf_env_buffers* bufs, const float*
     return 0;
 }
 
-static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_t st) {
+static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_t st, int count_step) {
     const int blocks = (c->P.num_envs + 1023) / 1024;
-    pf_finalize_kernel<<<blocks, 1024, 0, st>>>(c->P, *bufs, c->S, c->envs_per_block, c->num_blocks);
+    pf_finalize_kernel<<<blocks, 1024, 0, st>>>(c->P, *bufs, c->S, c->envs_per_block, c->num_blocks, count_step);
     PF_CUDA(cudaGetLastError());
     return 0;
 }
@@ -475,7 +496,7 @@ extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64
     pf_post_physics_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_block,
                                                                              (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
-    return pf_launch_finalize(c, bufs, st);
+    return pf_launch_finalize(c, bufs, st, 1);
 }
 
 extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
@@ -485,7 +506,7 @@ extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t commo
     pf_reset_all_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_block,
                                                                           (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
-    return pf_launch_finalize(c, bufs, st);
+    return pf_launch_finalize(c, bufs, st, 0);
 }
 
 extern "C" int pf_push_forces(pf_ctx* c, const pf_env_buffers* bufs, float* forces, float max_push_force,
@@ -501,23 +522,33 @@ extern "C" int pf_push_forces(pf_ctx* c, const pf_env_buffers* bufs, float* forc
     return 0;
 }
 
-extern "C" int pf_step_host(pf_ctx* c, const pf_env_buffers* bufs, const float* actions_host, float* obs_host,
-                            float* priv_obs_host, float* rew_host, uint8_t* reset_host,
-                            int64_t common_step_counter, void* stream) {
+extern "C" int pf_step_host(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
+                            float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
+                            float* torques_host, int64_t common_step_counter, void* stream) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     if (!actions_host || !obs_host || !rew_host || !reset_host) return pf_fail(1, "%s", "pf_step_host: null host buffer");
     const pf_params& P = c->P;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = (size_t)P.num_envs;
-    PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, cudaMemcpyHostToDevice, st));
+    const cudaMemcpyKind H2D = cudaMemcpyHostToDevice, D2H = cudaMemcpyDeviceToHost;
+    if (hs) {
+        if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, st));
+        if (hs->dof_state) PF_CUDA(cudaMemcpyAsync(bufs->dof_state, hs->dof_state, 4 * N * P.num_dof * 2, H2D, st));
+        if (hs->contact_forces)
+            PF_CUDA(cudaMemcpyAsync((void*)bufs->contact_forces, hs->contact_forces, 4 * N * P.num_bodies * 3, H2D, st));
+        if (hs->rigid_body_states)
+            PF_CUDA(cudaMemcpyAsync((void*)bufs->rigid_body_states, hs->rigid_body_states, 4 * N * P.num_bodies * 13, H2D, st));
+    }
+    PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, H2D, st));
     for (int i = 0; i < P.decimation; ++i)
         if (int rc = pf_pd_torques(c, bufs, i == 0 ? (const float*)c->d_actions_in : nullptr, stream)) return rc;
     if (int rc = pf_post_physics_step(c, bufs, common_step_counter, stream)) return rc;
-    PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, cudaMemcpyDeviceToHost, st));
+    PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, st));
     if (priv_obs_host && bufs->priv_obs_buf)
-        PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, cudaMemcpyDeviceToHost, st));
-    PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, cudaMemcpyDeviceToHost, st));
-    PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, cudaMemcpyDeviceToHost, st));
+        PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, st));
+    PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, D2H, st));
+    PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, D2H, st));
+    if (torques_host) PF_CUDA(cudaMemcpyAsync(torques_host, bufs->torques, sizeof(float) * N * P.num_dof, D2H, st));
     PF_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

@@ -119,7 +119,9 @@ struct PfEnvIn {
     const float* dof;         // D pairs (pos, vel)
     const float* cf;          // B*3 contact forces
     const float* feet_pos[PF_NUM_FEET];   // xyz of rigid_body_states[feet_indices[f]]
-    float height_sum;         // sum_p (root_z - measured_heights[p]) over the P scan points (0 if P == 0)
+    float height_mean;        // mean_p (root_z - measured_heights[p]) over the P scan points: fp32 terms summed in
+                              // double, rounded once (ATen's cascade sum order depends on the host ISA; this is
+                              // the closest order-free statement of torch.mean, PF:1144-1147)
     bool have_heights;        // measured_heights is a tensor (rough) rather than the int 0 (PF:775)
 };
 
@@ -233,7 +235,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
         case PF_REW_ANG_VEL_XY: r = pf_sq(out.ang_vel[0]) + pf_sq(out.ang_vel[1]); break;
         case PF_REW_ORIENTATION: r = pf_sq(out.gravity[0]) + pf_sq(out.gravity[1]); break;
         case PF_REW_BASE_HEIGHT: {
-            const float bh = in.have_heights ? in.height_sum / (float)P.num_height_points : in.root[2];
+            const float bh = in.have_heights ? in.height_mean : in.root[2];
             r = pf_sq(bh - P.base_height_target);
         } break;
         case PF_REW_TORQUES: for (int d = 0; d < D; ++d) r += pf_sq(B.torques[e * D + d]); break;

@@ -80,6 +80,8 @@ def alloc_buffers(P, state, device="cpu", with_measured_heights=True):
     t["reset_ids"] = torch.zeros(N, dtype=torch.int32, device=dev)
     t["reset_count"] = torch.zeros(1, dtype=torch.int32, device=dev)
     t["episode_stats"] = z(R + 2)
+    t["extras_time_outs"] = z(N, dt=torch.bool)
+    t["step_counter"] = None
     b = capi.PfEnvBuffers()
     for name in capi.ENV_BUFFER_FIELDS:
         setattr(b, name, None if t[name] is None else t[name].data_ptr())

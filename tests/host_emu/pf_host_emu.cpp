@@ -36,7 +36,7 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
         in.cf = B.contact_forces + (size_t)e * P.num_bodies * 3;
         for (int f = 0; f < PF_NUM_FEET; ++f)
             in.feet_pos[f] = B.rigid_body_states + ((size_t)e * P.num_bodies + P.feet_indices[f]) * 13;
-        in.height_sum = 0.0f; in.have_heights = Pn > 0;
+        double hsum = 0.0; in.height_mean = 0.0f; in.have_heights = Pn > 0;
         if (Pn > 0) {
             float zn, wn; pf_yaw_quat(root_pre + 3, zn, wn);
             for (int p = 0; p < Pn; ++p) {
@@ -44,8 +44,9 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
                                        height_points_xy[2 * p + 1], root_pre[0], root_pre[1]);
                 const float h = (float)raw[p] * P.vertical_scale;
                 if (B.measured_heights) B.measured_heights[(size_t)e * Pn + p] = h;
-                in.height_sum += root_pre[2] - h;
+                hsum += (double)(root_pre[2] - h);
             }
+            in.height_mean = (float)(hsum / (double)Pn);
         }
         pf_env_step(P, B, e, in, step, nullptr, out);
         if (out.reset) {
@@ -71,6 +72,7 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
         for (int i = 0; i < 6; ++i) B.last_root_vel[e * 6 + i] = B.root_states[e * 13 + 7 + i];
     }
     *B.reset_count = count;
+    if (count > 0 && B.extras_time_outs) for (int e = 0; e < N; ++e) B.extras_time_outs[e] = B.time_out_buf[e];
     if (count > 0) {
         for (int k = 0; k < R; ++k) B.episode_stats[k] = (float)(stat[k] / count) / P.max_episode_length_s;
         double lv = 0; if (B.terrain_levels) for (int e = 0; e < N; ++e) lv += (double)B.terrain_levels[e];

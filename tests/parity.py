@@ -16,7 +16,7 @@ from pointfoot_b200 import capi, synth
 RTOL, ATOL = 1e-5, 2e-6
 
 EXACT = ("reset_buf", "time_out_buf", "terminate", "episode_length_buf", "contact_filt", "first_contact",
-         "last_contacts", "terrain_levels")
+         "last_contacts", "terrain_levels", "extras_time_outs")
 # fp32 state that is bit-identical by construction (no libm, no long sums)
 EXACT_F32 = ("torques", "actions", "base_lin_vel", "base_ang_vel", "projected_gravity", "last_actions",
              "last_dof_vel", "last_root_vel", "feet_air_time", "last_feet_air_time", "current_max_feet_height",
@@ -158,12 +158,12 @@ GOLDEN = {"pointfoot_flat_n64.npz": ("pointfoot_flat", None),
           "pointfoot_rough_n64.npz": ("pointfoot_rough", None),
           "pointfoot_rough_p187_n64.npz": ("pointfoot_rough", common.grid187)}
 _GOLD_EXACT = ("reset", "terminate", "time_out_buf", "episode_length_buf", "contact_filt", "first_contact",
-               "last_contacts", "terrain_levels", "torques", "base_lin_vel", "base_ang_vel", "projected_gravity",
+               "last_contacts", "terrain_levels", "time_outs", "torques", "base_lin_vel", "base_ang_vel", "projected_gravity",
                "last_actions", "last_dof_vel", "last_root_vel", "feet_air_time", "last_feet_air_time",
                "current_max_feet_height", "last_max_feet_height", "root_states", "dof_state", "env_origins",
                "measured_heights")
 _GOLD_CLOSE = ("obs", "priv", "rew", "episode_sums", "commands")
-_GOLD_NAME = {"reset": "reset_buf", "obs": "obs_buf", "priv": "priv_obs_buf", "rew": "rew_buf"}
+_GOLD_NAME = {"time_outs": "extras_time_outs", "reset": "reset_buf", "obs": "obs_buf", "priv": "priv_obs_buf", "rew": "rew_buf"}
 
 
 def load_golden(fname):

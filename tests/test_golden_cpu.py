@@ -36,7 +36,7 @@ def test_live_reference_matches_golden():
 
         def fetch(name):
             obs, priv, rew, reset, extras = last["out"]
-            special = {"obs_buf": obs, "priv_obs_buf": priv, "rew_buf": rew, "reset_buf": reset,
+            special = {"extras_time_outs": extras["time_outs"], "obs_buf": obs, "priv_obs_buf": priv, "rew_buf": rew, "reset_buf": reset,
                        "reset_ids": reset.nonzero().flatten()}
             if name in special:
                 return special[name]
