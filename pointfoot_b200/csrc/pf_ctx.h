@@ -5,9 +5,9 @@
 
 // Device scratch the step kernel hands to the finalize kernel (per-CTA partials).
 struct PfCtxScratch {
-    int* blk_count;        // [max_blocks] resets in the CTA
-    long long* blk_level;  // [max_blocks] sum of terrain levels in the CTA
-    double* blk_sums;      // [max_blocks][PF_MAX_REWARD_TERMS] episode sums of the CTA's reset envs
+    int* blk_count;        // [num_slabs] resets in the warp slab (envs_per_warp consecutive envs)
+    long long* blk_level;  // [num_slabs] sum of terrain levels in the slab
+    double* blk_sums;      // [num_slabs][PF_MAX_REWARD_TERMS] episode sums of the slab's reset envs (valid iff count > 0)
     const float* noise_vec;       // [max(num_obs, num_priv_obs)]
     const float* height_points;   // [P][2]
 };
@@ -17,8 +17,9 @@ struct pf_ctx {
     PfCtxScratch S;
     int device;
     int num_sms;
-    int envs_per_block;    // EPB of the step kernel
-    int num_blocks;        // ceil(num_envs / EPB)
+    int envs_per_warp;     // envs owned by one warp of the step kernel (8, 16 or 32)
+    int num_slabs;         // ceil(num_envs / envs_per_warp)
+    int num_blocks;        // CTAs of the step kernel
     int max_blocks;
     size_t smem_bytes;
     // pinned host staging for pf_step_host

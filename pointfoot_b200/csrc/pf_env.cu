@@ -2,22 +2,16 @@
 // episode statistics, push forces, reset-all.  The per-env arithmetic lives in pf_env_core.cuh (shared with
 // the host emulation in tests/); this file is the staging, the thread mapping and the block reductions.
 //
-// Mapping: a CTA of PF_THREADS threads owns EPB consecutive envs.
-//   phase 0  cooperative, coalesced copy of the CTA's PhysX rows (root [EPB,13], dof [EPB,2D], contact forces
-//            [EPB,3B]) into shared memory -- the AoS -> per-thread transpose happens there, not in HBM;
-//   phase A  height scan: the EPB*P scan points are spread over all threads (min of 3 int16 samples each, the
-//            5.46 MB field stays L2 resident), raw samples parked in shared memory;
-//   phase B  one thread per env: pf_env_step (+ pf_env_reset for the few that reset);
-//   phase C  cooperative, coalesced write of the observation rows (noise + clip fused);
-//   phase D  CTA partials for extras["episode"] (count, per-term sums over reset envs, terrain-level sum).
-// A second, tiny kernel (pf_finalize_kernel) turns the per-CTA partials into the ascending reset id list
-// (PF:221 nonzero()), the device count and the episode statistics, deterministically (no float atomics).
+// Mapping: one WARP owns envs_per_warp (8/16/32) consecutive envs and never synchronises
+// with another warp; phases are described at pf_post_physics_kernel.  A second, tiny kernel
+// (pf_finalize_kernel) turns the per-warp partials into the ascending reset id list (PF:221 nonzero()), the
+// device count and the episode statistics, deterministically (no float atomics).
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include "pf_env_core.cuh"
 #include "pf_ctx.h"
 
-#define PF_THREADS 128
+#define PF_THREADS 256
 
 // ------------------------------------------------------------------------------------------------ K1
 // _compute_torques, PF:523-547 (+ the action clip of PF:176-177 when actions_in != NULL).
@@ -41,243 +35,291 @@ __global__ void __launch_bounds__(256) pf_pd_torques_kernel(const pf_params P, c
 }
 
 // ------------------------------------------------------------------------------------------------ helpers
-// dynamic shared memory carve-up for the step kernel
-struct PfSmem {
-    float* root;      // [EPB][13]
-    float* dof;       // [EPB][2D+1]   (+1: odd stride, conflict-free per-thread rows)
-    float* cf;        // [EPB][3B]
-    float* feet;      // [EPB][6]
-    float* base;      // [EPB][base_w] observation columns before noise
-    float* rootz;     // [EPB] post-reset root z
-    float* zw;        // [EPB][2] yaw quaternion (z, w)
-    float* sums;      // [EPB][R] episode sums of reset envs
-    uint32_t* nkey;   // [EPB] noise key
-    int16_t* raw;     // [EPB][P]
+// Per-WARP shared memory slab of the step kernel (epw = envs per warp: 8, 16 or 32).  Warps never talk to each
+// other: there is no __syncthreads in the step kernel, only __syncwarp, so every warp runs ahead on its own
+// loads.  Row strides are odd (13, 27) or small (12) so that one-thread-per-env row reads are (nearly)
+// conflict free.
+struct PfWarpSmem {
+    float* root;      // [epw][13]   pre-reset root rows
+    float* dof;       // [epw][2D]
+    float* cf;        // [epw][cfw]  contact forces; reused for the observation columns before noise
+    float* misc;      // [epw][4]    yaw quaternion (z, w), post-reset root z, noise key (bits)
 };
 
-__host__ __device__ inline size_t pf_smem_floats(const pf_params& P, int epb) {
-    const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
-    return (size_t)epb * (13 + (2 * P.num_dof + 1) + 3 * P.num_bodies + 6 + (6 + 3 * P.num_dof + 3) + 1 + 2 + R + 1);
+__host__ __device__ inline int pf_cf_width(const pf_params& P) {
+    const int a = 3 * P.num_bodies, b = 6 + 3 * P.num_dof + 3;
+    return (a > b ? a : b) | 1;
 }
-__host__ __device__ inline size_t pf_smem_bytes(const pf_params& P, int epb) {
-    size_t b = pf_smem_floats(P, epb) * 4 + (size_t)epb * P.num_height_points * 2;
-    return (b + 15) & ~(size_t)15;
+__host__ __device__ inline int pf_warp_smem_floats(const pf_params& P, int epw) {
+    const int n = epw * (13 + 2 * P.num_dof + pf_cf_width(P) + 4);
+    return (n + 3) & ~3;                                  // keep every warp slab 16-byte aligned
 }
 
-__device__ __forceinline__ PfSmem pf_carve(const pf_params& P, int epb, unsigned char* smem) {
-    PfSmem s;
-    const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
-    float* f = reinterpret_cast<float*>(smem);
-    s.root = f; f += epb * 13;
-    s.dof = f; f += epb * (2 * P.num_dof + 1);
-    s.cf = f; f += epb * 3 * P.num_bodies;
-    s.feet = f; f += epb * 6;
-    s.base = f; f += epb * (6 + 3 * P.num_dof + 3);
-    s.rootz = f; f += epb;
-    s.zw = f; f += epb * 2;
-    s.sums = f; f += epb * R;
-    s.nkey = reinterpret_cast<uint32_t*>(f); f += epb;
-    s.raw = reinterpret_cast<int16_t*>(f);
+__device__ __forceinline__ PfWarpSmem pf_carve_warp(const pf_params& P, int epw, float* f) {
+    PfWarpSmem s;
+    s.root = f; f += epw * 13;
+    s.dof = f; f += epw * 2 * P.num_dof;
+    s.cf = f; f += epw * pf_cf_width(P);
+    s.misc = f;
     return s;
 }
 
-// CTA partials for extras["episode"] (PF:276-288).  `is_reset` per thread (threads >= nenv pass false),
-// `lvl` = this env's terrain level after the update (0 if none).
-__device__ __forceinline__ void pf_block_partials(const pf_params& P, const PfCtxScratch& S, const PfSmem& s,
-                                                  bool is_reset, long long lvl, int R) {
-    __shared__ unsigned s_mask[PF_THREADS / 32];
-    __shared__ unsigned long long s_lvl;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid == 0) s_lvl = 0ull;
-    const unsigned m = __ballot_sync(0xffffffffu, is_reset);
-    if (lane == 0) s_mask[warp] = m;
-    // levels are >= 0 and < max_terrain_level: exact integer sum
-    unsigned lv = __reduce_add_sync(0xffffffffu, (unsigned)lvl);
-    __syncthreads();
-    if (lane == 0 && lv) atomicAdd(&s_lvl, (unsigned long long)lv);
-    __syncthreads();
-    int cnt = 0;
-    for (int w = 0; w < PF_THREADS / 32; ++w) cnt += __popc(s_mask[w]);
-    if (tid == 0) {
-        S.blk_count[blockIdx.x] = cnt;
-        S.blk_level[blockIdx.x] = (long long)s_lvl;
-    }
-    // per-term sums over this CTA's reset envs, in env order, double accumulation (deterministic)
-    if (tid < R) {
-        double acc = 0.0;
-        if (cnt) {
-            for (int w = 0; w < PF_THREADS / 32; ++w) {
-                unsigned mm = s_mask[w];
-                while (mm) {
-                    const int b = __ffs(mm) - 1;
-                    mm &= mm - 1;
-                    acc += (double)s.sums[(w * 32 + b) * R + tid];
-                }
-            }
-        }
-        S.blk_sums[(size_t)blockIdx.x * PF_MAX_REWARD_TERMS + tid] = acc;
+// coalesced copy of `n` floats global -> shared by one warp; 128-bit when both sides allow it
+__device__ __forceinline__ void pf_warp_copy(float* __restrict__ dst, const float* __restrict__ src, int n, int lane) {
+    if (((reinterpret_cast<uintptr_t>(src) | (uintptr_t)__cvta_generic_to_shared(dst)) & 15) == 0 && (n & 3) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (int i = lane; i < (n >> 2); i += 32) d4[i] = __ldg(s4 + i);
+    } else {
+        for (int i = lane; i < n; i += 32) dst[i] = __ldg(src + i);
     }
 }
 
+__device__ __forceinline__ double pf_warp_sum(double v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);      // fixed tree: deterministic
+    return v;
+}
+
+// Height scan of ONE env by the whole warp (PF:1048-1075, 1100-1112): lane l takes points l, l+32, ...
+// Writes measured_heights (if materialised) and the height columns of obs / priv obs (PF:367-369, 328-338,
+// 189-192) with `root_z`; returns (to every lane) sum_p (root_z_pre - h_p) in double for the base-height mean.
+struct PfScanLane {               // hoisted per-lane constants of the scan loop (same for every env of the warp)
+    float gx[PF_MAX_HEIGHT_POINTS / 32], gy[PF_MAX_HEIGHT_POINTS / 32], ns[PF_MAX_HEIGHT_POINTS / 32];
+};
+
+template <bool kWriteObs>
+__device__ __forceinline__ double pf_scan_env(const pf_params& P, const pf_env_buffers& B, const PfScanLane& L,
+                                              const float* __restrict__ root, float zn, float wn, float root_z_obs,
+                                              uint32_t nkey, int e, int lane, bool want_sum) {
+    const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
+    const bool rough = P.terrain_kind == PF_TERRAIN_HEIGHTFIELD;
+    const float bx = root[0], by = root[1], rz = root[2];
+    float* mh = B.measured_heights ? B.measured_heights + (size_t)e * Pn : nullptr;
+    float* oh = (kWriteObs && P.measure_heights_actor) ? B.obs_buf + (size_t)e * P.num_obs + base_w : nullptr;
+    float* ph = (kWriteObs && P.measure_heights_critic && B.priv_obs_buf)
+                    ? B.priv_obs_buf + (size_t)e * P.num_priv_obs + base_w : nullptr;
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < PF_MAX_HEIGHT_POINTS / 32; ++k) {
+        const int p = lane + 32 * k;
+        if (p < Pn) {
+            int16_t r = 0;                                       // plane: zeros, PF:1061-1062
+            if (rough) r = pf_scan_point(P, B.height_samples, zn, wn, L.gx[k], L.gy[k], bx, by);
+            const float h = (float)r * P.vertical_scale;
+            if (mh) mh[p] = h;
+            if (want_sum) acc += (double)(rz - h);
+            if (kWriteObs && (oh || ph)) {
+                float v = pf_clipf((root_z_obs - 0.5f) - h, -1.0f, 1.0f) * P.obs_scale_height;
+                if (P.add_noise && L.ns[k] != 0.0f)
+                    v = v + (2.0f * pf_rng_uniform(nkey, (uint32_t)(base_w + p)) - 1.0f) * L.ns[k];
+                v = pf_clipf(v, -P.clip_obs, P.clip_obs);
+                if (oh) oh[p] = v;
+                if (ph) ph[p] = v;
+            }
+        }
+    }
+    return want_sum ? pf_warp_sum(acc) : 0.0;
+}
+
+// Warp partials for extras["episode"] (PF:276-288): count, terrain-level sum, per-term episode sums of the
+// warp's reset envs (read back BEFORE pf_env_reset zeroes them).  Entry index = global warp-slab index.
+__device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_env_buffers& B, const PfCtxScratch& S,
+                                                 int slab, int e, bool active, bool is_reset, int R, int lane) {
+    const unsigned m = __ballot_sync(0xffffffffu, is_reset);
+    if (m) {
+        const int N = P.num_envs;
+        for (int k = 0; k < R; ++k) {
+            const double v = is_reset ? (double)B.episode_sums[(size_t)k * N + e] : 0.0;
+            const double t = pf_warp_sum(v);
+            if (lane == 0) S.blk_sums[(size_t)slab * PF_MAX_REWARD_TERMS + k] = t;
+        }
+    }
+    if (lane == 0) S.blk_count[slab] = __popc(m);
+    (void)active;
+}
+
 // ------------------------------------------------------------------------------------------------ K2
-// Fused post_physics_step (PF:195-227) + obs clip (PF:189-192).  `epb` envs per CTA (32, 64 or 128).
-__global__ void __launch_bounds__(PF_THREADS) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
-                                                                     const PfCtxScratch S, const int epb,
-                                                                     const uint32_t step_arg) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const PfSmem s = pf_carve(P, epb, smem_raw);
-    const int tid = threadIdx.x;
-    const int e0 = blockIdx.x * epb;
-    const int nenv = min(epb, P.num_envs - e0);
+// Fused post_physics_step (PF:195-227) + obs clip (PF:189-192).  One warp owns `epw` consecutive envs.
+//   phase 0  coalesced 128-bit copies of the warp's PhysX rows (root, dof, contact) into its smem slab
+//   phase 1  height scan, warp-cooperative per env (lanes = scan points): int16 min-of-3 gathers from the L2
+//            resident field, height observation columns written straight from registers, base-height sum
+//            by warp shuffle
+//   phase 2  one lane per env: pf_env_step (+ pf_env_reset for the few that reset)
+//   phase 3  the 27 leading observation columns, flattened over the warp's envs -> coalesced row writes
+//   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
+//            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
+__global__ void __launch_bounds__(PF_THREADS, 3) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
+                                                                        const PfCtxScratch S, const int epw,
+                                                                        const uint32_t step_arg) {
+    extern __shared__ __align__(16) float smem_f[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slab = blockIdx.x * (PF_THREADS / 32) + warp;
+    const int e0 = slab * epw;
+    if (e0 >= P.num_envs) return;
+    const PfWarpSmem s = pf_carve_warp(P, epw, smem_f + (size_t)warp * pf_warp_smem_floats(P, epw));
+    const int nenv = min(epw, P.num_envs - e0);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     const int D = P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
-    const int base_w = pf_obs_base_width(P);
+    const int base_w = pf_obs_base_width(P), cfw = pf_cf_width(P);
+    const bool active = lane < nenv;
+    const int e = e0 + lane;
 
-    // ---- phase 0: coalesced AoS rows -> shared memory ----
-    {
-        const float* g = B.root_states + (size_t)e0 * 13;
-        for (int i = tid; i < nenv * 13; i += PF_THREADS) s.root[i] = g[i];
-        g = B.dof_state + (size_t)e0 * 2 * D;
-        const int w = 2 * D;
-        for (int i = tid; i < nenv * w; i += PF_THREADS) s.dof[(i / w) * (w + 1) + (i % w)] = g[i];
-        g = B.contact_forces + (size_t)e0 * 3 * NB;
-        for (int i = tid; i < nenv * 3 * NB; i += PF_THREADS) s.cf[i] = g[i];
-        for (int i = tid; i < nenv * 6; i += PF_THREADS) {
-            const int e = i / 6, c = i % 6;
-            s.feet[i] = B.rigid_body_states[((size_t)(e0 + e) * NB + P.feet_indices[c / 3]) * 13 + (c % 3)];
+    // ---- phase 0: AoS rows -> shared memory ----
+    pf_warp_copy(s.root, B.root_states + (size_t)e0 * 13, nenv * 13, lane);
+    pf_warp_copy(s.dof, B.dof_state + (size_t)e0 * 2 * D, nenv * 2 * D, lane);
+    if (cfw == 3 * NB) {
+        pf_warp_copy(s.cf, B.contact_forces + (size_t)e0 * 3 * NB, nenv * 3 * NB, lane);
+    } else {
+        const float* g = B.contact_forces + (size_t)e0 * 3 * NB;
+        for (int i = lane; i < nenv * 3 * NB; i += 32) s.cf[(i / (3 * NB)) * cfw + (i % (3 * NB))] = __ldg(g + i);
+    }
+    float feet[6];
+    if (active) {
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const float* g = B.rigid_body_states + ((size_t)e * NB + P.feet_indices[f]) * 13;
+            feet[3 * f] = __ldg(g); feet[3 * f + 1] = __ldg(g + 1); feet[3 * f + 2] = __ldg(g + 2);
         }
     }
-    __syncthreads();
+    const uint32_t nkey = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
+    __syncwarp();
 
-    // ---- phase A: height scan (PF:1048-1075, 1100-1112) ----
+    // ---- phase 1: height scan ----
+    float height_mean = 0.0f;
+    PfScanLane L;
     if (Pn > 0) {
-        if (tid < nenv) {
+#pragma unroll
+        for (int k = 0; k < PF_MAX_HEIGHT_POINTS / 32; ++k) {
+            const int p = lane + 32 * k;
+            const bool ok = p < Pn;
+            const float2 g = ok ? reinterpret_cast<const float2*>(S.height_points)[p] : make_float2(0.f, 0.f);
+            L.gx[k] = g.x; L.gy[k] = g.y;
+            L.ns[k] = ok ? S.noise_vec[base_w + p] : 0.0f;
+        }
+        if (active) {
             float zn, wn;
-            pf_yaw_quat(s.root + tid * 13 + 3, zn, wn);
-            s.zw[2 * tid] = zn; s.zw[2 * tid + 1] = wn;
+            pf_yaw_quat(s.root + lane * 13 + 3, zn, wn);
+            s.misc[4 * lane] = zn; s.misc[4 * lane + 1] = wn;
+            s.misc[4 * lane + 3] = __uint_as_float(nkey);
         }
-        __syncthreads();
-        const bool rough = P.terrain_kind == PF_TERRAIN_HEIGHTFIELD;
-        for (int i = tid; i < nenv * Pn; i += PF_THREADS) {
-            const int e = i / Pn, p = i - e * Pn;
-            int16_t r = 0;                                       // plane: zeros, PF:1061-1062
-            if (rough) {
-                const float2 g = reinterpret_cast<const float2*>(S.height_points)[p];
-                r = pf_scan_point(P, B.height_samples, s.zw[2 * e], s.zw[2 * e + 1], g.x, g.y,
-                                  s.root[e * 13], s.root[e * 13 + 1]);
-            }
-            s.raw[i] = r;
-            if (B.measured_heights) B.measured_heights[(size_t)e0 * Pn + i] = (float)r * P.vertical_scale;
+        __syncwarp();
+        const bool want_sum = true;
+        for (int i = 0; i < nenv; ++i) {
+            const float* r = s.root + i * 13;
+            const double sum = pf_scan_env<true>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], r[2],
+                                                 __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, want_sum);
+            if (lane == i) height_mean = (float)(sum / (double)Pn);
         }
-        __syncthreads();
     }
 
-    // ---- phase B: one thread per env ----
+    // ---- phase 2: one lane per env ----
     bool is_reset = false;
-    long long lvl = 0;
-    if (tid < nenv) {
-        const int e = e0 + tid;
+    PfEnvOut out;
+    if (active) {
         PfEnvIn in;
-        PfEnvOut out;
-        in.root = s.root + tid * 13;
-        in.dof = s.dof + tid * (2 * D + 1);
-        in.cf = s.cf + tid * 3 * NB;
-        in.feet_pos[0] = s.feet + tid * 6;
-        in.feet_pos[1] = s.feet + tid * 6 + 3;
+        in.root = s.root + lane * 13;
+        in.dof = s.dof + lane * 2 * D;
+        in.cf = s.cf + lane * cfw;
+        in.feet_pos[0] = feet;
+        in.feet_pos[1] = feet + 3;
         in.have_heights = Pn > 0;
-        {
-            const float rz = in.root[2];
-            const int16_t* raw = s.raw + tid * Pn;
-            double hs = 0.0;          // terms in fp32 like the reference, summed in double (see pf_env_core.cuh)
-            for (int p = 0; p < Pn; ++p) hs += (double)(rz - (float)raw[p] * P.vertical_scale);
-            in.height_mean = Pn > 0 ? (float)(hs / (double)Pn) : 0.0f;
-        }
+        in.height_mean = height_mean;
         pf_env_step(P, B, e, in, step, nullptr, out);
         is_reset = out.reset;
-        if (is_reset) pf_env_reset(P, B, e, in.root, out.commands, step, true, s.sums + tid * R, out);
+    }
+    pf_warp_partials(P, B, S, slab, e, active, is_reset, R, lane);
+    long long lvl = 0;
+    if (active) {
+        if (is_reset) pf_env_reset(P, B, e, s.root + lane * 13, out.commands, step, true, nullptr, out);
         if (B.terrain_levels) lvl = B.terrain_levels[e];
         const float* act = B.actions + (size_t)e * D;
-        for (int j = 0; j < base_w; ++j) s.base[tid * base_w + j] = pf_obs_base_col(P, out, act, j);
-        s.rootz[tid] = out.root_z;
-        s.nkey[tid] = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
+        float* base = s.cf + lane * cfw;           // own row: the contact forces are no longer needed
+        for (int j = 0; j < base_w; ++j) base[j] = pf_obs_base_col(P, out, act, j);
+        s.misc[4 * lane + 2] = out.root_z;
+        s.misc[4 * lane + 3] = __uint_as_float(nkey);
         // PF:225-227
         for (int d = 0; d < D; ++d) {
             B.last_actions[(size_t)e * D + d] = act[d];
             B.last_dof_vel[(size_t)e * D + d] = out.dof_vel[d];
         }
-        const float* rv = is_reset ? B.root_states + (size_t)e * 13 + 7 : in.root + 7;
+        const float* rv = is_reset ? B.root_states + (size_t)e * 13 + 7 : s.root + lane * 13 + 7;
         for (int i = 0; i < 6; ++i) B.last_root_vel[(size_t)e * 6 + i] = rv[i];
     }
-    __syncthreads();
-
-    // ---- phase C: observation rows, coalesced (PF:320-382, 189-192) ----
     {
-        const int no = P.num_obs;
-        float* g = B.obs_buf + (size_t)e0 * no;
-        for (int i = tid; i < nenv * no; i += PF_THREADS) {
-            const int e = i / no, j = i - e * no;
-            const float v = j < base_w ? s.base[e * base_w + j]
-                                       : pf_obs_height_col(P, s.rootz[e], s.raw[e * Pn + (j - base_w)]);
-            g[i] = pf_obs_finish(P, v, s.nkey[e], j, S.noise_vec);
-        }
-        if (B.priv_obs_buf) {
-            const int np = P.num_priv_obs;
-            g = B.priv_obs_buf + (size_t)e0 * np;
-            for (int i = tid; i < nenv * np; i += PF_THREADS) {
-                const int e = i / np, j = i - e * np;
-                const float v = j < base_w ? s.base[e * base_w + j]
-                                           : pf_obs_height_col(P, s.rootz[e], s.raw[e * Pn + (j - base_w)]);
-                g[i] = pf_obs_finish(P, v, s.nkey[e], j, S.noise_vec);
-            }
+        const unsigned lv = __reduce_add_sync(0xffffffffu, (unsigned)lvl);   // levels are small and >= 0: exact
+        if (lane == 0) S.blk_level[slab] = (long long)lv;
+    }
+    __syncwarp();
+
+    // ---- phase 3: leading observation columns, coalesced (PF:376-382, 328-338, 189-192) ----
+    {
+        const int no = P.num_obs, np = P.num_priv_obs;
+        const uint32_t magic = ((1u << 20) + (uint32_t)base_w - 1u) / (uint32_t)base_w;    // i / base_w for i < 2^20 / base_w
+        float* go = B.obs_buf + (size_t)e0 * no;
+        float* gp = B.priv_obs_buf ? B.priv_obs_buf + (size_t)e0 * np : nullptr;
+        for (int i = lane; i < nenv * base_w; i += 32) {
+            const int le = (int)(((uint32_t)i * magic) >> 20), j = i - le * base_w;
+            const float v = pf_obs_finish(P, s.cf[le * cfw + j], __float_as_uint(s.misc[4 * le + 3]), j, S.noise_vec);
+            go[le * no + j] = v;
+            if (gp) gp[le * np + j] = v;
         }
     }
 
-    // ---- phase D: CTA partials ----
-    pf_block_partials(P, S, s, is_reset, lvl, R);
+    // ---- phase 4: height columns of the envs that reset ----
+    if (Pn > 0 && (P.measure_heights_actor || P.measure_heights_critic)) {
+        unsigned m = __ballot_sync(0xffffffffu, is_reset);
+        while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1;
+            const float* r = s.root + i * 13;
+            pf_scan_env<true>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], s.misc[4 * i + 2],
+                              __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, false);
+        }
+    }
 }
 
 // reset_idx over ALL envs (PF:137-139 reset(), before the zero-action step).
 __global__ void __launch_bounds__(PF_THREADS) pf_reset_all_kernel(const pf_params P, const pf_env_buffers B,
-                                                                  const PfCtxScratch S, const int epb,
+                                                                  const PfCtxScratch S, const int epw,
                                                                   const uint32_t step_arg) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const PfSmem s = pf_carve(P, epb, smem_raw);
-    const int tid = threadIdx.x;
-    const int e0 = blockIdx.x * epb;
-    const int nenv = min(epb, P.num_envs - e0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slab = blockIdx.x * (PF_THREADS / 32) + warp;
+    const int e0 = slab * epw;
+    if (e0 >= P.num_envs) return;
+    const int nenv = min(epw, P.num_envs - e0);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter) : step_arg;   // reset() does not count a step
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
+    const bool active = lane < nenv;
+    const int e = e0 + lane;
+    pf_warp_partials(P, B, S, slab, e, active, active, R, lane);
     long long lvl = 0;
-    const bool active = tid < nenv;
     if (active) {
-        const int e = e0 + tid;
         PfEnvOut out;
         float root_pre[13], cmd[2];
         for (int i = 0; i < 13; ++i) root_pre[i] = B.root_states[(size_t)e * 13 + i];
         cmd[0] = B.commands[(size_t)e * P.num_commands];
         cmd[1] = B.commands[(size_t)e * P.num_commands + 1];
-        pf_env_reset(P, B, e, root_pre, cmd, step, true, s.sums + tid * R, out);
+        pf_env_reset(P, B, e, root_pre, cmd, step, true, nullptr, out);
         if (B.terrain_levels) lvl = B.terrain_levels[e];
     }
-    __syncthreads();
-    pf_block_partials(P, S, s, active, lvl, R);
+    const unsigned lv = __reduce_add_sync(0xffffffffu, (unsigned)lvl);
+    if (lane == 0) S.blk_level[slab] = (long long)lv;
 }
 
 // ------------------------------------------------------------------------------------------------ K3
 // Partials -> ascending reset ids (PF:221), device count, extras["episode"] statistics (PF:276-288).
-// Each CTA of 1024 threads compacts 1024 envs; its base offset is the sum of the step kernel's CTA counts
+// Each CTA of 1024 threads compacts 1024 envs; its base offset is the sum of the step kernel's warp counts
 // before it.  CTA 0 additionally reduces the per-term partials (one warp per statistic, fixed order).
 __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, const pf_env_buffers B,
-                                                           const PfCtxScratch S, const int epb,
-                                                           const int num_step_blocks, const int count_step) {
+                                                           const PfCtxScratch S, const int epw,
+                                                           const int num_slabs, const int count_step) {
     __shared__ int s_warp[32];
     __shared__ int s_base;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
 
-    // offset of this CTA = sum of blk_count over the step CTAs in front of it
-    const int before = (int)(((long long)blockIdx.x * 1024) / epb);
+    // offset of this CTA = sum of blk_count over the warp slabs in front of it
+    const int before = (int)(((long long)blockIdx.x * 1024) / epw);
     int part = 0;
     for (int i = tid; i < before; i += 1024) part += S.blk_count[i];
     part = __reduce_add_sync(0xffffffffu, part);
@@ -296,7 +338,7 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     __shared__ int s_total;
     {
         int tot = 0;
-        for (int i = tid; i < num_step_blocks; i += 1024) tot += S.blk_count[i];
+        for (int i = tid; i < num_slabs; i += 1024) tot += S.blk_count[i];
         tot = __reduce_add_sync(0xffffffffu, tot);
         __syncthreads();
         if (lane == 0) s_warp[warp] = tot;
@@ -329,12 +371,13 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
         if (total > 0 && warp < R + 1) {          // PF:259: extras rebuilt only when >= 1 env resets
             if (warp < R) {
                 double acc = 0.0;
-                for (int i = lane; i < num_step_blocks; i += 32) acc += S.blk_sums[(size_t)i * PF_MAX_REWARD_TERMS + warp];
-                for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                for (int i = lane; i < num_slabs; i += 32)
+                    if (S.blk_count[i] > 0) acc += S.blk_sums[(size_t)i * PF_MAX_REWARD_TERMS + warp];
+                acc = pf_warp_sum(acc);
                 if (lane == 0) B.episode_stats[warp] = (float)(acc / (double)total) / P.max_episode_length_s;
             } else {
                 long long acc = 0;
-                for (int i = lane; i < num_step_blocks; i += 32) acc += S.blk_level[i];
+                for (int i = lane; i < num_slabs; i += 32) acc += S.blk_level[i];
                 for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
                 if (lane == 0) {
                     B.episode_stats[R] = (float)((double)acc / (double)P.num_envs);
@@ -382,11 +425,12 @@ extern "C" int pf_abi_version(void) { return PF_ABI_VERSION; }
 extern "C" int pf_sizeof_params(void) { return (int)sizeof(pf_params); }
 extern "C" int pf_sizeof_env_buffers(void) { return (int)sizeof(pf_env_buffers); }
 
-static int pf_pick_epb(int num_envs, int num_sms) {
-    // enough CTAs to cover the SMs a couple of times before growing the per-CTA env count
-    if (num_envs <= num_sms * 2 * 32) return 32;
-    if (num_envs <= num_sms * 4 * 64) return 64;
-    return 128;
+static int pf_pick_epw(int num_envs, int num_sms) {
+    // envs per warp: small batches are latency bound, so spread them over more warps (idle lanes in the
+    // one-lane-per-env phase are cheaper than idle SMs); from ~16 warps per SM on, full warps
+    if (num_envs <= num_sms * 16 * 8) return 8;
+    if (num_envs <= num_sms * 16 * 16) return 16;
+    return 32;
 }
 
 extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_vec_host,
@@ -418,13 +462,13 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->P = P;
     PF_CUDA(cudaGetDevice(&c->device));
     PF_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device));
-    c->envs_per_block = pf_pick_epb(P.num_envs, c->num_sms);
-    c->num_blocks = (P.num_envs + c->envs_per_block - 1) / c->envs_per_block;
-    c->max_blocks = c->num_blocks;
-    c->smem_bytes = pf_smem_bytes(P, c->envs_per_block);
+    c->envs_per_warp = pf_pick_epw(P.num_envs, c->num_sms);
+    c->num_slabs = (P.num_envs + c->envs_per_warp - 1) / c->envs_per_warp;
+    c->num_blocks = (c->num_slabs + PF_THREADS / 32 - 1) / (PF_THREADS / 32);
+    c->max_blocks = c->num_slabs;
+    c->smem_bytes = (size_t)(PF_THREADS / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
     PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_reset_all_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -485,7 +529,7 @@ extern "C" int pf_pd_torques(pf_ctx* c, const pf_env_buffers* bufs, const float*
 
 static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_t st, int count_step) {
     const int blocks = (c->P.num_envs + 1023) / 1024;
-    pf_finalize_kernel<<<blocks, 1024, 0, st>>>(c->P, *bufs, c->S, c->envs_per_block, c->num_blocks, count_step);
+    pf_finalize_kernel<<<blocks, 1024, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp, c->num_slabs, count_step);
     PF_CUDA(cudaGetLastError());
     return 0;
 }
@@ -493,7 +537,7 @@ static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_
 extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    pf_post_physics_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_block,
+    pf_post_physics_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
                                                                              (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 1);
@@ -503,7 +547,7 @@ extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t commo
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     PF_CUDA(cudaMemsetAsync(bufs->reset_buf, 1, (size_t)c->P.num_envs, st));
-    pf_reset_all_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_block,
+    pf_reset_all_kernel<<<c->num_blocks, PF_THREADS, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
                                                                           (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 0);

@@ -77,7 +77,11 @@ PF_HD int16_t pf_terrain_min3(const pf_params& P, const int16_t* __restrict__ hs
     px = px < 0 ? 0 : (px > mx ? mx : px);
     py = py < 0 ? 0 : (py > my ? my : py);
     const int16_t* r = hs + px * (long long)P.hf_cols + py;
+#ifdef __CUDA_ARCH__
+    const int16_t h1 = __ldg(r), h2 = __ldg(r + P.hf_cols), h3 = __ldg(r + 1);   // read-only path: may move across stores
+#else
     const int16_t h1 = r[0], h2 = r[P.hf_cols], h3 = r[1];
+#endif
     const int16_t m = h1 < h2 ? h1 : h2;
     return m < h3 ? m : h3;
 }
