@@ -197,6 +197,113 @@ int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* s
                  float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
                  int64_t common_step_counter, void* stream);
 
+/* ================================================================================================
+ * rsl_rl v1.0.2 side of the path (third-party dependency of the reference; call sites
+ * legged_gym/utils/task_registry.py:147-154, legged_gym/scripts/train.py:44, play.py:59).
+ * ActorCritic.act / evaluate / act_inference, PPO.act / process_env_step / compute_returns / update,
+ * RolloutStorage.add_transitions / compute_returns / mini_batch_generator.
+ * ============================================================================================== */
+#define PF_MAX_MLP_LAYERS 6
+
+enum pf_rl_precision {
+    PF_RL_FP32 = 0,      /* hand-written fp32 SIMT kernels: the parity path (rtol 1e-4 against torch fp32) */
+    PF_RL_BF16_TC = 1    /* tcgen05 tensor-core tiles, bf16 operands, fp32 accumulation in TMEM (rtol 2e-2) */
+};
+
+/* Hyper-parameters and shapes (PointFootRoughCfgPPO, pointfoot_rough_config.py:216-259).  POD. */
+typedef struct pf_rl_params {
+    int32_t abi_version;
+    int32_t num_envs;                 /* envs on THIS device */
+    int64_t env_id_offset;            /* global id of local env 0 */
+    int32_t num_steps;                /* num_steps_per_env (24) */
+    int32_t num_obs, num_critic_obs, num_actions;
+    /* MLPs: Linear(dims[i] -> dims[i+1]) for i < layers, ELU between (actor_critic.py).  dims[0] is the
+     * observation width, dims[layers] the output width (num_actions / 1). */
+    int32_t actor_layers, actor_dims[PF_MAX_MLP_LAYERS + 1];
+    int32_t critic_layers, critic_dims[PF_MAX_MLP_LAYERS + 1];
+    uint32_t seed;
+    float gamma, lam, clip_param, value_loss_coef, entropy_coef, max_grad_norm;
+    int32_t use_clipped_value_loss, adaptive_schedule;
+    int32_t num_mini_batches, num_learning_epochs;
+    int32_t precision;                /* enum pf_rl_precision */
+    double desired_kl;                /* python floats upstream: kept in double so the schedule and Adam's */
+    double adam_beta1, adam_beta2, adam_eps;   /* bias corrections round like torch.optim.Adam's host arithmetic */
+} pf_rl_params;
+
+/* RolloutStorage tensors (rollout_storage.py), all [T, N, .] contiguous, caller-owned device memory. */
+typedef struct pf_rl_storage {
+    float* observations;              /* [T,N,num_obs] */
+    float* privileged_observations;   /* [T,N,num_critic_obs] or NULL (critic sees observations) */
+    float* actions;                   /* [T,N,A] */
+    float* rewards;                   /* [T,N,1] */
+    uint8_t* dones;                   /* [T,N,1] */
+    float* values;                    /* [T,N,1] */
+    float* actions_log_prob;          /* [T,N,1] */
+    float* mu; float* sigma;          /* [T,N,A] */
+    float* returns; float* advantages;/* [T,N,1] */
+} pf_rl_storage;
+
+/* Learner state, caller-owned device memory.  `params` is ONE flat fp32 buffer in ActorCritic.parameters()
+ * order: std[A], actor.{0,2,..}.weight[out,in] / .bias[out], critic.{0,2,..}.weight / .bias. */
+typedef struct pf_rl_learner {
+    float* params; float* grads;      /* [pf_rl_param_count] */
+    float* adam_m; float* adam_v;     /* [pf_rl_param_count] exp_avg / exp_avg_sq */
+    double* lr;                       /* [1] current learning rate (adaptive-KL schedule runs on the device) */
+    int64_t* adam_step;               /* [1] */
+    double* loss_stats;               /* [8] per minibatch: surrogate sum, value-loss sum, entropy sum, kl sum,
+                                         sample count, grad-norm^2, (2 spare); written by pf_rl_minibatch_grad
+                                         (grad-norm^2 by pf_rl_adam_step) */
+} pf_rl_learner;
+
+typedef struct pf_rl_ctx pf_rl_ctx;
+
+int pf_sizeof_rl_params(void);
+int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out);   /* allocates the activation workspace */
+int pf_rl_destroy(pf_rl_ctx* ctx);
+int64_t pf_rl_param_count(const pf_rl_ctx* ctx);
+/* offset (in floats) of a tensor inside the flat parameter buffer: net 0 = actor, 1 = critic, -1 = std;
+ * is_bias 0 = weight [out,in], 1 = bias [out] */
+int64_t pf_rl_param_offset(const pf_rl_ctx* ctx, int net, int layer, int is_bias);
+/* must be called after the caller changes `params` by other means than pf_rl_adam_step (init, load):
+ * refreshes the packed bf16 copies the tensor-core path reads */
+int pf_rl_params_changed(pf_rl_ctx* ctx, const float* params, void* stream);
+
+/* PPO.act (ppo.py act) fused with RolloutStorage.add_transitions' copies: actor forward -> Normal(mean, std)
+ * sample (RNG contract, purpose POLICY, step = policy_step) -> log-prob; critic forward; writes row `t` of the
+ * storage (observations, privileged_observations, actions, values, actions_log_prob, mu, sigma) and
+ * actions_out[N,A].  storage may be NULL (pure ActorCritic.act + evaluate; values_out / logp_out optional). */
+int pf_rl_act(pf_rl_ctx* ctx, const float* params, const float* obs, const float* critic_obs, int32_t t,
+              const pf_rl_storage* storage, int64_t policy_step, float* actions_out, float* values_out,
+              float* logp_out, void* stream);
+/* ActorCritic.act_inference: actions_out = actor(obs) */
+int pf_rl_act_inference(pf_rl_ctx* ctx, const float* params, const float* obs, float* actions_out, void* stream);
+/* ActorCritic.evaluate: values_out[N] = critic(critic_obs) */
+int pf_rl_evaluate(pf_rl_ctx* ctx, const float* params, const float* critic_obs, float* values_out, void* stream);
+/* PPO.process_env_step: rewards[t] = rew + gamma * values[t] * time_outs (time_outs may be NULL), dones[t] = dones */
+int pf_rl_process_env_step(pf_rl_ctx* ctx, const pf_rl_storage* storage, int32_t t, const float* rew,
+                           const uint8_t* dones, const uint8_t* time_outs, void* stream);
+/* RolloutStorage.compute_returns, first half: GAE reverse scan (one thread per env) -> returns, raw advantages;
+ * stats[3] (device, double) = sum, sum of squares, count of the raw advantages on THIS device.  Multi-GPU:
+ * all-reduce `stats` (sum) between the two calls. */
+int pf_rl_gae(pf_rl_ctx* ctx, const pf_rl_storage* storage, const float* last_values, double* stats, void* stream);
+/* second half: advantages = (adv - mean) / (std_unbiased + 1e-8) from stats */
+int pf_rl_normalize_advantages(pf_rl_ctx* ctx, const pf_rl_storage* storage, const double* stats, void* stream);
+/* mini_batch_generator's shuffle: the Feistel permutation contract (oracle/rsl_rl_ref.py feistel_permutation)
+ * for this `iteration`; kept inside the ctx.  Once per PPO.update. */
+int pf_rl_make_permutation(pf_rl_ctx* ctx, int64_t iteration, void* stream);
+/* copies the current permutation (num_mini_batches * minibatch_size int32 indices into the flattened [T*N]
+ * storage) to out: what mini_batch_generator's `indices` tensor would hold */
+int pf_rl_get_permutation(pf_rl_ctx* ctx, int32_t* out, void* stream);
+/* One minibatch of PPO.update up to (not including) the optimizer step: gather by permutation, actor + critic
+ * forward, adaptive-KL statistic, clipped surrogate + clipped value + entropy loss, backward.  Writes
+ * learner->grads (d loss / d params, mean over THIS device's minibatch) and learner->loss_stats.
+ * Multi-GPU: all-reduce grads (mean) and loss_stats (sum) before pf_rl_adam_step. */
+int pf_rl_minibatch_grad(pf_rl_ctx* ctx, const pf_rl_storage* storage, const pf_rl_learner* learner,
+                         int32_t minibatch, void* stream);
+/* adaptive-KL learning-rate update (ppo.py update), clip_grad_norm_(max_grad_norm), Adam step; also refreshes
+ * the packed bf16 parameter copies. */
+int pf_rl_adam_step(pf_rl_ctx* ctx, const pf_rl_learner* learner, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

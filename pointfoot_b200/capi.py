@@ -115,3 +115,51 @@ def ptr(t):
 
 class PfHostState(C.Structure):
     _fields_ = [(n, _P) for n in ("root_states", "dof_state", "contact_forces", "rigid_body_states")]
+
+
+# ------------------------------------------------------------------------------------------------ rsl_rl side
+MAX_MLP_LAYERS = 6
+RL_FP32, RL_BF16_TC = 0, 1
+
+
+class PfRlParams(C.Structure):
+    _fields_ = [
+        ("abi_version", _i), ("num_envs", _i), ("env_id_offset", C.c_int64), ("num_steps", _i),
+        ("num_obs", _i), ("num_critic_obs", _i), ("num_actions", _i),
+        ("actor_layers", _i), ("actor_dims", _i * (MAX_MLP_LAYERS + 1)),
+        ("critic_layers", _i), ("critic_dims", _i * (MAX_MLP_LAYERS + 1)),
+        ("seed", _u),
+        ("gamma", _f), ("lam", _f), ("clip_param", _f), ("value_loss_coef", _f), ("entropy_coef", _f),
+        ("max_grad_norm", _f),
+        ("use_clipped_value_loss", _i), ("adaptive_schedule", _i),
+        ("num_mini_batches", _i), ("num_learning_epochs", _i), ("precision", _i),
+        ("desired_kl", C.c_double), ("adam_beta1", C.c_double), ("adam_beta2", C.c_double), ("adam_eps", C.c_double),
+    ]
+
+
+RL_STORAGE_FIELDS = ("observations", "privileged_observations", "actions", "rewards", "dones", "values",
+                     "actions_log_prob", "mu", "sigma", "returns", "advantages")
+RL_LEARNER_FIELDS = ("params", "grads", "adam_m", "adam_v", "lr", "adam_step", "loss_stats")
+
+
+class PfRlStorage(C.Structure):
+    _fields_ = [(n, _P) for n in RL_STORAGE_FIELDS]
+
+
+class PfRlLearner(C.Structure):
+    _fields_ = [(n, _P) for n in RL_LEARNER_FIELDS]
+
+
+def load_rl():
+    """The same library, with the rsl_rl-side prototypes set and the struct layout checked."""
+    lib = load()
+    if getattr(lib, "_pf_rl_ready", False):
+        return lib
+    if lib.pf_sizeof_rl_params() != C.sizeof(PfRlParams):
+        raise RuntimeError("pointfoot_b200: pf_rl_params layout mismatch between capi.py and the header")
+    lib.pf_rl_param_count.restype = C.c_int64
+    lib.pf_rl_param_offset.restype = C.c_int64
+    lib.pf_rl_param_count.argtypes = [C.c_void_p]
+    lib.pf_rl_param_offset.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+    lib._pf_rl_ready = True
+    return lib

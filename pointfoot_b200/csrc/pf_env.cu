@@ -421,6 +421,7 @@ static int pf_fail(int code, const char* fmt, const char* detail) {
     } while (0)
 
 extern "C" const char* pf_last_error(void) { return g_err; }
+void pf_set_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }   // used by pf_rl.cu / pf_mlp_tc.cu
 extern "C" int pf_abi_version(void) { return PF_ABI_VERSION; }
 extern "C" int pf_sizeof_params(void) { return (int)sizeof(pf_params); }
 extern "C" int pf_sizeof_env_buffers(void) { return (int)sizeof(pf_env_buffers); }

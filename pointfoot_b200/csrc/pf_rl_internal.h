@@ -1,0 +1,49 @@
+// Internal layout of pf_rl_ctx (include/pointfoot_b200.h), shared by pf_rl.cu (fp32 kernels, everything that is
+// not a GEMM) and pf_mlp_tc.cu (tcgen05 tiles).
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "../../include/pointfoot_b200.h"
+
+struct PfNet {                                  // one MLP of ActorCritic (actor_critic.py)
+    int layers;
+    int dims[PF_MAX_MLP_LAYERS + 1];
+    long long w_off[PF_MAX_MLP_LAYERS];         // offsets into the flat fp32 parameter buffer
+    long long b_off[PF_MAX_MLP_LAYERS];
+    float* act[PF_MAX_MLP_LAYERS];              // saved post-ELU activations [rows_cap, dims[l+1]] (last = output)
+    // tensor-core path: packed bf16 weights in UMMA tile order + fp32 biases, see pf_mlp_tc.cu
+    void* tc_weights; size_t tc_weight_bytes;
+    int tc_plan_id;
+};
+
+struct pf_rl_ctx {
+    pf_rl_params P;
+    int device, num_sms;
+    long long n_params, std_off;
+    PfNet net[2];                               // 0 actor, 1 critic
+    int rows_cap;                               // max(num_envs, minibatch size)
+    int mb_size;                                // (N*T) / num_mini_batches
+    int* perm;                                  // [N*T] minibatch permutation of this iteration
+    float* dbuf[2];                             // [rows_cap, max_width] backward ping-pong (dY / dH)
+    float* part;                                // split-K / column-sum partials
+    long long part_floats;
+    int wgrad_splits;
+    float* mu; float* val;                      // [rows_cap, A], [rows_cap] forward outputs
+    float* dmu; float* dval;                    // loss gradients
+    double* loss_part;                          // [loss_blocks][8 + A] per-CTA partials of the loss kernel
+    int loss_blocks;
+    double* gae_part;                           // [gae_blocks][2]
+    int gae_blocks;
+    double* norm_part;                          // [norm_blocks] grad-norm^2 partials
+    int norm_blocks;
+    void* tc;                                   // opaque state of the tensor-core path (pf_mlp_tc.cu), or NULL
+};
+
+// ---- tensor-core path entry points (pf_mlp_tc.cu) ----
+int pf_tc_create(pf_rl_ctx* c);                                   // allocates packed weights, builds tile plans
+void pf_tc_destroy(pf_rl_ctx* c);
+int pf_tc_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st);
+// fused MLP forward of one net on `rows` rows of x[rows, dims[0]] (fp32, row stride ldx):
+// out[rows, dims[layers]] fp32.  Optionally copies the input rows to `copy_to` (rollout storage row).
+int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x, long long ldx, int rows,
+                      float* out, float* copy_to, cudaStream_t st);
