@@ -343,7 +343,7 @@ def run_b200(args):
 
     env, cfg, train_cfg, state = build_env(args.task, args.num_envs, device, rank, world)
     policy = make_policy(env, train_cfg, args)
-    actions = torch.zeros(env.num_envs, env.num_actions, device=device)
+    actions = policy.actions if policy is not None else torch.zeros(env.num_envs, env.num_actions, device=device)
     extra = (lambda: policy.act_into(env, actions)) if policy is not None else None
     launches_per_step = cfg.control.decimation + 2 + (policy.launches_per_act if policy is not None else 0)
     env.reset()

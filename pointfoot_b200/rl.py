@@ -453,3 +453,43 @@ class OnPolicyRunner:
     def get_inference_policy(self, device=None):
         self.alg.actor_critic.eval()
         return self.alg.actor_critic.act_inference
+
+
+class BenchPolicy:
+    """What bench.py times next to env.step: PPO.act (actor + critic forward, sampling, log-prob, rollout-storage
+    row) writing the next actions in place.  Captured inside the step's CUDA graph, so the storage row and the
+    sampling step are the captured ones on every replay (same work, repeated noise)."""
+
+    def __init__(self, env, train_cfg, precision="bf16"):
+        from .config import class_to_dict
+        cfg = class_to_dict(train_cfg)
+        nc = env.num_privileged_obs if env.num_privileged_obs is not None else env.num_obs
+        self.ac = ActorCritic(env.num_obs, nc, env.num_actions, device=str(env.device), **cfg["policy"])
+        self.alg = PPO(self.ac, device=str(env.device), seed=cfg.get("seed", 1), precision=precision,
+                       env_id_offset=getattr(env, "env_id_offset", 0), **cfg["algorithm"])
+        self.alg.init_storage(env.num_envs, cfg["runner"]["num_steps_per_env"], [env.num_obs], [env.num_privileged_obs],
+                              [env.num_actions])
+        self.precision = precision
+        self.dtype_name = "bf16 (tcgen05 MLP, fp32 accumulate) + f32 env" if precision == "bf16" else "f32"
+        n_layers = len(self.ac.actor_dims) - 1 + len(self.ac.critic_dims) - 1
+        self.launches_per_act = 3 if precision == "bf16" else n_layers + 3
+        self.t = 0
+        self.actions = self.alg._actions          # pf_rl_act writes the sampled actions here: step them directly
+
+    def describe(self):
+        return (f"ActorCritic actor {self.ac.actor_dims} critic {self.ac.critic_dims} ELU, {self.precision}; "
+                "act + evaluate + sample + log-prob + rollout-storage row")
+
+    def act_into(self, env, actions):
+        alg = self.alg
+        alg.storage.step = self.t
+        obs = env.get_observations()
+        priv = env.get_privileged_observations()
+        a = alg.act(obs, priv if priv is not None else obs)
+        if actions.data_ptr() != a.data_ptr():
+            actions.copy_(a)
+        self.t = (self.t + 1) % alg.storage.num_transitions_per_env
+
+
+def make_bench_policy(env, train_cfg, precision=None):
+    return BenchPolicy(env, train_cfg, precision or os.environ.get("PF_RL_PRECISION", "bf16"))

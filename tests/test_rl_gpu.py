@@ -12,6 +12,13 @@ def test_act_storage_and_returns_match_oracle(hidden, nc):
     parity_rl.run_act_and_gae(num_envs=300, num_critic_obs=nc, hidden=hidden, T=6)
 
 
+@pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 300), ((512, 256, 128), 148, 300), ((512, 256, 128), 148, 4096),
+                                         ((256, 128), 48, 129), ((64, 64, 64, 64), 235, 1)])
+def test_tcgen05_mlp_act_matches_oracle_bf16(hidden, nc, n):
+    """PF_RL_BF16_TC: fused tcgen05 MLP (bf16 operands, fp32 accumulate in TMEM); tolerance rtol = atol = 2e-2"""
+    parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
+
+
 def test_gae_bit_exact():
     parity_rl.run_gae_exact(num_envs=1000, T=24)
     parity_rl.run_gae_exact(num_envs=1, T=3, seed=5)
