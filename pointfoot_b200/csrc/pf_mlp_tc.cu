@@ -23,10 +23,11 @@ void pf_set_error(const char* msg);
 
 #define TC_ROWS 128          // rows per CTA (UMMA M)
 #define TC_NCHUNK 128        // output columns per accumulator chunk (UMMA N <= 128)
-#define TC_KTILE 64          // K extent of one weight tile
+#define TC_KTILE 32          // K extent of one weight tile
 #define TC_TILE_BYTES (TC_NCHUNK * TC_KTILE * 2)
 #define TC_MAX_STAGES 4
-#define TC_THREADS 160       // warps 0-3: staging + epilogue (one TMEM lane quarter each); warp 4: TMA + MMA issue
+#define TC_EPI_WARPS 8       // staging + epilogue warps: 4 TMEM lane quarters x 2 column halves
+#define TC_THREADS (TC_EPI_WARPS * 32 + 32)   // + one warp that owns TMEM, issues the bulk copies and the MMAs
 
 struct TcPlan {
     int layers;
@@ -36,7 +37,6 @@ struct TcPlan {
     int bufA_bytes, bufB_bytes;          // activations of odd / even layer index
     int smem_bytes;
     long long w_off[PF_MAX_MLP_LAYERS];      // byte offsets of each layer's packed weight tiles inside the blob
-    long long bias_off[PF_MAX_MLP_LAYERS];   // byte offsets of the padded fp32 biases inside the packed blob
     long long blob_bytes;
 };
 
@@ -114,29 +114,34 @@ __device__ __forceinline__ uint32_t make_idesc(int n) {
 // ------------------------------------------------------------------------------------------------ kernel
 struct TcArgs {
     TcPlan plan;
-    const unsigned char* blob;   // packed bf16 weight tiles + fp32 biases
+    const unsigned char* blob;   // packed bf16 weight + bias tiles
     const float* x; long long ldx; int rows;
     float* out;                  // [rows, dims[layers]] fp32
     float* copy_to;              // optional [rows, dims[0]] copy of the input rows (rollout storage)
 };
 
-// weight tile (layer l, column chunk c, k tile k): nt x kt bf16, contiguous in the blob
-__device__ __forceinline__ long long tile_offset(const TcPlan& P, int l, int c, int k, int nt) {
-    return P.w_off[l] + (long long)c * TC_NCHUNK * P.pdims[l] * 2 + (long long)k * nt * TC_KTILE * 2;
+// Tiles of one (layer l, column chunk c), contiguous in the blob: first the BIAS tile (nt x 16: column 0 = bf16(b),
+// column 1 = bf16(b - bf16(b)), multiplied by a constant "ones" A operand, so the bias add is one extra K=16 MMA
+// per chunk instead of epilogue work), then the K tiles of TC_KTILE columns.
+__device__ __forceinline__ long long chunk_offset(const TcPlan& P, int l, int c) {
+    return P.w_off[l] + (long long)c * TC_NCHUNK * (P.pdims[l] + 16) * 2;
 }
+
+__device__ __forceinline__ float elu_fast(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
 
 __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const TcPlan& P = a.plan;
     unsigned char* bufA = smem;
     unsigned char* bufB = smem + P.bufA_bytes;
-    unsigned char* ring = bufB + P.bufB_bytes;
+    unsigned char* ones = bufB + P.bufB_bytes;                 // [128 x 16] bf16: columns 0,1 = 1
+    unsigned char* ring = ones + TC_ROWS * 16 * 2;
     uint64_t* bars = reinterpret_cast<uint64_t*>(ring + P.stages * TC_TILE_BYTES);
     const int S = P.stages;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_MAX_STAGES), accum0 = smem_u32(bars + 2 * TC_MAX_STAGES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + 2);
-    const int tid = threadIdx.x, warp = tid >> 5;
-    const bool leader = tid == 128;              // lane 0 of warp 4
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool leader = tid == TC_EPI_WARPS * 32;              // lane 0 of the last warp
     const int row0 = blockIdx.x * TC_ROWS;
     const int nrows = min(TC_ROWS, a.rows - row0);
     const int L = P.layers;
@@ -146,33 +151,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
         mbar_init(accum0, 1); mbar_init(accum0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {
+    if (warp == TC_EPI_WARPS) {
         __syncwarp();
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-
-    // ---- stage the input rows: fp32 global -> bf16 core-matrix layout (layer 0 reads bufB) ----
-    if (tid < TC_ROWS) {
-        const int K0 = P.dims[0], K0p = P.pdims[0];
-        const bool live = tid < nrows;
-        const float* xr = a.x + (long long)(row0 + tid) * a.ldx;
-        float* cr = a.copy_to ? a.copy_to + (long long)(row0 + tid) * K0 : nullptr;
-        for (int kb = 0; kb < K0p / 8; ++kb) {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int k = kb * 8 + i;
-                v[i] = (live && k < K0) ? __ldg(xr + k) : 0.0f;
-                if (cr && live && k < K0) cr[k] = v[i];
+    } else {
+        // ---- stage the input rows, coalesced: fp32 global -> bf16 core-matrix layout (layer 0 reads bufB) ----
+        const int K0 = P.dims[0], half = P.pdims[0] >> 1;                    // pairs of columns per padded row
+        const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)half - 1) / (uint32_t)half);
+        for (int i = tid; i < TC_ROWS * half; i += TC_EPI_WARPS * 32) {
+            const int r = (int)__umulhi((uint32_t)i, magic), k = (i - r * half) * 2;
+            float v0 = 0.0f, v1 = 0.0f;
+            if (r < nrows) {
+                const float* xr = a.x + (long long)(row0 + r) * a.ldx;
+                float* cr = a.copy_to ? a.copy_to + (long long)(row0 + r) * K0 : nullptr;
+                if (k < K0) { v0 = __ldg(xr + k); if (cr) cr[k] = v0; }
+                if (k + 1 < K0) { v1 = __ldg(xr + k + 1); if (cr) cr[k + 1] = v1; }
             }
-            __nv_bfloat162 p0 = __floats2bfloat162_rn(v[0], v[1]), p1 = __floats2bfloat162_rn(v[2], v[3]);
-            __nv_bfloat162 p2 = __floats2bfloat162_rn(v[4], v[5]), p3 = __floats2bfloat162_rn(v[6], v[7]);
-            uint4 q;
-            q.x = *reinterpret_cast<uint32_t*>(&p0); q.y = *reinterpret_cast<uint32_t*>(&p1);
-            q.z = *reinterpret_cast<uint32_t*>(&p2); q.w = *reinterpret_cast<uint32_t*>(&p3);
-            *reinterpret_cast<uint4*>(bufB + (size_t)kb * (TC_ROWS * 16) + tid * 16) = q;
+            __nv_bfloat162 pr = __floats2bfloat162_rn(v0, v1);
+            *reinterpret_cast<uint32_t*>(bufB + (size_t)(k >> 3) * (TC_ROWS * 16) + r * 16 + (k & 7) * 2) = *reinterpret_cast<uint32_t*>(&pr);
         }
+        for (int i = tid; i < TC_ROWS * 2; i += TC_EPI_WARPS * 32)           // ones operand: 2 column blocks x 128 rows x 16 B
+            *reinterpret_cast<uint4*>(ones + i * 16) = i < TC_ROWS ? make_uint4(0x3F803F80u, 0u, 0u, 0u) : make_uint4(0u, 0u, 0u, 0u);
     }
     fence_async_smem();
     tc_fence_before();
@@ -180,20 +180,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // total number of weight tiles, and the loader's cursor over (layer, chunk, k tile)
+    // total number of tiles, and the loader's cursor over (layer, chunk, tile-in-chunk)
     int total_tiles = 0;
-    for (int l = 0; l < L; ++l) total_tiles += ((P.pdims[l + 1] + TC_NCHUNK - 1) / TC_NCHUNK) * ((P.pdims[l] + TC_KTILE - 1) / TC_KTILE);
-    int ld_idx = 0, ld_l = 0, ld_c = 0, ld_k = 0;
+    for (int l = 0; l < L; ++l) total_tiles += ((P.pdims[l + 1] + TC_NCHUNK - 1) / TC_NCHUNK) * ((P.pdims[l] + TC_KTILE - 1) / TC_KTILE + 1);
+    int ld_idx = 0, ld_l = 0, ld_c = 0, ld_t = 0;
     auto issue_load = [&]() {         // leader only: tile ld_idx -> slot ld_idx % S
         const int Kp = P.pdims[ld_l], Np = P.pdims[ld_l + 1];
-        const int nt = min(TC_NCHUNK, Np - ld_c * TC_NCHUNK), kt = min(TC_KTILE, Kp - ld_k * TC_KTILE);
+        const int nt = min(TC_NCHUNK, Np - ld_c * TC_NCHUNK);
+        const int kt = ld_t == 0 ? 16 : min(TC_KTILE, Kp - (ld_t - 1) * TC_KTILE);
+        const long long off = chunk_offset(P, ld_l, ld_c) + (ld_t == 0 ? 0 : (long long)nt * 32 + (long long)(ld_t - 1) * nt * TC_KTILE * 2);
         const uint32_t bytes = (uint32_t)(nt * kt * 2);
         const int slot = ld_idx % S;
         mbar_expect_tx(full0 + 8 * slot, bytes);
-        bulk_g2s(smem_u32(ring + slot * TC_TILE_BYTES), a.blob + tile_offset(P, ld_l, ld_c, ld_k, nt), bytes, full0 + 8 * slot);
+        bulk_g2s(smem_u32(ring + slot * TC_TILE_BYTES), a.blob + off, bytes, full0 + 8 * slot);
         ++ld_idx;
-        if (++ld_k == (Kp + TC_KTILE - 1) / TC_KTILE) {
-            ld_k = 0;
+        if (++ld_t == (Kp + TC_KTILE - 1) / TC_KTILE + 1) {
+            ld_t = 0;
             if (++ld_c == (Np + TC_NCHUNK - 1) / TC_NCHUNK) { ld_c = 0; ++ld_l; }
         }
     };
@@ -205,8 +207,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
         unsigned char* in = (l & 1) ? bufA : bufB;
         unsigned char* outb = (l & 1) ? bufB : bufA;
         const int Kp = P.pdims[l], Np = P.pdims[l + 1];
-        const int nch = (Np + TC_NCHUNK - 1) / TC_NCHUNK, nkt = (Kp + TC_KTILE - 1) / TC_KTILE;
-        const float* bias = reinterpret_cast<const float*>(a.blob + P.bias_off[l]);
+        const int nch = (Np + TC_NCHUNK - 1) / TC_NCHUNK, ntl = (Kp + TC_KTILE - 1) / TC_KTILE + 1;
         const bool last = l == L - 1;
         for (int c = 0; c <= nch; ++c) {
             // ---- MMAs of chunk c (async), issued by one thread ----
@@ -218,17 +219,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
                     const uint32_t idesc = make_idesc(nt);
                     // leading byte offset = next 8 K-columns, stride byte offset = next 8 rows (verified on B200)
                     const uint32_t a_lbo = (uint32_t)(TC_ROWS * 16), a_sbo = 128u, b_lbo = (uint32_t)(nt * 16), b_sbo = 128u;
-                    for (int k = 0; k < nkt; ++k) {
-                        const int kt = min(TC_KTILE, Kp - k * TC_KTILE);
+                    for (int t = 0; t < ntl; ++t) {
+                        const int kt = t == 0 ? 16 : min(TC_KTILE, Kp - (t - 1) * TC_KTILE);
                         const int slot = use_idx % S;
                         mbar_wait(full0 + 8 * slot, (uint32_t)((use_idx / S) & 1));
                         tc_fence_after();
                         const uint32_t bs = smem_u32(ring + slot * TC_TILE_BYTES);
-                        const uint32_t as = smem_u32(in) + (uint32_t)(k * (TC_KTILE / 8) * (TC_ROWS * 16));
+                        const uint32_t as = t == 0 ? smem_u32(ones) : smem_u32(in) + (uint32_t)((t - 1) * (TC_KTILE / 8) * (TC_ROWS * 16));
                         for (int kk = 0; kk < kt / 16; ++kk) {
                             const uint64_t ad = make_desc(as + (uint32_t)(kk * 2 * (TC_ROWS * 16)), a_lbo, a_sbo);
                             const uint64_t bd = make_desc(bs + (uint32_t)(kk * 2 * (nt * 16)), b_lbo, b_sbo);
-                            umma_bf16(tmem_base + (uint32_t)(buf * TC_NCHUNK), ad, bd, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                            umma_bf16(tmem_base + (uint32_t)(buf * TC_NCHUNK), ad, bd, idesc, (t > 0 || kk > 0) ? 1u : 0u);
                         }
                         umma_commit(empty0 + 8 * slot);            // slot is free once these MMAs have read it
                         // refill the slot of the PREVIOUS tile (its MMAs are done or nearly so): keeps the issue
@@ -241,22 +242,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
                         ++use_idx;
                     }
                     umma_commit(accum0 + 8 * buf);
-                } else {
-                    use_idx += nkt;
                 }
                 ++chunk_seq;
             }
-            // ---- epilogue of chunk c-1 (warps 0-3; warp 4 only joins the barrier) ----
-            if (c > 0 && warp == 4) { tc_fence_before(); __syncthreads(); }
-            if (c > 0 && warp < 4) {
+            // ---- epilogue of chunk c-1: 8 warps = 4 TMEM lane quarters x 2 column halves; the issuing warp only
+            //      joins the barrier ----
+            if (c > 0 && warp == TC_EPI_WARPS) { tc_fence_before(); __syncthreads(); }
+            if (c > 0 && warp < TC_EPI_WARPS) {
                 const int pc = c - 1;
                 const int seq = chunk_seq - (c < nch ? 2 : 1);
                 const int buf = seq & 1;
                 const int nt = min(TC_NCHUNK, Np - pc * TC_NCHUNK);
+                const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
                 mbar_wait(accum0 + 8 * buf, (uint32_t)((seq >> 1) & 1));
                 tc_fence_after();
-                const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * TC_NCHUNK);
-                for (int g = 0; g < nt; g += 32) {
+                const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * TC_NCHUNK);
+                for (int g = h * 32; g < nt; g += 64) {
                     uint32_t v[32];
                     const int w = min(32, nt - g);
                     if (w == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
@@ -264,22 +265,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
                     const int n0 = pc * TC_NCHUNK + g;
                     if (last) {
                         const int no = P.dims[L];
-                        if (tid < nrows)
+                        if (row < nrows)
                             for (int j = 0; j < w; ++j)
-                                if (n0 + j < no) a.out[(long long)(row0 + tid) * no + n0 + j] = __uint_as_float(v[j]) + __ldg(bias + n0 + j);
+                                if (n0 + j < no) a.out[(long long)(row0 + row) * no + n0 + j] = __uint_as_float(v[j]);
                     } else {
                         for (int j = 0; j < w; j += 8) {
                             uint32_t pk[4];
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                float x0 = __uint_as_float(v[j + 2 * i]) + __ldg(bias + n0 + j + 2 * i);
-                                float x1 = __uint_as_float(v[j + 2 * i + 1]) + __ldg(bias + n0 + j + 2 * i + 1);
-                                x0 = x0 > 0.0f ? x0 : expm1f(x0);
-                                x1 = x1 > 0.0f ? x1 : expm1f(x1);
-                                __nv_bfloat162 p = __floats2bfloat162_rn(x0, x1);
+                                __nv_bfloat162 p = __floats2bfloat162_rn(elu_fast(__uint_as_float(v[j + 2 * i])),
+                                                                         elu_fast(__uint_as_float(v[j + 2 * i + 1])));
                                 pk[i] = *reinterpret_cast<uint32_t*>(&p);
                             }
-                            *reinterpret_cast<uint4*>(outb + (size_t)((n0 + j) >> 3) * (TC_ROWS * 16) + tid * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                            *reinterpret_cast<uint4*>(outb + (size_t)((n0 + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                         }
                     }
                 }
@@ -291,14 +289,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == TC_EPI_WARPS) {
         __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
     }
 }
 
 // ------------------------------------------------------------------------------------------------ packing
-// fp32 nn.Linear weight [out, in] -> bf16 tiles in consumption order + padded fp32 bias
+// fp32 nn.Linear weight [out, in] + bias -> bf16 tiles in consumption order (see chunk_offset)
 __global__ void pf_tc_pack_kernel(const TcPlan P, int l, const float* __restrict__ W, const float* __restrict__ b,
                                   unsigned char* blob) {
     const int Kp = P.pdims[l], Np = P.pdims[l + 1], K = P.dims[l], N = P.dims[l + 1];
@@ -307,11 +305,18 @@ __global__ void pf_tc_pack_kernel(const TcPlan P, int l, const float* __restrict
     const int n = (int)(i / Kp), k = (int)(i % Kp);
     const int c = n / TC_NCHUNK, nl = n % TC_NCHUNK, nt = min(TC_NCHUNK, Np - c * TC_NCHUNK);
     const int kt_i = k / TC_KTILE, kk = k % TC_KTILE;
-    const long long off = P.w_off[l] + (long long)c * TC_NCHUNK * Kp * 2 + (long long)kt_i * nt * TC_KTILE * 2 +
+    const long long base = P.w_off[l] + (long long)c * TC_NCHUNK * (Kp + 16) * 2;
+    const long long off = base + (long long)nt * 32 + (long long)kt_i * nt * TC_KTILE * 2 +
                           ((long long)(kk >> 3) * (nt >> 3) + (nl >> 3)) * 128 + (nl & 7) * 16 + (kk & 7) * 2;
     const float v = (n < N && k < K) ? W[(long long)n * K + k] : 0.0f;
     *reinterpret_cast<__nv_bfloat16*>(blob + off) = __float2bfloat16_rn(v);
-    if (k == 0) reinterpret_cast<float*>(blob + P.bias_off[l])[n] = n < N ? b[n] : 0.0f;
+    if (k == 0) {           // bias tile: columns 0 / 1 = high / low bf16 parts of the bias, the rest stays zero
+        const float bv = n < N ? b[n] : 0.0f;
+        const __nv_bfloat16 hi = __float2bfloat16_rn(bv);
+        const __nv_bfloat16 lo = __float2bfloat16_rn(bv - __bfloat162float(hi));
+        __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(blob + base + (long long)(nl >> 3) * 128 + (nl & 7) * 16);
+        d[0] = hi; d[1] = lo;
+    }
 }
 
 static int tc_fail(int code, const char* msg) { pf_set_error(msg); return code; }
@@ -326,14 +331,13 @@ static int build_plan(TcPlan& P, const PfNet& n) {
     }
     P.bufA_bytes = TC_ROWS * wa * 2;
     P.bufB_bytes = TC_ROWS * wb * 2;
-    const int limit = 227 * 1024 - 256;
+    const int limit = 227 * 1024 - 256 - TC_ROWS * 16 * 2;
     int S = (limit - P.bufA_bytes - P.bufB_bytes) / TC_TILE_BYTES;
     if (S < 2) return 1;
     P.stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
-    P.smem_bytes = P.bufA_bytes + P.bufB_bytes + P.stages * TC_TILE_BYTES + 256;
+    P.smem_bytes = P.bufA_bytes + P.bufB_bytes + TC_ROWS * 16 * 2 + P.stages * TC_TILE_BYTES + 256;
     long long off = 0;
-    for (int l = 0; l < n.layers; ++l) { P.w_off[l] = off; off += (long long)P.pdims[l] * P.pdims[l + 1] * 2; }
-    for (int l = 0; l < n.layers; ++l) { P.bias_off[l] = off; off += (long long)P.pdims[l + 1] * 4; }
+    for (int l = 0; l < n.layers; ++l) { P.w_off[l] = off; off += (long long)(P.pdims[l] + 16) * P.pdims[l + 1] * 2; }
     P.blob_bytes = off;
     return 0;
 }
@@ -347,6 +351,7 @@ int pf_tc_create(pf_rl_ctx* c) {
             return tc_fail(6, "pf_rl_create: MLP too wide for the fused tensor-core kernel (activations of one 128-row tile must fit in shared memory)");
         }
         if (cudaMalloc(&c->net[k].tc_weights, (size_t)t->plan[k].blob_bytes) != cudaSuccess) { delete t; return tc_fail(2, "pf_rl_create: cudaMalloc of the packed weights failed"); }
+        cudaMemset(c->net[k].tc_weights, 0, (size_t)t->plan[k].blob_bytes);      // padding columns of the bias tiles stay zero
         c->net[k].tc_weight_bytes = (size_t)t->plan[k].blob_bytes;
         max_smem = t->plan[k].smem_bytes > max_smem ? t->plan[k].smem_bytes : max_smem;
     }
