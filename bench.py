@@ -38,7 +38,8 @@ def parse_args():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-policy", action="store_true")
-    p.add_argument("--sweep", default="", help="comma separated extra env counts reported under 'sweep'")
+    p.add_argument("--l2", default="flush", choices=["flush", "none"],
+                   help="'none' is a DIAGNOSTIC (hot caches): such a line is marked invalid")
     return p.parse_args()
 
 
@@ -339,7 +340,8 @@ def run_b200(args):
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=device)
 
     def flush():
-        flush_buf.fill_(1)
+        if args.l2 == "flush":
+            flush_buf.fill_(1)
 
     env, cfg, train_cfg, state = build_env(args.task, args.num_envs, device, rank, world)
     policy = make_policy(env, train_cfg, args)
@@ -386,7 +388,8 @@ def run_b200(args):
                            "policy": policy.describe() if policy else "none",
                            "physics": "excluded (Isaac Gym not installable): synthetic state tensors resident in HBM",
                            "cuda_graph": not args.no_graph,
-                           "l2": "256 MB write before every timed step, excluded from the per-step CUDA-event time",
+                           "l2": "256 MB write before every timed step, excluded from the per-step CUDA-event time"
+                                 if args.l2 == "flush" else "DIAGNOSTIC RUN, caches hot: not a valid bench line",
                            "parallelism": f"env-sharded x{world}, no data-path collective"},
                 "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roof,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

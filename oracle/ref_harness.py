@@ -75,8 +75,11 @@ def install_stubs():
     if not reference_available():
         raise RuntimeError(f"reference not found under {REFERENCE_ROOT}")
 
+    import importlib.machinery
+
     def mod(name, **attrs):
         m = types.ModuleType(name)
+        m.__spec__ = importlib.machinery.ModuleSpec(name, None)     # find_spec() on a stub must not raise
         m.__dict__.update(attrs)
         sys.modules[name] = m
         return m
@@ -89,6 +92,7 @@ def install_stubs():
 
     def anymod(name):
         m = _ModAny(name)
+        m.__spec__ = importlib.machinery.ModuleSpec(name, None)
         sys.modules[name] = m
         return m
 
