@@ -19,7 +19,7 @@ from collections import deque
 
 import torch
 
-from . import capi
+from . import capi, shard
 
 
 def _ptr(t):
@@ -155,9 +155,6 @@ class RolloutStorage:
         self.step = 0
 
 
-def _dist():
-    import torch.distributed as dist
-    return dist if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 else None
 
 
 class PPO:
@@ -263,20 +260,16 @@ class PPO:
         capi.check(lib.pf_rl_evaluate(self._ctx, _ptr(self.actor_critic.flat), _ptr(last_critic_obs), _ptr(self._last_values), st),
                    "pf_rl_evaluate")
         capi.check(lib.pf_rl_gae(self._ctx, C.byref(self.storage.c), _ptr(self._last_values), _ptr(self._gae_stats), st), "pf_rl_gae")
-        d = _dist()
-        if d:
-            d.all_reduce(self._gae_stats)
+        shard.allreduce_sum_(self._gae_stats)              # advantage mean / std span all shards
         capi.check(lib.pf_rl_normalize_advantages(self._ctx, C.byref(self.storage.c), _ptr(self._gae_stats), st),
                    "pf_rl_normalize_advantages")
 
     def minibatch_grad(self, mb):
         capi.check(self._lib.pf_rl_minibatch_grad(self._ctx, C.byref(self.storage.c), C.byref(self._L), C.c_int32(mb), self._st()),
                    "pf_rl_minibatch_grad")
-        d = _dist()
-        if d:       # one flat buffer -> ONE all-reduce per optimizer step (1.68 MB rough / 112 KB flat)
-            d.all_reduce(self.grads)
-            self.grads.div_(d.get_world_size())
-            d.all_reduce(self.loss_stats)
+        if shard.dist_or_none():   # one flat buffer -> ONE all-reduce per optimizer step (1.68 MB rough / 112 KB flat)
+            shard.allreduce_mean_(self.grads)
+            shard.allreduce_sum_(self.loss_stats)
 
     def update(self):
         lib, st = self._lib, self._st()
