@@ -267,6 +267,10 @@ int64_t pf_rl_param_offset(const pf_rl_ctx* ctx, int net, int layer, int is_bias
 /* must be called after the caller changes `params` by other means than pf_rl_adam_step (init, load):
  * refreshes the packed bf16 copies the tensor-core path reads */
 int pf_rl_params_changed(pf_rl_ctx* ctx, const float* params, void* stream);
+/* Host-only diagnostic, no device needed: can the fused tensor-core kernel (PF_RL_BF16_TC) run an MLP of this shape
+ * (dims[0..layers], the ctor args of actor_critic.py ActorCritic)?  0 yes, 6 no -- the code pf_rl_create would return.
+ * If `text` is non-NULL the kernel's static schedule is printed into it. */
+int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, int32_t cap);
 
 /* PPO.act (ppo.py act) fused with RolloutStorage.add_transitions' copies: actor forward -> Normal(mean, std)
  * sample (RNG contract, purpose POLICY, step = policy_step) -> log-prob; critic forward; writes row `t` of the

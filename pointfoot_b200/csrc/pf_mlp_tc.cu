@@ -1,14 +1,22 @@
-// Tensor-core path of ActorCritic (rsl_rl modules/actor_critic.py): the whole MLP -- every Linear + bias + ELU of
-// one network -- fused into ONE sm_100a kernel built on tcgen05.mma with accumulators in TMEM.
+// Tensor-core path of ActorCritic (rsl_rl modules/actor_critic.py): every Linear + bias + ELU of BOTH networks, the
+// Normal sample / log-prob of PPO.act and the rollout-storage writes fused into ONE persistent sm_100a kernel built
+// on tcgen05.mma with accumulators in TMEM.
 //
-//   * a CTA owns a tile of 128 rows (envs / samples): UMMA M = 128, cta_group::1, bf16 operands, fp32 accumulate;
-//   * activations never leave the SM: each layer's output tile goes TMEM -> registers (tcgen05.ld) -> bias + ELU
-//     -> bf16 -> shared memory, already in the K-major core-matrix layout the next layer's A descriptor reads;
-//   * weights are pre-packed (pf_tc_pack_weights, after every optimizer step) into that same layout, tile by tile
-//     in consumption order, so a weight tile is ONE contiguous bulk async copy (cp.async.bulk, the TMA engine,
-//     completion by mbarrier transaction bytes) into a small ring that runs ahead of the MMAs;
-//   * the layer output is produced in chunks of <= 128 columns, double-buffered in TMEM (2 x 128 columns): the
-//     MMAs of chunk c+1 are issued before the epilogue of chunk c, so the tensor pipe works under the epilogue.
+//   * a work item is (net, tile of 128 rows): UMMA M = 128, cta_group::1, bf16 operands, fp32 accumulate; one CTA
+//     per SM walks the items round-robin, so weights of the next item stream in under the tail of the current one;
+//   * activations never leave the SM and are never held whole: the output of a layer is produced in chunks of
+//     <= 128 columns (TMEM -> registers -> ELU -> bf16 -> shared memory, in the K-major core-matrix layout an A
+//     descriptor reads) and every chunk is consumed at once as a K-slice of the NEXT layer, whose accumulator
+//     (<= 256 columns) sits in the other half of TMEM.  Two 32 KB chunk buffers + the staged input rows are all the
+//     activation storage there is, which leaves ~110 KB for the weight ring;
+//   * weights are pre-packed (pf_tc_pack_weights, after every optimizer step) in exactly the order the MMAs consume
+//     them, <= 8 KB tiles, so a tile is ONE contiguous bulk async copy (cp.async.bulk / TMA engine, completion by
+//     mbarrier transaction bytes) issued by a dedicated loader thread that runs up to 14 tiles ahead;
+//   * the bias add is one extra K = 16 MMA per accumulator against a constant "ones" operand (bias split in
+//     hi + lo bf16), so the epilogue is only ELU + pack;
+//   * warp roles: warps 0-7 stage inputs and run the epilogues (4 TMEM lane quarters x 2 column halves), warp 8
+//     owns TMEM and issues the MMAs, warp 9 issues the bulk copies.  They only meet at mbarriers; the schedule
+//     (which group waits for / signals which barrier, with which phase) is a small static PROGRAM built on the host.
 //
 // Shared-memory operand layout (no swizzle, "interleave"): 8 rows x 16 bytes core matrices, stored contiguously
 // (128 B); for an operand with R rows: element (r, k) of bf16 at  (k/8) * (R*16) + r*16 + (k%8)*2  bytes.
@@ -17,30 +25,65 @@
 #include <cuda_bf16.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include "pf_rl_internal.h"
+#include "pf_rng.cuh"
 
 void pf_set_error(const char* msg);
 
-#define TC_ROWS 128          // rows per CTA (UMMA M)
-#define TC_NCHUNK 128        // output columns per accumulator chunk (UMMA N <= 128)
-#define TC_KTILE 32          // K extent of one weight tile
-#define TC_TILE_BYTES (TC_NCHUNK * TC_KTILE * 2)
-#define TC_MAX_STAGES 4
-#define TC_EPI_WARPS 8       // staging + epilogue warps: 4 TMEM lane quarters x 2 column halves
-#define TC_THREADS (TC_EPI_WARPS * 32 + 32)   // + one warp that owns TMEM, issues the bulk copies and the MMAs
+#define TC_ROWS 128                          // rows per work item (UMMA M)
+#define TC_CHUNK 128                         // columns of one activation chunk
+#define TC_ACHUNK_BYTES (TC_ROWS * TC_CHUNK * 2)
+#define TC_SLOT_BYTES 8192                   // weight ring slot = largest tile (N x K x 2 B: 256x16, 128x32, 64x64 ...)
+#define TC_MAX_STAGES 16
+#define TC_EPI_WARPS 8
+#define TC_EPI_THREADS (TC_EPI_WARPS * 32)
+#define TC_THREADS (TC_EPI_THREADS + 64)     // + MMA warp + loader warp
+#define TC_MAX_GROUPS 24
+#define TC_MAX_EPIS 16
+#define TC_TMEM_COLS 512
 
-struct TcPlan {
+// program barriers (besides the ring's full / empty pairs)
+enum { BAR_ACC0 = 0, BAR_ACC1 = 1, BAR_ACC2 = 2,      // accumulator complete: TMEM cols [0,128) or [0,256) / [128,256) / [256,512)
+       BAR_AFREE0 = 3, BAR_AFREE1 = 4,               // MMAs that read activation chunk buffer b have completed
+       BAR_E0 = 5, BAR_E1 = 6,                       // epilogue wrote chunk buffer b (and drained its accumulator)
+       BAR_XFULL = 7, TC_NBARS = 8 };                // input rows of the item are staged
+
+// One accumulation step: D[128 x nt] (+)= A[128 x kc] * W^T, A = staged input rows or an activation chunk.
+struct TcGroup {
+    uint32_t blob_off;                 // first tile of the group inside the net's packed blob
+    uint16_t nt, kc, kt;               // UMMA N, K extent of the group, K per weight tile
+    uint16_t tmem_col;                 // accumulator column
+    uint16_t n_base, k_base;           // origin inside the layer's weight matrix (packing)
+    int8_t layer;
+    int8_t a_src;                      // 0 staged input, 1 + b activation chunk buffer b
+    int8_t bias;                       // starts the accumulation with the bias tile
+    int8_t wait_bar, wait_k;           // barrier (+ completion index inside the item) to wait for before the first MMA
+    int8_t commit_bar, commit2_bar;    // barriers the completion of the group's MMAs arrives on (-1: none)
+    int8_t pad;
+};
+// One epilogue step: accumulator columns [tmem_col, tmem_col + nt) -> activation chunk buffer or the final output.
+struct TcEpi {
+    uint16_t tmem_col, nt, n0;         // n0: first output column (final layer)
+    int8_t acc_bar, acc_k;             // accumulator-complete barrier + completion index
+    int8_t dst;                        // -1 final output, else chunk buffer
+    int8_t free_bar, free_k;           // MMAs still reading the chunk buffer (-1: none)
+    int8_t done_bar;                   // arrives here when written
+    int8_t pad[2];
+};
+struct TcProgram {
     int layers;
     int dims[PF_MAX_MLP_LAYERS + 1];     // true widths
     int pdims[PF_MAX_MLP_LAYERS + 1];    // padded to a multiple of 16
-    int stages;
-    int bufA_bytes, bufB_bytes;          // activations of odd / even layer index
-    int smem_bytes;
-    long long w_off[PF_MAX_MLP_LAYERS];      // byte offsets of each layer's packed weight tiles inside the blob
+    int ngroups, nepis;
+    uint32_t parity_mask;                // bit b: barrier b completes an odd number of times per item
+    int x0_bytes;
     long long blob_bytes;
+    TcGroup g[TC_MAX_GROUPS];
+    TcEpi e[TC_MAX_EPIS];
 };
 
-struct TcState { TcPlan plan[2]; };
+struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; };   // [actor only, critic only, both]
 
 static inline int pad16(int x) { return (x + 15) & ~15; }
 
@@ -111,67 +154,56 @@ __device__ __forceinline__ uint32_t make_idesc(int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_ROWS >> 4) << 24);
 }
 
-// ------------------------------------------------------------------------------------------------ kernel
-struct TcArgs {
-    TcPlan plan;
-    const unsigned char* blob;   // packed bf16 weight + bias tiles
-    const float* x; long long ldx; int rows;
-    float* out;                  // [rows, dims[layers]] fp32
-    float* copy_to;              // optional [rows, dims[0]] copy of the input rows (rollout storage)
-};
-
-// Tiles of one (layer l, column chunk c), contiguous in the blob: first the BIAS tile (nt x 16: column 0 = bf16(b),
-// column 1 = bf16(b - bf16(b)), multiplied by a constant "ones" A operand, so the bias add is one extra K=16 MMA
-// per chunk instead of epilogue work), then the K tiles of TC_KTILE columns.
-__device__ __forceinline__ long long chunk_offset(const TcPlan& P, int l, int c) {
-    return P.w_off[l] + (long long)c * TC_NCHUNK * (P.pdims[l] + 16) * 2;
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+
+// ------------------------------------------------------------------------------------------------ kernel
+enum { TC_OUT_PLAIN = 0, TC_OUT_SAMPLE = 1, TC_OUT_VALUE = 2 };
+
+struct TcNetArgs {
+    const unsigned char* blob;   // packed bf16 weight + bias tiles
+    const float* x; long long ldx;
+    float* out;                  // TC_OUT_PLAIN: [rows, dims[layers]] fp32
+    float* copy_to;              // optional [rows, dims[0]] copy of the input rows (rollout storage)
+    int mode;
+};
+struct TcArgs {
+    TcProgram prog[2];
+    TcNetArgs net[2];
+    int nnets, rows, tiles, stages, x0_bytes;
+    // PPO.act tail (TC_OUT_SAMPLE / TC_OUT_VALUE)
+    uint32_t seed, policy_step; int env_id_offset, num_actions;
+    const float* std;
+    pf_rl_storage S; int has_storage; long long storage_row0;
+    float* actions_out; float* values_out; float* logp_out;
+};
 
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a) {
+__global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const TcPlan& P = a.plan;
-    unsigned char* bufA = smem;
-    unsigned char* bufB = smem + P.bufA_bytes;
-    unsigned char* ones = bufB + P.bufB_bytes;                 // [128 x 16] bf16: columns 0,1 = 1
-    unsigned char* ring = ones + TC_ROWS * 16 * 2;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + P.stages * TC_TILE_BYTES);
-    const int S = P.stages;
-    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_MAX_STAGES), accum0 = smem_u32(bars + 2 * TC_MAX_STAGES);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + 2);
+    unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] bf16
+    unsigned char* ach = smem + a.x0_bytes;                    // 2 activation chunk buffers [128 x 128] bf16
+    unsigned char* ones = ach + 2 * TC_ACHUNK_BYTES;           // [128 x 16] bf16: columns 0,1 = 1
+    unsigned char* ring = ones + TC_ROWS * 32;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + a.stages * TC_SLOT_BYTES);
+    const int S = a.stages;
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_MAX_STAGES), pb0 = smem_u32(bars + 2 * TC_MAX_STAGES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + TC_NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const bool leader = tid == TC_EPI_WARPS * 32;              // lane 0 of the last warp
-    const int row0 = blockIdx.x * TC_ROWS;
-    const int nrows = min(TC_ROWS, a.rows - row0);
-    const int L = P.layers;
+    const int items = a.nnets * a.tiles;
 
-    if (leader) {
+    if (warp == TC_EPI_WARPS + 1 && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        mbar_init(accum0, 1); mbar_init(accum0 + 8, 1);
+        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, b >= BAR_E0 ? TC_EPI_THREADS : 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == TC_EPI_WARPS) {
-        __syncwarp();
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256u) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    } else {
-        // ---- stage the input rows, coalesced: fp32 global -> bf16 core-matrix layout (layer 0 reads bufB) ----
-        const int K0 = P.dims[0], half = P.pdims[0] >> 1;                    // pairs of columns per padded row
-        const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)half - 1) / (uint32_t)half);
-        for (int i = tid; i < TC_ROWS * half; i += TC_EPI_WARPS * 32) {
-            const int r = (int)__umulhi((uint32_t)i, magic), k = (i - r * half) * 2;
-            float v0 = 0.0f, v1 = 0.0f;
-            if (r < nrows) {
-                const float* xr = a.x + (long long)(row0 + r) * a.ldx;
-                float* cr = a.copy_to ? a.copy_to + (long long)(row0 + r) * K0 : nullptr;
-                if (k < K0) { v0 = __ldg(xr + k); if (cr) cr[k] = v0; }
-                if (k + 1 < K0) { v1 = __ldg(xr + k + 1); if (cr) cr[k + 1] = v1; }
-            }
-            __nv_bfloat162 pr = __floats2bfloat162_rn(v0, v1);
-            *reinterpret_cast<uint32_t*>(bufB + (size_t)(k >> 3) * (TC_ROWS * 16) + r * 16 + (k & 7) * 2) = *reinterpret_cast<uint32_t*>(&pr);
-        }
-        for (int i = tid; i < TC_ROWS * 2; i += TC_EPI_WARPS * 32)           // ones operand: 2 column blocks x 128 rows x 16 B
+    } else if (warp < TC_EPI_WARPS) {
+        for (int i = tid; i < TC_ROWS * 2; i += TC_EPI_THREADS)             // ones operand: 2 column blocks x 128 rows x 16 B
             *reinterpret_cast<uint4*>(ones + i * 16) = i < TC_ROWS ? make_uint4(0x3F803F80u, 0u, 0u, 0u) : make_uint4(0u, 0u, 0u, 0u);
     }
     fence_async_smem();
@@ -180,96 +212,117 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // total number of tiles, and the loader's cursor over (layer, chunk, tile-in-chunk)
-    int total_tiles = 0;
-    for (int l = 0; l < L; ++l) total_tiles += ((P.pdims[l + 1] + TC_NCHUNK - 1) / TC_NCHUNK) * ((P.pdims[l] + TC_KTILE - 1) / TC_KTILE + 1);
-    int ld_idx = 0, ld_l = 0, ld_c = 0, ld_t = 0;
-    auto issue_load = [&]() {         // leader only: tile ld_idx -> slot ld_idx % S
-        const int Kp = P.pdims[ld_l], Np = P.pdims[ld_l + 1];
-        const int nt = min(TC_NCHUNK, Np - ld_c * TC_NCHUNK);
-        const int kt = ld_t == 0 ? 16 : min(TC_KTILE, Kp - (ld_t - 1) * TC_KTILE);
-        const long long off = chunk_offset(P, ld_l, ld_c) + (ld_t == 0 ? 0 : (long long)nt * 32 + (long long)(ld_t - 1) * nt * TC_KTILE * 2);
-        const uint32_t bytes = (uint32_t)(nt * kt * 2);
-        const int slot = ld_idx % S;
-        mbar_expect_tx(full0 + 8 * slot, bytes);
-        bulk_g2s(smem_u32(ring + slot * TC_TILE_BYTES), a.blob + off, bytes, full0 + 8 * slot);
-        ++ld_idx;
-        if (++ld_t == (Kp + TC_KTILE - 1) / TC_KTILE + 1) {
-            ld_t = 0;
-            if (++ld_c == (Np + TC_NCHUNK - 1) / TC_NCHUNK) { ld_c = 0; ++ld_l; }
+    if (warp == TC_EPI_WARPS + 1) {
+        // ================================================================ loader: one thread, runs ahead of the MMAs
+        if (lane == 0) {
+            uint32_t n = 0;
+            for (int w = blockIdx.x; w < items; w += gridDim.x) {
+                const int k = w / a.tiles;
+                const TcProgram& P = a.prog[k];
+                const unsigned char* blob = a.net[k].blob;
+                for (int gi = 0; gi < P.ngroups; ++gi) {
+                    const TcGroup& G = P.g[gi];
+                    uint32_t off = G.blob_off;
+                    const int nt = G.nt, kc = G.kc, kt = G.kt;
+                    for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
+                        const uint32_t bytes = (uint32_t)(nt * (k0 < 0 ? 16 : min(kt, kc - k0)) * 2);
+                        const uint32_t slot = n % (uint32_t)S;
+                        if (n >= (uint32_t)S) mbar_wait(empty0 + 8 * slot, ((n / (uint32_t)S) - 1u) & 1u);
+                        mbar_expect_tx(full0 + 8 * slot, bytes);
+                        bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
+                        off += bytes;
+                        ++n;
+                    }
+                }
+            }
         }
-    };
-    if (leader)
-        for (int s = 0; s < S && ld_idx < total_tiles; ++s) issue_load();
-
-    int use_idx = 0, chunk_seq = 0;
-    for (int l = 0; l < L; ++l) {
-        unsigned char* in = (l & 1) ? bufA : bufB;
-        unsigned char* outb = (l & 1) ? bufB : bufA;
-        const int Kp = P.pdims[l], Np = P.pdims[l + 1];
-        const int nch = (Np + TC_NCHUNK - 1) / TC_NCHUNK, ntl = (Kp + TC_KTILE - 1) / TC_KTILE + 1;
-        const bool last = l == L - 1;
-        for (int c = 0; c <= nch; ++c) {
-            // ---- MMAs of chunk c (async), issued by one thread ----
-            if (c < nch) {
-                const int nt = min(TC_NCHUNK, Np - c * TC_NCHUNK);
-                const int buf = chunk_seq & 1;
-                if (leader) {
+    } else if (warp == TC_EPI_WARPS) {
+        // ================================================================ MMA issue: one thread
+        if (lane == 0) {
+            uint32_t n = 0, pbits = 0;
+            for (int w = blockIdx.x; w < items; w += gridDim.x) {
+                const TcProgram& P = a.prog[w / a.tiles];
+                for (int gi = 0; gi < P.ngroups; ++gi) {
+                    const TcGroup& G = P.g[gi];
+                    if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, ((pbits >> G.wait_bar) ^ (uint32_t)G.wait_k) & 1u);
                     tc_fence_after();
+                    const int nt = G.nt, kc = G.kc, kt = G.kt;
                     const uint32_t idesc = make_idesc(nt);
-                    // leading byte offset = next 8 K-columns, stride byte offset = next 8 rows (verified on B200)
-                    const uint32_t a_lbo = (uint32_t)(TC_ROWS * 16), a_sbo = 128u, b_lbo = (uint32_t)(nt * 16), b_sbo = 128u;
-                    for (int t = 0; t < ntl; ++t) {
-                        const int kt = t == 0 ? 16 : min(TC_KTILE, Kp - (t - 1) * TC_KTILE);
-                        const int slot = use_idx % S;
-                        mbar_wait(full0 + 8 * slot, (uint32_t)((use_idx / S) & 1));
+                    const uint32_t tmem_d = tmem_base + G.tmem_col;
+                    const uint32_t a_base = G.a_src == 0 ? smem_u32(x0) : smem_u32(ach) + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
+                    const uint32_t a_lbo = TC_ROWS * 16, b_lbo = (uint32_t)(nt * 16);
+                    uint32_t acc = G.bias ? 0u : 1u;
+                    for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
+                        const uint32_t slot = n % (uint32_t)S;
+                        mbar_wait(full0 + 8 * slot, (n / (uint32_t)S) & 1u);
                         tc_fence_after();
-                        const uint32_t bs = smem_u32(ring + slot * TC_TILE_BYTES);
-                        const uint32_t as = t == 0 ? smem_u32(ones) : smem_u32(in) + (uint32_t)((t - 1) * (TC_KTILE / 8) * (TC_ROWS * 16));
-                        for (int kk = 0; kk < kt / 16; ++kk) {
-                            const uint64_t ad = make_desc(as + (uint32_t)(kk * 2 * (TC_ROWS * 16)), a_lbo, a_sbo);
-                            const uint64_t bd = make_desc(bs + (uint32_t)(kk * 2 * (nt * 16)), b_lbo, b_sbo);
-                            umma_bf16(tmem_base + (uint32_t)(buf * TC_NCHUNK), ad, bd, idesc, (t > 0 || kk > 0) ? 1u : 0u);
+                        const uint32_t bs = smem_u32(ring + slot * TC_SLOT_BYTES);
+                        if (k0 < 0) {
+                            umma_bf16(tmem_d, make_desc(smem_u32(ones), a_lbo, 128u), make_desc(bs, b_lbo, 128u), idesc, 0u);
+                            acc = 1u;
+                        } else {
+                            const int kk_n = min(kt, kc - k0) >> 4;
+                            for (int kk = 0; kk < kk_n; ++kk) {
+                                const uint64_t ad = make_desc(a_base + (uint32_t)(((k0 >> 3) + kk * 2) * (TC_ROWS * 16)), a_lbo, 128u);
+                                const uint64_t bd = make_desc(bs + (uint32_t)(kk * 2 * (nt * 16)), b_lbo, 128u);
+                                umma_bf16(tmem_d, ad, bd, idesc, acc);
+                                acc = 1u;
+                            }
                         }
                         umma_commit(empty0 + 8 * slot);            // slot is free once these MMAs have read it
-                        // refill the slot of the PREVIOUS tile (its MMAs are done or nearly so): keeps the issue
-                        // of this tile's MMAs off the wait
-                        if (use_idx >= 1 && ld_idx < total_tiles && ld_idx == use_idx - 1 + S) {
-                            const int ps = (use_idx - 1) % S;
-                            mbar_wait(empty0 + 8 * ps, (uint32_t)(((use_idx - 1) / S) & 1));
-                            issue_load();
-                        }
-                        ++use_idx;
+                        ++n;
                     }
-                    umma_commit(accum0 + 8 * buf);
+                    if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
+                    if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
                 }
-                ++chunk_seq;
+                pbits ^= P.parity_mask;
             }
-            // ---- epilogue of chunk c-1: 8 warps = 4 TMEM lane quarters x 2 column halves; the issuing warp only
-            //      joins the barrier ----
-            if (c > 0 && warp == TC_EPI_WARPS) { tc_fence_before(); __syncthreads(); }
-            if (c > 0 && warp < TC_EPI_WARPS) {
-                const int pc = c - 1;
-                const int seq = chunk_seq - (c < nch ? 2 : 1);
-                const int buf = seq & 1;
-                const int nt = min(TC_NCHUNK, Np - pc * TC_NCHUNK);
-                const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
-                mbar_wait(accum0 + 8 * buf, (uint32_t)((seq >> 1) & 1));
+        }
+    } else {
+        // ================================================================ staging + epilogues: 8 warps
+        const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
+        uint32_t pbits = 0;
+        for (int w = blockIdx.x; w < items; w += gridDim.x) {
+            const int k = w / a.tiles, tile = w - k * a.tiles;
+            const TcProgram& P = a.prog[k];
+            const TcNetArgs& N = a.net[k];
+            const int row0 = tile * TC_ROWS;
+            const int nrows = min(TC_ROWS, a.rows - row0);
+            const int L = P.layers;
+            {   // ---- stage the input rows, coalesced: fp32 global -> bf16 core-matrix layout ----
+                const int K0 = P.dims[0], half = P.pdims[0] >> 1;                    // pairs of columns per padded row
+                const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)half - 1) / (uint32_t)half);
+                for (int i = tid; i < TC_ROWS * half; i += TC_EPI_THREADS) {
+                    const int r = (int)__umulhi((uint32_t)i, magic), kx = (i - r * half) * 2;
+                    float v0 = 0.0f, v1 = 0.0f;
+                    if (r < nrows) {
+                        const float* xr = N.x + (long long)(row0 + r) * N.ldx;
+                        float* cr = N.copy_to ? N.copy_to + (long long)(row0 + r) * K0 : nullptr;
+                        if (kx < K0) { v0 = __ldg(xr + kx); if (cr) cr[kx] = v0; }
+                        if (kx + 1 < K0) { v1 = __ldg(xr + kx + 1); if (cr) cr[kx + 1] = v1; }
+                    }
+                    __nv_bfloat162 pr = __floats2bfloat162_rn(v0, v1);
+                    *reinterpret_cast<uint32_t*>(x0 + (size_t)(kx >> 3) * (TC_ROWS * 16) + r * 16 + (kx & 7) * 2) = *reinterpret_cast<uint32_t*>(&pr);
+                }
+                fence_async_smem();
+                mbar_arrive(pb0 + 8 * BAR_XFULL);
+            }
+            for (int ei = 0; ei < P.nepis; ++ei) {
+                const TcEpi& E = P.e[ei];
+                mbar_wait(pb0 + 8 * E.acc_bar, ((pbits >> E.acc_bar) ^ (uint32_t)E.acc_k) & 1u);
+                if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, ((pbits >> E.free_bar) ^ (uint32_t)E.free_k) & 1u);
                 tc_fence_after();
-                const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * TC_NCHUNK);
-                for (int g = h * 32; g < nt; g += 64) {
+                const int nt = E.nt, units = nt >> 4, u0 = (units + 1) >> 1;
+                const int c_lo = h == 0 ? 0 : u0 * 16, c_hi = h == 0 ? u0 * 16 : nt;
+                const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + E.tmem_col;
+                unsigned char* outb = E.dst >= 0 ? ach + E.dst * TC_ACHUNK_BYTES : nullptr;
+                for (int g = c_lo; g < c_hi; g += 32) {
                     uint32_t v[32];
-                    const int w = min(32, nt - g);
-                    if (w == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
+                    const int wd = min(32, c_hi - g);
+                    if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
                     tmem_ld_wait();
-                    const int n0 = pc * TC_NCHUNK + g;
-                    if (last) {
-                        const int no = P.dims[L];
-                        if (row < nrows)
-                            for (int j = 0; j < w; ++j)
-                                if (n0 + j < no) a.out[(long long)(row0 + row) * no + n0 + j] = __uint_as_float(v[j]);
-                    } else {
-                        for (int j = 0; j < w; j += 8) {
+                    if (outb) {
+                        for (int j = 0; j < wd; j += 8) {
                             uint32_t pk[4];
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
@@ -277,83 +330,303 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const TcArgs a
                                                                          elu_fast(__uint_as_float(v[j + 2 * i + 1])));
                                 pk[i] = *reinterpret_cast<uint32_t*>(&p);
                             }
-                            *reinterpret_cast<uint4*>(outb + (size_t)((n0 + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                            *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        }
+                    } else if (row < nrows) {
+                        const int no = P.dims[L], n0 = E.n0 + g;
+                        const long long er = (long long)row0 + row;
+                        if (N.mode == TC_OUT_PLAIN) {
+                            for (int j = 0; j < wd; ++j)
+                                if (n0 + j < no) N.out[er * no + n0 + j] = __uint_as_float(v[j]);
+                        } else if (N.mode == TC_OUT_VALUE) {
+                            if (n0 == 0) {
+                                const float val = __uint_as_float(v[0]);
+                                if (a.values_out) a.values_out[er] = val;
+                                if (a.has_storage) a.S.values[a.storage_row0 + er] = val;
+                            }
+                        } else if (n0 == 0) {
+                            // Normal(mean, std).sample() under the RNG contract + log_prob(actions).sum(-1)
+                            // (actor_critic.py act / get_actions_log_prob; rollout_storage.py add_transitions)
+                            const int A = a.num_actions;
+                            const uint32_t ek = pf_rng_env_key(pf_rng_key(a.seed, a.policy_step, PF_RNG_POLICY), (uint32_t)(a.env_id_offset + (int)er));
+                            const long long srow = a.storage_row0 + er;
+                            float logp = 0.0f;
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                if (j < A) {
+                                    const float m = __uint_as_float(v[j]), s = a.std[j];
+                                    const float act = m + s * pf_rng_normal(ek, (uint32_t)j);
+                                    const float d = act - m;
+                                    logp += -(d * d) / (2.0f * (s * s)) - logf(s) - 0.9189385332046727f;
+                                    if (a.actions_out) a.actions_out[er * A + j] = act;
+                                    if (a.has_storage) {
+                                        a.S.actions[srow * A + j] = act;
+                                        a.S.mu[srow * A + j] = m;
+                                        a.S.sigma[srow * A + j] = s;
+                                    }
+                                }
+                            }
+                            if (a.logp_out) a.logp_out[er] = logp;
+                            if (a.has_storage) a.S.actions_log_prob[srow] = logp;
                         }
                     }
                 }
-                fence_async_smem();
-                tc_fence_before();
-                __syncthreads();
+                if (outb) {
+                    fence_async_smem();
+                    tc_fence_before();
+                    mbar_arrive(pb0 + 8 * E.done_bar);
+                }
             }
+            tc_fence_before();
+            pbits ^= P.parity_mask;
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == TC_EPI_WARPS) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC_TMEM_COLS) : "memory");
     }
 }
 
 // ------------------------------------------------------------------------------------------------ packing
-// fp32 nn.Linear weight [out, in] + bias -> bf16 tiles in consumption order (see chunk_offset)
-__global__ void pf_tc_pack_kernel(const TcPlan P, int l, const float* __restrict__ W, const float* __restrict__ b,
-                                  unsigned char* blob) {
-    const int Kp = P.pdims[l], Np = P.pdims[l + 1], K = P.dims[l], N = P.dims[l + 1];
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (long long)Np * Kp) return;
-    const int n = (int)(i / Kp), k = (int)(i % Kp);
-    const int c = n / TC_NCHUNK, nl = n % TC_NCHUNK, nt = min(TC_NCHUNK, Np - c * TC_NCHUNK);
-    const int kt_i = k / TC_KTILE, kk = k % TC_KTILE;
-    const long long base = P.w_off[l] + (long long)c * TC_NCHUNK * (Kp + 16) * 2;
-    const long long off = base + (long long)nt * 32 + (long long)kt_i * nt * TC_KTILE * 2 +
-                          ((long long)(kk >> 3) * (nt >> 3) + (nl >> 3)) * 128 + (nl & 7) * 16 + (kk & 7) * 2;
-    const float v = (n < N && k < K) ? W[(long long)n * K + k] : 0.0f;
-    *reinterpret_cast<__nv_bfloat16*>(blob + off) = __float2bfloat16_rn(v);
-    if (k == 0) {           // bias tile: columns 0 / 1 = high / low bf16 parts of the bias, the rest stays zero
-        const float bv = n < N ? b[n] : 0.0f;
-        const __nv_bfloat16 hi = __float2bfloat16_rn(bv);
-        const __nv_bfloat16 lo = __float2bfloat16_rn(bv - __bfloat162float(hi));
-        __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(blob + base + (long long)(nl >> 3) * 128 + (nl & 7) * 16);
-        d[0] = hi; d[1] = lo;
+// fp32 nn.Linear weight [out, in] + bias -> bf16 tiles in consumption order.  Tiles of a group, contiguous: the BIAS
+// tile if the group starts an accumulation (nt x 16: column 0 = bf16(b), column 1 = bf16(b - bf16(b)), multiplied by
+// the "ones" A operand), then the K tiles of kt columns.  blockIdx.y = group (both nets in one launch).
+struct TcPackArgs { TcProgram prog[2]; unsigned char* blob[2]; long long w_off[2][PF_MAX_MLP_LAYERS], b_off[2][PF_MAX_MLP_LAYERS]; };
+
+__global__ void pf_tc_pack_kernel(const __grid_constant__ TcPackArgs a, const float* __restrict__ params) {
+    int gi = blockIdx.y, k = 0;
+    if (gi >= a.prog[0].ngroups) { gi -= a.prog[0].ngroups; k = 1; }
+    const TcProgram& P = a.prog[k];
+    const TcGroup& G = P.g[gi];
+    const int l = G.layer, nt = G.nt, kc = G.kc, kt = G.kt;
+    const int K = P.dims[l], N = P.dims[l + 1];
+    const float* W = params + a.w_off[k][l];
+    const float* b = params + a.b_off[k][l];
+    unsigned char* blob = a.blob[k] + G.blob_off;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nt * kc; i += gridDim.x * blockDim.x) {
+        const int nl = i / kc, kl = i - nl * kc;
+        const int n = G.n_base + nl, kg = G.k_base + kl;
+        const int t = kl / kt, kk = kl - t * kt;
+        const long long off = (G.bias ? nt * 32 : 0) + (long long)t * nt * kt * 2 +
+                              ((long long)(kk >> 3) * (nt >> 3) + (nl >> 3)) * 128 + (nl & 7) * 16 + (kk & 7) * 2;
+        const float v = (n < N && kg < K) ? W[(long long)n * K + kg] : 0.0f;
+        *reinterpret_cast<__nv_bfloat16*>(blob + off) = __float2bfloat16_rn(v);
+        if (kl == 0 && G.bias) {   // bias tile: columns 0 / 1 = high / low bf16 parts of the bias, the rest stays zero
+            const float bv = n < N ? b[n] : 0.0f;
+            const __nv_bfloat16 hi = __float2bfloat16_rn(bv);
+            const __nv_bfloat16 lo = __float2bfloat16_rn(bv - __bfloat162float(hi));
+            __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(blob + (long long)(nl >> 3) * 128 + (nl & 7) * 16);
+            d[0] = hi; d[1] = lo;
+        }
     }
 }
 
 static int tc_fail(int code, const char* msg) { pf_set_error(msg); return code; }
 
-static int build_plan(TcPlan& P, const PfNet& n) {
-    P.layers = n.layers;
-    for (int i = 0; i <= n.layers; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
-    int wa = 16, wb = 16;
-    for (int i = 0; i < n.layers; ++i) {
-        if (i & 1) wa = P.pdims[i] > wa ? P.pdims[i] : wa;
-        else wb = P.pdims[i] > wb ? P.pdims[i] : wb;
-    }
-    P.bufA_bytes = TC_ROWS * wa * 2;
-    P.bufB_bytes = TC_ROWS * wb * 2;
-    const int limit = 227 * 1024 - 256 - TC_ROWS * 16 * 2;
-    int S = (limit - P.bufA_bytes - P.bufB_bytes) / TC_TILE_BYTES;
-    if (S < 2) return 1;
-    P.stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
-    P.smem_bytes = P.bufA_bytes + P.bufB_bytes + TC_ROWS * 16 * 2 + P.stages * TC_TILE_BYTES + 256;
+static int pick_kt(int nt, int kc) {
+    int kt = (TC_SLOT_BYTES / 2 / nt) & ~15;
+    if (kt > 128) kt = 128;
+    return kt < kc ? kt : kc;
+}
+
+// Builds the static schedule of one net (see the header comment).  Returns non-zero if the shape does not fit.
+static int build_program(TcProgram& P, const PfNet& n) {
+    memset(&P, 0, sizeof(P));
+    const int L = n.layers;
+    P.layers = L;
+    for (int i = 0; i <= L; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
+    if (P.pdims[0] > 256) return 1;                                   // staged input rows: <= 64 KB
+    for (int l = 1; l < L; ++l) if (P.pdims[l + 1] > 256) return 1;    // accumulators of layers >= 1 live whole in half of TMEM
+    const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK;
+    if (nch0 > 8 || (L == 1 && nch0 > 2)) return 1;
+    P.x0_bytes = TC_ROWS * P.pdims[0] * 2;
+    int compl_[TC_NBARS] = {0};
+    int last_free_k[2] = {-1, -1};
+    int ach_next = 0;
     long long off = 0;
-    for (int l = 0; l < n.layers; ++l) { P.w_off[l] = off; off += (long long)(P.pdims[l] + 16) * P.pdims[l + 1] * 2; }
+    auto add_group = [&](TcGroup g) -> int {
+        if (P.ngroups == TC_MAX_GROUPS) return 1;
+        g.kt = (uint16_t)pick_kt(g.nt, g.kc);
+        g.blob_off = (uint32_t)off;
+        off += (long long)g.nt * ((g.bias ? 16 : 0) + g.kc) * 2;
+        P.g[P.ngroups++] = g;
+        return 0;
+    };
+    auto add_epi = [&](TcEpi e) -> int {
+        if (P.nepis == TC_MAX_EPIS) return 1;
+        P.e[P.nepis++] = e;
+        return 0;
+    };
+    auto region_col = [](int l) { return (l & 1) ? 256 : 0; };
+    auto region_bar = [](int l) { return (l & 1) ? BAR_ACC2 : BAR_ACC0; };
+
+    // ---- layer 0: chunk c accumulates in TMEM slot c & 1 from the staged input ----
+    int acc_k0[8] = {0}, e_k0[8] = {0}, e_b0[8] = {0};
+    auto layer0_group = [&](int c) -> int {
+        TcGroup g = {};
+        g.layer = 0; g.n_base = (uint16_t)(c * TC_CHUNK); g.k_base = 0;
+        g.nt = (uint16_t)((P.pdims[1] - c * TC_CHUNK) < TC_CHUNK ? (P.pdims[1] - c * TC_CHUNK) : TC_CHUNK);
+        g.kc = (uint16_t)P.pdims[0]; g.a_src = 0; g.bias = 1; g.tmem_col = (uint16_t)((c & 1) * TC_CHUNK);
+        g.wait_bar = -1; g.wait_k = 0;
+        if (c == 0) { g.wait_bar = BAR_XFULL; g.wait_k = 0; }
+        else if (c >= 2 && L > 1) { g.wait_bar = (int8_t)(BAR_E0 + e_b0[c - 2]); g.wait_k = (int8_t)e_k0[c - 2]; }   // slot drained
+        g.commit_bar = (int8_t)(BAR_ACC0 + (c & 1)); g.commit2_bar = -1;
+        acc_k0[c] = compl_[BAR_ACC0 + (c & 1)]++;
+        return add_group(g);
+    };
+    // consumer of one produced chunk: K-slice j of layer l reading chunk buffer b
+    auto consumer_group = [&](int l, int j, int width, int b, int e_k, bool last) -> int {
+        TcGroup g = {};
+        g.layer = (int8_t)l; g.n_base = 0; g.k_base = (uint16_t)(j * TC_CHUNK);
+        g.nt = (uint16_t)P.pdims[l + 1]; g.kc = (uint16_t)width; g.a_src = (int8_t)(1 + b); g.bias = j == 0;
+        g.tmem_col = (uint16_t)region_col(l);
+        g.wait_bar = (int8_t)(BAR_E0 + b); g.wait_k = (int8_t)e_k;
+        g.commit_bar = (int8_t)(BAR_AFREE0 + b);
+        last_free_k[b] = compl_[BAR_AFREE0 + b]++;
+        g.commit2_bar = -1;
+        if (last) { g.commit2_bar = (int8_t)region_bar(l); }
+        return add_group(g);
+    };
+    if (layer0_group(0)) return 1;
+    if (nch0 > 1 && layer0_group(1)) return 1;
+    int acc_k_prev = 0;                         // completion index of the accumulator the next epilogues read (layers >= 1)
+    for (int c = 0; c < nch0; ++c) {
+        TcEpi e = {};
+        const int nt = (P.pdims[1] - c * TC_CHUNK) < TC_CHUNK ? (P.pdims[1] - c * TC_CHUNK) : TC_CHUNK;
+        e.tmem_col = (uint16_t)((c & 1) * TC_CHUNK); e.nt = (uint16_t)nt; e.n0 = (uint16_t)(c * TC_CHUNK);
+        e.acc_bar = (int8_t)(BAR_ACC0 + (c & 1)); e.acc_k = (int8_t)acc_k0[c];
+        e.dst = -1; e.free_bar = -1; e.free_k = 0; e.done_bar = -1;
+        if (L > 1) {
+            const int b = ach_next; ach_next ^= 1;
+            e.dst = (int8_t)b; e.done_bar = (int8_t)(BAR_E0 + b);
+            if (last_free_k[b] >= 0) { e.free_bar = (int8_t)(BAR_AFREE0 + b); e.free_k = (int8_t)last_free_k[b]; }
+            e_b0[c] = b; e_k0[c] = compl_[BAR_E0 + b]++;
+            if (add_epi(e)) return 1;
+            if (consumer_group(1, c, nt, b, e_k0[c], c == nch0 - 1)) return 1;
+            if (c == nch0 - 1) acc_k_prev = compl_[region_bar(1)]++;
+        } else if (add_epi(e)) return 1;
+        if (c + 2 < nch0 && layer0_group(c + 2)) return 1;
+    }
+    // ---- layers >= 1: whole accumulator, epilogue in chunks, each chunk feeds layer l + 1 at once ----
+    for (int l = 1; l < L; ++l) {
+        const int Np = P.pdims[l + 1];
+        const int nch = (Np + TC_CHUNK - 1) / TC_CHUNK;
+        const int acc_k = acc_k_prev;
+        for (int j = 0; j < nch; ++j) {
+            TcEpi e = {};
+            const int nt = (Np - j * TC_CHUNK) < TC_CHUNK ? (Np - j * TC_CHUNK) : TC_CHUNK;
+            e.tmem_col = (uint16_t)(region_col(l) + j * TC_CHUNK); e.nt = (uint16_t)nt; e.n0 = (uint16_t)(j * TC_CHUNK);
+            e.acc_bar = (int8_t)region_bar(l); e.acc_k = (int8_t)acc_k;
+            e.dst = -1; e.free_bar = -1; e.free_k = 0; e.done_bar = -1;
+            if (l < L - 1) {
+                const int b = ach_next; ach_next ^= 1;
+                e.dst = (int8_t)b; e.done_bar = (int8_t)(BAR_E0 + b);
+                if (last_free_k[b] >= 0) { e.free_bar = (int8_t)(BAR_AFREE0 + b); e.free_k = (int8_t)last_free_k[b]; }
+                const int e_k = compl_[BAR_E0 + b]++;
+                if (add_epi(e)) return 1;
+                if (consumer_group(l + 1, j, nt, b, e_k, j == nch - 1)) return 1;
+                if (j == nch - 1) acc_k_prev = compl_[region_bar(l + 1)]++;
+            } else if (add_epi(e)) return 1;
+        }
+    }
+    compl_[BAR_XFULL] = 1;
+    for (int b = 0; b < TC_NBARS; ++b) if (compl_[b] & 1) P.parity_mask |= 1u << b;
     P.blob_bytes = off;
+    return 0;
+}
+
+// Dry run of the schedule on the host: MMA issuer and epilogue as two in-order agents that only advance when the
+// barrier completion they wait for has happened.  A schedule that cannot finish two consecutive items is rejected
+// at create time instead of trapping on the device.
+static int check_program(const TcProgram& P) {
+    int done[TC_NBARS] = {0}, per_item[TC_NBARS] = {0};
+    for (int item = 0; item < 2; ++item) {
+        int base[TC_NBARS];
+        for (int b = 0; b < TC_NBARS; ++b) base[b] = done[b];
+        int gi = 0, ei = 0;
+        bool staged = false, progress = true;
+        while ((gi < P.ngroups || ei < P.nepis) && progress) {
+            progress = false;
+            if (!staged) { done[BAR_XFULL]++; staged = true; progress = true; }
+            while (gi < P.ngroups) {
+                const TcGroup& G = P.g[gi];
+                if (G.wait_bar >= 0 && done[G.wait_bar] <= base[G.wait_bar] + G.wait_k) break;
+                if (G.commit_bar >= 0) done[G.commit_bar]++;
+                if (G.commit2_bar >= 0) done[G.commit2_bar]++;
+                ++gi; progress = true;
+            }
+            while (ei < P.nepis) {
+                const TcEpi& E = P.e[ei];
+                if (done[E.acc_bar] <= base[E.acc_bar] + E.acc_k) break;
+                if (E.free_bar >= 0 && done[E.free_bar] <= base[E.free_bar] + E.free_k) break;
+                if (E.done_bar >= 0) done[E.done_bar]++;
+                ++ei; progress = true;
+            }
+        }
+        if (gi < P.ngroups || ei < P.nepis) return 1;
+        for (int b = 0; b < TC_NBARS; ++b) {
+            if (item == 0) per_item[b] = done[b] - base[b];
+            if (done[b] - base[b] != per_item[b] || ((per_item[b] & 1) != (int)((P.parity_mask >> b) & 1u))) return 1;
+        }
+    }
+    return 0;
+}
+
+// Diagnostic (no device needed): builds + dry-runs the schedule for an MLP shape and prints it.  Returns 0 if the
+// fused kernel supports the shape, 6 if not.
+extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, int32_t cap) {
+    if (!dims || layers < 1 || layers > PF_MAX_MLP_LAYERS) return 1;
+    PfNet n = {};
+    n.layers = layers;
+    for (int i = 0; i <= layers; ++i) n.dims[i] = dims[i];
+    TcProgram P;
+    if (build_program(P, n) || check_program(P)) return 6;
+    int w = 0;
+    auto put = [&](const char* fmt, auto... v) { if (text && w < cap) { int r = snprintf(text + w, (size_t)(cap - w), fmt, v...); if (r > 0) w += r; } };
+    put("groups=%d epilogues=%d blob_bytes=%lld x0_bytes=%d parity_mask=0x%x\n", P.ngroups, P.nepis, P.blob_bytes, P.x0_bytes, P.parity_mask);
+    for (int i = 0; i < P.ngroups; ++i) {
+        const TcGroup& G = P.g[i];
+        put("G%d layer=%d a_src=%d nt=%d kc=%d kt=%d col=%d bias=%d wait=%d@%d commit=%d,%d off=%u\n", i, G.layer, G.a_src, G.nt, G.kc, G.kt,
+            G.tmem_col, G.bias, G.wait_bar, G.wait_k, G.commit_bar, G.commit2_bar, G.blob_off);
+    }
+    for (int i = 0; i < P.nepis; ++i) {
+        const TcEpi& E = P.e[i];
+        put("E%d col=%d nt=%d n0=%d acc=%d@%d dst=%d free=%d@%d done=%d\n", i, E.tmem_col, E.nt, E.n0, E.acc_bar, E.acc_k, E.dst, E.free_bar, E.free_k, E.done_bar);
+    }
+    return 0;
+}
+
+static int smem_layout(int x0_bytes, int* stages, int* smem_bytes) {
+    const int fixed = x0_bytes + 2 * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
+    int S = (227 * 1024 - fixed) / TC_SLOT_BYTES;
+    if (S < 3) return 1;
+    *stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
+    *smem_bytes = fixed + *stages * TC_SLOT_BYTES;
     return 0;
 }
 
 int pf_tc_create(pf_rl_ctx* c) {
     TcState* t = new TcState();
-    int max_smem = 0;
     for (int k = 0; k < 2; ++k) {
-        if (build_plan(t->plan[k], c->net[k])) {
+        if (build_program(t->prog[k], c->net[k]) || check_program(t->prog[k])) {
             delete t;
-            return tc_fail(6, "pf_rl_create: MLP too wide for the fused tensor-core kernel (activations of one 128-row tile must fit in shared memory)");
+            return tc_fail(6, "pf_rl_create: MLP shape not supported by the fused tensor-core kernel (input <= 256 wide, "
+                              "first hidden layer <= 1024, later layers <= 256)");
         }
-        if (cudaMalloc(&c->net[k].tc_weights, (size_t)t->plan[k].blob_bytes) != cudaSuccess) { delete t; return tc_fail(2, "pf_rl_create: cudaMalloc of the packed weights failed"); }
-        cudaMemset(c->net[k].tc_weights, 0, (size_t)t->plan[k].blob_bytes);      // padding columns of the bias tiles stay zero
-        c->net[k].tc_weight_bytes = (size_t)t->plan[k].blob_bytes;
-        max_smem = t->plan[k].smem_bytes > max_smem ? t->plan[k].smem_bytes : max_smem;
+    }
+    int max_smem = 0;
+    for (int v = 0; v < 3; ++v) {
+        const int xa = t->prog[0].x0_bytes, xc = t->prog[1].x0_bytes;
+        t->x0_bytes[v] = v == 0 ? xa : v == 1 ? xc : (xa > xc ? xa : xc);
+        if (smem_layout(t->x0_bytes[v], &t->stages[v], &t->smem_bytes[v])) { delete t; return tc_fail(6, "pf_rl_create: shared memory layout does not fit"); }
+        max_smem = t->smem_bytes[v] > max_smem ? t->smem_bytes[v] : max_smem;
+    }
+    for (int k = 0; k < 2; ++k) {
+        if (cudaMalloc(&c->net[k].tc_weights, (size_t)t->prog[k].blob_bytes) != cudaSuccess) { delete t; return tc_fail(2, "pf_rl_create: cudaMalloc of the packed weights failed"); }
+        cudaMemset(c->net[k].tc_weights, 0, (size_t)t->prog[k].blob_bytes);      // padding columns of the bias tiles stay zero
+        c->net[k].tc_weight_bytes = (size_t)t->prog[k].blob_bytes;
     }
     if (cudaFuncSetAttribute(pf_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess) {
         delete t;
@@ -371,15 +644,26 @@ void pf_tc_destroy(pf_rl_ctx* c) {
 
 int pf_tc_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
+    TcPackArgs a;
     for (int k = 0; k < 2; ++k) {
-        const TcPlan& P = t->plan[k];
-        for (int l = 0; l < P.layers; ++l) {
-            const long long n = (long long)P.pdims[l] * P.pdims[l + 1];
-            pf_tc_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, l, params + c->net[k].w_off[l], params + c->net[k].b_off[l],
-                                                                          static_cast<unsigned char*>(c->net[k].tc_weights));
-        }
+        a.prog[k] = t->prog[k];
+        a.blob[k] = static_cast<unsigned char*>(c->net[k].tc_weights);
+        for (int l = 0; l < PF_MAX_MLP_LAYERS; ++l) { a.w_off[k][l] = c->net[k].w_off[l]; a.b_off[k][l] = c->net[k].b_off[l]; }
     }
+    pf_tc_pack_kernel<<<dim3(16, (unsigned)(t->prog[0].ngroups + t->prog[1].ngroups)), 256, 0, st>>>(a, params);
     return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_tc_pack_weights: launch failed");
+}
+
+static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
+    TcState* t = static_cast<TcState*>(c->tc);
+    a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
+    a.stages = t->stages[variant];
+    a.x0_bytes = t->x0_bytes[variant];
+    const int items = a.nnets * a.tiles;
+    if (items == 0) return 0;
+    const int grid = items < c->num_sms ? items : c->num_sms;
+    pf_mlp_tc_kernel<<<grid, TC_THREADS, t->smem_bytes[variant], st>>>(a);
+    return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }
 
 int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x, long long ldx, int rows, float* out,
@@ -387,9 +671,46 @@ int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x
     (void)params;
     TcState* t = static_cast<TcState*>(c->tc);
     TcArgs a;
-    a.plan = t->plan[net];
-    a.blob = static_cast<const unsigned char*>(c->net[net].tc_weights);
-    a.x = x; a.ldx = ldx; a.rows = rows; a.out = out; a.copy_to = copy_to;
-    pf_mlp_tc_kernel<<<(rows + TC_ROWS - 1) / TC_ROWS, TC_THREADS, a.plan.smem_bytes, st>>>(a);
-    return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_tc_mlp_forward: launch failed");
+    memset(&a, 0, sizeof(a));
+    a.prog[0] = t->prog[net];
+    a.net[0].blob = static_cast<const unsigned char*>(c->net[net].tc_weights);
+    a.net[0].x = x; a.net[0].ldx = ldx; a.net[0].out = out; a.net[0].copy_to = copy_to; a.net[0].mode = TC_OUT_PLAIN;
+    a.nnets = 1; a.rows = rows;
+    return tc_launch(c, a, net, st);
+}
+
+int pf_tc_act_fusable(const pf_rl_ctx* c) {
+    const TcState* t = static_cast<const TcState*>(c->tc);
+    return t && t->prog[0].pdims[t->prog[0].layers] == 16 && t->prog[1].dims[t->prog[1].layers] == 1;
+}
+
+// PPO.act in one launch: critic items first (the longer ones), then the actor items with the sample / log-prob tail.
+int pf_tc_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
+              int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st) {
+    TcState* t = static_cast<TcState*>(c->tc);
+    const pf_rl_params& P = c->P;
+    TcArgs a;
+    memset(&a, 0, sizeof(a));
+    const long long row0 = (long long)t_row * P.num_envs;
+    for (int i = 0; i < 2; ++i) {
+        const int k = 1 - i;                       // item order: critic, actor
+        a.prog[i] = t->prog[k];
+        a.net[i].blob = static_cast<const unsigned char*>(c->net[k].tc_weights);
+        a.net[i].x = k == 0 ? obs : critic_obs;
+        a.net[i].ldx = c->net[k].dims[0];
+        a.net[i].out = nullptr;
+        a.net[i].mode = k == 0 ? TC_OUT_SAMPLE : TC_OUT_VALUE;
+        a.net[i].copy_to = nullptr;
+        if (storage) {
+            if (k == 0) a.net[i].copy_to = storage->observations + row0 * P.num_obs;
+            else if (storage->privileged_observations) a.net[i].copy_to = storage->privileged_observations + row0 * P.num_critic_obs;
+        }
+    }
+    a.nnets = 2; a.rows = P.num_envs;
+    a.seed = (uint32_t)P.seed; a.policy_step = (uint32_t)policy_step; a.env_id_offset = (int)P.env_id_offset; a.num_actions = P.num_actions;
+    a.std = params + c->std_off;
+    if (storage) { a.S = *storage; a.has_storage = 1; }
+    a.storage_row0 = row0;
+    a.actions_out = actions_out; a.values_out = values_out; a.logp_out = logp_out;
+    return tc_launch(c, a, 2, st);
 }

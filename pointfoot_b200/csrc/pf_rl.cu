@@ -346,6 +346,8 @@ extern "C" int pf_rl_act(pf_rl_ctx* c, const float* params, const float* obs, co
     cudaStream_t st = (cudaStream_t)stream;
     if (storage && (t < 0 || t >= P.num_steps)) return rl_fail(5, "pf_rl_act", "Rollout buffer overflow");
     if (!critic_obs) critic_obs = obs;
+    if (c->tc && pf_tc_act_fusable(c))
+        return pf_tc_act(c, params, obs, critic_obs, storage, storage ? t : 0, policy_step, actions_out, values_out, logp_out, st);
     const long long row0 = (long long)t * P.num_envs;
     float* mean = nullptr; float* val = nullptr;
     float* copy_obs = storage ? storage->observations + row0 * P.num_obs : nullptr;

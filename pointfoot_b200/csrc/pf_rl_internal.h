@@ -47,3 +47,7 @@ int pf_tc_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st);
 // out[rows, dims[layers]] fp32.  Optionally copies the input rows to `copy_to` (rollout storage row).
 int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x, long long ldx, int rows,
                       float* out, float* copy_to, cudaStream_t st);
+// PPO.act of both nets + Normal sample / log-prob + rollout-storage writes in ONE launch (when pf_tc_act_fusable).
+int pf_tc_act_fusable(const pf_rl_ctx* c);
+int pf_tc_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
+              int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st);
