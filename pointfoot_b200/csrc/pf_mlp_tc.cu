@@ -34,7 +34,8 @@ void pf_set_error(const char* msg);
 #define TC_ROWS 128                          // rows per work item (UMMA M)
 #define TC_CHUNK 128                         // columns of one activation chunk
 #define TC_ACHUNK_BYTES (TC_ROWS * TC_CHUNK * 2)
-#define TC_SLOT_BYTES 8192                   // weight ring slot = largest tile (N x K x 2 B: 256x16, 128x32, 64x64 ...)
+#define TC_X0_LBO (TC_ROWS * 16 + 16)        // staged input: byte distance between 8-column blocks, padded (see tc_stage_item)
+#define TC_SLOT_BYTES 16384                  // weight ring slot = largest tile (N x K x 2 B: 256x32, 128x64, 64x128 ...)
 #define TC_MAX_STAGES 16
 #define TC_EPI_WARPS 8
 #define TC_EPI_THREADS (TC_EPI_WARPS * 32)
@@ -42,6 +43,7 @@ void pf_set_error(const char* msg);
 #define TC_MAX_GROUPS 24
 #define TC_MAX_EPIS 16
 #define TC_TMEM_COLS 512
+#define TC_TRACE_CAP 512
 
 // program barriers (besides the ring's full / empty pairs)
 enum { BAR_ACC0 = 0, BAR_ACC1 = 1, BAR_ACC2 = 2,      // accumulator complete: TMEM cols [0,128) or [0,256) / [128,256) / [256,512)
@@ -77,13 +79,14 @@ struct TcProgram {
     int pdims[PF_MAX_MLP_LAYERS + 1];    // padded to a multiple of 16
     int ngroups, nepis;
     uint32_t parity_mask;                // bit b: barrier b completes an odd number of times per item
+    int stage_after;                     // epilogue after which the staged input rows are dead (last chunk of layer 0)
     int x0_bytes;
     long long blob_bytes;
     TcGroup g[TC_MAX_GROUPS];
     TcEpi e[TC_MAX_EPIS];
 };
 
-struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; };   // [actor only, critic only, both]
+struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; unsigned long long* trace; };   // [actor only, critic only, both]
 
 static inline int pad16(int x) { return (x + 15) & ~15; }
 
@@ -115,6 +118,20 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// one lane of a converged warp (the others skip): tcgen05.mma / commit / bulk copies are warp-level instructions, so
+// the issuing warps run their loops converged and elect a lane per issue instead of diverging on lane == 0
+// (divergent code makes the compiler wrap every such instruction in an elect-and-retry loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+// accumulate variant: D += A * B (no predicate to set up)
+__device__ __forceinline__ void umma_bf16_acc(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.b32 p, 0, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -177,9 +194,134 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
+    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 2 no ELU
+    unsigned long long* trace;   // optional timeline of CTA 0: 3 roles x TC_TRACE_CAP (tag << 48 | clock)
+};
+
+struct TcTrace {
+    unsigned long long* p; int n;
+    __device__ __forceinline__ void init(unsigned long long* base, int role, bool on) { p = on && base ? base + role * TC_TRACE_CAP : nullptr; n = 0; }
+    __device__ __forceinline__ void ev(unsigned tag) { if (p && n < TC_TRACE_CAP) p[n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); }
 };
 
 __device__ __forceinline__ float elu_fast(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
+
+// ---- input rows of item w: fp32 global -> bf16 core-matrix layout (+ the rollout-storage copy); 8 epilogue warps.
+// The tile is one contiguous block of global memory, read (and copied to the storage row) with fully coalesced
+// 128-bit accesses, 8 loads in flight per thread.  The four bf16 of a float4 land in one core-matrix row as a 64-bit
+// shared store; consecutive lanes hold consecutive 8-column blocks, which is why the staged operand uses a PADDED
+// leading byte offset (TC_X0_LBO = 2048 + 16): with the natural 2048 every lane of the warp would hit the same
+// bank.  Out of line so that the loads in flight do not add to the epilogue's register pressure.
+__device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid) {
+    const int lane = tid & 31;
+    const int k = w / a.tiles, tile = w - k * a.tiles;
+    const TcProgram& P = a.prog[k];
+    const TcNetArgs& N = a.net[k];
+    const int row0 = tile * TC_ROWS;
+    const int nrows = min(TC_ROWS, a.rows - row0);
+    const int K0 = P.dims[0], Kp = P.pdims[0];
+    const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)K0 - 1) / (uint32_t)K0);
+    const float* xb = N.x + (long long)row0 * N.ldx;
+    float* cb = (N.copy_to && !(a.debug & 1)) ? N.copy_to + (long long)row0 * K0 : nullptr;
+    const int total = nrows * K0;
+    auto put = [&](int e, float v) {            // element e of the contiguous tile -> (row, column)
+        const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
+        *reinterpret_cast<__nv_bfloat16*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = __float2bfloat16_rn(v);
+    };
+    if (N.ldx == K0 && ((reinterpret_cast<uintptr_t>(xb) | reinterpret_cast<uintptr_t>(cb)) & 15) == 0) {
+        const int n4 = total >> 2;
+        const float4* x4 = reinterpret_cast<const float4*>(xb);
+        float4* c4 = reinterpret_cast<float4*>(cb);
+        const bool row4 = (K0 & 3) == 0;        // a float4 never straddles rows or 8-column blocks
+        for (int base = tid; base < n4; base += 8 * TC_EPI_THREADS) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * TC_EPI_THREADS;
+                if (idx < n4) v[u] = (a.debug & 2) ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * TC_EPI_THREADS;
+                if (idx < n4) {
+                    if (c4) c4[idx] = v[u];
+                    if (row4) {
+                        const int e = idx * 4, r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
+                        __nv_bfloat162 p0 = __floats2bfloat162_rn(v[u].x, v[u].y), p1 = __floats2bfloat162_rn(v[u].z, v[u].w);
+                        *reinterpret_cast<uint2*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) =
+                            make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
+                    } else {
+                        put(idx * 4, v[u].x); put(idx * 4 + 1, v[u].y); put(idx * 4 + 2, v[u].z); put(idx * 4 + 3, v[u].w);
+                    }
+                }
+            }
+        }
+        for (int e = n4 * 4 + tid; e < total; e += TC_EPI_THREADS) {
+            const float v = __ldg(xb + e);
+            if (cb) cb[e] = v;
+            put(e, v);
+        }
+    } else {
+        for (int e = tid; e < total; e += TC_EPI_THREADS) {
+            const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
+            const float v = __ldg(xb + (long long)r * N.ldx + kx);
+            if (cb) cb[e] = v;
+            put(e, v);
+        }
+    }
+    // zero padding: columns [K0, Kp) of the valid rows, and whole rows past the end of the batch
+    const int padw = Kp - K0;
+    for (int i = tid; i < nrows * padw; i += TC_EPI_THREADS) {
+        const int r = i / padw, kx = K0 + (i - r * padw);
+        *reinterpret_cast<__nv_bfloat16*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = __float2bfloat16_rn(0.0f);
+    }
+    for (int i = tid; i < (TC_ROWS - nrows) * (Kp >> 3); i += TC_EPI_THREADS) {
+        const int r = nrows + i / (Kp >> 3), kb = i % (Kp >> 3);
+        *reinterpret_cast<uint4*>(x0 + (size_t)kb * TC_X0_LBO + r * 16) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(xfull_bar);
+    // Pull the rows of the item after this one into L2 now.  All CTAs run in step, so without this every CTA would
+    // hit HBM in the same instant one item later and sit out the burst inside its critical path; the prefetch spreads
+    // that traffic under a whole item of MMAs and turns the next staging pass into L2 hits.
+    const int w2 = w + (int)gridDim.x;
+    if (w2 < a.nnets * a.tiles) {
+        const int k2 = w2 / a.tiles, tile2 = w2 - k2 * a.tiles;
+        const TcNetArgs& N2 = a.net[k2];
+        const int rows2 = min(TC_ROWS, a.rows - tile2 * TC_ROWS);
+        const char* base = reinterpret_cast<const char*>(N2.x + (long long)tile2 * TC_ROWS * N2.ldx);
+        const long long bytes = ((long long)(rows2 - 1) * N2.ldx + a.prog[k2].dims[0]) * 4;
+        for (long long o = (long long)tid * 128; o < bytes; o += TC_EPI_THREADS * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
+    }
+}
+
+// PPO.act tail of one row: Normal(mean, std).sample() under the RNG contract + log_prob(actions).sum(-1)
+// (actor_critic.py act / get_actions_log_prob) written straight into the rollout storage (rollout_storage.py
+// add_transitions).  Out of line and rolled: logf / cosf / sqrtf are long, sixteen inlined copies of them made
+// the kernel several times larger than the instruction cache.
+__device__ __noinline__ void tc_sample_row(const TcArgs& a, long long er, const float* mean) {
+    const int A = a.num_actions;
+    const uint32_t ek = pf_rng_env_key(pf_rng_key(a.seed, a.policy_step, PF_RNG_POLICY), (uint32_t)(a.env_id_offset + (int)er));
+    const long long srow = a.storage_row0 + er;
+    float logp = 0.0f;
+#pragma unroll 1
+    for (int j = 0; j < A; ++j) {
+        const float m = mean[j], sd = a.std[j];
+        const float act = m + sd * pf_rng_normal(ek, (uint32_t)j);
+        const float d = act - m;
+        logp += -(d * d) / (2.0f * (sd * sd)) - logf(sd) - 0.9189385332046727f;
+        if (a.actions_out) a.actions_out[er * A + j] = act;
+        if (a.has_storage) {
+            a.S.actions[srow * A + j] = act;
+            a.S.mu[srow * A + j] = m;
+            a.S.sigma[srow * A + j] = sd;
+        }
+    }
+    if (a.logp_out) a.logp_out[er] = logp;
+    if (a.has_storage) a.S.actions_log_prob[srow] = logp;
+}
 
 __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -196,7 +338,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
 
     if (warp == TC_EPI_WARPS + 1 && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, b >= BAR_E0 ? TC_EPI_THREADS : 1);
+        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, b >= BAR_E0 ? TC_EPI_WARPS : 1);   // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == TC_EPI_WARPS) {
@@ -214,66 +356,99 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
 
     if (warp == TC_EPI_WARPS + 1) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
-        if (lane == 0) {
-            uint32_t n = 0;
+        {
+            uint32_t slot = 0, round = 0;           // ring position: slot index and how many times the ring wrapped
+            TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0 && lane == 0);
             for (int w = blockIdx.x; w < items; w += gridDim.x) {
                 const int k = w / a.tiles;
                 const TcProgram& P = a.prog[k];
                 const unsigned char* blob = a.net[k].blob;
                 for (int gi = 0; gi < P.ngroups; ++gi) {
                     const TcGroup& G = P.g[gi];
+                    tr.ev(0x100 + gi);
                     uint32_t off = G.blob_off;
                     const int nt = G.nt, kc = G.kc, kt = G.kt;
                     for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
                         const uint32_t bytes = (uint32_t)(nt * (k0 < 0 ? 16 : min(kt, kc - k0)) * 2);
-                        const uint32_t slot = n % (uint32_t)S;
-                        if (n >= (uint32_t)S) mbar_wait(empty0 + 8 * slot, ((n / (uint32_t)S) - 1u) & 1u);
-                        mbar_expect_tx(full0 + 8 * slot, bytes);
-                        bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
+                        if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
+                        if (elect_one()) {
+                            mbar_expect_tx(full0 + 8 * slot, bytes);
+                            bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
+                        }
                         off += bytes;
-                        ++n;
+                        if (++slot == (uint32_t)S) { slot = 0; ++round; }
                     }
                 }
             }
         }
     } else if (warp == TC_EPI_WARPS) {
         // ================================================================ MMA issue: one thread
-        if (lane == 0) {
-            uint32_t n = 0, pbits = 0;
+        // A lone thread retires about one instruction every 4-5 cycles (tools/umma_microbench.cu), and an N = 128
+        // MMA keeps the tensor pipe busy for only 64 cycles, so the loop below is written for instruction count:
+        // descriptors advance by 64-bit adds, ring addresses incrementally, no division, no per-MMA predicate setup.
+        {
+            uint32_t slot = 0, round = 0, pbits = 0;
+            uint32_t full_bar = full0, empty_bar = empty0;
+            const uint64_t ring_desc0 = make_desc(smem_u32(ring), 0u, 128u);        // leading byte offset added per group
+            uint64_t ring_desc = ring_desc0;
+            const uint64_t ones_desc = make_desc(smem_u32(ones), TC_ROWS * 16, 128u);
+            TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0 && lane == 0);
+            auto next_slot = [&]() {
+                full_bar += 8; empty_bar += 8; ring_desc += TC_SLOT_BYTES >> 4;
+                if (++slot == (uint32_t)S) { slot = 0; ++round; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
+            };
             for (int w = blockIdx.x; w < items; w += gridDim.x) {
                 const TcProgram& P = a.prog[w / a.tiles];
                 for (int gi = 0; gi < P.ngroups; ++gi) {
                     const TcGroup& G = P.g[gi];
+                    tr.ev(0x200 + gi);
                     if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, ((pbits >> G.wait_bar) ^ (uint32_t)G.wait_k) & 1u);
                     tc_fence_after();
-                    const int nt = G.nt, kc = G.kc, kt = G.kt;
+                    tr.ev(0x300 + gi);
+                    const int nt = G.nt;
                     const uint32_t idesc = make_idesc(nt);
                     const uint32_t tmem_d = tmem_base + G.tmem_col;
                     const uint32_t a_base = G.a_src == 0 ? smem_u32(x0) : smem_u32(ach) + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
-                    const uint32_t a_lbo = TC_ROWS * 16, b_lbo = (uint32_t)(nt * 16);
-                    uint32_t acc = G.bias ? 0u : 1u;
-                    for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
-                        const uint32_t slot = n % (uint32_t)S;
-                        mbar_wait(full0 + 8 * slot, (n / (uint32_t)S) & 1u);
+                    const uint32_t a_lbo = G.a_src == 0 ? TC_X0_LBO : TC_ROWS * 16;
+                    uint64_t adesc = make_desc(a_base, a_lbo, 128u);
+                    const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4);               // K = 16 further along the A operand
+                    const uint64_t b_lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16;  // next 8 K-columns of a weight tile
+                    const uint64_t b_step = (uint64_t)(nt * 2);                         // K = 16 further inside a tile, in 16 B units
+                    if (G.bias) {
+                        mbar_wait(full_bar, round & 1u);
                         tc_fence_after();
-                        const uint32_t bs = smem_u32(ring + slot * TC_SLOT_BYTES);
-                        if (k0 < 0) {
-                            umma_bf16(tmem_d, make_desc(smem_u32(ones), a_lbo, 128u), make_desc(bs, b_lbo, 128u), idesc, 0u);
-                            acc = 1u;
-                        } else {
-                            const int kk_n = min(kt, kc - k0) >> 4;
-                            for (int kk = 0; kk < kk_n; ++kk) {
-                                const uint64_t ad = make_desc(a_base + (uint32_t)(((k0 >> 3) + kk * 2) * (TC_ROWS * 16)), a_lbo, 128u);
-                                const uint64_t bd = make_desc(bs + (uint32_t)(kk * 2 * (nt * 16)), b_lbo, 128u);
-                                umma_bf16(tmem_d, ad, bd, idesc, acc);
-                                acc = 1u;
-                            }
+                        if (elect_one()) {
+                            umma_bf16(tmem_d, ones_desc, ring_desc + b_lbo, idesc, 0u);
+                            umma_commit(empty_bar);
                         }
-                        umma_commit(empty0 + 8 * slot);            // slot is free once these MMAs have read it
-                        ++n;
+                        next_slot();
                     }
-                    if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
-                    if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
+                    int left = G.kc >> 4;                       // K = 16 steps still to issue
+                    const int per_tile = G.kt >> 4;
+                    while (left > 0) {
+                        mbar_wait(full_bar, round & 1u);
+                        tc_fence_after();
+                        uint64_t bdesc = ring_desc + b_lbo;
+                        const int nk = left < per_tile ? left : per_tile;
+                        if (elect_one()) {
+                            uint64_t ad = adesc;
+                            for (int kk = 0; kk < nk; ++kk) {
+                                umma_bf16_acc(tmem_d, ad, bdesc, idesc);
+                                ad += a_step;
+                                bdesc += b_step;
+                            }
+                            umma_commit(empty_bar);             // slot is free once these MMAs have read it
+                        }
+                        adesc += (uint64_t)nk * a_step;
+                        next_slot();
+                        left -= nk;
+                    }
+                    if (elect_one()) {
+                        if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
+                        if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
+                    }
+                    __syncwarp();
+                    tr.ev(0x400 + gi);
                 }
                 pbits ^= P.parity_mask;
             }
@@ -282,6 +457,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
         // ================================================================ staging + epilogues: 8 warps
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
         uint32_t pbits = 0;
+        TcTrace tr; tr.init(a.trace, 0, blockIdx.x == 0 && tid == 0);
+        // ELU + bf16 pack of 32 accumulator columns [g, g + 32) of this thread's row into a chunk buffer
+        auto pack32 = [&](const uint32_t (&v)[32], unsigned char* outb, int g, int wd) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                if (j < wd) {
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        __nv_bfloat162 p = __floats2bfloat162_rn(elu_fast(__uint_as_float(v[j + 2 * i])),
+                                                                 elu_fast(__uint_as_float(v[j + 2 * i + 1])));
+                        pk[i] = *reinterpret_cast<uint32_t*>(&p);
+                    }
+                    *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                }
+            }
+        };
+        if ((int)blockIdx.x < items) { tr.ev(0x500); tc_stage_item(a, blockIdx.x, x0, pb0 + 8 * BAR_XFULL, tid); tr.ev(0x502); }
         for (int w = blockIdx.x; w < items; w += gridDim.x) {
             const int k = w / a.tiles, tile = w - k * a.tiles;
             const TcProgram& P = a.prog[k];
@@ -289,55 +482,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
             const int row0 = tile * TC_ROWS;
             const int nrows = min(TC_ROWS, a.rows - row0);
             const int L = P.layers;
-            {   // ---- stage the input rows, coalesced: fp32 global -> bf16 core-matrix layout ----
-                const int K0 = P.dims[0], half = P.pdims[0] >> 1;                    // pairs of columns per padded row
-                const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)half - 1) / (uint32_t)half);
-                for (int i = tid; i < TC_ROWS * half; i += TC_EPI_THREADS) {
-                    const int r = (int)__umulhi((uint32_t)i, magic), kx = (i - r * half) * 2;
-                    float v0 = 0.0f, v1 = 0.0f;
-                    if (r < nrows) {
-                        const float* xr = N.x + (long long)(row0 + r) * N.ldx;
-                        float* cr = N.copy_to ? N.copy_to + (long long)(row0 + r) * K0 : nullptr;
-                        if (kx < K0) { v0 = __ldg(xr + kx); if (cr) cr[kx] = v0; }
-                        if (kx + 1 < K0) { v1 = __ldg(xr + kx + 1); if (cr) cr[kx + 1] = v1; }
-                    }
-                    __nv_bfloat162 pr = __floats2bfloat162_rn(v0, v1);
-                    *reinterpret_cast<uint32_t*>(x0 + (size_t)(kx >> 3) * (TC_ROWS * 16) + r * 16 + (kx & 7) * 2) = *reinterpret_cast<uint32_t*>(&pr);
-                }
-                fence_async_smem();
-                mbar_arrive(pb0 + 8 * BAR_XFULL);
-            }
             for (int ei = 0; ei < P.nepis; ++ei) {
                 const TcEpi& E = P.e[ei];
+                tr.ev(0x600 + ei);
                 mbar_wait(pb0 + 8 * E.acc_bar, ((pbits >> E.acc_bar) ^ (uint32_t)E.acc_k) & 1u);
                 if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, ((pbits >> E.free_bar) ^ (uint32_t)E.free_k) & 1u);
                 tc_fence_after();
+                tr.ev(0x700 + ei);
                 const int nt = E.nt, units = nt >> 4, u0 = (units + 1) >> 1;
                 const int c_lo = h == 0 ? 0 : u0 * 16, c_hi = h == 0 ? u0 * 16 : nt;
                 const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + E.tmem_col;
-                unsigned char* outb = E.dst >= 0 ? ach + E.dst * TC_ACHUNK_BYTES : nullptr;
-                for (int g = c_lo; g < c_hi; g += 32) {
-                    uint32_t v[32];
-                    const int wd = min(32, c_hi - g);
-                    if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
-                    tmem_ld_wait();
-                    if (outb) {
-                        for (int j = 0; j < wd; j += 8) {
-                            uint32_t pk[4];
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                __nv_bfloat162 p = __floats2bfloat162_rn(elu_fast(__uint_as_float(v[j + 2 * i])),
-                                                                         elu_fast(__uint_as_float(v[j + 2 * i + 1])));
-                                pk[i] = *reinterpret_cast<uint32_t*>(&p);
-                            }
-                            *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                if (E.dst >= 0) {
+                    unsigned char* outb = ach + E.dst * TC_ACHUNK_BYTES;
+                    if (c_hi - c_lo == 64) {                  // the common 128-column chunk: both TMEM loads in flight
+                        uint32_t v0[32], v1[32];
+                        tmem_ld32(trow + c_lo, v0);
+                        tmem_ld32(trow + c_lo + 32, v1);
+                        tmem_ld_wait();
+                        pack32(v0, outb, c_lo, 32);
+                        pack32(v1, outb, c_lo + 32, 32);
+                    } else {
+                        for (int g = c_lo; g < c_hi; g += 32) {
+                            uint32_t v[32];
+                            const int wd = min(32, c_hi - g);
+                            if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
+                            tmem_ld_wait();
+                            pack32(v, outb, g, wd);
                         }
-                    } else if (row < nrows) {
+                    }
+                    tr.ev(0x800 + ei);
+                    fence_async_smem();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(pb0 + 8 * E.done_bar);
+                } else {
+                    for (int g = c_lo; g < c_hi; g += 32) {
+                        uint32_t v[32];
+                        const int wd = min(32, c_hi - g);
+                        if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
+                        tmem_ld_wait();
+                        if (row >= nrows) continue;
                         const int no = P.dims[L], n0 = E.n0 + g;
                         const long long er = (long long)row0 + row;
                         if (N.mode == TC_OUT_PLAIN) {
-                            for (int j = 0; j < wd; ++j)
-                                if (n0 + j < no) N.out[er * no + n0 + j] = __uint_as_float(v[j]);
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (j < wd && n0 + j < no) N.out[er * no + n0 + j] = __uint_as_float(v[j]);
                         } else if (N.mode == TC_OUT_VALUE) {
                             if (n0 == 0) {
                                 const float val = __uint_as_float(v[0]);
@@ -345,37 +535,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                                 if (a.has_storage) a.S.values[a.storage_row0 + er] = val;
                             }
                         } else if (n0 == 0) {
-                            // Normal(mean, std).sample() under the RNG contract + log_prob(actions).sum(-1)
-                            // (actor_critic.py act / get_actions_log_prob; rollout_storage.py add_transitions)
-                            const int A = a.num_actions;
-                            const uint32_t ek = pf_rng_env_key(pf_rng_key(a.seed, a.policy_step, PF_RNG_POLICY), (uint32_t)(a.env_id_offset + (int)er));
-                            const long long srow = a.storage_row0 + er;
-                            float logp = 0.0f;
+                            float m16[16];
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                if (j < A) {
-                                    const float m = __uint_as_float(v[j]), s = a.std[j];
-                                    const float act = m + s * pf_rng_normal(ek, (uint32_t)j);
-                                    const float d = act - m;
-                                    logp += -(d * d) / (2.0f * (s * s)) - logf(s) - 0.9189385332046727f;
-                                    if (a.actions_out) a.actions_out[er * A + j] = act;
-                                    if (a.has_storage) {
-                                        a.S.actions[srow * A + j] = act;
-                                        a.S.mu[srow * A + j] = m;
-                                        a.S.sigma[srow * A + j] = s;
-                                    }
-                                }
-                            }
-                            if (a.logp_out) a.logp_out[er] = logp;
-                            if (a.has_storage) a.S.actions_log_prob[srow] = logp;
+                            for (int j = 0; j < 16; ++j) m16[j] = __uint_as_float(v[j]);
+                            tc_sample_row(a, er, m16);
                         }
                     }
+                    tr.ev(0x800 + ei);
                 }
-                if (outb) {
-                    fence_async_smem();
-                    tc_fence_before();
-                    mbar_arrive(pb0 + 8 * E.done_bar);
-                }
+                tr.ev(0x900 + ei);
+                // the staged input is dead once the last layer-0 accumulator is complete (this epilogue waited for
+                // it): stage the NEXT item's rows now, under the MMAs of the remaining layers
+                if (ei == P.stage_after && w + (int)gridDim.x < items) { tr.ev(0x500); tc_stage_item(a, w + gridDim.x, x0, pb0 + 8 * BAR_XFULL, tid); tr.ev(0x502); }
             }
             tc_fence_before();
             pbits ^= P.parity_mask;
@@ -441,7 +612,7 @@ static int build_program(TcProgram& P, const PfNet& n) {
     for (int l = 1; l < L; ++l) if (P.pdims[l + 1] > 256) return 1;    // accumulators of layers >= 1 live whole in half of TMEM
     const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK;
     if (nch0 > 8 || (L == 1 && nch0 > 2)) return 1;
-    P.x0_bytes = TC_ROWS * P.pdims[0] * 2;
+    P.x0_bytes = (((P.pdims[0] >> 3) * TC_X0_LBO) + 127) & ~127;
     int compl_[TC_NBARS] = {0};
     int last_free_k[2] = {-1, -1};
     int ach_next = 0;
@@ -532,6 +703,7 @@ static int build_program(TcProgram& P, const PfNet& n) {
         }
     }
     compl_[BAR_XFULL] = 1;
+    P.stage_after = nch0 - 1;
     for (int b = 0; b < TC_NBARS; ++b) if (compl_[b] & 1) P.parity_mask |= 1u << b;
     P.blob_bytes = off;
     return 0;
@@ -571,6 +743,14 @@ static int check_program(const TcProgram& P) {
             if (done[b] - base[b] != per_item[b] || ((per_item[b] & 1) != (int)((P.parity_mask >> b) & 1u))) return 1;
         }
     }
+    return 0;
+}
+
+// Diagnostic: device buffer of 3 * TC_TRACE_CAP uint64 that CTA 0 of every following launch fills with its role
+// timelines (tools/tc_trace.py); NULL switches it off.
+extern "C" int pf_rl_tc_trace(pf_rl_ctx* c, unsigned long long* device_buf) {
+    if (!c || !c->tc) return 1;
+    static_cast<TcState*>(c->tc)->trace = device_buf;
     return 0;
 }
 
@@ -659,6 +839,8 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
     a.stages = t->stages[variant];
     a.x0_bytes = t->x0_bytes[variant];
+    a.trace = t->trace;
+    { const char* e = getenv("PF_TC_DEBUG"); a.debug = e ? atoi(e) : 0; }
     const int items = a.nnets * a.tiles;
     if (items == 0) return 0;
     const int grid = items < c->num_sms ? items : c->num_sms;
