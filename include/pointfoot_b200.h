@@ -271,7 +271,7 @@ int pf_rl_params_changed(pf_rl_ctx* ctx, const float* params, void* stream);
  * (dims[0..layers], the ctor args of actor_critic.py ActorCritic)?  0 yes, 6 no -- the code pf_rl_create would return.
  * If `text` is non-NULL the kernel's static schedule is printed into it. */
 int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, int32_t cap);
-/* Diagnostic: CTA 0 of every following tensor-core launch writes its role timelines (3 x 512 uint64, tag << 48 |
+/* Diagnostic: CTA 0 of every following tensor-core launch writes its role timelines (4 x 512 uint64, tag << 48 |
  * SM clock) into `device_buf`; NULL switches it off (tools/tc_trace.py). */
 int pf_rl_tc_trace(pf_rl_ctx* ctx, unsigned long long* device_buf);
 

@@ -14,9 +14,11 @@
 //     mbarrier transaction bytes) issued by a dedicated loader thread that runs up to 14 tiles ahead;
 //   * the bias add is one extra K = 16 MMA per accumulator against a constant "ones" operand (bias split in
 //     hi + lo bf16), so the epilogue is only ELU + pack;
-//   * warp roles: warps 0-7 stage inputs and run the epilogues (4 TMEM lane quarters x 2 column halves), warp 8
-//     owns TMEM and issues the MMAs, warp 9 issues the bulk copies.  They only meet at mbarriers; the schedule
-//     (which group waits for / signals which barrier, with which phase) is a small static PROGRAM built on the host.
+//   * warp roles: warps 0-7 run the epilogues (4 TMEM lane quarters x 2 column halves), warps 8-15 stage the input
+//     rows of the NEXT item (fp32 -> bf16 operand layout + the rollout-storage copy) as soon as the current item's
+//     first layer has consumed its rows, warp 16 owns TMEM and issues the MMAs, warp 17 issues the bulk copies.
+//     They only meet at mbarriers; the schedule (which group waits for / signals which barrier, with which phase)
+//     is a small static PROGRAM built on the host.
 //
 // Shared-memory operand layout (no swizzle, "interleave"): 8 rows x 16 bytes core matrices, stored contiguously
 // (128 B); for an operand with R rows: element (r, k) of bf16 at  (k/8) * (R*16) + r*16 + (k%8)*2  bytes.
@@ -37,19 +39,25 @@ void pf_set_error(const char* msg);
 #define TC_X0_LBO (TC_ROWS * 16 + 16)        // staged input: byte distance between 8-column blocks, padded (see tc_stage_item)
 #define TC_SLOT_BYTES 16384                  // weight ring slot = largest tile (N x K x 2 B: 256x32, 128x64, 64x128 ...)
 #define TC_MAX_STAGES 16
-#define TC_EPI_WARPS 8
+#define TC_EPI_WARPS 8                       // epilogue warps: 4 TMEM lane quarters x 2 column halves (the ELU is MUFU-bound: more warps do not help)
 #define TC_EPI_THREADS (TC_EPI_WARPS * 32)
-#define TC_THREADS (TC_EPI_THREADS + 64)     // + MMA warp + loader warp
+#define TC_STG_WARPS 8                       // staging warps: input rows of the NEXT item, under the tail of the current one
+#define TC_STG_THREADS (TC_STG_WARPS * 32)
+#define TC_MMA_WARP (TC_EPI_WARPS + TC_STG_WARPS)
+#define TC_LOAD_WARP (TC_MMA_WARP + 1)
+#define TC_THREADS ((TC_LOAD_WARP + 1) * 32)
 #define TC_MAX_GROUPS 24
 #define TC_MAX_EPIS 16
 #define TC_TMEM_COLS 512
 #define TC_TRACE_CAP 512
+#define TC_TRACE_ROLES 4
 
 // program barriers (besides the ring's full / empty pairs)
 enum { BAR_ACC0 = 0, BAR_ACC1 = 1, BAR_ACC2 = 2,      // accumulator complete: TMEM cols [0,128) or [0,256) / [128,256) / [256,512)
        BAR_AFREE0 = 3, BAR_AFREE1 = 4,               // MMAs that read activation chunk buffer b have completed
        BAR_E0 = 5, BAR_E1 = 6,                       // epilogue wrote chunk buffer b (and drained its accumulator)
-       BAR_XFULL = 7, TC_NBARS = 8 };                // input rows of the item are staged
+       BAR_XFULL = 7,                                // input rows of the item are staged
+       BAR_XFREE = 8, TC_NBARS = 9 };                // the MMAs that read the staged rows have completed
 
 // One accumulation step: D[128 x nt] (+)= A[128 x kc] * W^T, A = staged input rows or an activation chunk.
 struct TcGroup {
@@ -79,7 +87,6 @@ struct TcProgram {
     int pdims[PF_MAX_MLP_LAYERS + 1];    // padded to a multiple of 16
     int ngroups, nepis;
     uint32_t parity_mask;                // bit b: barrier b completes an odd number of times per item
-    int stage_after;                     // epilogue after which the staged input rows are dead (last chunk of layer 0)
     int x0_bytes;
     long long blob_bytes;
     TcGroup g[TC_MAX_GROUPS];
@@ -102,6 +109,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 // bounded wait: a protocol bug must end in a trap, never in a hung GPU
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok = 0;
+#pragma unroll 1
     for (uint32_t it = 0; it < 50000000u; ++it) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
@@ -194,8 +202,8 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
-    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 2 no ELU
-    unsigned long long* trace;   // optional timeline of CTA 0: 3 roles x TC_TRACE_CAP (tag << 48 | clock)
+    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs
+    unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
 struct TcTrace {
@@ -204,15 +212,21 @@ struct TcTrace {
     __device__ __forceinline__ void ev(unsigned tag) { if (p && n < TC_TRACE_CAP) p[n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); }
 };
 
-__device__ __forceinline__ float elu_fast(float x) { return x > 0.0f ? x : __expf(x) - 1.0f; }
+// branch-free ELU: the exponential is evaluated unconditionally (one MUFU) and selected, so that 32 of them schedule
+// as straight-line code (a data-dependent branch per element serialises the epilogue)
+__device__ __forceinline__ float elu_fast(float x) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fminf(x, 0.0f) * 1.4426950408889634f));
+    return x > 0.0f ? x : e - 1.0f;
+}
 
-// ---- input rows of item w: fp32 global -> bf16 core-matrix layout (+ the rollout-storage copy); 8 epilogue warps.
+// ---- input rows of item w: fp32 global -> bf16 core-matrix layout (+ the rollout-storage copy); all epilogue warps.
 // The tile is one contiguous block of global memory, read (and copied to the storage row) with fully coalesced
-// 128-bit accesses, 8 loads in flight per thread.  The four bf16 of a float4 land in one core-matrix row as a 64-bit
+// 128-bit accesses, 4 loads in flight per thread.  The four bf16 of a float4 land in one core-matrix row as a 64-bit
 // shared store; consecutive lanes hold consecutive 8-column blocks, which is why the staged operand uses a PADDED
 // leading byte offset (TC_X0_LBO = 2048 + 16): with the natural 2048 every lane of the warp would hit the same
 // bank.  Out of line so that the loads in flight do not add to the epilogue's register pressure.
-__device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid) {
+__device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid, TcTrace& tr) {
     const int lane = tid & 31;
     const int k = w / a.tiles, tile = w - k * a.tiles;
     const TcProgram& P = a.prog[k];
@@ -233,16 +247,16 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
         const float4* x4 = reinterpret_cast<const float4*>(xb);
         float4* c4 = reinterpret_cast<float4*>(cb);
         const bool row4 = (K0 & 3) == 0;        // a float4 never straddles rows or 8-column blocks
-        for (int base = tid; base < n4; base += 8 * TC_EPI_THREADS) {
-            float4 v[8];
+        for (int base = tid; base < n4; base += 4 * TC_STG_THREADS) {
+            float4 v[4];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int idx = base + u * TC_EPI_THREADS;
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * TC_STG_THREADS;
                 if (idx < n4) v[u] = (a.debug & 2) ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int idx = base + u * TC_EPI_THREADS;
+            for (int u = 0; u < 4; ++u) {
+                const int idx = base + u * TC_STG_THREADS;
                 if (idx < n4) {
                     if (c4) c4[idx] = v[u];
                     if (row4) {
@@ -256,32 +270,35 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                 }
             }
         }
-        for (int e = n4 * 4 + tid; e < total; e += TC_EPI_THREADS) {
+        for (int e = n4 * 4 + tid; e < total; e += TC_STG_THREADS) {
             const float v = __ldg(xb + e);
             if (cb) cb[e] = v;
             put(e, v);
         }
     } else {
-        for (int e = tid; e < total; e += TC_EPI_THREADS) {
+        for (int e = tid; e < total; e += TC_STG_THREADS) {
             const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
             const float v = __ldg(xb + (long long)r * N.ldx + kx);
             if (cb) cb[e] = v;
             put(e, v);
         }
     }
+    tr.ev(0x503);
     // zero padding: columns [K0, Kp) of the valid rows, and whole rows past the end of the batch
     const int padw = Kp - K0;
-    for (int i = tid; i < nrows * padw; i += TC_EPI_THREADS) {
+    for (int i = tid; i < nrows * padw; i += TC_STG_THREADS) {
         const int r = i / padw, kx = K0 + (i - r * padw);
         *reinterpret_cast<__nv_bfloat16*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = __float2bfloat16_rn(0.0f);
     }
-    for (int i = tid; i < (TC_ROWS - nrows) * (Kp >> 3); i += TC_EPI_THREADS) {
+    for (int i = tid; i < (TC_ROWS - nrows) * (Kp >> 3); i += TC_STG_THREADS) {
         const int r = nrows + i / (Kp >> 3), kb = i % (Kp >> 3);
         *reinterpret_cast<uint4*>(x0 + (size_t)kb * TC_X0_LBO + r * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
+    tr.ev(0x504);
     fence_async_smem();
     __syncwarp();
     if (lane == 0) mbar_arrive(xfull_bar);
+    tr.ev(0x505);
     // Pull the rows of the item after this one into L2 now.  All CTAs run in step, so without this every CTA would
     // hit HBM in the same instant one item later and sit out the burst inside its critical path; the prefetch spreads
     // that traffic under a whole item of MMAs and turns the next staging pass into L2 hits.
@@ -292,7 +309,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
         const int rows2 = min(TC_ROWS, a.rows - tile2 * TC_ROWS);
         const char* base = reinterpret_cast<const char*>(N2.x + (long long)tile2 * TC_ROWS * N2.ldx);
         const long long bytes = ((long long)(rows2 - 1) * N2.ldx + a.prog[k2].dims[0]) * 4;
-        for (long long o = (long long)tid * 128; o < bytes; o += TC_EPI_THREADS * 128)
+        for (long long o = (long long)tid * 128; o < bytes; o += TC_STG_THREADS * 128)
             asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
     }
 }
@@ -336,12 +353,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int items = a.nnets * a.tiles;
 
-    if (warp == TC_EPI_WARPS + 1 && lane == 0) {
+    if (warp == TC_LOAD_WARP && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, b >= BAR_E0 ? TC_EPI_WARPS : 1);   // one arrival per epilogue warp
+        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, (b == BAR_E0 || b == BAR_E1) ? TC_EPI_WARPS : b == BAR_XFULL ? TC_STG_WARPS : 1);   // one arrival per warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == TC_EPI_WARPS) {
+    if (warp == TC_MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else if (warp < TC_EPI_WARPS) {
@@ -354,7 +371,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == TC_EPI_WARPS + 1) {
+    if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
         {
             uint32_t slot = 0, round = 0;           // ring position: slot index and how many times the ring wrapped
@@ -372,8 +389,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                         const uint32_t bytes = (uint32_t)(nt * (k0 < 0 ? 16 : min(kt, kc - k0)) * 2);
                         if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
                         if (elect_one()) {
-                            mbar_expect_tx(full0 + 8 * slot, bytes);
-                            bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
+                            if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
+                            else {
+                                mbar_expect_tx(full0 + 8 * slot, bytes);
+                                bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
+                            }
                         }
                         off += bytes;
                         if (++slot == (uint32_t)S) { slot = 0; ++round; }
@@ -381,7 +401,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 }
             }
         }
-    } else if (warp == TC_EPI_WARPS) {
+    } else if (warp == TC_MMA_WARP) {
         // ================================================================ MMA issue: one thread
         // A lone thread retires about one instruction every 4-5 cycles (tools/umma_microbench.cu), and an N = 128
         // MMA keeps the tensor pipe busy for only 64 cycles, so the loop below is written for instruction count:
@@ -433,7 +453,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                         if (elect_one()) {
                             uint64_t ad = adesc;
                             for (int kk = 0; kk < nk; ++kk) {
-                                umma_bf16_acc(tmem_d, ad, bdesc, idesc);
+                                if (!(a.debug & 16)) umma_bf16_acc(tmem_d, ad, bdesc, idesc);   // experiment: no MMAs
                                 ad += a_step;
                                 bdesc += b_step;
                             }
@@ -453,8 +473,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 pbits ^= P.parity_mask;
             }
         }
+    } else if (warp >= TC_EPI_WARPS) {
+        // ================================================================ staging: 8 warps, one item ahead
+        // The staged rows of item i are dead once its last layer-0 MMAs have completed (BAR_XFREE); the rows of
+        // item i + 1 are staged right then, under the MMAs and epilogues of the remaining layers.
+        TcTrace tr; tr.init(a.trace, 3, blockIdx.x == 0 && tid == TC_EPI_THREADS);
+        uint32_t it = 0;
+        for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+            if (it) mbar_wait(pb0 + 8 * BAR_XFREE, (it - 1u) & 1u);
+            tr.ev(0x500);
+            tc_stage_item(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr);
+            tr.ev(0x502);
+        }
     } else {
-        // ================================================================ staging + epilogues: 8 warps
+        // ================================================================ epilogues: 8 warps
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
         uint32_t pbits = 0;
         TcTrace tr; tr.init(a.trace, 0, blockIdx.x == 0 && tid == 0);
@@ -474,7 +506,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 }
             }
         };
-        if ((int)blockIdx.x < items) { tr.ev(0x500); tc_stage_item(a, blockIdx.x, x0, pb0 + 8 * BAR_XFULL, tid); tr.ev(0x502); }
         for (int w = blockIdx.x; w < items; w += gridDim.x) {
             const int k = w / a.tiles, tile = w - k * a.tiles;
             const TcProgram& P = a.prog[k];
@@ -489,26 +520,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, ((pbits >> E.free_bar) ^ (uint32_t)E.free_k) & 1u);
                 tc_fence_after();
                 tr.ev(0x700 + ei);
-                const int nt = E.nt, units = nt >> 4, u0 = (units + 1) >> 1;
+                const int nt = E.nt, units = nt >> 4, u0 = (units + 1) >> 1;               // 16-column units over the 2 column halves
                 const int c_lo = h == 0 ? 0 : u0 * 16, c_hi = h == 0 ? u0 * 16 : nt;
                 const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + E.tmem_col;
                 if (E.dst >= 0) {
                     unsigned char* outb = ach + E.dst * TC_ACHUNK_BYTES;
-                    if (c_hi - c_lo == 64) {                  // the common 128-column chunk: both TMEM loads in flight
-                        uint32_t v0[32], v1[32];
-                        tmem_ld32(trow + c_lo, v0);
-                        tmem_ld32(trow + c_lo + 32, v1);
+                    for (int g = c_lo; g < c_hi; g += 32) {
+                        uint32_t v[32];
+                        const int wd = min(32, c_hi - g);
+                        tr.ev(0xC00 + ei);
+                        if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
                         tmem_ld_wait();
-                        pack32(v0, outb, c_lo, 32);
-                        pack32(v1, outb, c_lo + 32, 32);
-                    } else {
-                        for (int g = c_lo; g < c_hi; g += 32) {
-                            uint32_t v[32];
-                            const int wd = min(32, c_hi - g);
-                            if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
-                            tmem_ld_wait();
-                            pack32(v, outb, g, wd);
-                        }
+                        tr.ev(0xD00 + ei);
+                        pack32(v, outb, g, wd);
                     }
                     tr.ev(0x800 + ei);
                     fence_async_smem();
@@ -525,9 +549,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                         const int no = P.dims[L], n0 = E.n0 + g;
                         const long long er = (long long)row0 + row;
                         if (N.mode == TC_OUT_PLAIN) {
+                            float o32[32];
 #pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (j < wd && n0 + j < no) N.out[er * no + n0 + j] = __uint_as_float(v[j]);
+                            for (int j = 0; j < 32; ++j) o32[j] = __uint_as_float(v[j]);
+                            float* dst = N.out + er * no + n0;
+                            const int cnt = min(wd, no - n0);
+#pragma unroll 1
+                            for (int j = 0; j < cnt; ++j) dst[j] = o32[j];       // rolled on purpose (code size)
                         } else if (N.mode == TC_OUT_VALUE) {
                             if (n0 == 0) {
                                 const float val = __uint_as_float(v[0]);
@@ -544,9 +572,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                     tr.ev(0x800 + ei);
                 }
                 tr.ev(0x900 + ei);
-                // the staged input is dead once the last layer-0 accumulator is complete (this epilogue waited for
-                // it): stage the NEXT item's rows now, under the MMAs of the remaining layers
-                if (ei == P.stage_after && w + (int)gridDim.x < items) { tr.ev(0x500); tc_stage_item(a, w + gridDim.x, x0, pb0 + 8 * BAR_XFULL, tid); tr.ev(0x502); }
             }
             tc_fence_before();
             pbits ^= P.parity_mask;
@@ -554,7 +579,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == TC_EPI_WARPS) {
+    if (warp == TC_MMA_WARP) {
         __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC_TMEM_COLS) : "memory");
     }
@@ -643,7 +668,8 @@ static int build_program(TcProgram& P, const PfNet& n) {
         g.wait_bar = -1; g.wait_k = 0;
         if (c == 0) { g.wait_bar = BAR_XFULL; g.wait_k = 0; }
         else if (c >= 2 && L > 1) { g.wait_bar = (int8_t)(BAR_E0 + e_b0[c - 2]); g.wait_k = (int8_t)e_k0[c - 2]; }   // slot drained
-        g.commit_bar = (int8_t)(BAR_ACC0 + (c & 1)); g.commit2_bar = -1;
+        g.commit_bar = (int8_t)(BAR_ACC0 + (c & 1));
+        g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_XFREE : -1);    // last reader of the staged rows
         acc_k0[c] = compl_[BAR_ACC0 + (c & 1)]++;
         return add_group(g);
     };
@@ -703,7 +729,7 @@ static int build_program(TcProgram& P, const PfNet& n) {
         }
     }
     compl_[BAR_XFULL] = 1;
-    P.stage_after = nch0 - 1;
+    compl_[BAR_XFREE] = 1;
     for (int b = 0; b < TC_NBARS; ++b) if (compl_[b] & 1) P.parity_mask |= 1u << b;
     P.blob_bytes = off;
     return 0;

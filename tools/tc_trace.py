@@ -18,16 +18,16 @@ obs, cobs = torch.randn(N, 27, device="cuda"), torch.randn(N, nc, device="cuda")
 for _ in range(3):
     ppo.storage.step = 0; ppo.act(obs, cobs)
 CAP = 512
-buf = torch.zeros(3 * CAP, dtype=torch.int64, device="cuda")
+buf = torch.zeros(4 * CAP, dtype=torch.int64, device="cuda")
 assert ppo._lib.pf_rl_tc_trace(ppo._ctx, C.c_void_p(buf.data_ptr())) == 0
 ppo.storage.step = 0; ppo.act(obs, cobs)
 torch.cuda.synchronize()
 ppo._lib.pf_rl_tc_trace(ppo._ctx, None)
 raw = buf.cpu().tolist()
 NAMES = {0x1: "load  group", 0x2: "mma   reach", 0x3: "mma   issue", 0x4: "mma   done ", 0x5: "epi   item ", 0x6: "epi   reach",
-         0x7: "epi   start", 0x8: "epi   work ", 0x9: "epi   done ", 0xA: "mma   tile got", 0xB: "mma   tile issued"}
+         0x7: "epi   start", 0x8: "epi   work ", 0x9: "epi   done ", 0xA: "mma   tile got", 0xB: "mma   tile issued", 0xC: "epi   tmem ld", 0xD: "epi   tmem got"}
 ev = []
-for role in range(3):
+for role in range(4):
     for v in raw[role * CAP:(role + 1) * CAP]:
         if v:
             tag, clk = (v >> 48) & 0xFFFF, v & ((1 << 48) - 1)
@@ -38,7 +38,7 @@ prev = {}
 for clk, role, tag in ev[:limit]:
     d = clk - prev.get(role, t0)
     prev[role] = clk
-    sub = {0x500: "begin", 0x501: "staged", 0x502: "arrived"}.get(tag, str(tag & 0xFF))
+    sub = {0x500: "begin", 0x501: "staged", 0x502: "arrived", 0x503: "loaded", 0x504: "padded", 0x505: "signalled"}.get(tag, str(tag & 0xFF))
     print(f"{(clk - t0):9d} cyc  (+{d:7d})  {'  ' * role}{NAMES[tag >> 8]} {sub}")
 last = max(c for c, r, t in ev if r == 0)
 items = sum(1 for c, r, t in ev if t == 0x500)
