@@ -39,6 +39,7 @@ void pf_set_error(const char* msg);
 #define TC_X0_LBO (TC_ROWS * 16 + 16)        // staged input: byte distance between 8-column blocks, padded (see tc_stage_item)
 #define TC_SLOT_BYTES 16384                  // weight ring slot = largest tile (N x K x 2 B: 256x32, 128x64, 64x128 ...)
 #define TC_MAX_STAGES 16
+#define TC_X0_KSTEP ((2 * TC_X0_LBO) / 16)    // K = 16 further along the staged input, in descriptor units
 #define TC_EPI_WARPS 8                       // epilogue warps: 4 TMEM lane quarters x 2 column halves (the ELU is MUFU-bound: more warps do not help)
 #define TC_EPI_THREADS (TC_EPI_WARPS * 32)
 #define TC_STG_WARPS 8                       // staging warps: input rows of the NEXT item, under the tail of the current one
@@ -109,7 +110,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 // bounded wait: a protocol bug must end in a trap, never in a hung GPU
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok = 0;
-#pragma unroll 1
+#pragma unroll 4
     for (uint32_t it = 0; it < 50000000u; ++it) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
@@ -141,6 +142,8 @@ __device__ __forceinline__ void umma_bf16_acc(uint32_t tmem_d, uint64_t adesc, u
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc) : "memory");
 }
+template <int A_STEP, int B_STEP, int NK>
+__device__ __forceinline__ void issue_mmas(uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc);
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -183,6 +186,12 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
+template <int A_STEP, int B_STEP, int NK>
+__device__ __forceinline__ void issue_mmas(uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc) {
+#pragma unroll
+    for (int kk = 0; kk < NK; ++kk) umma_bf16_acc(tmem_d, ad + (uint64_t)(kk * A_STEP), bd + (uint64_t)(kk * B_STEP), idesc);
+}
+
 // ------------------------------------------------------------------------------------------------ kernel
 enum { TC_OUT_PLAIN = 0, TC_OUT_SAMPLE = 1, TC_OUT_VALUE = 2 };
 
@@ -202,7 +211,7 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
-    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs
+    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies
     unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
@@ -446,16 +455,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                     int left = G.kc >> 4;                       // K = 16 steps still to issue
                     const int per_tile = G.kt >> 4;
                     while (left > 0) {
-                        mbar_wait(full_bar, round & 1u);
-                        tc_fence_after();
+                        mbar_wait(full_bar, round & 1u);      // bulk copy -> MMA: both async proxy, the mbarrier orders them
                         uint64_t bdesc = ring_desc + b_lbo;
                         const int nk = left < per_tile ? left : per_tile;
                         if (elect_one()) {
-                            uint64_t ad = adesc;
-                            for (int kk = 0; kk < nk; ++kk) {
-                                if (!(a.debug & 16)) umma_bf16_acc(tmem_d, ad, bdesc, idesc);   // experiment: no MMAs
-                                ad += a_step;
-                                bdesc += b_step;
+                            // the common tile shapes with compile-time descriptor strides (immediate uniform adds:
+                            // three instructions per MMA), anything else through the generic loop
+                            const bool xs = G.a_src == 0;
+                            if (nt == 128 && nk == 4) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 4>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 4>(tmem_d, adesc, bdesc, idesc); }
+                            else if (nt == 128 && nk == 2) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 2>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 2>(tmem_d, adesc, bdesc, idesc); }
+                            else if (nt == 256 && nk == 2 && !xs) issue_mmas<256, 512, 2>(tmem_d, adesc, bdesc, idesc);
+                            else {
+                                uint64_t ad = adesc;
+                                for (int kk = 0; kk < nk; ++kk) {
+                                    umma_bf16_acc(tmem_d, ad, bdesc, idesc);
+                                    ad += a_step;
+                                    bdesc += b_step;
+                                }
                             }
                             umma_commit(empty_bar);             // slot is free once these MMAs have read it
                         }

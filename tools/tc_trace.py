@@ -25,7 +25,7 @@ torch.cuda.synchronize()
 ppo._lib.pf_rl_tc_trace(ppo._ctx, None)
 raw = buf.cpu().tolist()
 NAMES = {0x1: "load  group", 0x2: "mma   reach", 0x3: "mma   issue", 0x4: "mma   done ", 0x5: "epi   item ", 0x6: "epi   reach",
-         0x7: "epi   start", 0x8: "epi   work ", 0x9: "epi   done ", 0xA: "mma   tile got", 0xB: "mma   tile issued", 0xC: "epi   tmem ld", 0xD: "epi   tmem got"}
+         0x7: "epi   start", 0x8: "epi   work ", 0x9: "epi   done ", 0xA: "mma   tile wait", 0xB: "mma   tile got", 0xC: "epi   tmem ld", 0xD: "epi   tmem got"}
 ev = []
 for role in range(4):
     for v in raw[role * CAP:(role + 1) * CAP]:
