@@ -34,19 +34,6 @@ static int rl_fail(int code, const char* what, const char* detail) {
 // batch index, so minibatches are never materialised.
 // Tile 64x64x16, 256 threads, 4x4 outputs per thread; the accumulation order over k is fixed (ascending), and
 // split-K partials are reduced in a fixed order by a second kernel: results are run-to-run deterministic.
-struct GemmArgs {
-    const float* A; long long sam, sak; const int* a_rows;   // a_rows gathers the m index (forward)
-    const float* B; long long sbk, sbn; const int* b_rows;   // b_rows gathers the k index (wgrad)
-    float* C; long long ldc;
-    int M, N, K;
-    int k_per_split;              // K range of one blockIdx.z slice
-    long long split_stride;       // C offset between slices (partials buffer), 0 when unsplit
-    const float* bias;            // [N] or NULL
-    int elu;                      // 1: C = elu(acc + bias)
-    const float* elu_out;         // dgrad: multiply by ELU'(x) recovered from the saved activation y: y > 0 ? 1 : y + 1
-    long long ld_elu;
-};
-
 #define GT 64
 #define GK 16
 __global__ void __launch_bounds__(256) pf_sgemm_kernel(const GemmArgs g) {
@@ -144,7 +131,8 @@ __global__ void pf_colsum_kernel(const float* __restrict__ dY, long long ld, int
     }
 }
 
-static int launch_gemm(const GemmArgs& g, int splits, cudaStream_t st) {
+static int launch_gemm(pf_rl_ctx* c, const GemmArgs& g, int splits, cudaStream_t st) {
+    if (pf_tc_gemm_supported(c, g.M, g.N, g.K)) return pf_tc_gemm(c, g, splits, st);
     dim3 grid((g.N + GT - 1) / GT, (g.M + GT - 1) / GT, splits);
     pf_sgemm_kernel<<<grid, 256, 0, st>>>(g);
     RL_CUDA(cudaGetLastError());
@@ -225,6 +213,7 @@ extern "C" int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out) {
     c->tc = nullptr;
     if (P.precision == PF_RL_BF16_TC) {
         if (int rc = pf_tc_create(c)) { return rc; }
+        if (int rc = pf_tc_gemm_create(c)) { return rc; }
     } else if (P.precision != PF_RL_FP32) {
         return rl_fail(1, "pf_rl_create", "unknown precision");
     }
@@ -235,6 +224,7 @@ extern "C" int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out) {
 extern "C" int pf_rl_destroy(pf_rl_ctx* c) {
     if (!c) return 0;
     if (c->tc) pf_tc_destroy(c);
+    pf_tc_gemm_destroy(c);
     for (int k = 0; k < 2; ++k)
         for (int l = 0; l < c->net[k].layers; ++l) cudaFree(c->net[k].act[l]);
     cudaFree(c->perm); cudaFree(c->dbuf[0]); cudaFree(c->dbuf[1]); cudaFree(c->part);
@@ -275,7 +265,7 @@ static int forward_fp32(pf_rl_ctx* c, int k, const float* params, const float* x
         g.M = rows; g.N = n.dims[l + 1]; g.K = n.dims[l]; g.k_per_split = g.K; g.split_stride = 0;
         g.bias = params + n.b_off[l];
         g.elu = l < n.layers - 1;
-        if (int rc = launch_gemm(g, 1, st)) return rc;
+        if (int rc = launch_gemm(c, g, 1, st)) return rc;
         in = n.act[l]; ld = n.dims[l + 1];
     }
     return 0;
@@ -647,14 +637,15 @@ static int backward_fp32(pf_rl_ctx* c, int k, const pf_rl_learner* L, const floa
         // ---- wgrad: dW[out,in] = dY^T X, split over the batch ----
         int splits = c->wgrad_splits;
         int kps = (rows + splits - 1) / splits;
-        kps = (kps + GK - 1) / GK * GK;
+        const int kq = c->tc_gemm ? 64 : GK;            // split granularity: one pipeline stage of the tensor-core GEMM
+        kps = (kps + kq - 1) / kq * kq;
         splits = (rows + kps - 1) / kps;
         GemmArgs g = {};
         g.A = dY; g.sam = 1; g.sak = out; g.a_rows = nullptr;
         g.B = X; g.sbk = ldx; g.sbn = 1; g.b_rows = l == 0 ? rows_idx : nullptr;
         g.C = c->part; g.ldc = in; g.M = out; g.N = in; g.K = rows; g.k_per_split = kps;
         g.split_stride = (long long)out * in;
-        if (int rc = launch_gemm(g, splits, st)) return rc;
+        if (int rc = launch_gemm(c, g, splits, st)) return rc;
         const long long wn = (long long)out * in;
         pf_reduce_partials_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, st>>>(c->part, splits, wn, L->grads + n.w_off[l], wn);
         RL_CUDA(cudaGetLastError());
@@ -671,7 +662,7 @@ static int backward_fp32(pf_rl_ctx* c, int k, const pf_rl_learner* L, const floa
             d.B = params + n.w_off[l]; d.sbk = in; d.sbn = 1;
             d.C = c->dbuf[cur]; d.ldc = in; d.M = rows; d.N = in; d.K = out; d.k_per_split = out;
             d.elu_out = n.act[l - 1]; d.ld_elu = in;
-            if (int rc = launch_gemm(d, 1, st)) return rc;
+            if (int rc = launch_gemm(c, d, 1, st)) return rc;
             dY = c->dbuf[cur];
             cur ^= 1;
         }

@@ -37,6 +37,7 @@ struct pf_rl_ctx {
     double* norm_part;                          // [norm_blocks] grad-norm^2 partials
     int norm_blocks;
     void* tc;                                   // opaque state of the tensor-core path (pf_mlp_tc.cu), or NULL
+    void* tc_gemm;                              // opaque state of the tensor-core training GEMM (pf_gemm_tc.cu), or NULL
 };
 
 // ---- tensor-core path entry points (pf_mlp_tc.cu) ----
@@ -51,3 +52,23 @@ int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x
 int pf_tc_act_fusable(const pf_rl_ctx* c);
 int pf_tc_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
               int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st);
+
+// ---- GEMM contract shared by the fp32 kernel (pf_rl.cu) and the tensor-core kernel (pf_gemm_tc.cu) ----
+struct GemmArgs {
+    const float* A; long long sam, sak; const int* a_rows;   // a_rows gathers the m index (forward)
+    const float* B; long long sbk, sbn; const int* b_rows;   // b_rows gathers the k index (wgrad)
+    float* C; long long ldc;
+    int M, N, K;
+    int k_per_split;              // K range of one blockIdx.z slice
+    long long split_stride;       // C offset between slices (partials buffer), 0 when unsplit
+    const float* bias;            // [N] or NULL
+    int elu;                      // 1: C = elu(acc + bias)
+    const float* elu_out;         // dgrad: multiply by ELU'(x) recovered from the saved activation y: y > 0 ? 1 : y + 1
+    long long ld_elu;
+};
+
+
+int pf_tc_gemm_create(pf_rl_ctx* c);
+void pf_tc_gemm_destroy(pf_rl_ctx* c);
+int pf_tc_gemm_supported(const pf_rl_ctx* c, int M, int N, int K);
+int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& g, int splits, cudaStream_t st);

@@ -37,6 +37,14 @@ def test_ppo_update_rough_net():
     parity_rl.run_update(num_envs=256, num_critic_obs=148, hidden=(512, 256, 128), T=24)
 
 
+@pytest.mark.parametrize("hidden,nc,n", [((512, 256, 128), 148, 256), ((128, 64, 32), 27, 700)])
+def test_ppo_update_tensor_core_gemms_bf16(hidden, nc, n):
+    """PF_RL_BF16_TC: forward / dgrad / wgrad of PPO.update on the tcgen05 GEMM (bf16 operands, fp32 accumulate);
+    first-minibatch gradient within 10 x rtol 2e-2 of the fp32 oracle (relative to the largest gradient entry),
+    parameters after the whole update within 25 % of the update's own L2 movement."""
+    parity_rl.run_update(num_envs=n, num_critic_obs=nc, hidden=hidden, T=24, precision="bf16")
+
+
 def test_rollout_buffer_overflow_raises():
     ppo, oppo = parity_rl.make_pair(8, 27, 27, [32, 16, 8], T=2)
     try:
