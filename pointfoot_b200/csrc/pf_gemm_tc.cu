@@ -23,7 +23,7 @@ void pf_set_error(const char* msg);
 
 #define GT_ROWS 128
 #define GT_KSTEP 64
-#define GT_STAGES 4
+#define GT_STAGES 4                          // deepest ring; short-K launches use fewer (two CTAs per SM then fit)
 #define GT_EPI_WARPS 4
 #define GT_THREADS ((GT_EPI_WARPS + 2) * 32)
 
@@ -74,17 +74,26 @@ struct TcGemmArgs {
     int kblocks;                  // 8-column blocks per packed row tile (K padded to a multiple of GT_KSTEP)
     int stages_per_split;         // K steps of GT_KSTEP per blockIdx.z slice
     int nt;                       // B rows per tile: 128 or 256 (UMMA N)
+    int stages;                   // ring depth of this launch (<= GT_STAGES)
     float* C; long long ldc; long long split_stride;
     int M, N;
     const float* bias; int elu;
     const float* elu_out; long long ld_elu;
 };
 
-__global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_constant__ TcGemmArgs g) {
+// ELU with the exponential on the MUFU unit (ex2.approx), branch-free; the operands were rounded to bf16 anyway
+__device__ __forceinline__ float gt_elu(float x) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fminf(x, 0.0f) * 1.4426950408889634f));
+    return x > 0.0f ? x : e - 1.0f;
+}
+
+__global__ void __launch_bounds__(GT_THREADS, 2) pf_tc_gemm_kernel(const __grid_constant__ TcGemmArgs g) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int NT = g.nt;
     const uint32_t a_bytes = GT_ROWS * GT_KSTEP * 2, b_bytes = (uint32_t)NT * GT_KSTEP * 2, stage_bytes = a_bytes + b_bytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GT_STAGES * stage_bytes);
+    const int S = g.stages;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * stage_bytes);
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + GT_STAGES), acc_bar = smem_u32(bars + 2 * GT_STAGES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * GT_STAGES + 1);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -95,12 +104,12 @@ __global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_
     const int nst = s_end - s_beg;
 
     if (warp == GT_EPI_WARPS + 1 && lane == 0) {
-        for (int s = 0; s < GT_STAGES; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+        for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
         mbar_init(acc_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == GT_EPI_WARPS) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256u) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)NT) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -113,8 +122,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_
         const unsigned char* a_src = g.ap + ((size_t)mt * g.kblocks + (size_t)s_beg * (GT_KSTEP / 8)) * (GT_ROWS * 16);
         const unsigned char* b_src = g.bp + ((size_t)ntile * g.kblocks + (size_t)s_beg * (GT_KSTEP / 8)) * ((size_t)NT * 16);
         for (int s = 0; s < nst; ++s) {
-            const int slot = s % GT_STAGES;
-            if (s >= GT_STAGES) mbar_wait(empty0 + 8 * slot, (uint32_t)((s / GT_STAGES) - 1) & 1u);
+            const int slot = s % S;
+            if (s >= S) mbar_wait(empty0 + 8 * slot, (uint32_t)((s / S) - 1) & 1u);
             if (elect_one()) {
                 mbar_expect_tx(full0 + 8 * slot, stage_bytes);
                 bulk_g2s(smem_u32(smem + slot * stage_bytes), a_src + (size_t)s * a_bytes, a_bytes, full0 + 8 * slot);
@@ -126,8 +135,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_
         const uint32_t idesc = make_idesc(NT);
         const uint64_t b_lbo = (uint64_t)((uint32_t)(NT * 16) >> 4) << 16;
         for (int s = 0; s < nst; ++s) {
-            const int slot = s % GT_STAGES;
-            mbar_wait(full0 + 8 * slot, (uint32_t)(s / GT_STAGES) & 1u);
+            const int slot = s % S;
+            mbar_wait(full0 + 8 * slot, (uint32_t)(s / S) & 1u);
             if (elect_one()) {
                 const uint64_t ad = make_desc(smem_u32(smem + slot * stage_bytes), GT_ROWS * 16, 128u);
                 const uint64_t bd = make_desc(smem_u32(smem + slot * stage_bytes + a_bytes), 0u, 128u) + b_lbo;
@@ -141,12 +150,16 @@ __global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_
         }
     } else {
         // ---- epilogue: 4 warps, warp q owns TMEM lanes [32q, 32q+32) = rows of the tile ----
-        const int row = warp * 32 + lane;
-        const int m = mt * GT_ROWS + row;
+        // TMEM hands a thread one ROW (32 consecutive columns); written as is, every store instruction of a warp
+        // would touch 32 different rows.  Each 32 x 32 piece therefore goes through a padded shared-memory square
+        // (the pipeline ring is idle by now) and leaves with lanes along the columns: 128-byte coalesced stores,
+        // and the bias / ELU' operands are read coalesced in the same pass.
+        const int row0 = mt * GT_ROWS + warp * 32;
         if (nst > 0) {
             mbar_wait(acc_bar, 0u);
             tc_fence_after();
         }
+        float* sq = reinterpret_cast<float*>(smem) + warp * (32 * 33);
         float* C = g.C + (long long)z * g.split_stride;
         const int n_base = ntile * NT;
         for (int c0 = 0; c0 < NT; c0 += 32) {
@@ -159,28 +172,36 @@ __global__ void __launch_bounds__(GT_THREADS, 1) pf_tc_gemm_kernel(const __grid_
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = 0u;
             }
-            if (m < g.M) {
-                float* crow = C + (long long)m * g.ldc + n_base + c0;
-                const float* erow = g.elu_out ? g.elu_out + (long long)m * g.ld_elu + n_base + c0 : nullptr;
-                const int cnt = min(32, g.N - n_base - c0);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    if (j < cnt) {
-                        float x = __uint_as_float(v[j]);
-                        if (g.bias) x += g.bias[n_base + c0 + j];
-                        if (g.elu) x = x > 0.0f ? x : expm1f(x);
-                        if (erow) { const float y = erow[j]; x *= y > 0.0f ? 1.0f : y + 1.0f; }
-                        crow[j] = x;
+            for (int j = 0; j < 32; ++j) sq[lane * 33 + j] = __uint_as_float(v[j]);
+            __syncwarp();
+            const int n = n_base + c0 + lane;
+            const bool nv = n < g.N;
+            const float bias = (g.bias && nv) ? g.bias[n] : 0.0f;
+            const int rmax = min(32, g.M - row0);
+            for (int rb = 0; rb < 32; rb += 8) {                 // 8 rows per pass: the ELU' operand loads are all in flight
+                float y[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    y[u] = (g.elu_out && nv && rb + u < rmax) ? __ldg(g.elu_out + (long long)(row0 + rb + u) * g.ld_elu + n) : 1.0f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    if (nv && rb + u < rmax) {
+                        float x = sq[(rb + u) * 33 + lane] + bias;
+                        if (g.elu) x = gt_elu(x);
+                        x *= y[u] > 0.0f ? 1.0f : y[u] + 1.0f;
+                        C[(long long)(row0 + rb + u) * g.ldc + n] = x;
                     }
                 }
             }
+            __syncwarp();
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == GT_EPI_WARPS) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)NT) : "memory");
     }
 }
 
@@ -217,9 +238,9 @@ void pf_tc_gemm_destroy(pf_rl_ctx* c) {
     c->tc_gemm = nullptr;
 }
 
-// worth the packing passes only when every extent fills a tile reasonably
+// worth the two packing passes once there is real work; thin extents (6 actions, 1 value) are padded to a tile
 int pf_tc_gemm_supported(const pf_rl_ctx* c, int M, int N, int K) {
-    return c->tc_gemm && M >= 64 && N >= 32 && K >= 32;
+    return c->tc_gemm && (long long)M * N * K >= (1ll << 20) && (M >= 64 || N >= 64);
 }
 
 int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& d, int splits, cudaStream_t st) {
@@ -247,7 +268,10 @@ int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& d, int splits, cudaStream_t st) {
     g.kblocks = kblocks; g.stages_per_split = sps; g.nt = NT;
     g.C = d.C; g.ldc = d.ldc; g.split_stride = d.split_stride; g.M = d.M; g.N = d.N;
     g.bias = d.bias; g.elu = d.elu; g.elu_out = d.elu_out; g.ld_elu = d.ld_elu;
-    const int smem = GT_STAGES * (GT_ROWS * GT_KSTEP * 2 + NT * GT_KSTEP * 2) + 256;
+    const int per_split = sps < total_stages ? sps : total_stages;
+    g.stages = per_split < 2 ? 2 : per_split > GT_STAGES ? GT_STAGES : per_split;
+    if (NT == 256 && g.stages == 3) g.stages = 2;         // 2 x 48 KB stages: two CTAs per SM; 3 would only fit one
+    const int smem = g.stages * (GT_ROWS * GT_KSTEP * 2 + NT * GT_KSTEP * 2) + 256;
     pf_tc_gemm_kernel<<<dim3(ntiles, mtiles, splits), GT_THREADS, smem, st>>>(g);
     return cudaGetLastError() == cudaSuccess ? 0 : gt_fail(2, "pf_tc_gemm: launch failed");
 }

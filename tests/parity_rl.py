@@ -208,7 +208,8 @@ def run_update(num_envs=512, num_obs=27, num_critic_obs=148, hidden=(512, 256, 1
         err = (p_cuda - p_ref).norm().item()
         assert err <= (0.02 if precision == "fp32" else 0.25) * moved, f"parameters after update: |err| {err:.3e} vs |movement| {moved:.3e}"
         assert abs(ppo.learning_rate - oppo.learning_rate) <= 1e-12 + 1e-9 * oppo.learning_rate, (ppo.learning_rate, oppo.learning_rate)
-        assert abs(vl - ovl) <= 1e-3 * abs(ovl) + 1e-5 and abs(sl - osl) <= 1e-3 * abs(osl) + 1e-5, (vl, ovl, sl, osl)
+        lr_, la_ = (1e-3, 1e-5) if precision == "fp32" else (2e-2, 2e-4)      # mean losses: bf16 operands move them by ~1 %
+        assert abs(vl - ovl) <= lr_ * abs(ovl) + la_ and abs(sl - osl) <= lr_ * abs(osl) + la_, (vl, ovl, sl, osl)
     finally:
         ppo.close()
     return True

@@ -14,6 +14,7 @@ iters = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 T = 24
 nc, hidden = (148, (512, 256, 128)) if task == "rough" else (27, (128, 64, 32))
 precision = os.environ.get("PF_RL_PRECISION", "fp32")
+torch.manual_seed(0)
 ac = rl.ActorCritic(27, nc, 6, hidden, hidden)
 ppo = rl.PPO(ac, num_learning_epochs=5, num_mini_batches=4, gamma=0.99, lam=0.95, entropy_coef=0.01, schedule="adaptive",
              desired_kl=0.01, precision=precision)
