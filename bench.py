@@ -254,7 +254,7 @@ def time_steps(step_fn, steps, warmup, flush, barrier):
     return sum(a.elapsed_time(b) for a, b in evs)          # ms over the K steps
 
 
-def kernel_roofline(env, steps, flush, peaks):
+def kernel_roofline(env, steps, flush, peaks, task):
     """Device time of the dominant kernel (pf_post_physics_kernel + its finalize) alone, CUDA events, L2 flushed."""
     import torch
     from pointfoot_b200 import capi
@@ -276,9 +276,15 @@ def kernel_roofline(env, steps, flush, peaks):
     nbytes = algorithmic_bytes_per_env(env._P)["post_physics"] * env.num_envs
     achieved = nbytes / (ms * 1e-3) / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
+    traffic = None
+    try:        # measured DRAM bytes of the same kernel on the same workload, from the committed ncu capture
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(f"{task}:{env.num_envs}", {}).get("bytes")
+    except (OSError, ValueError):
+        pass
     return {"bound": "hbm", "kernel": "pf_post_physics_kernel(+pf_finalize_kernel)", "achieved": achieved,
             "peak": peak, "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-            "unit": "GB/s", "frac": achieved / peak, "traffic": None, "us_per_launch": ms * 1e3,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "us_per_launch": ms * 1e3,
             "algorithmic_bytes_per_launch": nbytes}
 
 
@@ -368,7 +374,7 @@ def run_b200(args):
     ms = float(t.item())
     clocks = sampler.stop() if rank == 0 else None
 
-    roof = kernel_roofline(env, args.steps, flush, peaks)
+    roof = kernel_roofline(env, args.steps, flush, peaks, args.task)
     e2e_s, h2d, d2h = e2e_host(env, min(args.steps, 200), max(3, min(args.warmup, 10)), barrier)
     t = torch.tensor([e2e_s], device=device, dtype=torch.float64)
     if world > 1:

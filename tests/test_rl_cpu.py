@@ -53,3 +53,33 @@ def test_oracle_ppo_iteration_config_c1():
     p1 = torch.cat([p.detach().flatten() for p in ac.parameters()])
     assert np.isfinite(vl) and np.isfinite(sl) and (p1 - p0).abs().max() > 0 and len(ppo.last_kl) == 20
     assert abs(float(ppo.storage.advantages.mean())) < 1e-5 and abs(float(ppo.storage.advantages.std()) - 1) < 1e-4
+
+
+def test_tensor_core_mlp_schedule_is_built_and_dry_run_on_the_host():
+    """pf_rl_tc_plan (no device): shapes the fused tcgen05 MLP kernel accepts, and the structure of its static schedule
+    for the PointFoot critic [148, 512, 256, 128, 1]: 4 layer-0 chunks + 4 + 2 + 1 K-slices = 11 MMA groups, 8 epilogues,
+    every chunk buffer hand-over guarded by a barrier."""
+    import ctypes as C
+    import re
+    from pointfoot_b200 import capi
+    lib = capi.load()
+
+    def plan(dims, cap=8192):
+        arr = (C.c_int32 * len(dims))(*dims)
+        buf = C.create_string_buffer(cap)
+        return lib.pf_rl_tc_plan(arr, len(dims) - 1, buf, cap), buf.value.decode()
+
+    for ok in ([148, 512, 256, 128, 1], [27, 128, 64, 32, 6], [48, 256, 128, 6], [235, 64, 64, 64, 12], [27, 6], [27, 1024, 256, 6]):
+        assert plan(ok)[0] == 0, ok
+    for bad in ([300, 64, 6], [27, 64, 512, 6], [27, 1100, 32, 1]):      # input > 256, later layer > 256, first layer > 1024
+        assert plan(bad)[0] == 6, bad
+    rc, text = plan([148, 512, 256, 128, 1])
+    groups = re.findall(r"^G\d+ layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+) bias=(\d+) wait=(-?\d+)@", text, re.M)
+    epis = re.findall(r"^E\d+ col=(\d+) nt=(\d+) n0=(\d+) acc=(\d+)@(\d+) dst=(-?\d+)", text, re.M)
+    assert len(groups) == 11 and len(epis) == 8
+    assert [g[0] for g in groups].count("0") == 4 and [g[0] for g in groups].count("1") == 4
+    assert all(int(g[2]) * int(g[4]) * 2 <= 16384 for g in groups)            # a weight tile fits a ring slot
+    assert all(int(g[7]) >= 0 for g in groups if g[1] != "0")                 # chunk consumers wait for their producer
+    assert [e[5] for e in epis][-1] == "-1" and all(e[5] in "01" for e in epis[:-1])
+    blob = int(re.search(r"blob_bytes=(\d+)", text).group(1))
+    assert blob == 2 * ((160 + 16) * 512 + (512 + 16) * 256 + (256 + 16) * 128 + (128 + 16) * 16)
