@@ -288,7 +288,7 @@ def kernel_roofline(env, steps, flush, peaks, task):
             "algorithmic_bytes_per_launch": nbytes}
 
 
-def e2e_host(env, steps, warmup, barrier):
+def e2e_host(env, steps, warmup, barrier, policy=None, use_graph=True):
     """Same metric through the host-buffer C-ABI call: PhysX state tensors + actions H2D, results D2H, per step."""
     import torch
     from pointfoot_b200 import capi
@@ -299,15 +299,39 @@ def e2e_host(env, steps, warmup, barrier):
     act = pin(torch.zeros(N, P.num_dof))
     obs = pin(torch.zeros(N, P.num_obs)); priv = pin(torch.zeros(N, max(P.num_priv_obs, 1)))
     rew = pin(torch.zeros(N)); rst = pin(torch.zeros(N, dtype=torch.uint8)); tq = pin(torch.zeros(N, P.num_dof))
-    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     lib, ctx, b = env._lib, env._ctx, C.byref(env._bufs)
+
+    def enqueue(sync):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        fn = lib.pf_step_host if sync else lib.pf_step_host_async
+        capi.check(fn(ctx, b, C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
+                      C.c_void_p(priv.data_ptr()) if P.num_priv_obs else None, C.c_void_p(rew.data_ptr()),
+                      C.c_void_p(rst.data_ptr()), C.c_void_p(tq.data_ptr()), C.c_int64(0), st), "pf_step_host")
+        if policy is not None:      # same metric as `value`: the policy runs on the device observations and its actions
+            policy.act_into(env, policy.actions)          # go back to the host for the next physics step
+            act.copy_(policy.actions, non_blocking=True)
+
+    graph = None
+    if policy is not None and use_graph:
+        # the whole host-facing step (H2D copies from the pinned buffers, kernels, D2H copies) as ONE graph launch:
+        # what a caller stepping a fixed set of pinned PhysX buffers does to get the ~15 API calls off the CPU path
+        for _ in range(2):
+            enqueue(False)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            enqueue(False)
 
     def one():
         env.common_step_counter += 1
-        capi.check(lib.pf_step_host(ctx, b, C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
-                                    C.c_void_p(priv.data_ptr()) if P.num_priv_obs else None, C.c_void_p(rew.data_ptr()),
-                                    C.c_void_p(rst.data_ptr()), C.c_void_p(tq.data_ptr()), C.c_int64(0), st),
-                   "pf_step_host")
+        if graph is not None:
+            graph.replay()
+            torch.cuda.current_stream().synchronize()
+        elif policy is not None:
+            enqueue(False)
+            torch.cuda.current_stream().synchronize()
+        else:
+            enqueue(True)
     for _ in range(warmup):
         one()
     barrier(); torch.cuda.synchronize()
@@ -316,8 +340,11 @@ def e2e_host(env, steps, warmup, barrier):
         one()
     torch.cuda.synchronize(); barrier()
     el = time.perf_counter() - t0
-    h2d = sum(v.numel() * 4 for v in hs_t.values()) + act.numel() * 4
+    h2d = sum(v.numel() * 4 for k, v in hs_t.items() if k != "rigid_body_states") + act.numel() * 4
+    h2d += hs_t["rigid_body_states"].numel() * 4 if os.environ.get("PF_HOST_RBS", "") == "full" else N * 2 * 3 * 4   # feet xyz only
     d2h = obs.numel() * 4 + (priv.numel() * 4 if P.num_priv_obs else 0) + rew.numel() * 4 + rst.numel() + tq.numel() * 4
+    if policy is not None:
+        d2h += act.numel() * 4
     return el, h2d, d2h
 
 
@@ -375,7 +402,7 @@ def run_b200(args):
     clocks = sampler.stop() if rank == 0 else None
 
     roof = kernel_roofline(env, args.steps, flush, peaks, args.task)
-    e2e_s, h2d, d2h = e2e_host(env, min(args.steps, 200), max(3, min(args.warmup, 10)), barrier)
+    e2e_s, h2d, d2h = e2e_host(env, min(args.steps, 200), max(3, min(args.warmup, 10)), barrier, policy, not args.no_graph)
     t = torch.tensor([e2e_s], device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -399,7 +426,7 @@ def run_b200(args):
                            "parallelism": f"env-sharded x{world}, no data-path collective"},
                 "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roof,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "api": "pf_step_host (C-ABI, pinned host buffers: PhysX state + actions in, obs/priv/rew/reset/torques out)",
+                        "api": ("one CUDA-graph launch per step of: " if (policy and not args.no_graph) else "") + "pf_step_host[_async] (C-ABI, pinned host buffers: PhysX state + actions in, obs/priv/rew/reset/torques out)" + (" + pf_rl_act on the device observations, sampled actions back to the host" if policy else ""),
                         "steps": e2e_steps}}
         if not args.no_cpu_baseline and world == 1:
             v, n, cores, with_pol = cpu_env_steps_per_sec(args.task, env.num_envs)

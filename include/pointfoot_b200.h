@@ -190,12 +190,18 @@ typedef struct pf_host_state {
     const float* root_states;         /* [N,13] */
     const float* dof_state;           /* [N*D,2] */
     const float* contact_forces;      /* [N*B,3] */
-    const float* rigid_body_states;   /* [N*B,13] */
+    const float* rigid_body_states;   /* [N*B,13]; only the feet position columns are transferred (all the path reads) */
 } pf_host_state;
 
 int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* state, const float* actions_host,
                  float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
                  int64_t common_step_counter, void* stream);
+/* Same, but everything is only ENQUEUED on `stream` (pinned host buffers required): the caller adds what follows
+ * the env step -- e.g. pf_rl_act on the device observations and the copy of the sampled actions back to the host --
+ * and synchronises once.  The host buffers are valid after that synchronisation. */
+int pf_step_host_async(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* state, const float* actions_host,
+                       float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
+                       int64_t common_step_counter, void* stream);
 
 /* ================================================================================================
  * rsl_rl v1.0.2 side of the path (third-party dependency of the reference; call sites

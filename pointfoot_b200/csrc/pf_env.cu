@@ -7,6 +7,7 @@
 // (pf_finalize_kernel) turns the per-warp partials into the ascending reset id list (PF:221 nonzero()), the
 // device count and the episode statistics, deterministically (no float atomics).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <stdio.h>
 #include "pf_env_core.cuh"
 #include "pf_ctx.h"
@@ -567,33 +568,60 @@ extern "C" int pf_push_forces(pf_ctx* c, const pf_env_buffers* bufs, float* forc
     return 0;
 }
 
-extern "C" int pf_step_host(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
-                            float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
-                            float* torques_host, int64_t common_step_counter, void* stream) {
+static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
+                             float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
+                             float* torques_host, int64_t common_step_counter, void* stream, bool sync) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     if (!actions_host || !obs_host || !rew_host || !reset_host) return pf_fail(1, "%s", "pf_step_host: null host buffer");
     const pf_params& P = c->P;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = (size_t)P.num_envs;
     const cudaMemcpyKind H2D = cudaMemcpyHostToDevice, D2H = cudaMemcpyDeviceToHost;
+    cudaStream_t q[4] = {st, st, st, st};      // (fanning the copies out over side streams was measured: no gain)
     if (hs) {
-        if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, st));
-        if (hs->dof_state) PF_CUDA(cudaMemcpyAsync(bufs->dof_state, hs->dof_state, 4 * N * P.num_dof * 2, H2D, st));
+        if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, q[1]));
+        if (hs->dof_state) PF_CUDA(cudaMemcpyAsync(bufs->dof_state, hs->dof_state, 4 * N * P.num_dof * 2, H2D, q[2]));
         if (hs->contact_forces)
-            PF_CUDA(cudaMemcpyAsync((void*)bufs->contact_forces, hs->contact_forces, 4 * N * P.num_bodies * 3, H2D, st));
-        if (hs->rigid_body_states)
-            PF_CUDA(cudaMemcpyAsync((void*)bufs->rigid_body_states, hs->rigid_body_states, 4 * N * P.num_bodies * 13, H2D, st));
+            PF_CUDA(cudaMemcpyAsync((void*)bufs->contact_forces, hs->contact_forces, 4 * N * P.num_bodies * 3, H2D, q[3]));
+        if (hs->rigid_body_states) {
+            // the path reads only the feet positions (PF:1083-1086, 1114-1129): move those 12-byte columns with one
+            // pitched copy per foot instead of the whole [N*B,13] tensor (24 B instead of 468 B per env);
+            // PF_HOST_RBS=full switches back to the whole tensor
+            static const bool full = [] { const char* e = getenv("PF_HOST_RBS"); return e && e[0] == 'f' && e[1] == 'u'; }();
+            const size_t pitch = sizeof(float) * 13 * P.num_bodies;
+            if (full) PF_CUDA(cudaMemcpyAsync((void*)bufs->rigid_body_states, hs->rigid_body_states, N * pitch, H2D, q[0]));
+            else
+                for (int f = 0; f < PF_NUM_FEET; ++f) {
+                    const size_t off = (size_t)P.feet_indices[f] * 13;
+                    PF_CUDA(cudaMemcpy2DAsync((void*)(bufs->rigid_body_states + off), pitch, hs->rigid_body_states + off, pitch,
+                                              3 * sizeof(float), N, H2D, q[f & 1 ? 1 : 0]));
+                }
+        }
     }
-    PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, H2D, st));
+    PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, H2D, q[2]));
     for (int i = 0; i < P.decimation; ++i)
         if (int rc = pf_pd_torques(c, bufs, i == 0 ? (const float*)c->d_actions_in : nullptr, stream)) return rc;
     if (int rc = pf_post_physics_step(c, bufs, common_step_counter, stream)) return rc;
-    PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, st));
+    PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, q[0]));
     if (priv_obs_host && bufs->priv_obs_buf)
-        PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, st));
-    PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, D2H, st));
-    PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, D2H, st));
-    if (torques_host) PF_CUDA(cudaMemcpyAsync(torques_host, bufs->torques, sizeof(float) * N * P.num_dof, D2H, st));
-    PF_CUDA(cudaStreamSynchronize(st));
+        PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, q[1]));
+    PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, D2H, q[2]));
+    PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, D2H, q[3]));
+    if (torques_host) PF_CUDA(cudaMemcpyAsync(torques_host, bufs->torques, sizeof(float) * N * P.num_dof, D2H, q[2]));
+    if (sync) PF_CUDA(cudaStreamSynchronize(st));
     return 0;
+}
+
+extern "C" int pf_step_host(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
+                            float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
+                            float* torques_host, int64_t common_step_counter, void* stream) {
+    return pf_step_host_impl(c, bufs, hs, actions_host, obs_host, priv_obs_host, rew_host, reset_host, torques_host,
+                             common_step_counter, stream, true);
+}
+
+extern "C" int pf_step_host_async(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
+                                  float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
+                                  float* torques_host, int64_t common_step_counter, void* stream) {
+    return pf_step_host_impl(c, bufs, hs, actions_host, obs_host, priv_obs_host, rew_host, reset_host, torques_host,
+                             common_step_counter, stream, false);
 }

@@ -465,7 +465,7 @@ class BenchPolicy:
         self.precision = precision
         self.dtype_name = "bf16 (tcgen05 MLP, fp32 accumulate) + f32 env" if precision == "bf16" else "f32"
         n_layers = len(self.ac.actor_dims) - 1 + len(self.ac.critic_dims) - 1
-        self.launches_per_act = 3 if precision == "bf16" else n_layers + 3
+        self.launches_per_act = 1 if precision == "bf16" else n_layers + 3      # bf16: ONE fused tcgen05 launch
         self.t = 0
         self.actions = self.alg._actions          # pf_rl_act writes the sampled actions here: step them directly
 
