@@ -175,6 +175,7 @@ class PPO:
         precision = precision or os.environ.get("PF_RL_PRECISION", "fp32")
         self.precision = {"fp32": capi.RL_FP32, "bf16": capi.RL_BF16_TC}[precision]
         self.storage, self._ctx, self._t = None, None, 0
+        self._update_graph, self._graph_updates = None, os.environ.get("PF_RL_UPDATE_GRAPH", "1") != "0"
         self._lib = capi.load_rl()
 
     # learning_rate mirrors the device scalar the adaptive schedule updates (one sync when read)
@@ -271,16 +272,31 @@ class PPO:
             shard.allreduce_mean_(self.grads)
             shard.allreduce_sum_(self.loss_stats)
 
-    def update(self):
-        lib, st = self._lib, self._st()
-        capi.check(lib.pf_rl_make_permutation(self._ctx, C.c_int64(self.iteration), st), "pf_rl_make_permutation")
-        self._loss_acc.zero_()
+    def _update_steps(self):
+        """num_learning_epochs x num_mini_batches optimizer steps (ppo.py update(), the body of its generator loop)"""
+        lib = self._lib
         for _ in range(self.num_learning_epochs):
             for mb in range(self.num_mini_batches):
                 self.minibatch_grad(mb)
-                capi.check(lib.pf_rl_adam_step(self._ctx, C.byref(self._L), st), "pf_rl_adam_step")
+                capi.check(lib.pf_rl_adam_step(self._ctx, C.byref(self._L), self._st()), "pf_rl_adam_step")
                 self._loss_acc += self.loss_stats
-        n = self.num_learning_epochs * self.num_mini_batches
+
+    def update(self):
+        capi.check(self._lib.pf_rl_make_permutation(self._ctx, C.c_int64(self.iteration), self._st()), "pf_rl_make_permutation")
+        self._loss_acc.zero_()
+        # All optimizer steps of one update are a fixed sequence of ~2,000 small launches on fixed buffers (learning
+        # rate, Adam state and the permutation live on the device): captured once, replayed as ONE graph launch.
+        # With more than one rank the NCCL all-reduces stay outside a graph, so the steps are launched one by one.
+        if self._graph_updates and shard.dist_or_none() is None:
+            if self._update_graph is None:
+                torch.cuda.synchronize(self.device)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._update_steps()
+                self._update_graph = g
+            self._update_graph.replay()
+        else:
+            self._update_steps()
         acc = self._loss_acc.tolist()                      # the one host sync of update(), like upstream's .item()
         self.storage.clear()
         self.iteration += 1

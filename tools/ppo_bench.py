@@ -16,7 +16,7 @@ nc, hidden = (148, (512, 256, 128)) if task == "rough" else (27, (128, 64, 32))
 precision = os.environ.get("PF_RL_PRECISION", "fp32")
 torch.manual_seed(0)
 ac = rl.ActorCritic(27, nc, 6, hidden, hidden)
-ppo = rl.PPO(ac, num_learning_epochs=5, num_mini_batches=4, gamma=0.99, lam=0.95, entropy_coef=0.01, schedule="adaptive",
+ppo = rl.PPO(ac, num_learning_epochs=5, num_mini_batches=4, gamma=0.99, lam=0.95, entropy_coef=0.01, schedule=os.environ.get("PF_SCHEDULE", "adaptive"),
              desired_kl=0.01, precision=precision)
 ppo.init_storage(N, T, [27], [nc], [6])
 g = torch.Generator(device="cuda").manual_seed(0)
@@ -50,4 +50,4 @@ m = [sorted(r[i] for r in res)[len(res) // 2] for i in range(3)]
 fwd = sum(a * b for a, b in zip(ac.actor_dims[:-1], ac.actor_dims[1:])) + sum(a * b for a, b in zip(ac.critic_dims[:-1], ac.critic_dims[1:]))
 upd_flops = 5 * T * N * 2 * fwd * 3          # fwd + dgrad + wgrad per sample per epoch
 print(json.dumps({"num_envs": N, "task": task, "precision": precision, "rollout_policy_ms": m[0], "gae_ms": m[1], "update_ms": m[2],
-                  "iteration_ms": sum(m), "update_tflops": upd_flops / m[2] / 1e9, "value_loss": vl, "surrogate_loss": sl}))
+                  "iteration_ms": sum(m), "update_tflops": upd_flops / m[2] / 1e9, "value_loss": vl, "surrogate_loss": sl, "learning_rate": ppo.learning_rate}))
