@@ -85,7 +85,7 @@ struct TcGemmArgs {
 __device__ __forceinline__ float gt_elu(float x) {
     float e;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fminf(x, 0.0f) * 1.4426950408889634f));
-    return x > 0.0f ? x : e - 1.0f;
+    return fmaxf(x, e - 1.0f);          // x > 0: e = 1 -> max(x, 0) = x;  x <= 0: exp(x) - 1 >= x
 }
 
 __global__ void __launch_bounds__(GT_THREADS, 2) pf_tc_gemm_kernel(const __grid_constant__ TcGemmArgs g) {

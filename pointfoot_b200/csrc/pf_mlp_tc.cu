@@ -119,7 +119,7 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
-    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies
+    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs
     unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
@@ -134,7 +134,7 @@ struct TcTrace {
 __device__ __forceinline__ float elu_fast(float x) {
     float e;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fminf(x, 0.0f) * 1.4426950408889634f));
-    return x > 0.0f ? x : e - 1.0f;
+    return fmaxf(x, e - 1.0f);          // x > 0: e = 1 -> max(x, 0) = x;  x <= 0: exp(x) - 1 >= x
 }
 
 // ---- input rows of item w: fp32 global -> bf16 core-matrix layout (+ the rollout-storage copy); all epilogue warps.
@@ -370,7 +370,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                             // the common tile shapes with compile-time descriptor strides (immediate uniform adds:
                             // three instructions per MMA), anything else through the generic loop
                             const bool xs = G.a_src == 0;
-                            if (nt == 128 && nk == 4) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 4>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 4>(tmem_d, adesc, bdesc, idesc); }
+                            if (a.debug & 16) { }                                   // experiment: no MMAs
+                            else if (nt == 128 && nk == 4) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 4>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 4>(tmem_d, adesc, bdesc, idesc); }
                             else if (nt == 128 && nk == 2) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 2>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 2>(tmem_d, adesc, bdesc, idesc); }
                             else if (nt == 256 && nk == 2 && !xs) issue_mmas<256, 512, 2>(tmem_d, adesc, bdesc, idesc);
                             else {
