@@ -430,6 +430,7 @@ extern "C" int pf_sizeof_env_buffers(void) { return (int)sizeof(pf_env_buffers);
 static int pf_pick_epw(int num_envs, int num_sms) {
     // envs per warp: small batches are latency bound, so spread them over more warps (idle lanes in the
     // one-lane-per-env phase are cheaper than idle SMs); from ~16 warps per SM on, full warps
+    if (const char* e = getenv("PF_EPW")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) return v; }
     if (num_envs <= num_sms * 16 * 8) return 8;
     if (num_envs <= num_sms * 16 * 16) return 16;
     return 32;

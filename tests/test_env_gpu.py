@@ -34,6 +34,35 @@ def test_cuda_matches_oracle_large_multi_epb():
     parity.run("pointfoot_flat", 70001, steps=2)
 
 
+@pytest.mark.parametrize("task", ["pointfoot_flat", "pointfoot_rough"])
+def test_cuda_matches_oracle_at_full_size(task):
+    """BASELINE.json's largest per-GPU size (262,144 envs, 32 envs per warp): the same bars as the small cases, on
+    every env -- bit-exact flags / indices / reset ids, rtol 1e-5 on observations and rewards."""
+    out = parity.run(task, 262144, steps=2, adversarial=False)
+    assert out[-1]["num_resets"] > 0                      # the synthetic state makes ~0.3 % of the envs reset per step
+
+
+def test_envs_per_warp_geometries_agree_bit_for_bit(monkeypatch):
+    """The step kernel's result must not depend on how many envs a warp owns (PF_EPW overrides the size heuristic)."""
+    from pointfoot_b200 import synth
+    state = synth.make_state(3000, "pointfoot_rough", seed=7)
+    outs = []
+    for epw in ("8", "16", "32"):
+        monkeypatch.setenv("PF_EPW", epw)
+        e = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=7)
+        e.step(state["actions"])
+        e.step(state["actions"] * 0.5)
+        outs.append({k: e.t[k].clone() for k in ("obs_buf", "priv_obs_buf", "rew_buf", "reset_buf", "episode_sums", "reset_ids",
+                                                   "terrain_levels", "root_states", "episode_stats")})
+        e.close()
+    for o in outs[1:]:
+        for k, v in o.items():
+            if k == "episode_stats":                       # per-warp partial sums: fixed tree per geometry, not across them
+                torch.testing.assert_close(v, outs[0][k], rtol=1e-5, atol=1e-6)
+            else:
+                assert torch.equal(v, outs[0][k]), k
+
+
 def test_sharded_equals_unsharded():
     """env_id_offset: RNG draws are functions of the global env id, so two half shards == one full run."""
     import common

@@ -13,7 +13,9 @@ def test_act_storage_and_returns_match_oracle(hidden, nc):
 
 
 @pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 300), ((512, 256, 128), 148, 300), ((512, 256, 128), 148, 4096),
-                                         ((256, 128), 48, 129), ((64, 64, 64, 64), 235, 1)])
+                                         ((256, 128), 48, 129), ((64, 64, 64, 64), 235, 1),
+                                         # more items than SMs: every persistent CTA walks several (net, tile) items
+                                         ((512, 256, 128), 148, 40000), ((128, 64, 32), 27, 50001)])
 def test_tcgen05_mlp_act_matches_oracle_bf16(hidden, nc, n):
     """PF_RL_BF16_TC: fused tcgen05 MLP (bf16 operands, fp32 accumulate in TMEM); tolerance rtol = atol = 2e-2"""
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
