@@ -144,6 +144,29 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
                        PfEnvOut& out) {
     const int D = P.num_dof;
     const float dt = P.dt;
+    const int N = P.num_envs;
+    // Everything the step reads from env-owned global buffers, loaded up front: the loads are independent of each
+    // other, so they are all in flight together.  Left where they are used, each one sits behind an earlier store
+    // the compiler must assume aliases it, and the step pays ~60 memory latencies one after another.
+    const int R_all = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
+    float es[PF_MAX_REWARD_TERMS + 1];
+    for (int k = 0; k < R_all; ++k) es[k] = B.episode_sums[(size_t)k * N + e];
+    float tq_[PF_MAX_DOF], ldv_[PF_MAX_DOF], la_[PF_MAX_DOF], ac_[PF_MAX_DOF];
+    for (int d = 0; d < D; ++d) {
+        tq_[d] = B.torques[e * D + d]; ldv_[d] = B.last_dof_vel[e * D + d];
+        la_[d] = B.last_actions[e * D + d]; ac_[d] = B.actions[e * D + d];
+    }
+    bool fc_old_[PF_NUM_FEET], cfilt_old_[PF_NUM_FEET], lc_old_[PF_NUM_FEET];
+    float fat_old_[PF_NUM_FEET], lfat_old_[PF_NUM_FEET], lmfh_old_[PF_NUM_FEET], cmfh_old_[PF_NUM_FEET];
+    for (int f = 0; f < PF_NUM_FEET; ++f) {
+        const int k = e * PF_NUM_FEET + f;
+        fc_old_[f] = B.first_contact[k] != 0; cfilt_old_[f] = B.contact_filt[k] != 0; lc_old_[f] = B.last_contacts[k] != 0;
+        fat_old_[f] = B.feet_air_time[k]; lfat_old_[f] = B.last_feet_air_time[k];
+        lmfh_old_[f] = B.last_max_feet_height[k];
+        cmfh_old_[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
+    }
+    float cmd_old_[4];
+    for (int i = 0; i < 4; ++i) cmd_old_[i] = i < P.num_commands ? B.commands[e * P.num_commands + i] : 0.0f;
     // ---- PF:204 ----
     const long long ep_len = B.episode_length_buf[e] + 1;
 
@@ -165,14 +188,14 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
     bool first_contact[PF_NUM_FEET];
     for (int f = 0; f < PF_NUM_FEET; ++f) {
         const int k = e * PF_NUM_FEET + f;
-        const bool fc_old = B.first_contact[k] != 0;
-        const bool cfilt_old = B.contact_filt[k] != 0;
-        float fat_f = B.feet_air_time[k];
-        lfat[f] = fc_old ? fat_f : B.last_feet_air_time[k];
+        const bool fc_old = fc_old_[f];
+        const bool cfilt_old = cfilt_old_[f];
+        float fat_f = fat_old_[f];
+        lfat[f] = fc_old ? fat_f : lfat_old_[f];
         fat_f = cfilt_old ? 0.0f : fat_f;
-        lmfh[f] = B.last_max_feet_height[k];
+        lmfh[f] = lmfh_old_[f];
         if (P.include_feet_height_rewards) {
-            float cm = B.current_max_feet_height[k];
+            float cm = cmfh_old_[f];
             lmfh[f] = fc_old ? cm : lmfh[f];
             cm = cfilt_old ? 0.0f : cm;
             float below = 0.0f;                                   // PF:1089-1090 plane
@@ -186,7 +209,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
             B.last_max_feet_height[k] = lmfh[f];
         }
         const bool contact = in.cf[P.feet_indices[f] * 3 + 2] > 1.0f;
-        const bool cfilt = contact || (B.last_contacts[k] != 0);
+        const bool cfilt = contact || lc_old_[f];
         first_contact[f] = (fat_f > 0.0f) && cfilt;
         fat_f = fat_f + dt;
         fat[f] = fat_f;
@@ -196,7 +219,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
 
     // ---- PF:479-493 callback: commands ----
     const int C = P.num_commands;
-    for (int i = 0; i < 4; ++i) out.commands[i] = i < C ? B.commands[e * C + i] : 0.0f;
+    for (int i = 0; i < 4; ++i) out.commands[i] = cmd_old_[i];
     const uint32_t genv = (uint32_t)(P.env_id_offset + e);
     if (P.resample_commands && (ep_len % P.resample_period) == 0) {       // LR:337-351
         const uint32_t ek = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_RESAMPLE), genv);
@@ -231,7 +254,6 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
 
     // ---- PF:301-318 rewards, summed in cfg (alphabetical) order ----
     float rew = 0.0f;
-    const int N = P.num_envs;
     for (int k = 0; k < P.num_reward_terms; ++k) {
         float r = 0.0f;
         switch (P.reward_ids[k]) {
@@ -242,13 +264,13 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
             const float bh = in.have_heights ? in.height_mean : in.root[2];
             r = pf_sq(bh - P.base_height_target);
         } break;
-        case PF_REW_TORQUES: for (int d = 0; d < D; ++d) r += pf_sq(B.torques[e * D + d]); break;
+        case PF_REW_TORQUES: for (int d = 0; d < D; ++d) r += pf_sq(tq_[d]); break;
         case PF_REW_DOF_VEL: for (int d = 0; d < D; ++d) r += pf_sq(in.dof[2 * d + 1]); break;
         case PF_REW_DOF_ACC:
-            for (int d = 0; d < D; ++d) r += pf_sq((B.last_dof_vel[e * D + d] - in.dof[2 * d + 1]) / dt);
+            for (int d = 0; d < D; ++d) r += pf_sq((ldv_[d] - in.dof[2 * d + 1]) / dt);
             break;
         case PF_REW_ACTION_RATE:
-            for (int d = 0; d < D; ++d) r += pf_sq(B.last_actions[e * D + d] - B.actions[e * D + d]);
+            for (int d = 0; d < D; ++d) r += pf_sq(la_[d] - ac_[d]);
             break;
         case PF_REW_COLLISION:
             for (int i = 0; i < P.num_penalised; ++i) {
@@ -269,7 +291,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
             break;
         case PF_REW_TORQUE_LIMITS:
             for (int d = 0; d < D; ++d)
-                r += pf_maxf(fabsf(B.torques[e * D + d]) - P.torque_limits[d] * P.soft_torque_limit, 0.0f);
+                r += pf_maxf(fabsf(tq_[d]) - P.torque_limits[d] * P.soft_torque_limit, 0.0f);
             break;
         case PF_REW_TRACKING_LIN_VEL: {
             const float err = pf_sq(out.commands[0] - lin_vel[0]) + pf_sq(out.commands[1] - lin_vel[1]);
@@ -328,7 +350,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
         }
         r = r * P.reward_scales[k];
         rew += r;
-        const float s = B.episode_sums[(size_t)k * N + e] + r;
+        const float s = es[k] + r;
         B.episode_sums[(size_t)k * N + e] = s;
         if (sums_out) sums_out[k] = s;
     }
@@ -337,7 +359,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
         const int k = P.num_reward_terms;
         const float r = ((reset && !time_out) ? 1.0f : 0.0f) * P.termination_scale;
         rew += r;
-        const float s = B.episode_sums[(size_t)k * N + e] + r;
+        const float s = es[k] + r;
         B.episode_sums[(size_t)k * N + e] = s;
         if (sums_out) sums_out[k] = s;
     }
