@@ -185,7 +185,9 @@ int pf_reset_all(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_co
  * reference's actual deployment (the fork runs PhysX on the CPU pipeline, PF:41,50: state tensors live in host
  * memory).  If `state` != NULL its non-NULL members (HOST, same AoS layouts as pf_env_buffers) are copied into the
  * device tensors first; then actions_host[N,D] -> H2D, decimation x pd_torques, post_physics_step,
- * obs / priv / rew / reset (+ torques if torques_host != NULL) -> D2H, stream sync. */
+ * obs / priv / rew / reset (+ torques if torques_host != NULL) -> D2H, stream sync.
+ * PINNED host buffers (cudaHostAlloc / torch pin_memory) are read and written by the device directly: one gather
+ * kernel in, one scatter kernel out; pageable buffers go through cudaMemcpyAsync. */
 typedef struct pf_host_state {
     const float* root_states;         /* [N,13] */
     const float* dof_state;           /* [N*D,2] */

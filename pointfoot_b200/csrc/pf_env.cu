@@ -569,6 +569,54 @@ extern "C" int pf_push_forces(pf_ctx* c, const pf_env_buffers* bufs, float* forc
     return 0;
 }
 
+// ---- pf_step_host data movement -----------------------------------------------------------------------------------
+// With PINNED (mapped) host buffers the device reads / writes them directly over the bus: ONE gather kernel pulls the
+// PhysX state + actions in, ONE scatter kernel pushes the results out, instead of a dozen cudaMemcpyAsync calls whose
+// fixed costs add up (measured at 4,096 envs: 113 us of copies in for 1 MB, 59 us out).  Pageable buffers fall
+// back to the copies.
+#define PF_IO_SEGS 8
+struct PfIoSeg { const void* src; void* dst; unsigned long long bytes; };
+struct PfIoArgs {
+    PfIoSeg seg[PF_IO_SEGS]; int nseg;
+    // feet rows of rigid_body_states: xyz of body feet_idx[f] of every env (the only columns the path reads)
+    const float* rbs_src; float* rbs_dst; int num_envs, num_bodies, feet_idx[PF_NUM_FEET];
+};
+
+__global__ void __launch_bounds__(256) pf_host_io_kernel(const PfIoArgs a) {
+    const int s = blockIdx.y;
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (unsigned long long)gridDim.x * blockDim.x;
+    if (s < a.nseg) {
+        const PfIoSeg g = a.seg[s];
+        if (((reinterpret_cast<uintptr_t>(g.src) | reinterpret_cast<uintptr_t>(g.dst)) & 15) == 0) {
+            const unsigned long long n16 = g.bytes >> 4;
+            const uint4* src = static_cast<const uint4*>(g.src);
+            uint4* dst = static_cast<uint4*>(g.dst);
+            for (unsigned long long i = tid; i < n16; i += nth) dst[i] = src[i];
+            const unsigned char* sb = static_cast<const unsigned char*>(g.src);
+            unsigned char* db = static_cast<unsigned char*>(g.dst);
+            for (unsigned long long i = (n16 << 4) + tid; i < g.bytes; i += nth) db[i] = sb[i];
+        } else {
+            const unsigned char* sb = static_cast<const unsigned char*>(g.src);
+            unsigned char* db = static_cast<unsigned char*>(g.dst);
+            for (unsigned long long i = tid; i < g.bytes; i += nth) db[i] = sb[i];
+        }
+    } else if (a.rbs_src) {
+        const unsigned long long n = (unsigned long long)a.num_envs * PF_NUM_FEET * 3;
+        for (unsigned long long i = tid; i < n; i += nth) {
+            const int e = (int)(i / (PF_NUM_FEET * 3)), r = (int)(i % (PF_NUM_FEET * 3)), f = r / 3, c = r % 3;
+            const size_t off = ((size_t)e * a.num_bodies + a.feet_idx[f]) * 13 + c;
+            a.rbs_dst[off] = a.rbs_src[off];
+        }
+    }
+}
+
+// device-visible alias of a pinned host pointer, or NULL if the memory is pageable
+static const void* pf_mapped(const void* host) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return (at.type == cudaMemoryTypeHost) ? at.devicePointer : nullptr;
+}
+
 static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
                              float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
                              float* torques_host, int64_t common_step_counter, void* stream, bool sync) {
@@ -578,37 +626,82 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = (size_t)P.num_envs;
     const cudaMemcpyKind H2D = cudaMemcpyHostToDevice, D2H = cudaMemcpyDeviceToHost;
-    cudaStream_t q[4] = {st, st, st, st};      // (fanning the copies out over side streams was measured: no gain)
-    if (hs) {
-        if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, q[1]));
-        if (hs->dof_state) PF_CUDA(cudaMemcpyAsync(bufs->dof_state, hs->dof_state, 4 * N * P.num_dof * 2, H2D, q[2]));
-        if (hs->contact_forces)
-            PF_CUDA(cudaMemcpyAsync((void*)bufs->contact_forces, hs->contact_forces, 4 * N * P.num_bodies * 3, H2D, q[3]));
-        if (hs->rigid_body_states) {
-            // the path reads only the feet positions (PF:1083-1086, 1114-1129): move those 12-byte columns with one
-            // pitched copy per foot instead of the whole [N*B,13] tensor (24 B instead of 468 B per env);
-            // PF_HOST_RBS=full switches back to the whole tensor
-            static const bool full = [] { const char* e = getenv("PF_HOST_RBS"); return e && e[0] == 'f' && e[1] == 'u'; }();
-            const size_t pitch = sizeof(float) * 13 * P.num_bodies;
-            if (full) PF_CUDA(cudaMemcpyAsync((void*)bufs->rigid_body_states, hs->rigid_body_states, N * pitch, H2D, q[0]));
-            else
-                for (int f = 0; f < PF_NUM_FEET; ++f) {
-                    const size_t off = (size_t)P.feet_indices[f] * 13;
-                    PF_CUDA(cudaMemcpy2DAsync((void*)(bufs->rigid_body_states + off), pitch, hs->rigid_body_states + off, pitch,
-                                              3 * sizeof(float), N, H2D, q[f & 1 ? 1 : 0]));
-                }
+    static const int dbg = [] { const char* e = getenv("PF_HOST_DEBUG"); return e ? atoi(e) : 0; }();   // experiments: 1 no copies in, 2 none out, 4 always cudaMemcpy
+    const size_t rbs_pitch = sizeof(float) * 13 * P.num_bodies;
+
+    // ---- in ----
+    PfIoArgs in = {};
+    bool mapped = !(dbg & 4);
+    auto add = [&](PfIoArgs& a, const void* src, void* dst, size_t bytes, bool src_is_host) {
+        if (!src || !dst) return;
+        const void* h = src_is_host ? src : dst;
+        const void* m = mapped ? pf_mapped(h) : nullptr;
+        if (!m) { mapped = false; return; }
+        PfIoSeg& g = a.seg[a.nseg++];
+        g.src = src_is_host ? m : src; g.dst = src_is_host ? dst : const_cast<void*>(m); g.bytes = bytes;
+    };
+    if (!(dbg & 1)) {
+        if (hs) {
+            add(in, hs->root_states, bufs->root_states, 4 * N * 13, true);
+            add(in, hs->dof_state, bufs->dof_state, 4 * N * P.num_dof * 2, true);
+            add(in, hs->contact_forces, (void*)bufs->contact_forces, 4 * N * P.num_bodies * 3, true);
+            if (hs->rigid_body_states) {
+                const void* m = mapped ? pf_mapped(hs->rigid_body_states) : nullptr;
+                if (m) {
+                    in.rbs_src = static_cast<const float*>(m); in.rbs_dst = const_cast<float*>(bufs->rigid_body_states);
+                    in.num_envs = P.num_envs; in.num_bodies = P.num_bodies;
+                    for (int f = 0; f < PF_NUM_FEET; ++f) in.feet_idx[f] = P.feet_indices[f];
+                } else mapped = false;
+            }
+        }
+        add(in, actions_host, c->d_actions_in, sizeof(float) * N * P.num_dof, true);
+        if (mapped) {
+            const unsigned gx = (unsigned)((N * 13 * 4 / 16 + 255) / 256 < 1 ? 1 : (N * 13 * 4 / 16 + 255) / 256);
+            pf_host_io_kernel<<<dim3(gx > 592 ? 592 : gx, in.nseg + (in.rbs_src ? 1 : 0)), 256, 0, st>>>(in);
+            PF_CUDA(cudaGetLastError());
+        } else {
+            if (hs) {
+                if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, st));
+                if (hs->dof_state) PF_CUDA(cudaMemcpyAsync(bufs->dof_state, hs->dof_state, 4 * N * P.num_dof * 2, H2D, st));
+                if (hs->contact_forces)
+                    PF_CUDA(cudaMemcpyAsync((void*)bufs->contact_forces, hs->contact_forces, 4 * N * P.num_bodies * 3, H2D, st));
+                if (hs->rigid_body_states)      // only the feet position columns (PF:1083-1086, 1114-1129): one pitched copy per foot
+                    for (int f = 0; f < PF_NUM_FEET; ++f) {
+                        const size_t off = (size_t)P.feet_indices[f] * 13;
+                        PF_CUDA(cudaMemcpy2DAsync((void*)(bufs->rigid_body_states + off), rbs_pitch, hs->rigid_body_states + off,
+                                                  rbs_pitch, 3 * sizeof(float), N, H2D, st));
+                    }
+            }
+            PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, H2D, st));
         }
     }
-    PF_CUDA(cudaMemcpyAsync(c->d_actions_in, actions_host, sizeof(float) * N * P.num_dof, H2D, q[2]));
     for (int i = 0; i < P.decimation; ++i)
         if (int rc = pf_pd_torques(c, bufs, i == 0 ? (const float*)c->d_actions_in : nullptr, stream)) return rc;
     if (int rc = pf_post_physics_step(c, bufs, common_step_counter, stream)) return rc;
-    PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, q[0]));
-    if (priv_obs_host && bufs->priv_obs_buf)
-        PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, q[1]));
-    PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, D2H, q[2]));
-    PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, D2H, q[3]));
-    if (torques_host) PF_CUDA(cudaMemcpyAsync(torques_host, bufs->torques, sizeof(float) * N * P.num_dof, D2H, q[2]));
+
+    // ---- out ----
+    if (!(dbg & 2)) {
+        PfIoArgs out = {};
+        mapped = !(dbg & 4);
+        add(out, bufs->obs_buf, obs_host, sizeof(float) * N * P.num_obs, false);
+        if (priv_obs_host && bufs->priv_obs_buf) add(out, bufs->priv_obs_buf, priv_obs_host, sizeof(float) * N * P.num_priv_obs, false);
+        add(out, bufs->rew_buf, rew_host, sizeof(float) * N, false);
+        add(out, bufs->reset_buf, reset_host, N, false);
+        if (torques_host) add(out, bufs->torques, torques_host, sizeof(float) * N * P.num_dof, false);
+        if (mapped) {
+            const size_t big = sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs) / 16;
+            const unsigned gx = (unsigned)((big + 255) / 256 < 1 ? 1 : (big + 255) / 256);
+            pf_host_io_kernel<<<dim3(gx > 592 ? 592 : gx, out.nseg), 256, 0, st>>>(out);
+            PF_CUDA(cudaGetLastError());
+        } else {
+            PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, st));
+            if (priv_obs_host && bufs->priv_obs_buf)
+                PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, st));
+            PF_CUDA(cudaMemcpyAsync(rew_host, bufs->rew_buf, sizeof(float) * N, D2H, st));
+            PF_CUDA(cudaMemcpyAsync(reset_host, bufs->reset_buf, N, D2H, st));
+            if (torques_host) PF_CUDA(cudaMemcpyAsync(torques_host, bufs->torques, sizeof(float) * N * P.num_dof, D2H, st));
+        }
+    }
     if (sync) PF_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

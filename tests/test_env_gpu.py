@@ -92,3 +92,37 @@ def test_sharded_equals_unsharded():
         assert torch.equal(got, e.t[name]), name
     for h in halves + [e]:
         h.close()
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_buffer_step_equals_device_step(pinned):
+    """pf_step_host (PhysX tensors in host memory, PF:41,50): pinned buffers go through the zero-copy gather / scatter
+    kernels, pageable ones through cudaMemcpy; both must reproduce the device-resident step bit for bit."""
+    import ctypes as C
+    from pointfoot_b200 import capi, synth
+    N = 1234
+    state = synth.make_state(N, "pointfoot_rough", seed=11)
+    dev = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=11)
+    host = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=11)
+    a = state["actions"].contiguous()
+    dev.step(a)
+    mk = (lambda t: t.contiguous().pin_memory()) if pinned else (lambda t: t.contiguous().clone())
+    hs_t = {k: mk(state[k]) for k in ("root_states", "dof_state", "contact_forces", "rigid_body_states")}
+    for k in hs_t:                       # the device copies must come from the host buffers: scramble them first
+        host.t[k].fill_(7.0) if k != "rigid_body_states" else None
+    hs = capi.PfHostState(**{k: v.data_ptr() for k, v in hs_t.items()})
+    P = host.P
+    act = mk(a)
+    obs, priv = mk(torch.zeros(N, P.num_obs)), mk(torch.zeros(N, P.num_priv_obs))
+    rew, rst, tq = mk(torch.zeros(N)), mk(torch.zeros(N, dtype=torch.uint8)), mk(torch.zeros(N, P.num_dof))
+    host.step_counter += 1
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check(host.lib.pf_step_host(host.ctx, C.byref(host.b), C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
+                                     C.c_void_p(priv.data_ptr()), C.c_void_p(rew.data_ptr()), C.c_void_p(rst.data_ptr()),
+                                     C.c_void_p(tq.data_ptr()), C.c_int64(host.step_counter), st), "pf_step_host")
+    assert torch.equal(obs, dev.t["obs_buf"].cpu()) and torch.equal(priv, dev.t["priv_obs_buf"].cpu())
+    assert torch.equal(rew, dev.t["rew_buf"].cpu()) and torch.equal(rst.bool(), dev.t["reset_buf"].cpu())
+    assert torch.equal(tq, dev.t["torques"].cpu())
+    for k in ("root_states", "dof_state", "episode_sums", "reset_ids"):
+        assert torch.equal(host.t[k], dev.t[k]), k
+    dev.close(); host.close()
