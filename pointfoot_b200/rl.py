@@ -214,6 +214,10 @@ class PPO:
             capi.check(self._lib.pf_rl_create(C.byref(P), C.byref(ctx)), "pf_rl_create")
         self._ctx = ctx
         ac.bind(self._lib, ctx)
+        d = shard.dist_or_none()
+        if d:                                      # every shard starts from rank 0's initial parameters
+            d.broadcast(ac.flat, 0)
+            ac.params_changed()
         crit = critic_obs_shape if critic_obs_shape[0] is not None else [None]
         self.storage = RolloutStorage(num_envs, num_transitions_per_env, actor_obs_shape, crit, action_shape, self.device)
         n, dev = ac.flat.numel(), self.device

@@ -1,7 +1,7 @@
 """How the path shards over GPUs: environments are independent, so rank r owns a contiguous range of GLOBAL env
 ids and every kernel is handed ``env_id_offset`` (the RNG contract of csrc/pf_rng.cuh keys on the global id, so the
-union of the shards is the same simulation as one big launch).  The only exchanges are the three PPO reductions
-below (BASELINE.json north_star: "NCCL ... only for the PPO gradient allreduce and the reward/episode statistics");
+union of the shards is the same simulation as one big launch).  The only exchanges are the PPO reductions
+below and the broadcast of rank 0's initial parameters (BASELINE.json north_star: "NCCL ... only for the PPO gradient allreduce and the reward/episode statistics");
 the env kernels need no collective.  Pure host logic: works on any torch.distributed backend (nccl on the GPUs,
 gloo in tests/test_shard_gloo.py)."""
 import torch
