@@ -303,13 +303,15 @@ def e2e_host(env, steps, warmup, barrier, policy=None, use_graph=True):
 
     def enqueue(sync):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        fn = lib.pf_step_host if sync else lib.pf_step_host_async
+        fn = lib.pf_step_host if sync else lib.pf_step_host_begin
         capi.check(fn(ctx, b, C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
                       C.c_void_p(priv.data_ptr()) if P.num_priv_obs else None, C.c_void_p(rew.data_ptr()),
                       C.c_void_p(rst.data_ptr()), C.c_void_p(tq.data_ptr()), C.c_int64(0), st), "pf_step_host")
         if policy is not None:      # same metric as `value`: the policy runs on the device observations and its actions
             policy.act_into(env, policy.actions)          # go back to the host for the next physics step
             act.copy_(policy.actions, non_blocking=True)
+        if not sync:                # the results' transfer ran beside the policy kernel; the stream waits for it here
+            capi.check(lib.pf_step_host_join(ctx, st), "pf_step_host_join")
 
     graph = None
     if policy is not None and use_graph:
@@ -426,7 +428,7 @@ def run_b200(args):
                            "parallelism": f"env-sharded x{world}, no data-path collective"},
                 "clocks": clocks, "gpu_launches": launches_per_step * args.steps, "roofline": roof,
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "api": ("one CUDA-graph launch per step of: " if (policy and not args.no_graph) else "") + "pf_step_host[_async] (C-ABI, pinned host buffers: PhysX state + actions in, obs/priv/rew/reset/torques out)" + (" + pf_rl_act on the device observations, sampled actions back to the host" if policy else ""),
+                        "api": ("one CUDA-graph launch per step of: " if (policy and not args.no_graph) else "") + "pf_step_host / pf_step_host_begin + _join (C-ABI, pinned host buffers: PhysX state + actions in, obs/priv/rew/reset/torques out)" + (" + pf_rl_act on the device observations, sampled actions back to the host" if policy else ""),
                         "steps": e2e_steps}}
         if not args.no_cpu_baseline and world == 1:
             v, n, cores, with_pol = cpu_env_steps_per_sec(args.task, env.num_envs)

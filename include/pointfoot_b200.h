@@ -204,6 +204,15 @@ int pf_step_host(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* s
 int pf_step_host_async(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* state, const float* actions_host,
                        float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
                        int64_t common_step_counter, void* stream);
+/* pf_step_host_async in two halves.  _begin enqueues the step but leaves the results' transfer to the (pinned) host
+ * buffers running on a context-owned stream, so that what the caller queues next on `stream` (pf_rl_act on the device
+ * observations) overlaps it; _join makes `stream` wait for that transfer.  _join must come before the host reads the
+ * outputs, before the next step and before a stream capture ends.  (Inside, the state tensors the torque law does
+ * not read cross the bus on the same side stream while the torque sub-steps run.) */
+int pf_step_host_begin(pf_ctx* ctx, const pf_env_buffers* bufs, const pf_host_state* state, const float* actions_host,
+                       float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host, float* torques_host,
+                       int64_t common_step_counter, void* stream);
+int pf_step_host_join(pf_ctx* ctx, void* stream);
 
 /* ================================================================================================
  * rsl_rl v1.0.2 side of the path (third-party dependency of the reference; call sites

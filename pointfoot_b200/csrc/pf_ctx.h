@@ -1,6 +1,7 @@
 // The opaque pf_ctx of include/pointfoot_b200.h: constants + small device scratch.  Internal header.
 #pragma once
 #include <stdint.h>
+#include <cuda_runtime.h>
 #include "../../include/pointfoot_b200.h"
 
 // Device scratch the step kernel hands to the finalize kernel (per-CTA partials).
@@ -24,4 +25,9 @@ struct pf_ctx {
     size_t smem_bytes;
     // pinned host staging for pf_step_host
     void* d_actions_in;    // [N,D] device copy of host actions
+    // pf_step_host with pinned buffers: the transfers the first torque kernel does not need, and the results' way
+    // out, run on io_stream beside the kernels (fork / join by events, so the pattern can be stream-captured)
+    cudaStream_t io_stream;
+    cudaEvent_t ev_fork, ev_in, ev_post, ev_out;
+    int out_pending;       // a scatter is in flight on io_stream: pf_step_host_join makes a stream wait for it
 };

@@ -490,6 +490,9 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     PF_CUDA(cudaMalloc(&c->S.blk_sums, sizeof(double) * PF_MAX_REWARD_TERMS * c->max_blocks));
     PF_CUDA(cudaMemset(c->S.blk_count, 0, sizeof(int) * c->max_blocks));
     PF_CUDA(cudaMalloc(&c->d_actions_in, sizeof(float) * (size_t)P.num_envs * P.num_dof));
+    PF_CUDA(cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
+    for (cudaEvent_t* e : {&c->ev_fork, &c->ev_in, &c->ev_post, &c->ev_out}) PF_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    c->out_pending = 0;
     *out = c;
     return 0;
 }
@@ -498,6 +501,8 @@ extern "C" int pf_ctx_destroy(pf_ctx* c) {
     if (!c) return 0;
     cudaFree((void*)c->S.noise_vec); cudaFree((void*)c->S.height_points);
     cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
+    if (c->io_stream) cudaStreamDestroy(c->io_stream);
+    for (cudaEvent_t e : {c->ev_fork, c->ev_in, c->ev_post, c->ev_out}) if (e) cudaEventDestroy(e);
     delete c;
     return 0;
 }
@@ -619,19 +624,23 @@ static const void* pf_mapped(const void* host) {
 
 static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
                              float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
-                             float* torques_host, int64_t common_step_counter, void* stream, bool sync) {
+                             float* torques_host, int64_t common_step_counter, void* stream, bool sync, bool join) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     if (!actions_host || !obs_host || !rew_host || !reset_host) return pf_fail(1, "%s", "pf_step_host: null host buffer");
     const pf_params& P = c->P;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t N = (size_t)P.num_envs;
     const cudaMemcpyKind H2D = cudaMemcpyHostToDevice, D2H = cudaMemcpyDeviceToHost;
-    static const int dbg = [] { const char* e = getenv("PF_HOST_DEBUG"); return e ? atoi(e) : 0; }();   // experiments: 1 no copies in, 2 none out, 4 always cudaMemcpy
+    static const int dbg = [] { const char* e = getenv("PF_HOST_DEBUG"); return e ? atoi(e) : 0; }();   // experiments: 1 no copies in, 2 none out, 4 always cudaMemcpy, 8 no side stream
     const size_t rbs_pitch = sizeof(float) * 13 * P.num_bodies;
+    const cudaStream_t io = (dbg & 8) ? st : c->io_stream;          // 8: no side stream (everything in order on `stream`)
 
     // ---- in ----
-    PfIoArgs in = {};
+    // `in` = what the first torque kernel reads (dof_state, actions); `in2` = the rest (root, contacts, feet rows), which
+    // only post_physics_step needs: on io_stream it crosses the bus while the torque sub-steps run.
+    PfIoArgs in = {}, in2 = {};
     bool mapped = !(dbg & 4);
+    bool forked = false;
     auto add = [&](PfIoArgs& a, const void* src, void* dst, size_t bytes, bool src_is_host) {
         if (!src || !dst) return;
         const void* h = src_is_host ? src : dst;
@@ -640,25 +649,36 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
         PfIoSeg& g = a.seg[a.nseg++];
         g.src = src_is_host ? m : src; g.dst = src_is_host ? dst : const_cast<void*>(m); g.bytes = bytes;
     };
+    auto io_grid = [&](size_t bytes, int ny) {
+        const size_t gx = (bytes / 16 + 255) / 256;
+        return dim3((unsigned)(gx < 1 ? 1 : gx > 592 ? 592 : gx), (unsigned)ny);
+    };
     if (!(dbg & 1)) {
         if (hs) {
-            add(in, hs->root_states, bufs->root_states, 4 * N * 13, true);
             add(in, hs->dof_state, bufs->dof_state, 4 * N * P.num_dof * 2, true);
-            add(in, hs->contact_forces, (void*)bufs->contact_forces, 4 * N * P.num_bodies * 3, true);
+            add(in2, hs->root_states, bufs->root_states, 4 * N * 13, true);
+            add(in2, hs->contact_forces, (void*)bufs->contact_forces, 4 * N * P.num_bodies * 3, true);
             if (hs->rigid_body_states) {
                 const void* m = mapped ? pf_mapped(hs->rigid_body_states) : nullptr;
                 if (m) {
-                    in.rbs_src = static_cast<const float*>(m); in.rbs_dst = const_cast<float*>(bufs->rigid_body_states);
-                    in.num_envs = P.num_envs; in.num_bodies = P.num_bodies;
-                    for (int f = 0; f < PF_NUM_FEET; ++f) in.feet_idx[f] = P.feet_indices[f];
+                    in2.rbs_src = static_cast<const float*>(m); in2.rbs_dst = const_cast<float*>(bufs->rigid_body_states);
+                    in2.num_envs = P.num_envs; in2.num_bodies = P.num_bodies;
+                    for (int f = 0; f < PF_NUM_FEET; ++f) in2.feet_idx[f] = P.feet_indices[f];
                 } else mapped = false;
             }
         }
         add(in, actions_host, c->d_actions_in, sizeof(float) * N * P.num_dof, true);
         if (mapped) {
-            const unsigned gx = (unsigned)((N * 13 * 4 / 16 + 255) / 256 < 1 ? 1 : (N * 13 * 4 / 16 + 255) / 256);
-            pf_host_io_kernel<<<dim3(gx > 592 ? 592 : gx, in.nseg + (in.rbs_src ? 1 : 0)), 256, 0, st>>>(in);
+            pf_host_io_kernel<<<io_grid(4 * N * P.num_dof * 2, in.nseg), 256, 0, st>>>(in);
             PF_CUDA(cudaGetLastError());
+            if (in2.nseg || in2.rbs_src) {           // forked behind the first gather: the bus is not shared with it
+                PF_CUDA(cudaEventRecord(c->ev_fork, st));
+                PF_CUDA(cudaStreamWaitEvent(io, c->ev_fork, 0));
+                pf_host_io_kernel<<<io_grid(4 * N * P.num_bodies * 3, in2.nseg + (in2.rbs_src ? 1 : 0)), 256, 0, io>>>(in2);
+                PF_CUDA(cudaGetLastError());
+                PF_CUDA(cudaEventRecord(c->ev_in, io));
+                forked = true;
+            }
         } else {
             if (hs) {
                 if (hs->root_states) PF_CUDA(cudaMemcpyAsync(bufs->root_states, hs->root_states, 4 * N * 13, H2D, st));
@@ -677,9 +697,10 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
     }
     for (int i = 0; i < P.decimation; ++i)
         if (int rc = pf_pd_torques(c, bufs, i == 0 ? (const float*)c->d_actions_in : nullptr, stream)) return rc;
+    if (forked) PF_CUDA(cudaStreamWaitEvent(st, c->ev_in, 0));
     if (int rc = pf_post_physics_step(c, bufs, common_step_counter, stream)) return rc;
 
-    // ---- out ----
+    // ---- out ----  (pinned: on io_stream, so that work the caller queues next -- the policy -- overlaps the transfer)
     if (!(dbg & 2)) {
         PfIoArgs out = {};
         mapped = !(dbg & 4);
@@ -689,10 +710,13 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
         add(out, bufs->reset_buf, reset_host, N, false);
         if (torques_host) add(out, bufs->torques, torques_host, sizeof(float) * N * P.num_dof, false);
         if (mapped) {
-            const size_t big = sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs) / 16;
-            const unsigned gx = (unsigned)((big + 255) / 256 < 1 ? 1 : (big + 255) / 256);
-            pf_host_io_kernel<<<dim3(gx > 592 ? 592 : gx, out.nseg), 256, 0, st>>>(out);
+            PF_CUDA(cudaEventRecord(c->ev_post, st));
+            PF_CUDA(cudaStreamWaitEvent(io, c->ev_post, 0));
+            pf_host_io_kernel<<<io_grid(sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs), out.nseg), 256, 0, io>>>(out);
             PF_CUDA(cudaGetLastError());
+            PF_CUDA(cudaEventRecord(c->ev_out, io));
+            c->out_pending = 1;
+            if (join) { PF_CUDA(cudaStreamWaitEvent(st, c->ev_out, 0)); c->out_pending = 0; }
         } else {
             PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, st));
             if (priv_obs_host && bufs->priv_obs_buf)
@@ -710,12 +734,32 @@ extern "C" int pf_step_host(pf_ctx* c, const pf_env_buffers* bufs, const pf_host
                             float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
                             float* torques_host, int64_t common_step_counter, void* stream) {
     return pf_step_host_impl(c, bufs, hs, actions_host, obs_host, priv_obs_host, rew_host, reset_host, torques_host,
-                             common_step_counter, stream, true);
+                             common_step_counter, stream, true, true);
 }
 
 extern "C" int pf_step_host_async(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
                                   float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
                                   float* torques_host, int64_t common_step_counter, void* stream) {
     return pf_step_host_impl(c, bufs, hs, actions_host, obs_host, priv_obs_host, rew_host, reset_host, torques_host,
-                             common_step_counter, stream, false);
+                             common_step_counter, stream, false, true);
+}
+
+// pf_step_host_async without the final join: the results' transfer to the pinned host buffers is left running on a
+// context-owned stream, so that what the caller queues next on `stream` (the policy's act kernel on the device
+// observations) overlaps it.  pf_step_host_join(ctx, stream) makes `stream` wait for that transfer; it must be called
+// before the host reads the outputs, before the next step, and before a stream capture ends.
+extern "C" int pf_step_host_begin(pf_ctx* c, const pf_env_buffers* bufs, const pf_host_state* hs, const float* actions_host,
+                                  float* obs_host, float* priv_obs_host, float* rew_host, uint8_t* reset_host,
+                                  float* torques_host, int64_t common_step_counter, void* stream) {
+    return pf_step_host_impl(c, bufs, hs, actions_host, obs_host, priv_obs_host, rew_host, reset_host, torques_host,
+                             common_step_counter, stream, false, false);
+}
+
+extern "C" int pf_step_host_join(pf_ctx* c, void* stream) {
+    if (!c) return pf_fail(1, "%s", "pf_step_host_join: null context");
+    if (c->out_pending) {
+        PF_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->ev_out, 0));
+        c->out_pending = 0;
+    }
+    return 0;
 }

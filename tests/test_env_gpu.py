@@ -94,10 +94,11 @@ def test_sharded_equals_unsharded():
         h.close()
 
 
-@pytest.mark.parametrize("pinned", [True, False])
-def test_host_buffer_step_equals_device_step(pinned):
+@pytest.mark.parametrize("pinned,split", [(True, False), (False, False), (True, True)])
+def test_host_buffer_step_equals_device_step(pinned, split):
     """pf_step_host (PhysX tensors in host memory, PF:41,50): pinned buffers go through the zero-copy gather / scatter
-    kernels, pageable ones through cudaMemcpy; both must reproduce the device-resident step bit for bit."""
+    kernels, pageable ones through cudaMemcpy; both must reproduce the device-resident step bit for bit.  ``split``:
+    the pf_step_host_begin / pf_step_host_join pair (results' transfer on the context's side stream), two steps."""
     import ctypes as C
     from pointfoot_b200 import capi, synth
     N = 1234
@@ -117,7 +118,19 @@ def test_host_buffer_step_equals_device_step(pinned):
     rew, rst, tq = mk(torch.zeros(N)), mk(torch.zeros(N, dtype=torch.uint8)), mk(torch.zeros(N, P.num_dof))
     host.step_counter += 1
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    capi.check(host.lib.pf_step_host(host.ctx, C.byref(host.b), C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
+    if split:
+        for k in hs_t:                   # second device step from the same synthetic PhysX tensors the host side re-sends
+            dev.t[k].copy_(state[k])
+        dev.step(a)
+        for it in range(2):
+            capi.check(host.lib.pf_step_host_begin(host.ctx, C.byref(host.b), C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
+                                                   C.c_void_p(priv.data_ptr()), C.c_void_p(rew.data_ptr()), C.c_void_p(rst.data_ptr()),
+                                                   C.c_void_p(tq.data_ptr()), C.c_int64(host.step_counter + it), st), "pf_step_host_begin")
+            capi.check(host.lib.pf_step_host_join(host.ctx, st), "pf_step_host_join")
+        host.step_counter += 1
+        torch.cuda.synchronize()
+    else:
+      capi.check(host.lib.pf_step_host(host.ctx, C.byref(host.b), C.byref(hs), C.c_void_p(act.data_ptr()), C.c_void_p(obs.data_ptr()),
                                      C.c_void_p(priv.data_ptr()), C.c_void_p(rew.data_ptr()), C.c_void_p(rst.data_ptr()),
                                      C.c_void_p(tq.data_ptr()), C.c_int64(host.step_counter), st), "pf_step_host")
     assert torch.equal(obs, dev.t["obs_buf"].cpu()) and torch.equal(priv, dev.t["priv_obs_buf"].cpu())
