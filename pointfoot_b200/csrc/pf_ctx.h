@@ -3,6 +3,7 @@
 #include <stdint.h>
 #include <cuda_runtime.h>
 #include "../../include/pointfoot_b200.h"
+#include "pf_env_core.cuh"
 
 // Device scratch the step kernel hands to the finalize kernel (per-CTA partials).
 struct PfCtxScratch {
@@ -11,6 +12,7 @@ struct PfCtxScratch {
     double* blk_sums;      // [num_slabs][PF_MAX_REWARD_TERMS] episode sums of the slab's reset envs (valid iff count > 0)
     const float* noise_vec;       // [max(num_obs, num_priv_obs)]
     const float* height_points;   // [P][2]
+    PfRewTab rew;                 // reward terms by id (row, scale): constant-bank operands of the step kernel
 };
 
 struct pf_ctx {
@@ -20,6 +22,8 @@ struct pf_ctx {
     int num_sms;
     int envs_per_warp;     // envs owned by one warp of the step kernel (8, 16 or 32)
     int num_slabs;         // ceil(num_envs / envs_per_warp)
+    int threads;           // CTA size of the step kernel (32..256: small batches use small CTAs)
+    int canonical;         // num_dof == 6 and reward terms in the reference's dir() order: specialised straight-line reward sum
     int num_blocks;        // CTAs of the step kernel
     int max_blocks;
     size_t smem_bytes;

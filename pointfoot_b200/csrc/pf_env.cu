@@ -11,6 +11,7 @@
 #include <stdio.h>
 #include "pf_env_core.cuh"
 #include "pf_ctx.h"
+#include "pf_tc_ptx.cuh"      // mbarrier + bulk-copy wrappers
 
 #define PF_THREADS 256
 
@@ -45,6 +46,7 @@ struct PfWarpSmem {
     float* dof;       // [epw][2D]
     float* cf;        // [epw][cfw]  contact forces; reused for the observation columns before noise
     float* misc;      // [epw][4]    yaw quaternion (z, w), post-reset root z, noise key (bits)
+    float* bar;       // 8-byte mbarrier of the warp's bulk copies (16 bytes reserved)
 };
 
 __host__ __device__ inline int pf_cf_width(const pf_params& P) {
@@ -53,7 +55,7 @@ __host__ __device__ inline int pf_cf_width(const pf_params& P) {
 }
 __host__ __device__ inline int pf_warp_smem_floats(const pf_params& P, int epw) {
     const int n = epw * (13 + 2 * P.num_dof + pf_cf_width(P) + 4);
-    return (n + 3) & ~3;                                  // keep every warp slab 16-byte aligned
+    return ((n + 3) & ~3) + 4;                            // + the mbarrier; every warp slab stays 16-byte aligned
 }
 
 __device__ __forceinline__ PfWarpSmem pf_carve_warp(const pf_params& P, int epw, float* f) {
@@ -61,7 +63,8 @@ __device__ __forceinline__ PfWarpSmem pf_carve_warp(const pf_params& P, int epw,
     s.root = f; f += epw * 13;
     s.dof = f; f += epw * 2 * P.num_dof;
     s.cf = f; f += epw * pf_cf_width(P);
-    s.misc = f;
+    s.misc = f; f += epw * 4;
+    s.bar = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(f) + 15) & ~(uintptr_t)15);
     return s;
 }
 
@@ -149,31 +152,54 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //   phase 3  the 27 leading observation columns, flattened over the warp's envs -> coalesced row writes
 //   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
-__global__ void __launch_bounds__(PF_THREADS, 3) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
+template <bool kFast>
+__global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
                                                                         const uint32_t step_arg) {
     extern __shared__ __align__(16) float smem_f[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int slab = blockIdx.x * (PF_THREADS / 32) + warp;
+    const int slab = blockIdx.x * (blockDim.x >> 5) + warp;
     const int e0 = slab * epw;
     if (e0 >= P.num_envs) return;
     const PfWarpSmem s = pf_carve_warp(P, epw, smem_f + (size_t)warp * pf_warp_smem_floats(P, epw));
     const int nenv = min(epw, P.num_envs - e0);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
-    const int D = P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
+    constexpr int kD = kFast ? PF_MAX_DOF : 0;
+    const int D = kFast ? PF_MAX_DOF : P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
-    const int base_w = pf_obs_base_width(P), cfw = pf_cf_width(P);
+    const int base_w = 6 + 3 * D + 3, cfw = pf_cf_width(P);
     const bool active = lane < nenv;
     const int e = e0 + lane;
 
     // ---- phase 0: AoS rows -> shared memory ----
-    pf_warp_copy(s.root, B.root_states + (size_t)e0 * 13, nenv * 13, lane);
-    pf_warp_copy(s.dof, B.dof_state + (size_t)e0 * 2 * D, nenv * 2 * D, lane);
-    if (cfw == 3 * NB) {
-        pf_warp_copy(s.cf, B.contact_forces + (size_t)e0 * 3 * NB, nenv * 3 * NB, lane);
+    // Full, 16-byte aligned slabs: one lane hands the three row blocks to the TMA engine (cp.async.bulk completing
+    // on the warp's own mbarrier), so the staging costs a dozen instructions instead of three copy loops.
+    const float* g_root = B.root_states + (size_t)e0 * 13;
+    const float* g_dof = B.dof_state + (size_t)e0 * 2 * D;
+    const float* g_cf = B.contact_forces + (size_t)e0 * 3 * NB;
+    const bool bulk = kFast && nenv == epw && (epw & 3) == 0 && cfw == 3 * NB &&
+                      ((reinterpret_cast<uintptr_t>(g_root) | reinterpret_cast<uintptr_t>(g_dof) |
+                        reinterpret_cast<uintptr_t>(g_cf)) & 15) == 0;
+    if (bulk) {
+        const uint32_t bar = smem_u32(s.bar);
+        if (lane == 0) {
+            mbar_init(bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            fence_async_smem();
+            const uint32_t b_root = epw * 13 * 4, b_dof = epw * 2 * D * 4, b_cf = epw * 3 * NB * 4;
+            mbar_expect_tx(bar, b_root + b_dof + b_cf);
+            bulk_g2s(smem_u32(s.root), g_root, b_root, bar);
+            bulk_g2s(smem_u32(s.dof), g_dof, b_dof, bar);
+            bulk_g2s(smem_u32(s.cf), g_cf, b_cf, bar);
+        }
     } else {
-        const float* g = B.contact_forces + (size_t)e0 * 3 * NB;
-        for (int i = lane; i < nenv * 3 * NB; i += 32) s.cf[(i / (3 * NB)) * cfw + (i % (3 * NB))] = __ldg(g + i);
+        pf_warp_copy(s.root, g_root, nenv * 13, lane);
+        pf_warp_copy(s.dof, g_dof, nenv * 2 * D, lane);
+        if (cfw == 3 * NB) {
+            pf_warp_copy(s.cf, g_cf, nenv * 3 * NB, lane);
+        } else {
+            for (int i = lane; i < nenv * 3 * NB; i += 32) s.cf[(i / (3 * NB)) * cfw + (i % (3 * NB))] = __ldg(g_cf + i);
+        }
     }
     float feet[6];
     if (active) {
@@ -184,6 +210,7 @@ __global__ void __launch_bounds__(PF_THREADS, 3) pf_post_physics_kernel(const pf
     }
     const uint32_t nkey = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
     __syncwarp();
+    if (bulk) mbar_wait(smem_u32(s.bar), 0);
 
     // ---- phase 1: height scan ----
     float height_mean = 0.0f;
@@ -225,26 +252,26 @@ __global__ void __launch_bounds__(PF_THREADS, 3) pf_post_physics_kernel(const pf
         in.feet_pos[1] = feet + 3;
         in.have_heights = Pn > 0;
         in.height_mean = height_mean;
-        pf_env_step(P, B, e, in, step, nullptr, out);
+        pf_env_step_t<kFast>(P, B, S.rew, e, in, step, nullptr, out);
         is_reset = out.reset;
     }
     pf_warp_partials(P, B, S, slab, e, active, is_reset, R, lane);
     long long lvl = 0;
     if (active) {
-        if (is_reset) pf_env_reset(P, B, e, s.root + lane * 13, out.commands, step, true, nullptr, out);
+        if (is_reset) pf_env_reset_t<kD>(P, B, e, s.root + lane * 13, out.commands, step, true, nullptr, out);
         if (B.terrain_levels) lvl = B.terrain_levels[e];
-        const float* act = B.actions + (size_t)e * D;
-        float* base = s.cf + lane * cfw;           // own row: the contact forces are no longer needed
-        for (int j = 0; j < base_w; ++j) base[j] = pf_obs_base_col(P, out, act, j);
+        pf_obs_base_row<kD>(P, out, s.cf + lane * cfw);    // own row: the contact forces are no longer needed
         s.misc[4 * lane + 2] = out.root_z;
         s.misc[4 * lane + 3] = __uint_as_float(nkey);
         // PF:225-227
-        for (int d = 0; d < D; ++d) {
-            B.last_actions[(size_t)e * D + d] = act[d];
-            B.last_dof_vel[(size_t)e * D + d] = out.dof_vel[d];
-        }
-        const float* rv = is_reset ? B.root_states + (size_t)e * 13 + 7 : s.root + lane * 13 + 7;
-        for (int i = 0; i < 6; ++i) B.last_root_vel[(size_t)e * 6 + i] = rv[i];
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) {
+                B.last_actions[(size_t)e * D + d] = out.actions[d];
+                B.last_dof_vel[(size_t)e * D + d] = out.dof_vel[d];
+            }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) B.last_root_vel[(size_t)e * 6 + i] = out.root_vel[i];
     }
     {
         const unsigned lv = __reduce_add_sync(0xffffffffu, (unsigned)lvl);   // levels are small and >= 0: exact
@@ -284,7 +311,7 @@ __global__ void __launch_bounds__(PF_THREADS) pf_reset_all_kernel(const pf_param
                                                                   const PfCtxScratch S, const int epw,
                                                                   const uint32_t step_arg) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int slab = blockIdx.x * (PF_THREADS / 32) + warp;
+    const int slab = blockIdx.x * (blockDim.x >> 5) + warp;
     const int e0 = slab * epw;
     if (e0 >= P.num_envs) return;
     const int nenv = min(epw, P.num_envs - e0);
@@ -467,11 +494,17 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     PF_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device));
     c->envs_per_warp = pf_pick_epw(P.num_envs, c->num_sms);
     c->num_slabs = (P.num_envs + c->envs_per_warp - 1) / c->envs_per_warp;
-    c->num_blocks = (c->num_slabs + PF_THREADS / 32 - 1) / (PF_THREADS / 32);
+    // CTA size of the step kernel: warps are independent, so a small batch is cut into small CTAs that reach every SM
+    c->threads = PF_THREADS;
+    while (c->threads > 32 && (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32) < 2 * c->num_sms) c->threads >>= 1;
+    if (const char* e = getenv("PF_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128 || v == 256) c->threads = v; }
+    c->num_blocks = (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32);
     c->max_blocks = c->num_slabs;
-    c->smem_bytes = (size_t)(PF_THREADS / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
+    c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
+    c->canonical = pf_build_reward_table(P, c->S.rew) && P.num_dof == PF_MAX_DOF && !getenv("PF_GENERIC_REWARDS");
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -545,8 +578,12 @@ static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_
 extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    pf_post_physics_kernel<<<c->num_blocks, PF_THREADS, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
-                                                                             (uint32_t)common_step_counter);
+    if (c->canonical)
+        pf_post_physics_kernel<true><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
+                                                                                       (uint32_t)common_step_counter);
+    else
+        pf_post_physics_kernel<false><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
+                                                                                        (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 1);
 }
@@ -555,7 +592,7 @@ extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t commo
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     PF_CUDA(cudaMemsetAsync(bufs->reset_buf, 1, (size_t)c->P.num_envs, st));
-    pf_reset_all_kernel<<<c->num_blocks, PF_THREADS, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
+    pf_reset_all_kernel<<<c->num_blocks, c->threads, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
                                                                           (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 0);

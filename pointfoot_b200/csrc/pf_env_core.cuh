@@ -29,6 +29,14 @@ PF_HD float pf_sq(float x) { return x * x; }
 PF_HD float pf_norm2(float x, float y) { return sqrtf(fmaf(y, y, x * x)); }
 PF_HD float pf_norm3(float x, float y, float z) { return sqrtf(fmaf(z, z, fmaf(y, y, x * x))); }
 
+PF_HD float pf_sumsq3(float x, float y, float z) { return fmaf(z, z, fmaf(y, y, x * x)); }   // pf_norm3 before the root
+// x / d for a fixed divisor, r = RN(1/d): quotient estimate + one exact-remainder correction (Markstein), the
+// correctly rounded quotient without the division sequence
+PF_HD float pf_div_by(float x, float d, float r) {
+    const float q = x * r;
+    return fmaf(fmaf(-q, d, x), r, q);
+}
+
 // torch.cross, ATen CPU: out[i] = fma(a[i+1], b[i+2], -(a[i+2]*b[i+1]))
 PF_HD void pf_cross(const float a[3], const float b[3], float o[3]) {
     o[0] = fmaf(a[1], b[2], -(a[2] * b[1]));
@@ -133,31 +141,240 @@ struct PfEnvIn {
 struct PfEnvOut {
     float ang_vel[3], gravity[3];     // pre-reset (PF:210-211)
     float dof_pos[PF_MAX_DOF], dof_vel[PF_MAX_DOF];   // post-reset
+    float actions[PF_MAX_DOF];        // this step's clipped actions (PF:177)
     float root_z;                     // post-reset
+    float root_vel[6];                // post-reset root lin / ang velocity (PF:227)
     float commands[4];                // after the heading update
     bool reset;
 };
 
+// The reward names in dir() (= alphabetical) order: the order class_to_dict hands them to
+// _prepare_reward_function (PF:796-820), hence the summation order of compute_reward (PF:307-311).
+#define PF_REWARD_CANON(X)                                                                                   \
+    X(PF_REW_ACTION_RATE) X(PF_REW_ANG_VEL_XY) X(PF_REW_BASE_HEIGHT) X(PF_REW_COLLISION) X(PF_REW_DOF_ACC)    \
+    X(PF_REW_DOF_POS_LIMITS) X(PF_REW_DOF_VEL) X(PF_REW_DOF_VEL_LIMITS) X(PF_REW_FEET_AIR_TIME)              \
+    X(PF_REW_FEET_CONTACT_FORCES) X(PF_REW_FEET_DISTANCE) X(PF_REW_LIN_VEL_Z) X(PF_REW_NO_FLY)               \
+    X(PF_REW_ORIENTATION) X(PF_REW_STAND_STILL) X(PF_REW_STUMBLE) X(PF_REW_SURVIVAL) X(PF_REW_TERMINATION)   \
+    X(PF_REW_TORQUE_LIMITS) X(PF_REW_TORQUES) X(PF_REW_TRACKING_ANG_VEL) X(PF_REW_TRACKING_LIN_VEL)          \
+    X(PF_REW_UNBALANCE_FEET_AIR_TIME) X(PF_REW_UNBALANCE_FEET_HEIGHT)
+
+// Reward terms by id: row of episode_sums (-1 = term not enabled) and scale.  Built once on the host; handed to the
+// step as a kernel parameter, so that every lookup below is a constant-bank operand at a compile-time offset.
+struct PfRewTab {
+    int32_t row[PF_REW_COUNT];
+    int32_t off[PF_REW_COUNT];        // row * num_envs: element offset of the term's episode_sums row
+    float scale[PF_REW_COUNT];
+    // sqrtf(x) > c  <=>  x >= sq_gt(c) for the two contact thresholds (PF:241: 1.0, PF:1167: 0.1): the squared
+    // norms are compared directly, no square root on the way to a bool
+    float sq_gt_termination, sq_gt_collision;
+    float rdt;                        // RN(1 / dt)
+};
+
+// smallest float t with sqrtf(t) > c (sqrtf is correctly rounded and monotone on both sides of the bus)
+static inline float pf_sq_gt(float c) {
+    float t = (float)((double)c * (double)c);
+    while (sqrtf(t) > c) t = nextafterf(t, 0.0f);
+    while (!(sqrtf(t) > c)) t = nextafterf(t, INFINITY);
+    return t;
+}
+
+// True when P.reward_ids is a subsequence of the canonical order (what the reference's cfg always yields): the
+// step then runs the straight-line statement of the reward sum, every term's code specialised at compile time.
+static inline bool pf_rewards_canonical(const pf_params& P) {
+    static const int canon[] = {
+#define PF_X(id) id,
+        PF_REWARD_CANON(PF_X)
+#undef PF_X
+    };
+    int pos = 0;
+    for (int k = 0; k < P.num_reward_terms; ++k) {
+        while (pos < PF_REW_COUNT && canon[pos] != P.reward_ids[k]) ++pos;
+        if (pos == PF_REW_COUNT) return false;
+        ++pos;
+    }
+    return true;
+}
+
+static inline bool pf_build_reward_table(const pf_params& P, PfRewTab& T) {
+    for (int i = 0; i < PF_REW_COUNT; ++i) { T.row[i] = -1; T.off[i] = 0; T.scale[i] = 0.0f; }
+    T.sq_gt_termination = pf_sq_gt(1.0f);
+    T.sq_gt_collision = pf_sq_gt(0.1f);
+    T.rdt = 1.0f / P.dt;
+    if ((long long)P.num_envs * (PF_MAX_REWARD_TERMS + 1) > 0x7fffffffLL) return false;
+    for (int k = 0; k < P.num_reward_terms; ++k) {
+        const int id = P.reward_ids[k];
+        if (id < 0 || id >= PF_REW_COUNT || T.row[id] >= 0) return false;      // unknown or repeated term: generic loop
+        T.row[id] = k; T.off[id] = k * P.num_envs; T.scale[id] = P.reward_scales[k];
+    }
+    return pf_rewards_canonical(P);
+}
+
+// What the _reward_* terms read.  Pointers to the caller's local arrays: every index below is a compile-time
+// constant once the guarded loops are unrolled, so the arrays stay in registers.
+struct PfRewIn {
+    const float *lin_vel, *ang_vel, *gravity, *commands;
+    const float *tq, *ldv, *la, *ac;      // torques, last_dof_vel, last_actions, actions   [D]
+    const float *dof, *cf;                // staged rows: (pos, vel) pairs; contact forces
+    const float *fat, *lfat, *lmfh;       // feet_air_time, last_feet_air_time, last_max_feet_height   [F]
+    const bool* first_contact;
+    const float *feet0, *feet1;
+    float bh;                             // base height (PF:1144-1147)
+    bool reset, time_out;
+};
+
+// One _reward_* term, unscaled (PF:1132-1253).
+template <int kD>
+PF_HD float pf_reward_term(const pf_params& P, const PfRewTab& T, const int id, const PfRewIn& c) {
+    const int D = kD ? kD : P.num_dof;
+    const float dt = P.dt;
+    float r = 0.0f;
+    switch (id) {
+    case PF_REW_LIN_VEL_Z: r = pf_sq(c.lin_vel[2]); break;
+    case PF_REW_ANG_VEL_XY: r = pf_sq(c.ang_vel[0]) + pf_sq(c.ang_vel[1]); break;
+    case PF_REW_ORIENTATION: r = pf_sq(c.gravity[0]) + pf_sq(c.gravity[1]); break;
+    case PF_REW_BASE_HEIGHT: r = pf_sq(c.bh - P.base_height_target); break;
+    case PF_REW_TORQUES:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d) if (d < D) r += pf_sq(c.tq[d]);
+        break;
+    case PF_REW_DOF_VEL:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d) if (d < D) r += pf_sq(c.dof[2 * d + 1]);
+        break;
+    case PF_REW_DOF_ACC:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) r += pf_sq(kD ? pf_div_by(c.ldv[d] - c.dof[2 * d + 1], dt, T.rdt) : (c.ldv[d] - c.dof[2 * d + 1]) / dt);
+        break;
+    case PF_REW_ACTION_RATE:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d) if (d < D) r += pf_sq(c.la[d] - c.ac[d]);
+        break;
+    case PF_REW_COLLISION:
+#pragma unroll
+        for (int i = 0; i < PF_MAX_BODIES; ++i)
+            if (i < P.num_penalised) {
+                const float* F = c.cf + P.penalised_indices[i] * 3;
+                const bool hit = kD ? pf_sumsq3(F[0], F[1], F[2]) >= T.sq_gt_collision : pf_norm3(F[0], F[1], F[2]) > 0.1f;
+                r += hit ? 1.0f : 0.0f;
+            }
+        break;
+    case PF_REW_TERMINATION: r = (c.reset && !c.time_out) ? 1.0f : 0.0f; break;
+    case PF_REW_DOF_POS_LIMITS:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) {
+                const float qd = c.dof[2 * d];
+                r += -pf_minf(qd - P.dof_pos_limits[d][0], 0.0f) + pf_maxf(qd - P.dof_pos_limits[d][1], 0.0f);
+            }
+        break;
+    case PF_REW_DOF_VEL_LIMITS:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) r += pf_clipf(fabsf(c.dof[2 * d + 1]) - P.dof_vel_limits[d] * P.soft_dof_vel_limit, 0.0f, 1.0f);
+        break;
+    case PF_REW_TORQUE_LIMITS:
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) r += pf_maxf(fabsf(c.tq[d]) - P.torque_limits[d] * P.soft_torque_limit, 0.0f);
+        break;
+    case PF_REW_TRACKING_LIN_VEL: {
+        const float err = pf_sq(c.commands[0] - c.lin_vel[0]) + pf_sq(c.commands[1] - c.lin_vel[1]);
+        r = expf(-err / P.tracking_sigma);
+    } break;
+    case PF_REW_TRACKING_ANG_VEL:
+        r = expf(-pf_sq(c.commands[2] - c.ang_vel[2]) / P.tracking_sigma);
+        break;
+    case PF_REW_FEET_AIR_TIME: {
+        float lo = 0.0f, hi = 0.0f;
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const float m = c.first_contact[f] ? 1.0f : 0.0f;
+            lo += pf_minf(c.fat[f] - P.min_feet_air_time, 0.0f) * m;
+            hi += pf_minf(P.max_feet_air_time - c.fat[f], 0.0f) * m;
+        }
+        r = lo + hi;
+    } break;
+    case PF_REW_NO_FLY: {
+        int n = 0;
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) n += c.cf[P.feet_indices[f] * 3 + 2] > 0.1f;
+        r = n == 1 ? 1.0f : 0.0f;
+    } break;
+    case PF_REW_UNBALANCE_FEET_AIR_TIME: {     // torch.var over 2 values, unbiased
+        const float m = (c.lfat[0] + c.lfat[1]) / 2.0f;
+        r = pf_sq(c.lfat[0] - m) + pf_sq(c.lfat[1] - m);
+    } break;
+    case PF_REW_UNBALANCE_FEET_HEIGHT: {
+        const float m = (c.lmfh[0] + c.lmfh[1]) / 2.0f;
+        r = pf_sq(c.lmfh[0] - m) + pf_sq(c.lmfh[1] - m);
+    } break;
+    case PF_REW_STUMBLE: {
+        bool any = false;
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const float* F = c.cf + P.feet_indices[f] * 3;
+            any = any || (pf_norm2(F[0], F[1]) > 5.0f * fabsf(F[2]));
+        }
+        r = any ? 1.0f : 0.0f;
+    } break;
+    case PF_REW_STAND_STILL:                   // signed comparison, PF:1233-1234
+        r = (fabsf(c.lin_vel[0]) * (c.commands[0] < 0.1f ? 1.0f : 0.0f)
+             + fabsf(c.lin_vel[1]) * (c.commands[1] < 0.1f ? 1.0f : 0.0f))
+            + fabsf(c.ang_vel[2]) * (c.commands[2] < 0.1f ? 1.0f : 0.0f);
+        break;
+    case PF_REW_FEET_CONTACT_FORCES:
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const float* F = c.cf + P.feet_indices[f] * 3;
+            r += pf_maxf(pf_norm3(F[0], F[1], F[2]) - P.max_contact_force, 0.0f);
+        }
+        break;
+    case PF_REW_FEET_DISTANCE: {
+        const float d = pf_norm2(c.feet0[0] - c.feet1[0], c.feet0[1] - c.feet1[1]);
+        r = pf_clipf(P.min_feet_distance - d, 0.0f, 1.0f);
+    } break;
+    case PF_REW_SURVIVAL: r = (c.reset ? 0.0f : 1.0f) * dt; break;
+    default: break;
+    }
+    return r;
+}
+
 // post_physics_step up to (and including) reset_idx: PF:204-222.  `e` = local env index, writes go to B.
-PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const PfEnvIn& in,
-                       uint32_t step, float* sums_out /* [R] scaled reward terms of this step or NULL */,
-                       PfEnvOut& out) {
-    const int D = P.num_dof;
+// kFast: the common shape -- P.num_dof == PF_MAX_DOF and P.reward_ids in canonical order (pf_build_reward_table
+// returned true for T) -> straight-line reward sum, no guards.  Otherwise: guarded loops, order-agnostic reward loop.
+template <bool kFast>
+PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
+                         uint32_t step, float* sums_out /* [R] scaled reward terms of this step or NULL */,
+                         PfEnvOut& out) {
+    constexpr bool kCanon = kFast;
+    constexpr int kD = kFast ? PF_MAX_DOF : 0;
+    const int D = kFast ? PF_MAX_DOF : P.num_dof;
     const float dt = P.dt;
     const int N = P.num_envs;
     // Everything the step reads from env-owned global buffers, loaded up front: the loads are independent of each
     // other, so they are all in flight together.  Left where they are used, each one sits behind an earlier store
     // the compiler must assume aliases it, and the step pays ~60 memory latencies one after another.
-    const int R_all = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
-    float es[PF_MAX_REWARD_TERMS + 1];
-    for (int k = 0; k < R_all; ++k) es[k] = B.episode_sums[(size_t)k * N + e];
-    float tq_[PF_MAX_DOF], ldv_[PF_MAX_DOF], la_[PF_MAX_DOF], ac_[PF_MAX_DOF];
-    for (int d = 0; d < D; ++d) {
-        tq_[d] = B.torques[e * D + d]; ldv_[d] = B.last_dof_vel[e * D + d];
-        la_[d] = B.last_actions[e * D + d]; ac_[d] = B.actions[e * D + d];
+    // Loops run to the compile-time maxima under a guard so that every array below lives in registers.
+    const int R_terms = P.num_reward_terms;
+    float es[PF_REW_COUNT];                       // indexed by term id (a compile-time constant where it is used)
+    if (kCanon) {
+        const float* es_in = B.episode_sums + e;
+#define PF_X(ID) es[ID] = T.row[ID] >= 0 ? es_in[T.off[ID]] : 0.0f;
+        PF_REWARD_CANON(PF_X)
+#undef PF_X
+    }
+    const float es_term = P.has_termination_term ? B.episode_sums[(size_t)R_terms * N + e] : 0.0f;
+    float tq_[PF_MAX_DOF], ldv_[PF_MAX_DOF], la_[PF_MAX_DOF];
+#pragma unroll
+    for (int d = 0; d < PF_MAX_DOF; ++d) {
+        const bool ok = d < D;
+        tq_[d] = ok ? B.torques[e * D + d] : 0.0f; ldv_[d] = ok ? B.last_dof_vel[e * D + d] : 0.0f;
+        la_[d] = ok ? B.last_actions[e * D + d] : 0.0f; out.actions[d] = ok ? B.actions[e * D + d] : 0.0f;
     }
     bool fc_old_[PF_NUM_FEET], cfilt_old_[PF_NUM_FEET], lc_old_[PF_NUM_FEET];
     float fat_old_[PF_NUM_FEET], lfat_old_[PF_NUM_FEET], lmfh_old_[PF_NUM_FEET], cmfh_old_[PF_NUM_FEET];
+#pragma unroll
     for (int f = 0; f < PF_NUM_FEET; ++f) {
         const int k = e * PF_NUM_FEET + f;
         fc_old_[f] = B.first_contact[k] != 0; cfilt_old_[f] = B.contact_filt[k] != 0; lc_old_[f] = B.last_contacts[k] != 0;
@@ -166,6 +383,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
         cmfh_old_[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
     }
     float cmd_old_[4];
+#pragma unroll
     for (int i = 0; i < 4; ++i) cmd_old_[i] = i < P.num_commands ? B.commands[e * P.num_commands + i] : 0.0f;
     // ---- PF:204 ----
     const long long ep_len = B.episode_length_buf[e] + 1;
@@ -177,6 +395,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
     pf_quat_rotate(q, in.root + 7, lin_vel, true);
     pf_quat_rotate(q, in.root + 10, out.ang_vel, true);
     pf_quat_rotate(q, grav, out.gravity, true);
+#pragma unroll
     for (int i = 0; i < 3; ++i) {
         B.base_lin_vel[e * 3 + i] = lin_vel[i];
         B.base_ang_vel[e * 3 + i] = out.ang_vel[i];
@@ -186,6 +405,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
     // ---- PF:1114-1129 feet state machine ----
     float fat[PF_NUM_FEET], lfat[PF_NUM_FEET], lmfh[PF_NUM_FEET];
     bool first_contact[PF_NUM_FEET];
+#pragma unroll
     for (int f = 0; f < PF_NUM_FEET; ++f) {
         const int k = e * PF_NUM_FEET + f;
         const bool fc_old = fc_old_[f];
@@ -219,6 +439,7 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
 
     // ---- PF:479-493 callback: commands ----
     const int C = P.num_commands;
+#pragma unroll
     for (int i = 0; i < 4; ++i) out.commands[i] = cmd_old_[i];
     const uint32_t genv = (uint32_t)(P.env_id_offset + e);
     if (P.resample_commands && (ep_len % P.resample_period) == 0) {       // LR:337-351
@@ -239,135 +460,80 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
         const float heading = atan2f(fwd[1], fwd[0]);
         out.commands[2] = pf_clipf(0.5f * pf_wrap_to_pi(out.commands[3] - heading), -1.0f, 1.0f);
     }
-    for (int i = 0; i < C; ++i) B.commands[e * C + i] = out.commands[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (i < C) B.commands[e * C + i] = out.commands[i];
 
     // ---- PF:239-247 termination ----
     bool terminate = false;
-    for (int i = 0; i < P.num_termination; ++i) {
-        const float* F = in.cf + P.termination_indices[i] * 3;
-        terminate = terminate || (pf_norm3(F[0], F[1], F[2]) > 1.0f);
-    }
+#pragma unroll
+    for (int i = 0; i < PF_MAX_BODIES; ++i)
+        if (i < P.num_termination) {
+            const float* F = in.cf + P.termination_indices[i] * 3;
+            terminate = terminate || (kFast ? pf_sumsq3(F[0], F[1], F[2]) >= T.sq_gt_termination
+                                            : pf_norm3(F[0], F[1], F[2]) > 1.0f);
+        }
     const bool time_out = (float)ep_len > P.max_episode_length;
     const bool reset = terminate || time_out;
     B.terminate[e] = terminate; B.time_out_buf[e] = time_out; B.reset_buf[e] = reset;
     out.reset = reset;
 
     // ---- PF:301-318 rewards, summed in cfg (alphabetical) order ----
+    PfRewIn c;
+    c.lin_vel = lin_vel; c.ang_vel = out.ang_vel; c.gravity = out.gravity; c.commands = out.commands;
+    c.tq = tq_; c.ldv = ldv_; c.la = la_; c.ac = out.actions; c.dof = in.dof; c.cf = in.cf;
+    c.fat = fat; c.lfat = lfat; c.lmfh = lmfh; c.first_contact = first_contact;
+    c.feet0 = in.feet_pos[0]; c.feet1 = in.feet_pos[1];
+    c.bh = in.have_heights ? in.height_mean : in.root[2];
+    c.reset = reset; c.time_out = time_out;
     float rew = 0.0f;
-    for (int k = 0; k < P.num_reward_terms; ++k) {
-        float r = 0.0f;
-        switch (P.reward_ids[k]) {
-        case PF_REW_LIN_VEL_Z: r = pf_sq(lin_vel[2]); break;
-        case PF_REW_ANG_VEL_XY: r = pf_sq(out.ang_vel[0]) + pf_sq(out.ang_vel[1]); break;
-        case PF_REW_ORIENTATION: r = pf_sq(out.gravity[0]) + pf_sq(out.gravity[1]); break;
-        case PF_REW_BASE_HEIGHT: {
-            const float bh = in.have_heights ? in.height_mean : in.root[2];
-            r = pf_sq(bh - P.base_height_target);
-        } break;
-        case PF_REW_TORQUES: for (int d = 0; d < D; ++d) r += pf_sq(tq_[d]); break;
-        case PF_REW_DOF_VEL: for (int d = 0; d < D; ++d) r += pf_sq(in.dof[2 * d + 1]); break;
-        case PF_REW_DOF_ACC:
-            for (int d = 0; d < D; ++d) r += pf_sq((ldv_[d] - in.dof[2 * d + 1]) / dt);
-            break;
-        case PF_REW_ACTION_RATE:
-            for (int d = 0; d < D; ++d) r += pf_sq(la_[d] - ac_[d]);
-            break;
-        case PF_REW_COLLISION:
-            for (int i = 0; i < P.num_penalised; ++i) {
-                const float* F = in.cf + P.penalised_indices[i] * 3;
-                r += (pf_norm3(F[0], F[1], F[2]) > 0.1f) ? 1.0f : 0.0f;
-            }
-            break;
-        case PF_REW_TERMINATION: r = (reset && !time_out) ? 1.0f : 0.0f; break;
-        case PF_REW_DOF_POS_LIMITS:
-            for (int d = 0; d < D; ++d) {
-                const float qd = in.dof[2 * d];
-                r += -pf_minf(qd - P.dof_pos_limits[d][0], 0.0f) + pf_maxf(qd - P.dof_pos_limits[d][1], 0.0f);
-            }
-            break;
-        case PF_REW_DOF_VEL_LIMITS:
-            for (int d = 0; d < D; ++d)
-                r += pf_clipf(fabsf(in.dof[2 * d + 1]) - P.dof_vel_limits[d] * P.soft_dof_vel_limit, 0.0f, 1.0f);
-            break;
-        case PF_REW_TORQUE_LIMITS:
-            for (int d = 0; d < D; ++d)
-                r += pf_maxf(fabsf(tq_[d]) - P.torque_limits[d] * P.soft_torque_limit, 0.0f);
-            break;
-        case PF_REW_TRACKING_LIN_VEL: {
-            const float err = pf_sq(out.commands[0] - lin_vel[0]) + pf_sq(out.commands[1] - lin_vel[1]);
-            r = expf(-err / P.tracking_sigma);
-        } break;
-        case PF_REW_TRACKING_ANG_VEL:
-            r = expf(-pf_sq(out.commands[2] - out.ang_vel[2]) / P.tracking_sigma);
-            break;
-        case PF_REW_FEET_AIR_TIME: {
-            float lo = 0.0f, hi = 0.0f;
-            for (int f = 0; f < PF_NUM_FEET; ++f) {
-                const float m = first_contact[f] ? 1.0f : 0.0f;
-                lo += pf_minf(fat[f] - P.min_feet_air_time, 0.0f) * m;
-                hi += pf_minf(P.max_feet_air_time - fat[f], 0.0f) * m;
-            }
-            r = lo + hi;
-        } break;
-        case PF_REW_NO_FLY: {
-            int n = 0;
-            for (int f = 0; f < PF_NUM_FEET; ++f) n += in.cf[P.feet_indices[f] * 3 + 2] > 0.1f;
-            r = n == 1 ? 1.0f : 0.0f;
-        } break;
-        case PF_REW_UNBALANCE_FEET_AIR_TIME: {     // torch.var over 2 values, unbiased
-            const float m = (lfat[0] + lfat[1]) / 2.0f;
-            r = pf_sq(lfat[0] - m) + pf_sq(lfat[1] - m);
-        } break;
-        case PF_REW_UNBALANCE_FEET_HEIGHT: {
-            const float m = (lmfh[0] + lmfh[1]) / 2.0f;
-            r = pf_sq(lmfh[0] - m) + pf_sq(lmfh[1] - m);
-        } break;
-        case PF_REW_STUMBLE: {
-            bool any = false;
-            for (int f = 0; f < PF_NUM_FEET; ++f) {
-                const float* F = in.cf + P.feet_indices[f] * 3;
-                any = any || (pf_norm2(F[0], F[1]) > 5.0f * fabsf(F[2]));
-            }
-            r = any ? 1.0f : 0.0f;
-        } break;
-        case PF_REW_STAND_STILL:                   // signed comparison, PF:1233-1234
-            r = (fabsf(lin_vel[0]) * (out.commands[0] < 0.1f ? 1.0f : 0.0f)
-                 + fabsf(lin_vel[1]) * (out.commands[1] < 0.1f ? 1.0f : 0.0f))
-                + fabsf(out.ang_vel[2]) * (out.commands[2] < 0.1f ? 1.0f : 0.0f);
-            break;
-        case PF_REW_FEET_CONTACT_FORCES:
-            for (int f = 0; f < PF_NUM_FEET; ++f) {
-                const float* F = in.cf + P.feet_indices[f] * 3;
-                r += pf_maxf(pf_norm3(F[0], F[1], F[2]) - P.max_contact_force, 0.0f);
-            }
-            break;
-        case PF_REW_FEET_DISTANCE: {
-            const float d = pf_norm2(in.feet_pos[0][0] - in.feet_pos[1][0], in.feet_pos[0][1] - in.feet_pos[1][1]);
-            r = pf_clipf(P.min_feet_distance - d, 0.0f, 1.0f);
-        } break;
-        case PF_REW_SURVIVAL: r = (reset ? 0.0f : 1.0f) * dt; break;
-        default: break;
+    if (kCanon) {
+        float* es_out = B.episode_sums + e;
+        // One pass over the canonical order.  Every comparison is warp uniform (constant bank), every term's code
+        // is specialised, every es[] index is a compile-time constant.
+#define PF_X(ID)                                                                                     \
+        if (T.row[ID] >= 0) {                                                                        \
+            const float r = pf_reward_term<kD>(P, T, (ID), c) * T.scale[ID];                         \
+            rew += r;                                                                                \
+            const float s = es[ID] + r;                                                              \
+            es_out[T.off[ID]] = s;                                                                   \
+            if (sums_out) sums_out[T.row[ID]] = s;                                                   \
         }
-        r = r * P.reward_scales[k];
-        rew += r;
-        const float s = es[k] + r;
-        B.episode_sums[(size_t)k * N + e] = s;
-        if (sums_out) sums_out[k] = s;
+        PF_REWARD_CANON(PF_X)
+#undef PF_X
+    } else {
+        for (int k = 0; k < R_terms; ++k) {
+            const float r = pf_reward_term<0>(P, T, P.reward_ids[k], c) * P.reward_scales[k];
+            rew += r;
+            const float s = B.episode_sums[(size_t)k * N + e] + r;
+            B.episode_sums[(size_t)k * N + e] = s;
+            if (sums_out) sums_out[k] = s;
+        }
     }
     if (P.only_positive_rewards) rew = pf_maxf(rew, 0.0f);
     if (P.has_termination_term) {
-        const int k = P.num_reward_terms;
+        const int k = R_terms;
         const float r = ((reset && !time_out) ? 1.0f : 0.0f) * P.termination_scale;
         rew += r;
-        const float s = es[k] + r;
+        const float s = es_term + r;
         B.episode_sums[(size_t)k * N + e] = s;
         if (sums_out) sums_out[k] = s;
     }
     B.rew_buf[e] = rew;
     B.episode_length_buf[e] = ep_len;
 
-    for (int d = 0; d < D; ++d) { out.dof_pos[d] = in.dof[2 * d]; out.dof_vel[d] = in.dof[2 * d + 1]; }
+#pragma unroll
+    for (int d = 0; d < PF_MAX_DOF; ++d) {
+        out.dof_pos[d] = d < D ? in.dof[2 * d] : 0.0f; out.dof_vel[d] = d < D ? in.dof[2 * d + 1] : 0.0f;
+    }
     out.root_z = in.root[2];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) out.root_vel[i] = in.root[7 + i];
+}
+
+PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
+                       uint32_t step, float* sums_out, PfEnvOut& out, bool fast) {
+    if (fast) pf_env_step_t<true>(P, B, T, e, in, step, sums_out, out);
+    else pf_env_step_t<false>(P, B, T, e, in, step, sums_out, out);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -375,10 +541,11 @@ PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, int e, const
 // dof_state (PhysX-owned), updates the curriculum, zeroes the per-env buffers and the episode sums.
 // `sums_out[R]` receives the episode sums before they are zeroed (for extras["episode"], PF:276-280).
 // `root_pre` = this env's root row BEFORE the reset (the curriculum measures the distance walked).
-PF_HD void pf_env_reset(const pf_params& P, const pf_env_buffers& B, int e, const float* root_pre,
-                        const float cmd_xy[2], uint32_t step, bool update_curriculum,
-                        float* sums_out, PfEnvOut& out) {
-    const int D = P.num_dof, N = P.num_envs;
+template <int kD>
+PF_HD void pf_env_reset_t(const pf_params& P, const pf_env_buffers& B, int e, const float* root_pre,
+                          const float cmd_xy[2], uint32_t step, bool update_curriculum,
+                          float* sums_out, PfEnvOut& out) {
+    const int D = kD ? kD : P.num_dof, N = P.num_envs;
     const uint32_t genv = (uint32_t)(P.env_id_offset + e);
 
     // ---- PF:613-636 terrain curriculum ----
@@ -401,28 +568,40 @@ PF_HD void pf_env_reset(const pf_params& P, const pf_env_buffers& B, int e, cons
     // ---- PF:549-559 dofs: pos = default * U(0.5, 1.5), vel = 0 ----
     {
         const uint32_t ek = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_RESET_DOF), genv);
-        for (int d = 0; d < D; ++d) {
-            const float u = (1.5f - 0.5f) * pf_rng_uniform(ek, d) + 0.5f;
-            const float p = P.default_dof_pos[d] * u;
-            B.dof_state[((size_t)e * D + d) * 2 + 0] = p;
-            B.dof_state[((size_t)e * D + d) * 2 + 1] = 0.0f;
-            out.dof_pos[d] = p; out.dof_vel[d] = 0.0f;
-        }
+#pragma unroll
+        for (int d = 0; d < PF_MAX_DOF; ++d)
+            if (d < D) {
+                const float u = (1.5f - 0.5f) * pf_rng_uniform(ek, d) + 0.5f;
+                const float p = P.default_dof_pos[d] * u;
+                B.dof_state[((size_t)e * D + d) * 2 + 0] = p;
+                B.dof_state[((size_t)e * D + d) * 2 + 1] = 0.0f;
+                out.dof_pos[d] = p; out.dof_vel[d] = 0.0f;
+            }
     }
     // ---- PF:566-584 root state ----
     {
         const uint32_t ek = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_RESET_ROOT), genv);
         float r[13];
+#pragma unroll
         for (int i = 0; i < 13; ++i) r[i] = P.base_init_state[i];
+#pragma unroll
         for (int i = 0; i < 3; ++i) r[i] = r[i] + B.env_origins[e * 3 + i];
-        if (P.custom_origins)
+        if (P.custom_origins) {
+#pragma unroll
             for (int i = 0; i < 2; ++i) r[i] = r[i] + ((1.0f - (-1.0f)) * pf_rng_uniform(ek, i) + (-1.0f));
+        }
+#pragma unroll
         for (int i = 0; i < 6; ++i) r[7 + i] = (0.5f - (-0.5f)) * pf_rng_uniform(ek, 2 + i) + (-0.5f);
+#pragma unroll
         for (int i = 0; i < 13; ++i) B.root_states[(size_t)e * 13 + i] = r[i];
         out.root_z = r[2];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) out.root_vel[i] = r[7 + i];
     }
     // ---- PF:290-299 buffers ----
-    for (int d = 0; d < D; ++d) { B.last_actions[e * D + d] = 0.0f; B.last_dof_vel[e * D + d] = 0.0f; }
+#pragma unroll
+    for (int d = 0; d < PF_MAX_DOF; ++d) if (d < D) { B.last_actions[e * D + d] = 0.0f; B.last_dof_vel[e * D + d] = 0.0f; }
+#pragma unroll
     for (int f = 0; f < PF_NUM_FEET; ++f) {
         const int k = e * PF_NUM_FEET + f;
         B.feet_air_time[k] = 0.0f; B.last_feet_air_time[k] = 0.0f;
@@ -436,6 +615,12 @@ PF_HD void pf_env_reset(const pf_params& P, const pf_env_buffers& B, int e, cons
         if (sums_out) sums_out[k] = B.episode_sums[(size_t)k * N + e];
         B.episode_sums[(size_t)k * N + e] = 0.0f;
     }
+}
+
+PF_HD void pf_env_reset(const pf_params& P, const pf_env_buffers& B, int e, const float* root_pre,
+                        const float cmd_xy[2], uint32_t step, bool update_curriculum,
+                        float* sums_out, PfEnvOut& out) {
+    pf_env_reset_t<0>(P, B, e, root_pre, cmd_xy, step, update_curriculum, sums_out, out);
 }
 
 // Number of leading (non height-scan) observation columns: PF:376-382.
@@ -454,6 +639,23 @@ PF_HD float pf_obs_base_col(const pf_params& P, const PfEnvOut& o, const float* 
     if (j < D) return actions[j];
     j -= D;
     return o.commands[j] * P.commands_scale[j];
+}
+
+// The same row written in one go with compile-time indices (the kernel's statement: `o` stays in registers).
+template <int kD>
+PF_HD void pf_obs_base_row(const pf_params& P, const PfEnvOut& o, float* row) {
+    const int D = kD ? kD : P.num_dof;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { row[i] = o.ang_vel[i] * P.obs_scale_ang_vel; row[3 + i] = o.gravity[i]; }
+#pragma unroll
+    for (int d = 0; d < PF_MAX_DOF; ++d)
+        if (d < D) {
+            row[6 + d] = (o.dof_pos[d] - P.default_dof_pos[d]) * P.obs_scale_dof_pos;
+            row[6 + D + d] = o.dof_vel[d] * P.obs_scale_dof_vel;
+            row[6 + 2 * D + d] = o.actions[d];
+        }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) row[6 + 3 * D + i] = o.commands[i] * P.commands_scale[i];
 }
 
 // Height-scan observation column, PF:367-369: clip(root_z - 0.5 - h, -1, 1) * scale

@@ -4,6 +4,7 @@
 // container without a GPU; the GPU parity tests then only have to catch staging / indexing mistakes.
 #include "../../pointfoot_b200/csrc/pf_env_core.cuh"
 #include <vector>
+#include <stdlib.h>
 
 extern "C" int pf_emu_pd_torques(const pf_params* Pp, const pf_env_buffers* Bp, const float* actions_in) {
     const pf_params& P = *Pp; const pf_env_buffers& B = *Bp;
@@ -24,6 +25,9 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
     const uint32_t step = (uint32_t)common_step_counter;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     const int base_w = pf_obs_base_width(P);
+    // PF_EMU_GENERIC=1 forces the order-agnostic reward loop (both statements must agree bit for bit)
+    PfRewTab T;
+    const bool canonical = pf_build_reward_table(P, T) && P.num_dof == PF_MAX_DOF && !getenv("PF_EMU_GENERIC");
     std::vector<int16_t> raw(Pn > 0 ? Pn : 1);
     std::vector<double> stat(R, 0.0);
     int count = 0;
@@ -48,7 +52,7 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
             }
             in.height_mean = (float)(hsum / (double)Pn);
         }
-        pf_env_step(P, B, e, in, step, nullptr, out);
+        pf_env_step(P, B, T, e, in, step, nullptr, out, canonical);
         if (out.reset) {
             std::vector<float> sums(R);
             pf_env_reset(P, B, e, root_pre, out.commands, step, true, sums.data(), out);

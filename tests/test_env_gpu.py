@@ -63,6 +63,28 @@ def test_envs_per_warp_geometries_agree_bit_for_bit(monkeypatch):
                 assert torch.equal(v, outs[0][k]), k
 
 
+def test_reward_statements_and_cta_sizes_agree_bit_for_bit(monkeypatch):
+    """The specialised straight-line reward sum (cfg terms in dir() order, what the reference always yields) and the
+    order-agnostic loop give the same bits; so does every CTA size the launch heuristic can pick."""
+    from pointfoot_b200 import synth
+    state = synth.make_state(3000, "pointfoot_rough", seed=5)
+    outs = []
+    for env in ({}, {"PF_GENERIC_REWARDS": "1"}, {"PF_BLOCK": "32"}, {"PF_BLOCK": "256", "PF_EPW": "4"}):
+        for k in ("PF_GENERIC_REWARDS", "PF_BLOCK", "PF_EPW"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        e = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=5)
+        e.step(state["actions"])
+        e.step(state["actions"] * 0.5)
+        outs.append({k: e.t[k].clone() for k in ("obs_buf", "priv_obs_buf", "rew_buf", "reset_buf", "episode_sums", "reset_ids",
+                                                   "terrain_levels", "root_states", "last_root_vel", "last_actions")})
+        e.close()
+    for o in outs[1:]:
+        for k, v in o.items():
+            assert torch.equal(v, outs[0][k]), k
+
+
 def test_sharded_equals_unsharded():
     """env_id_offset: RNG draws are functions of the global env id, so two half shards == one full run."""
     import common

@@ -49,3 +49,10 @@ def test_live_reference_matches_golden():
                 return torch.stack([ep["rew_" + n] for n in env.episode_sums.keys()])
             return getattr(env, name, None)
         parity.check_against_golden(fname, stepper, fetch)
+
+
+@pytest.mark.parametrize("task,n", [("pointfoot_flat", 33), ("pointfoot_rough", 65)])
+def test_generic_reward_loop_matches_oracle(task, n, monkeypatch):
+    """the order-agnostic reward loop (taken when the cfg's terms are not in dir() order) agrees with the oracle too"""
+    monkeypatch.setenv("PF_EMU_GENERIC", "1")
+    parity.run(task, n, steps=3, device="cpu", backend="emu")

@@ -13,7 +13,8 @@ from pointfoot_b200 import synth, capi         # noqa: E402
 
 def main():
     sizes = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else ["4096", "65536", "262144"])]
-    for task in ("pointfoot_flat", "pointfoot_rough"):
+    tasks = sys.argv[2].split(",") if len(sys.argv) > 2 else ["pointfoot_flat", "pointfoot_rough"]
+    for task in tasks:
         terrain = synth.make_heightfield(1) if task == "pointfoot_rough" else None
         for n in sizes:
             st = synth.make_state(n, task, seed=1, terrain=terrain)
