@@ -23,7 +23,7 @@ struct pf_ctx {
     int envs_per_warp;     // envs owned by one warp of the step kernel (8, 16 or 32)
     int num_slabs;         // ceil(num_envs / envs_per_warp)
     int threads;           // CTA size of the step kernel (32..256: small batches use small CTAs)
-    int canonical;         // num_dof == 6 and reward terms in the reference's dir() order: specialised straight-line reward sum
+    int canonical;         // statement of the step that applies (pf_step_mode): 0 generic, 1 table-driven, 2 pointfoot term set
     int num_blocks;        // CTAs of the step kernel
     int max_blocks;
     size_t smem_bytes;

@@ -91,10 +91,10 @@ struct PfScanLane {               // hoisted per-lane constants of the scan loop
     float gx[PF_MAX_HEIGHT_POINTS / 32], gy[PF_MAX_HEIGHT_POINTS / 32], ns[PF_MAX_HEIGHT_POINTS / 32];
 };
 
-template <bool kWriteObs>
+template <bool kWriteObs, bool kFast>
 __device__ __forceinline__ double pf_scan_env(const pf_params& P, const pf_env_buffers& B, const PfScanLane& L,
                                               const float* __restrict__ root, float zn, float wn, float root_z_obs,
-                                              uint32_t nkey, int e, int lane, bool want_sum) {
+                                              uint32_t nkey, int e, int lane, bool want_sum, const PfRewTab* T) {
     const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
     const bool rough = P.terrain_kind == PF_TERRAIN_HEIGHTFIELD;
     const float bx = root[0], by = root[1], rz = root[2];
@@ -108,7 +108,7 @@ __device__ __forceinline__ double pf_scan_env(const pf_params& P, const pf_env_b
         const int p = lane + 32 * k;
         if (p < Pn) {
             int16_t r = 0;                                       // plane: zeros, PF:1061-1062
-            if (rough) r = pf_scan_point(P, B.height_samples, zn, wn, L.gx[k], L.gy[k], bx, by);
+            if (rough) r = pf_scan_point(P, B.height_samples, zn, wn, L.gx[k], L.gy[k], bx, by, kFast ? T : nullptr);
             const float h = (float)r * P.vertical_scale;
             if (mh) mh[p] = h;
             if (want_sum) acc += (double)(rz - h);
@@ -152,7 +152,7 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //   phase 3  the 27 leading observation columns, flattened over the warp's envs -> coalesced row writes
 //   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
-template <bool kFast>
+template <uint32_t kMask>
 __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
                                                                         const uint32_t step_arg) {
@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf
     const PfWarpSmem s = pf_carve_warp(P, epw, smem_f + (size_t)warp * pf_warp_smem_floats(P, epw));
     const int nenv = min(epw, P.num_envs - e0);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
+    constexpr bool kFast = kMask != PF_MASK_GENERIC;
     constexpr int kD = kFast ? PF_MAX_DOF : 0;
     const int D = kFast ? PF_MAX_DOF : P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
@@ -234,8 +235,8 @@ __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf
         const bool want_sum = true;
         for (int i = 0; i < nenv; ++i) {
             const float* r = s.root + i * 13;
-            const double sum = pf_scan_env<true>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], r[2],
-                                                 __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, want_sum);
+            const double sum = pf_scan_env<true, kFast>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], r[2],
+                                                        __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, want_sum, &S.rew);
             if (lane == i) height_mean = (float)(sum / (double)Pn);
         }
     }
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf
         in.feet_pos[1] = feet + 3;
         in.have_heights = Pn > 0;
         in.height_mean = height_mean;
-        pf_env_step_t<kFast>(P, B, S.rew, e, in, step, nullptr, out);
+        pf_env_step_t<kMask>(P, B, S.rew, e, in, step, nullptr, out);
         is_reset = out.reset;
     }
     pf_warp_partials(P, B, S, slab, e, active, is_reset, R, lane);
@@ -280,11 +281,35 @@ __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf
     __syncwarp();
 
     // ---- phase 3: leading observation columns, coalesced (PF:376-382, 328-338, 189-192) ----
-    {
-        const int no = P.num_obs, np = P.num_priv_obs;
+    const int no = P.num_obs, np = P.num_priv_obs;
+    float* go = B.obs_buf + (size_t)e0 * no;
+    float* gp = B.priv_obs_buf ? B.priv_obs_buf + (size_t)e0 * np : nullptr;
+    if (kFast) {
+        // 27 columns: lane = column, one env per iteration.  What depends on the column alone (noise scale, the
+        // column's share of the RNG hash) is hoisted; a row write is one 108-byte coalesced store.
+        constexpr int W = 6 + 3 * PF_MAX_DOF + 3;
+        const bool col = lane < W;
+        const float ns = (col && P.add_noise) ? S.noise_vec[lane] : 0.0f;
+        const uint32_t lane_mix = (uint32_t)lane * 0x27D4EB2Fu;
+        const float lim = P.clip_obs;
+        const float* src = s.cf + lane;
+        float* o = go + lane;
+        float* p = gp ? gp + lane : nullptr;
+        for (int le = 0; le < nenv; ++le) {
+            if (col) {
+                float v = src[le * cfw];
+                if (ns != 0.0f) {
+                    const uint32_t key = __float_as_uint(s.misc[4 * le + 3]);
+                    const float u = (float)(pf_fmix32(key ^ lane_mix) >> 8) * (1.0f / 16777216.0f);
+                    v = v + (2.0f * u - 1.0f) * ns;
+                }
+                v = pf_clipf(v, -lim, lim);
+                o[(size_t)le * no] = v;
+                if (p) p[(size_t)le * np] = v;
+            }
+        }
+    } else {
         const uint32_t magic = ((1u << 20) + (uint32_t)base_w - 1u) / (uint32_t)base_w;    // i / base_w for i < 2^20 / base_w
-        float* go = B.obs_buf + (size_t)e0 * no;
-        float* gp = B.priv_obs_buf ? B.priv_obs_buf + (size_t)e0 * np : nullptr;
         for (int i = lane; i < nenv * base_w; i += 32) {
             const int le = (int)(((uint32_t)i * magic) >> 20), j = i - le * base_w;
             const float v = pf_obs_finish(P, s.cf[le * cfw + j], __float_as_uint(s.misc[4 * le + 3]), j, S.noise_vec);
@@ -300,8 +325,8 @@ __global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf
             const int i = __ffs(m) - 1;
             m &= m - 1;
             const float* r = s.root + i * 13;
-            pf_scan_env<true>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], s.misc[4 * i + 2],
-                              __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, false);
+            pf_scan_env<true, kFast>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], s.misc[4 * i + 2],
+                                     __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, false, &S.rew);
         }
     }
 }
@@ -501,10 +526,11 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->num_blocks = (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32);
     c->max_blocks = c->num_slabs;
     c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
-    c->canonical = pf_build_reward_table(P, c->S.rew) && P.num_dof == PF_MAX_DOF && !getenv("PF_GENERIC_REWARDS");
+    c->canonical = pf_step_mode(P, c->S.rew, getenv("PF_GENERIC_REWARDS") != nullptr, getenv("PF_TABLE_REWARDS") != nullptr);
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_POINTFOOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_TABLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_GENERIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -578,12 +604,13 @@ static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_
 extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (c->canonical)
-        pf_post_physics_kernel<true><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
-                                                                                       (uint32_t)common_step_counter);
+    const uint32_t step32 = (uint32_t)common_step_counter;
+    if (c->canonical == 2)
+        pf_post_physics_kernel<PF_MASK_POINTFOOT><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
+    else if (c->canonical == 1)
+        pf_post_physics_kernel<PF_MASK_TABLE><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
     else
-        pf_post_physics_kernel<false><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
-                                                                                        (uint32_t)common_step_counter);
+        pf_post_physics_kernel<PF_MASK_GENERIC><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 1);
 }

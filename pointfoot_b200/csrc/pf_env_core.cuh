@@ -16,8 +16,10 @@
 
 #ifdef __CUDACC__
 #define PF_HD __host__ __device__ __forceinline__
+#define PF_CE __host__ __device__ constexpr
 #else
 #define PF_HD static inline
+#define PF_CE constexpr
 #endif
 
 PF_HD float pf_minf(float a, float b) { return a < b ? a : b; }
@@ -35,6 +37,55 @@ PF_HD float pf_sumsq3(float x, float y, float z) { return fmaf(z, z, fmaf(y, y, 
 PF_HD float pf_div_by(float x, float d, float r) {
     const float q = x * r;
     return fmaf(fmaf(-q, d, x), r, q);
+}
+
+// Reward terms by id: row of episode_sums (-1 = term not enabled) and scale.  Built once on the host; handed to the
+// step as a kernel parameter, so that every lookup below is a constant-bank operand at a compile-time offset.
+struct PfRewTab {
+    int32_t row[PF_REW_COUNT];
+    int32_t off[PF_REW_COUNT];        // row * num_envs: element offset of the term's episode_sums row
+    float scale[PF_REW_COUNT];
+    // sqrtf(x) > c  <=>  x >= sq_gt(c) for the two contact thresholds (PF:241: 1.0, PF:1167: 0.1): the squared
+    // norms are compared directly, no square root on the way to a bool
+    float sq_gt_termination, sq_gt_collision;
+    float rdt;                        // RN(1 / dt)
+    int32_t dt_div_exact;             // pf_div_by(x, dt, rdt) == x / dt for every x (checked exhaustively on the host)
+    float r_hscale;                   // RN(1 / horizontal_scale)
+    int32_t index_div_kind;           // PF:1102 (x / horizontal_scale): 0 IEEE division, 1 x * r_hscale (CUDA eager),
+                                      // 2 pf_div_by (bit-identical to the division, checked exhaustively on the host)
+};
+
+// Is pf_div_by(x, d, RN(1/d)) the correctly rounded quotient for EVERY x?  One binade of x (all 2^23 significands)
+// decides it: scaling x by a power of two scales every intermediate exactly.  ~10 ms with hardware FMA; cached.
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("fma")))
+#endif
+static bool pf_div_by_scan(float d, float r) {
+    for (uint32_t m = 0; m < (1u << 23); ++m) {
+        union { uint32_t u; float f; } a;
+        a.u = 0x3f800000u + m;
+        const float q = a.f * r;
+        const float q1 = __builtin_fmaf(__builtin_fmaf(-q, d, a.f), r, q);
+        if (q1 != a.f / d) return false;
+    }
+    return true;
+}
+static inline bool pf_div_by_is_exact(float d) {
+    static float seen_d[8]; static int seen_ok[8]; static int n_seen = 0;      // benign race: same answer either way
+    if (!(d > 1e-30f && d < 1e30f)) return false;
+    for (int i = 0; i < n_seen && i < 8; ++i) if (seen_d[i] == d) return seen_ok[i] != 0;
+    const bool ok = pf_div_by_scan(d, 1.0f / d);
+    if (n_seen < 8) { seen_d[n_seen] = d; seen_ok[n_seen] = ok; ++n_seen; }
+    return ok;
+}
+
+
+// smallest float t with sqrtf(t) > c (sqrtf is correctly rounded and monotone on both sides of the bus)
+static inline float pf_sq_gt(float c) {
+    float t = (float)((double)c * (double)c);
+    while (sqrtf(t) > c) t = nextafterf(t, 0.0f);
+    while (!(sqrtf(t) > c)) t = nextafterf(t, INFINITY);
+    return t;
 }
 
 // torch.cross, ATen CPU: out[i] = fma(a[i+1], b[i+2], -(a[i+2]*b[i+1]))
@@ -94,6 +145,27 @@ PF_HD int16_t pf_terrain_min3(const pf_params& P, const int16_t* __restrict__ hs
     return m < h3 ? m : h3;
 }
 
+// The same lookup with the table's constants: division by the scale without the division sequence where that is
+// bit-identical (PfRewTab::index_div_kind), truncation + clamp done on the float (trunc and clamp commute, the
+// bounds are small integers, NaN -> 0 either way), 32-bit indexing.
+PF_HD int16_t pf_terrain_min3_fast(const pf_params& P, const PfRewTab& T, const int16_t* __restrict__ hs, float x, float y) {
+    x = x + P.border_size;
+    y = y + P.border_size;
+    if (T.index_div_kind == 2) { x = pf_div_by(x, P.horizontal_scale, T.r_hscale); y = pf_div_by(y, P.horizontal_scale, T.r_hscale); }
+    else if (T.index_div_kind == 1) { x = x * T.r_hscale; y = y * T.r_hscale; }
+    else { x = x / P.horizontal_scale; y = y / P.horizontal_scale; }
+    const int px = (int)pf_minf(pf_maxf(x, 0.0f), (float)(P.hf_rows - 2));
+    const int py = (int)pf_minf(pf_maxf(y, 0.0f), (float)(P.hf_cols - 2));
+    const int16_t* r = hs + (px * P.hf_cols + py);
+#ifdef __CUDA_ARCH__
+    const int16_t h1 = __ldg(r), h2 = __ldg(r + P.hf_cols), h3 = __ldg(r + 1);
+#else
+    const int16_t h1 = r[0], h2 = r[P.hf_cols], h3 = r[1];
+#endif
+    const int16_t m = h1 < h2 ? h1 : h2;
+    return m < h3 ? m : h3;
+}
+
 // Normalised yaw-only quaternion of quat_apply_yaw (math.py:38-42): returns (z, w) of normalize((0,0,qz,qw)).
 PF_HD void pf_yaw_quat(const float q[4], float& zn, float& wn) {
     float n = sqrtf(q[2] * q[2] + q[3] * q[3]);     // norm over 4 elements: plain sum; the two zeros are exact
@@ -105,13 +177,13 @@ PF_HD void pf_yaw_quat(const float q[4], float& zn, float& wn) {
 // One height-scan sample, PF:1070-1075: rotate grid point (gx,gy,0) by the yaw quaternion, add base xyz,
 // look the terrain up.  Returns the raw int16 sample.
 PF_HD int16_t pf_scan_point(const pf_params& P, const int16_t* __restrict__ hs, float zn, float wn,
-                            float gx, float gy, float base_x, float base_y) {
+                            float gx, float gy, float base_x, float base_y, const PfRewTab* T = nullptr) {
     // quat_apply((0,0,zn,wn), (gx,gy,0)) with the cross() formula above; zero products dropped (exact)
     const float t0 = -(zn * gy) * 2.0f;
     const float t1 = (zn * gx) * 2.0f;
     const float ox = (gx + wn * t0) + (-(zn * t1));
     const float oy = (gy + wn * t1) + (zn * t0);
-    return pf_terrain_min3(P, hs, ox + base_x, oy + base_y);
+    return T ? pf_terrain_min3_fast(P, *T, hs, ox + base_x, oy + base_y) : pf_terrain_min3(P, hs, ox + base_x, oy + base_y);
 }
 
 // wrap_to_pi, math.py:45-48 (torch remainder = fmod with the divisor's sign)
@@ -158,26 +230,6 @@ struct PfEnvOut {
     X(PF_REW_TORQUE_LIMITS) X(PF_REW_TORQUES) X(PF_REW_TRACKING_ANG_VEL) X(PF_REW_TRACKING_LIN_VEL)          \
     X(PF_REW_UNBALANCE_FEET_AIR_TIME) X(PF_REW_UNBALANCE_FEET_HEIGHT)
 
-// Reward terms by id: row of episode_sums (-1 = term not enabled) and scale.  Built once on the host; handed to the
-// step as a kernel parameter, so that every lookup below is a constant-bank operand at a compile-time offset.
-struct PfRewTab {
-    int32_t row[PF_REW_COUNT];
-    int32_t off[PF_REW_COUNT];        // row * num_envs: element offset of the term's episode_sums row
-    float scale[PF_REW_COUNT];
-    // sqrtf(x) > c  <=>  x >= sq_gt(c) for the two contact thresholds (PF:241: 1.0, PF:1167: 0.1): the squared
-    // norms are compared directly, no square root on the way to a bool
-    float sq_gt_termination, sq_gt_collision;
-    float rdt;                        // RN(1 / dt)
-};
-
-// smallest float t with sqrtf(t) > c (sqrtf is correctly rounded and monotone on both sides of the bus)
-static inline float pf_sq_gt(float c) {
-    float t = (float)((double)c * (double)c);
-    while (sqrtf(t) > c) t = nextafterf(t, 0.0f);
-    while (!(sqrtf(t) > c)) t = nextafterf(t, INFINITY);
-    return t;
-}
-
 // True when P.reward_ids is a subsequence of the canonical order (what the reference's cfg always yields): the
 // step then runs the straight-line statement of the reward sum, every term's code specialised at compile time.
 static inline bool pf_rewards_canonical(const pf_params& P) {
@@ -195,11 +247,68 @@ static inline bool pf_rewards_canonical(const pf_params& P) {
     return true;
 }
 
+// Position of a term in the canonical order, and the set of enabled terms as a bit mask over those positions.
+// The step is compiled three ways (template parameter kMask of pf_env_step_t):
+//   PF_MASK_GENERIC   any num_dof, terms in any order: guarded loops, order-agnostic reward loop
+//   PF_MASK_TABLE     6 DOF, canonical order, any subset: straight-line sum, every term behind a warp-uniform test
+//   a literal mask    6 DOF, exactly that subset (PF_MASK_POINTFOOT = the 19 terms of both pointfoot cfgs,
+//                     pointfoot_rough_config.py:131-154): disabled terms are not compiled at all, rows of
+//                     episode_sums are compile-time constants
+PF_CE int pf_canon_pos(int id) {
+    int p = 0;
+#define PF_X(ID) if (id == (ID)) return p; ++p;
+    PF_REWARD_CANON(PF_X)
+#undef PF_X
+    return -1;
+}
+PF_CE uint32_t pf_canon_bit(int id) { return 1u << pf_canon_pos(id); }
+PF_CE int pf_popc_const(uint32_t v) { int n = 0; for (; v; v &= v - 1) ++n; return n; }
+#define PF_MASK_GENERIC 0u
+#define PF_MASK_TABLE 0x80000000u
+constexpr uint32_t PF_MASK_POINTFOOT =
+    pf_canon_bit(PF_REW_ACTION_RATE) | pf_canon_bit(PF_REW_ANG_VEL_XY) | pf_canon_bit(PF_REW_BASE_HEIGHT) |
+    pf_canon_bit(PF_REW_COLLISION) | pf_canon_bit(PF_REW_DOF_ACC) | pf_canon_bit(PF_REW_FEET_AIR_TIME) |
+    pf_canon_bit(PF_REW_FEET_CONTACT_FORCES) | pf_canon_bit(PF_REW_FEET_DISTANCE) | pf_canon_bit(PF_REW_LIN_VEL_Z) |
+    pf_canon_bit(PF_REW_NO_FLY) | pf_canon_bit(PF_REW_ORIENTATION) | pf_canon_bit(PF_REW_STAND_STILL) |
+    pf_canon_bit(PF_REW_SURVIVAL) | pf_canon_bit(PF_REW_TORQUE_LIMITS) | pf_canon_bit(PF_REW_TORQUES) |
+    pf_canon_bit(PF_REW_TRACKING_ANG_VEL) | pf_canon_bit(PF_REW_TRACKING_LIN_VEL) |
+    pf_canon_bit(PF_REW_UNBALANCE_FEET_AIR_TIME) | pf_canon_bit(PF_REW_UNBALANCE_FEET_HEIGHT);
+
+// is term ID enabled / element offset of its episode_sums row: compile-time for a literal mask
+template <uint32_t kMask, int ID>
+PF_HD bool pf_term_on(const PfRewTab& T) {
+    constexpr bool on = ((kMask >> pf_canon_pos(ID)) & 1u) != 0;
+    return (kMask & PF_MASK_TABLE) ? T.row[ID] >= 0 : on;
+}
+template <uint32_t kMask, int ID>
+PF_HD int pf_term_row(const PfRewTab& T) {
+    constexpr int row = pf_popc_const(kMask & (pf_canon_bit(ID) - 1u));
+    return (kMask & PF_MASK_TABLE) ? T.row[ID] : row;
+}
+template <uint32_t kMask, int ID>
+PF_HD size_t pf_term_off(const PfRewTab& T, int N) {
+    constexpr int row = pf_popc_const(kMask & (pf_canon_bit(ID) - 1u));
+    return (kMask & PF_MASK_TABLE) ? (size_t)T.off[ID] : (size_t)row * (size_t)N;
+}
+
+// mask of P's enabled terms over the canonical positions (meaningful when the table is canonical)
+static inline uint32_t pf_reward_mask(const pf_params& P) {
+    uint32_t m = 0;
+    for (int k = 0; k < P.num_reward_terms; ++k) {
+        const int pos = pf_canon_pos(P.reward_ids[k]);
+        if (pos >= 0) m |= 1u << pos;
+    }
+    return m;
+}
+
 static inline bool pf_build_reward_table(const pf_params& P, PfRewTab& T) {
     for (int i = 0; i < PF_REW_COUNT; ++i) { T.row[i] = -1; T.off[i] = 0; T.scale[i] = 0.0f; }
     T.sq_gt_termination = pf_sq_gt(1.0f);
     T.sq_gt_collision = pf_sq_gt(0.1f);
     T.rdt = 1.0f / P.dt;
+    T.dt_div_exact = pf_div_by_is_exact(P.dt) ? 1 : 0;
+    T.r_hscale = 1.0f / P.horizontal_scale;
+    T.index_div_kind = P.index_div_mode == PF_DIV_RECIPROCAL ? 1 : (pf_div_by_is_exact(P.horizontal_scale) ? 2 : 0);
     if ((long long)P.num_envs * (PF_MAX_REWARD_TERMS + 1) > 0x7fffffffLL) return false;
     for (int k = 0; k < P.num_reward_terms; ++k) {
         const int id = P.reward_ids[k];
@@ -244,7 +353,8 @@ PF_HD float pf_reward_term(const pf_params& P, const PfRewTab& T, const int id, 
     case PF_REW_DOF_ACC:
 #pragma unroll
         for (int d = 0; d < PF_MAX_DOF; ++d)
-            if (d < D) r += pf_sq(kD ? pf_div_by(c.ldv[d] - c.dof[2 * d + 1], dt, T.rdt) : (c.ldv[d] - c.dof[2 * d + 1]) / dt);
+            if (d < D) r += pf_sq((kD && T.dt_div_exact) ? pf_div_by(c.ldv[d] - c.dof[2 * d + 1], dt, T.rdt)
+                                                         : (c.ldv[d] - c.dof[2 * d + 1]) / dt);
         break;
     case PF_REW_ACTION_RATE:
 #pragma unroll
@@ -341,12 +451,14 @@ PF_HD float pf_reward_term(const pf_params& P, const PfRewTab& T, const int id, 
 }
 
 // post_physics_step up to (and including) reset_idx: PF:204-222.  `e` = local env index, writes go to B.
-// kFast: the common shape -- P.num_dof == PF_MAX_DOF and P.reward_ids in canonical order (pf_build_reward_table
-// returned true for T) -> straight-line reward sum, no guards.  Otherwise: guarded loops, order-agnostic reward loop.
-template <bool kFast>
+// kMask: PF_MASK_GENERIC, PF_MASK_TABLE or a literal term mask (see pf_canon_pos).  Everything but GENERIC is the
+// common shape -- P.num_dof == PF_MAX_DOF and P.reward_ids in canonical order (pf_build_reward_table returned true
+// for T) -> straight-line reward sum, no guards.
+template <uint32_t kMask>
 PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
                          uint32_t step, float* sums_out /* [R] scaled reward terms of this step or NULL */,
                          PfEnvOut& out) {
+    constexpr bool kFast = kMask != PF_MASK_GENERIC;
     constexpr bool kCanon = kFast;
     constexpr int kD = kFast ? PF_MAX_DOF : 0;
     const int D = kFast ? PF_MAX_DOF : P.num_dof;
@@ -360,7 +472,7 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
     float es[PF_REW_COUNT];                       // indexed by term id (a compile-time constant where it is used)
     if (kCanon) {
         const float* es_in = B.episode_sums + e;
-#define PF_X(ID) es[ID] = T.row[ID] >= 0 ? es_in[T.off[ID]] : 0.0f;
+#define PF_X(ID) es[ID] = pf_term_on<kMask, ID>(T) ? es_in[pf_term_off<kMask, ID>(T, N)] : 0.0f;
         PF_REWARD_CANON(PF_X)
 #undef PF_X
     }
@@ -420,7 +532,8 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
             cm = cfilt_old ? 0.0f : cm;
             float below = 0.0f;                                   // PF:1089-1090 plane
             if (P.terrain_kind == PF_TERRAIN_HEIGHTFIELD)
-                below = (float)pf_terrain_min3(P, B.height_samples, in.feet_pos[f][0], in.feet_pos[f][1])
+                below = (float)(kFast ? pf_terrain_min3_fast(P, T, B.height_samples, in.feet_pos[f][0], in.feet_pos[f][1])
+                                      : pf_terrain_min3(P, B.height_samples, in.feet_pos[f][0], in.feet_pos[f][1]))
                         * P.vertical_scale;
             const float fh = in.feet_pos[f][2] - below;
             cm = pf_maxf(cm, fh);
@@ -491,12 +604,12 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
         // One pass over the canonical order.  Every comparison is warp uniform (constant bank), every term's code
         // is specialised, every es[] index is a compile-time constant.
 #define PF_X(ID)                                                                                     \
-        if (T.row[ID] >= 0) {                                                                        \
+        if (pf_term_on<kMask, ID>(T)) {                                                              \
             const float r = pf_reward_term<kD>(P, T, (ID), c) * T.scale[ID];                         \
             rew += r;                                                                                \
             const float s = es[ID] + r;                                                              \
-            es_out[T.off[ID]] = s;                                                                   \
-            if (sums_out) sums_out[T.row[ID]] = s;                                                   \
+            es_out[pf_term_off<kMask, ID>(T, N)] = s;                                                \
+            if (sums_out) sums_out[pf_term_row<kMask, ID>(T)] = s;                                   \
         }
         PF_REWARD_CANON(PF_X)
 #undef PF_X
@@ -530,10 +643,20 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
     for (int i = 0; i < 6; ++i) out.root_vel[i] = in.root[7 + i];
 }
 
+// `mode`: 0 generic, 1 table, 2 the literal pointfoot mask (the caller checked that it applies)
 PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
-                       uint32_t step, float* sums_out, PfEnvOut& out, bool fast) {
-    if (fast) pf_env_step_t<true>(P, B, T, e, in, step, sums_out, out);
-    else pf_env_step_t<false>(P, B, T, e, in, step, sums_out, out);
+                       uint32_t step, float* sums_out, PfEnvOut& out, int mode) {
+    if (mode == 2) pf_env_step_t<PF_MASK_POINTFOOT>(P, B, T, e, in, step, sums_out, out);
+    else if (mode == 1) pf_env_step_t<PF_MASK_TABLE>(P, B, T, e, in, step, sums_out, out);
+    else pf_env_step_t<PF_MASK_GENERIC>(P, B, T, e, in, step, sums_out, out);
+}
+
+// which statement of the step applies to P (and env overrides for tests: force the table / the generic one)
+static inline int pf_step_mode(const pf_params& P, PfRewTab& T, bool force_generic, bool force_table) {
+    const bool canon = pf_build_reward_table(P, T) && P.num_dof == PF_MAX_DOF;
+    if (!canon || force_generic) return 0;
+    if (force_table || pf_reward_mask(P) != PF_MASK_POINTFOOT) return 1;
+    return 2;
 }
 
 // ------------------------------------------------------------------------------------------------

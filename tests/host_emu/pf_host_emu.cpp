@@ -25,9 +25,10 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
     const uint32_t step = (uint32_t)common_step_counter;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     const int base_w = pf_obs_base_width(P);
-    // PF_EMU_GENERIC=1 forces the order-agnostic reward loop (both statements must agree bit for bit)
+    // PF_EMU_GENERIC=1 / PF_EMU_TABLE=1 force the order-agnostic reward loop / the table-driven statement
+    // (all three statements must agree bit for bit)
     PfRewTab T;
-    const bool canonical = pf_build_reward_table(P, T) && P.num_dof == PF_MAX_DOF && !getenv("PF_EMU_GENERIC");
+    const int canonical = pf_step_mode(P, T, getenv("PF_EMU_GENERIC") != nullptr, getenv("PF_EMU_TABLE") != nullptr);
     std::vector<int16_t> raw(Pn > 0 ? Pn : 1);
     std::vector<double> stat(R, 0.0);
     int count = 0;
@@ -45,7 +46,7 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
             float zn, wn; pf_yaw_quat(root_pre + 3, zn, wn);
             for (int p = 0; p < Pn; ++p) {
                 raw[p] = pf_scan_point(P, B.height_samples, zn, wn, height_points_xy[2 * p],
-                                       height_points_xy[2 * p + 1], root_pre[0], root_pre[1]);
+                                       height_points_xy[2 * p + 1], root_pre[0], root_pre[1], canonical ? &T : nullptr);
                 const float h = (float)raw[p] * P.vertical_scale;
                 if (B.measured_heights) B.measured_heights[(size_t)e * Pn + p] = h;
                 hsum += (double)(root_pre[2] - h);

@@ -64,13 +64,13 @@ def test_envs_per_warp_geometries_agree_bit_for_bit(monkeypatch):
 
 
 def test_reward_statements_and_cta_sizes_agree_bit_for_bit(monkeypatch):
-    """The specialised straight-line reward sum (cfg terms in dir() order, what the reference always yields) and the
-    order-agnostic loop give the same bits; so does every CTA size the launch heuristic can pick."""
+    """The three statements of the step (pointfoot term set compiled in, table-driven sum for any subset in dir()
+    order, order-agnostic loop) give the same bits; so does every CTA size the launch heuristic can pick."""
     from pointfoot_b200 import synth
     state = synth.make_state(3000, "pointfoot_rough", seed=5)
     outs = []
-    for env in ({}, {"PF_GENERIC_REWARDS": "1"}, {"PF_BLOCK": "32"}, {"PF_BLOCK": "256", "PF_EPW": "4"}):
-        for k in ("PF_GENERIC_REWARDS", "PF_BLOCK", "PF_EPW"):
+    for env in ({}, {"PF_GENERIC_REWARDS": "1"}, {"PF_TABLE_REWARDS": "1"}, {"PF_BLOCK": "32"}, {"PF_BLOCK": "256", "PF_EPW": "4"}):
+        for k in ("PF_GENERIC_REWARDS", "PF_TABLE_REWARDS", "PF_BLOCK", "PF_EPW"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)

@@ -51,8 +51,10 @@ def test_live_reference_matches_golden():
         parity.check_against_golden(fname, stepper, fetch)
 
 
+@pytest.mark.parametrize("var", ["PF_EMU_GENERIC", "PF_EMU_TABLE"])
 @pytest.mark.parametrize("task,n", [("pointfoot_flat", 33), ("pointfoot_rough", 65)])
-def test_generic_reward_loop_matches_oracle(task, n, monkeypatch):
-    """the order-agnostic reward loop (taken when the cfg's terms are not in dir() order) agrees with the oracle too"""
-    monkeypatch.setenv("PF_EMU_GENERIC", "1")
+def test_other_statements_of_the_step_match_oracle(task, n, var, monkeypatch):
+    """the step is compiled three ways (pf_env_core.cuh, pf_canon_pos): the pointfoot term set (default), the
+    table-driven sum for any subset in dir() order, the order-agnostic loop; the last two agree with the oracle too"""
+    monkeypatch.setenv(var, "1")
     parity.run(task, n, steps=3, device="cpu", backend="emu")
