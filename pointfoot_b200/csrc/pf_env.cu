@@ -152,8 +152,11 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //   phase 3  the 27 leading observation columns, flattened over the warp's envs -> coalesced row writes
 //   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
-template <uint32_t kMask>
-__global__ void __launch_bounds__(PF_THREADS, 2) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
+// kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
+// spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r2_step_kernel_sweeps.txt):
+// the spills cost more than the extra resident warps hide.
+template <uint32_t kMask, int kMinB>
+__global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
                                                                         const uint32_t step_arg) {
     extern __shared__ __align__(16) float smem_f[];
@@ -528,9 +531,9 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
     c->canonical = pf_step_mode(P, c->S.rew, getenv("PF_GENERIC_REWARDS") != nullptr, getenv("PF_TABLE_REWARDS") != nullptr);
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_POINTFOOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_TABLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_GENERIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_POINTFOOT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_TABLE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_GENERIC, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -606,11 +609,11 @@ extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64
     cudaStream_t st = (cudaStream_t)stream;
     const uint32_t step32 = (uint32_t)common_step_counter;
     if (c->canonical == 2)
-        pf_post_physics_kernel<PF_MASK_POINTFOOT><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
+        pf_post_physics_kernel<PF_MASK_POINTFOOT, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
     else if (c->canonical == 1)
-        pf_post_physics_kernel<PF_MASK_TABLE><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
+        pf_post_physics_kernel<PF_MASK_TABLE, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
     else
-        pf_post_physics_kernel<PF_MASK_GENERIC><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
+        pf_post_physics_kernel<PF_MASK_GENERIC, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 1);
 }
