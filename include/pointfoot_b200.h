@@ -173,6 +173,13 @@ int pf_pd_torques(pf_ctx* ctx, const pf_env_buffers* bufs, const float* actions_
  * reset_ids / reset_count / episode_stats (PF:221, 276-288). */
 int pf_post_physics_step(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
 
+/* pf_post_physics_step in two halves.  _begin leaves the step's tail (reset_ids, reset_count, episode_stats,
+ * extras_time_outs, step_counter: PF:221, 259-288) running on a context-owned stream; obs / priv / rew / reset flags and
+ * the reset rows are complete in `stream` order, so ActorCritic.act queued next overlaps it.  _join makes `stream` wait
+ * for the tail: call it before reading those outputs, before the next step of this ctx and before a capture ends. */
+int pf_post_physics_step_begin(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
+int pf_post_physics_step_join(pf_ctx* ctx, void* stream);
+
 /* PF:590-611: random push forces into forces[N,B,3] (body 0 rows; everything else zeroed).
  * max_push_force = base_mass.mean() * max_push_vel_xy / sim_dt, evaluated by the host in double (PF:592-596). */
 int pf_push_forces(pf_ctx* ctx, const pf_env_buffers* bufs, float* forces, float max_push_force,

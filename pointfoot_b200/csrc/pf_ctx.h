@@ -15,8 +15,11 @@ struct PfCtxScratch {
     PfRewTab rew;                 // reward terms by id (row, scale): constant-bank operands of the step kernel
 };
 
+typedef void (*pf_step_kernel_t)(const pf_params, const pf_env_buffers, const PfCtxScratch, const int, const uint32_t);
+
 struct pf_ctx {
     pf_params P;
+    pf_step_kernel_t step_kernel;   // instantiation of pf_post_physics_kernel picked at pf_ctx_create
     PfCtxScratch S;
     int device;
     int num_sms;
@@ -32,6 +35,7 @@ struct pf_ctx {
     // pf_step_host with pinned buffers: the transfers the first torque kernel does not need, and the results' way
     // out, run on io_stream beside the kernels (fork / join by events, so the pattern can be stream-captured)
     cudaStream_t io_stream;
-    cudaEvent_t ev_fork, ev_in, ev_post, ev_out;
+    cudaEvent_t ev_fork, ev_in, ev_post, ev_out, ev_fin;
+    int fin_pending;       // a finalize kernel is in flight on io_stream: pf_post_physics_step_join makes a stream wait for it
     int out_pending;       // a scatter is in flight on io_stream: pf_step_host_join makes a stream wait for it
 };

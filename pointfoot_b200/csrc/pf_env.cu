@@ -12,6 +12,7 @@
 #include "pf_env_core.cuh"
 #include "pf_ctx.h"
 #include "pf_tc_ptx.cuh"      // mbarrier + bulk-copy wrappers
+#include "pf_launch.h"
 
 #define PF_THREADS 256
 
@@ -21,6 +22,8 @@
 __global__ void __launch_bounds__(256) pf_pd_torques_kernel(const pf_params P, const pf_env_buffers B,
                                                             const float* __restrict__ actions_in) {
     const int n = P.num_envs * P.num_dof;
+    pf_grid_dep_launch();
+    pf_grid_dep_wait();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const int d = i % P.num_dof;
         float a;
@@ -132,10 +135,19 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
     const unsigned m = __ballot_sync(0xffffffffu, is_reset);
     if (m) {
         const int N = P.num_envs;
-        for (int k = 0; k < R; ++k) {
-            const double v = is_reset ? (double)B.episode_sums[(size_t)k * N + e] : 0.0;
-            const double t = pf_warp_sum(v);
-            if (lane == 0) S.blk_sums[(size_t)slab * PF_MAX_REWARD_TERMS + k] = t;
+        if ((m & (m - 1)) == 0) {
+            // one reset env in the slab (the usual case): its lane writes the sums itself -- the same values the
+            // tree below would produce (x + 0 + ... + 0), without 19 double-precision warp reductions on the
+            // critical path of the slowest warps of the launch
+            if (is_reset)
+                for (int k = 0; k < R; ++k)
+                    S.blk_sums[(size_t)slab * PF_MAX_REWARD_TERMS + k] = (double)B.episode_sums[(size_t)k * N + e];
+        } else {
+            for (int k = 0; k < R; ++k) {
+                const double v = is_reset ? (double)B.episode_sums[(size_t)k * N + e] : 0.0;
+                const double t = pf_warp_sum(v);
+                if (lane == 0) S.blk_sums[(size_t)slab * PF_MAX_REWARD_TERMS + k] = t;
+            }
         }
     }
     if (lane == 0) S.blk_count[slab] = __popc(m);
@@ -155,7 +167,10 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 // kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
 // spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r2_step_kernel_sweeps.txt):
 // the spills cost more than the extra resident warps hide.
-template <uint32_t kMask, int kMinB>
+// kScan: the task measures terrain heights (num_height_points > 0).  The plane task's kernel carries no scan code
+// and issues the per-env loads in front of the wait for the staged rows; the scan task issues them behind the scan,
+// which would otherwise hold ~70 registers across it.
+template <uint32_t kMask, int kMinB, bool kScan>
 __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
                                                                         const uint32_t step_arg) {
@@ -163,13 +178,15 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slab = blockIdx.x * (blockDim.x >> 5) + warp;
     const int e0 = slab * epw;
+    pf_grid_dep_launch();
     if (e0 >= P.num_envs) return;
     const PfWarpSmem s = pf_carve_warp(P, epw, smem_f + (size_t)warp * pf_warp_smem_floats(P, epw));
     const int nenv = min(epw, P.num_envs - e0);
+    pf_grid_dep_wait();
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     constexpr bool kFast = kMask != PF_MASK_GENERIC;
     constexpr int kD = kFast ? PF_MAX_DOF : 0;
-    const int D = kFast ? PF_MAX_DOF : P.num_dof, NB = P.num_bodies, Pn = P.num_height_points;
+    const int D = kFast ? PF_MAX_DOF : P.num_dof, NB = P.num_bodies, Pn = kScan ? P.num_height_points : 0;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     const int base_w = 6 + 3 * D + 3, cfw = pf_cf_width(P);
     const bool active = lane < nenv;
@@ -206,7 +223,9 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
         }
     }
     float feet[6];
+    PfEnvPre pre;
     if (active) {
+        if (!kScan) pf_env_preload<kMask>(P, B, S.rew, e, pre);       // in flight together with the staging above
         for (int f = 0; f < PF_NUM_FEET; ++f) {
             const float* g = B.rigid_body_states + ((size_t)e * NB + P.feet_indices[f]) * 13;
             feet[3 * f] = __ldg(g); feet[3 * f + 1] = __ldg(g + 1); feet[3 * f + 2] = __ldg(g + 2);
@@ -219,7 +238,7 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     // ---- phase 1: height scan ----
     float height_mean = 0.0f;
     PfScanLane L;
-    if (Pn > 0) {
+    if (kScan) {
 #pragma unroll
         for (int k = 0; k < PF_MAX_HEIGHT_POINTS / 32; ++k) {
             const int p = lane + 32 * k;
@@ -236,27 +255,30 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
         }
         __syncwarp();
         const bool want_sum = true;
+        double hsum = 0.0;
         for (int i = 0; i < nenv; ++i) {
             const float* r = s.root + i * 13;
             const double sum = pf_scan_env<true, kFast>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], r[2],
                                                         __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, want_sum, &S.rew);
-            if (lane == i) height_mean = (float)(sum / (double)Pn);
+            if (lane == i) hsum = sum;
         }
+        height_mean = (float)(hsum / (double)Pn);          // one division per lane, after the loop
     }
 
     // ---- phase 2: one lane per env ----
     bool is_reset = false;
     PfEnvOut out;
     if (active) {
+        if (kScan) pf_env_preload<kMask>(P, B, S.rew, e, pre);
         PfEnvIn in;
         in.root = s.root + lane * 13;
         in.dof = s.dof + lane * 2 * D;
         in.cf = s.cf + lane * cfw;
         in.feet_pos[0] = feet;
         in.feet_pos[1] = feet + 3;
-        in.have_heights = Pn > 0;
+        in.have_heights = kScan;
         in.height_mean = height_mean;
-        pf_env_step_t<kMask>(P, B, S.rew, e, in, step, nullptr, out);
+        pf_env_step_t<kMask>(P, B, S.rew, e, in, pre, step, nullptr, out);
         is_reset = out.reset;
     }
     pf_warp_partials(P, B, S, slab, e, active, is_reset, R, lane);
@@ -296,19 +318,33 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
         const uint32_t lane_mix = (uint32_t)lane * 0x27D4EB2Fu;
         const float lim = P.clip_obs;
         const float* src = s.cf + lane;
+        const float* keys = s.misc + 3;
         float* o = go + lane;
-        float* p = gp ? gp + lane : nullptr;
-        for (int le = 0; le < nenv; ++le) {
-            if (col) {
-                float v = src[le * cfw];
-                if (ns != 0.0f) {
-                    const uint32_t key = __float_as_uint(s.misc[4 * le + 3]);
-                    const float u = (float)(pf_fmix32(key ^ lane_mix) >> 8) * (1.0f / 16777216.0f);
-                    v = v + (2.0f * u - 1.0f) * ns;
+        if (col) {
+            if (gp) {
+                float* p = gp + lane;
+#pragma unroll 4
+                for (int le = 0; le < nenv; ++le) {
+                    float v = src[le * cfw];
+                    if (ns != 0.0f) {
+                        const float u = (float)(pf_fmix32(__float_as_uint(keys[4 * le]) ^ lane_mix) >> 8) * (1.0f / 16777216.0f);
+                        v = v + (2.0f * u - 1.0f) * ns;
+                    }
+                    v = pf_clipf(v, -lim, lim);
+                    *o = v; o += no;
+                    *p = v; p += np;
                 }
-                v = pf_clipf(v, -lim, lim);
-                o[(size_t)le * no] = v;
-                if (p) p[(size_t)le * np] = v;
+            } else {
+#pragma unroll 4
+                for (int le = 0; le < nenv; ++le) {
+                    float v = src[le * cfw];
+                    if (ns != 0.0f) {
+                        const float u = (float)(pf_fmix32(__float_as_uint(keys[4 * le]) ^ lane_mix) >> 8) * (1.0f / 16777216.0f);
+                        v = v + (2.0f * u - 1.0f) * ns;
+                    }
+                    v = pf_clipf(v, -lim, lim);
+                    *o = v; o += no;
+                }
             }
         }
     } else {
@@ -322,7 +358,7 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     }
 
     // ---- phase 4: height columns of the envs that reset ----
-    if (Pn > 0 && (P.measure_heights_actor || P.measure_heights_critic)) {
+    if (kScan && (P.measure_heights_actor || P.measure_heights_critic)) {
         unsigned m = __ballot_sync(0xffffffffu, is_reset);
         while (m) {
             const int i = __ffs(m) - 1;
@@ -332,6 +368,13 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
                                      __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, false, &S.rew);
         }
     }
+}
+
+// the instantiation of the step kernel for a context: statement of the step (pf_step_mode) x with / without height scan
+static pf_step_kernel_t pf_pick_step_kernel(int mode, bool scan) {
+    if (mode == 2) return scan ? pf_post_physics_kernel<PF_MASK_POINTFOOT, 2, true> : pf_post_physics_kernel<PF_MASK_POINTFOOT, 2, false>;
+    if (mode == 1) return scan ? pf_post_physics_kernel<PF_MASK_TABLE, 2, true> : pf_post_physics_kernel<PF_MASK_TABLE, 2, false>;
+    return scan ? pf_post_physics_kernel<PF_MASK_GENERIC, 2, true> : pf_post_physics_kernel<PF_MASK_GENERIC, 2, false>;
 }
 
 // reset_idx over ALL envs (PF:137-139 reset(), before the zero-action step).
@@ -369,54 +412,32 @@ __global__ void __launch_bounds__(PF_THREADS) pf_reset_all_kernel(const pf_param
 __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, const pf_env_buffers B,
                                                            const PfCtxScratch S, const int epw,
                                                            const int num_slabs, const int count_step) {
-    __shared__ int s_warp[32];
-    __shared__ int s_base;
+    __shared__ int s_before[32], s_total[32], s_flags[32];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
+    pf_grid_dep_launch();
+    pf_grid_dep_wait();
 
-    // offset of this CTA = sum of blk_count over the warp slabs in front of it
+    // One pass over the step kernel's per-slab counts gives both the number of resets in front of this CTA's envs
+    // and the total; one barrier; every warp then reduces the 32 per-warp partials itself (no serial loops).
     const int before = (int)(((long long)blockIdx.x * 1024) / epw);
-    int part = 0;
-    for (int i = tid; i < before; i += 1024) part += S.blk_count[i];
-    part = __reduce_add_sync(0xffffffffu, part);
-    if (lane == 0) s_warp[warp] = part;
-    __syncthreads();
-    if (tid == 0) {
-        int t = 0;
-        for (int w = 0; w < 32; ++w) t += s_warp[w];
-        s_base = t;
+    int part_b = 0, part_t = 0;
+    for (int i = tid; i < num_slabs; i += 1024) {
+        const int c = S.blk_count[i];
+        part_t += c;
+        part_b += i < before ? c : 0;
     }
-    __syncthreads();
-    const int base = s_base;
-    __syncthreads();
-
-    // total number of resets (every CTA needs it for extras["time_outs"])
-    __shared__ int s_total;
-    {
-        int tot = 0;
-        for (int i = tid; i < num_slabs; i += 1024) tot += S.blk_count[i];
-        tot = __reduce_add_sync(0xffffffffu, tot);
-        __syncthreads();
-        if (lane == 0) s_warp[warp] = tot;
-        __syncthreads();
-        if (tid == 0) {
-            int t = 0;
-            for (int w = 0; w < 32; ++w) t += s_warp[w];
-            s_total = t;
-        }
-        __syncthreads();
-    }
-    const int total = s_total;
-    __syncthreads();
-
     const int e = blockIdx.x * 1024 + tid;
-    if (B.extras_time_outs && total > 0 && e < P.num_envs) B.extras_time_outs[e] = B.time_out_buf[e];
     const bool flag = e < P.num_envs && B.reset_buf[e] != 0;
+    const bool tmo = e < P.num_envs && B.time_out_buf[e] != 0;
     const unsigned m = __ballot_sync(0xffffffffu, flag);
-    if (lane == 0) s_warp[warp] = __popc(m);
+    part_b = __reduce_add_sync(0xffffffffu, part_b);
+    part_t = __reduce_add_sync(0xffffffffu, part_t);
+    if (lane == 0) { s_before[warp] = part_b; s_total[warp] = part_t; s_flags[warp] = __popc(m); }
     __syncthreads();
-    int off = base;
-    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    const int total = __reduce_add_sync(0xffffffffu, s_total[lane]);
+    const int off = __reduce_add_sync(0xffffffffu, s_before[lane] + (lane < warp ? s_flags[lane] : 0));
+    if (B.extras_time_outs && total > 0 && e < P.num_envs) B.extras_time_outs[e] = tmo;
     if (flag) B.reset_ids[off + __popc(m & ((1u << lane) - 1u))] = e;
 
     if (blockIdx.x == 0) {
@@ -424,19 +445,43 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
             *B.reset_count = total;
             if (B.step_counter && count_step) *B.step_counter += 1;
         }
-        if (total > 0 && warp < R + 1) {          // PF:259: extras rebuilt only when >= 1 env resets
+        if (total > 0) {                          // PF:259: extras rebuilt only when >= 1 env resets
+            // thread t owns slabs t, t + 1024, ...: the (few) slabs with resets fetch their R partial sums in one
+            // go, warps without any skip the reduction; fixed order throughout (deterministic for a geometry)
+            __shared__ double s_stat[32][PF_MAX_REWARD_TERMS];
+            __shared__ long long s_lvl[32];
+            double acc[PF_MAX_REWARD_TERMS];
+#pragma unroll
+            for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) acc[k] = 0.0;
+            long long lvl = 0;
+            bool any = false;
+            for (int i = tid; i < num_slabs; i += 1024) {
+                lvl += S.blk_level[i];
+                if (S.blk_count[i] > 0) {
+                    any = true;
+                    const double* row = S.blk_sums + (size_t)i * PF_MAX_REWARD_TERMS;
+#pragma unroll
+                    for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) if (k < R) acc[k] += row[k];
+                }
+            }
+            const bool warp_any = __any_sync(0xffffffffu, any);
+#pragma unroll
+            for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) {
+                double v = 0.0;
+                if (warp_any && k < R) v = pf_warp_sum(acc[k]);
+                if (lane == 0) s_stat[warp][k] = v;
+            }
+            for (int o = 16; o > 0; o >>= 1) lvl += __shfl_xor_sync(0xffffffffu, lvl, o);
+            if (lane == 0) s_lvl[warp] = lvl;
+            __syncthreads();
             if (warp < R) {
-                double acc = 0.0;
-                for (int i = lane; i < num_slabs; i += 32)
-                    if (S.blk_count[i] > 0) acc += S.blk_sums[(size_t)i * PF_MAX_REWARD_TERMS + warp];
-                acc = pf_warp_sum(acc);
-                if (lane == 0) B.episode_stats[warp] = (float)(acc / (double)total) / P.max_episode_length_s;
-            } else {
-                long long acc = 0;
-                for (int i = lane; i < num_slabs; i += 32) acc += S.blk_level[i];
-                for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+                const double t = pf_warp_sum(s_stat[lane][warp]);
+                if (lane == 0) B.episode_stats[warp] = (float)(t / (double)total) / P.max_episode_length_s;
+            } else if (warp == R) {
+                long long t = s_lvl[lane];
+                for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
                 if (lane == 0) {
-                    B.episode_stats[R] = (float)((double)acc / (double)P.num_envs);
+                    B.episode_stats[R] = (float)((double)t / (double)P.num_envs);
                     B.episode_stats[R + 1] = (float)total;
                 }
             }
@@ -531,9 +576,8 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
     c->canonical = pf_step_mode(P, c->S.rew, getenv("PF_GENERIC_REWARDS") != nullptr, getenv("PF_TABLE_REWARDS") != nullptr);
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_POINTFOOT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_TABLE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
-    PF_CUDA(cudaFuncSetAttribute(pf_post_physics_kernel<PF_MASK_GENERIC, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    c->step_kernel = pf_pick_step_kernel(c->canonical, P.num_height_points > 0);
+    PF_CUDA(cudaFuncSetAttribute(c->step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -553,8 +597,9 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     PF_CUDA(cudaMemset(c->S.blk_count, 0, sizeof(int) * c->max_blocks));
     PF_CUDA(cudaMalloc(&c->d_actions_in, sizeof(float) * (size_t)P.num_envs * P.num_dof));
     PF_CUDA(cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
-    for (cudaEvent_t* e : {&c->ev_fork, &c->ev_in, &c->ev_post, &c->ev_out}) PF_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (cudaEvent_t* e : {&c->ev_fork, &c->ev_in, &c->ev_post, &c->ev_out, &c->ev_fin}) PF_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     c->out_pending = 0;
+    c->fin_pending = 0;
     *out = c;
     return 0;
 }
@@ -564,7 +609,7 @@ extern "C" int pf_ctx_destroy(pf_ctx* c) {
     cudaFree((void*)c->S.noise_vec); cudaFree((void*)c->S.height_points);
     cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
     if (c->io_stream) cudaStreamDestroy(c->io_stream);
-    for (cudaEvent_t e : {c->ev_fork, c->ev_in, c->ev_post, c->ev_out}) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : {c->ev_fork, c->ev_in, c->ev_post, c->ev_out, c->ev_fin}) if (e) cudaEventDestroy(e);
     delete c;
     return 0;
 }
@@ -592,30 +637,52 @@ extern "C" int pf_pd_torques(pf_ctx* c, const pf_env_buffers* bufs, const float*
     const int n = c->P.num_envs * c->P.num_dof;
     int blocks = (n + 255) / 256;
     if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
-    pf_pd_torques_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(c->P, *bufs, actions_in);
-    PF_CUDA(cudaGetLastError());
+    PF_CUDA(pf_launch_pdl(pf_pd_torques_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, c->P, *bufs, actions_in));
     return 0;
 }
 
 static int pf_launch_finalize(pf_ctx* c, const pf_env_buffers* bufs, cudaStream_t st, int count_step) {
     const int blocks = (c->P.num_envs + 1023) / 1024;
-    pf_finalize_kernel<<<blocks, 1024, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp, c->num_slabs, count_step);
-    PF_CUDA(cudaGetLastError());
+    PF_CUDA(pf_launch_pdl(pf_finalize_kernel, dim3(blocks), dim3(1024), 0, st, c->P, *bufs, c->S, c->envs_per_warp, c->num_slabs, count_step));
+    return 0;
+}
+
+// post_physics kernel on `st`; the finalize kernel behind it on `st`, or (side) forked onto the context's io stream so
+// that what the caller queues next on `st` runs beside it.
+static int pf_post_physics_impl(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, cudaStream_t st, bool side) {
+    if (int rc = pf_check_bufs(c, bufs)) return rc;
+    const uint32_t step32 = (uint32_t)common_step_counter;
+    const dim3 g(c->num_blocks), b(c->threads);
+    PF_CUDA(pf_launch_pdl(c->step_kernel, g, b, c->smem_bytes, st, c->P, *bufs, c->S, c->envs_per_warp, step32));
+    if (!side) return pf_launch_finalize(c, bufs, st, 1);
+    PF_CUDA(cudaEventRecord(c->ev_post, st));
+    PF_CUDA(cudaStreamWaitEvent(c->io_stream, c->ev_post, 0));
+    if (int rc = pf_launch_finalize(c, bufs, c->io_stream, 1)) return rc;
+    PF_CUDA(cudaEventRecord(c->ev_fin, c->io_stream));
+    c->fin_pending = 1;
     return 0;
 }
 
 extern "C" int pf_post_physics_step(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
-    if (int rc = pf_check_bufs(c, bufs)) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
-    const uint32_t step32 = (uint32_t)common_step_counter;
-    if (c->canonical == 2)
-        pf_post_physics_kernel<PF_MASK_POINTFOOT, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
-    else if (c->canonical == 1)
-        pf_post_physics_kernel<PF_MASK_TABLE, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
-    else
-        pf_post_physics_kernel<PF_MASK_GENERIC, 2><<<c->num_blocks, c->threads, c->smem_bytes, st>>>(c->P, *bufs, c->S, c->envs_per_warp, step32);
-    PF_CUDA(cudaGetLastError());
-    return pf_launch_finalize(c, bufs, st, 1);
+    return pf_post_physics_impl(c, bufs, common_step_counter, (cudaStream_t)stream, false);
+}
+
+// The same step with its tail (reset id list, device count, extras["episode"] statistics, the step counter) left
+// running on a context-owned stream: the observations, rewards and reset flags are complete in `stream` order, so
+// the policy's act kernel queued next overlaps the finalize kernel.  pf_post_physics_step_join makes `stream` wait for
+// the tail; it must come before anything reads reset_ids / reset_count / episode_stats / extras_time_outs, before
+// the next step of this context, and before a stream capture ends.
+extern "C" int pf_post_physics_step_begin(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
+    return pf_post_physics_impl(c, bufs, common_step_counter, (cudaStream_t)stream, true);
+}
+
+extern "C" int pf_post_physics_step_join(pf_ctx* c, void* stream) {
+    if (!c) return pf_fail(1, "%s", "pf_post_physics_step_join: null context");
+    if (c->fin_pending) {
+        PF_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->ev_fin, 0));
+        c->fin_pending = 0;
+    }
+    return 0;
 }
 
 extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream) {
@@ -765,7 +832,10 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
     for (int i = 0; i < P.decimation; ++i)
         if (int rc = pf_pd_torques(c, bufs, i == 0 ? (const float*)c->d_actions_in : nullptr, stream)) return rc;
     if (forked) PF_CUDA(cudaStreamWaitEvent(st, c->ev_in, 0));
-    if (int rc = pf_post_physics_step(c, bufs, common_step_counter, stream)) return rc;
+    // pinned buffers + side stream: the finalize kernel goes to the side stream too (in front of the scatter), off the
+    // path of what the caller queues next on `stream`
+    const bool side_tail = mapped && !(dbg & 8) && !(dbg & 2);
+    if (int rc = pf_post_physics_impl(c, bufs, common_step_counter, st, side_tail)) return rc;
 
     // ---- out ----  (pinned: on io_stream, so that work the caller queues next -- the policy -- overlaps the transfer)
     if (!(dbg & 2)) {
@@ -777,14 +847,17 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
         add(out, bufs->reset_buf, reset_host, N, false);
         if (torques_host) add(out, bufs->torques, torques_host, sizeof(float) * N * P.num_dof, false);
         if (mapped) {
-            PF_CUDA(cudaEventRecord(c->ev_post, st));
-            PF_CUDA(cudaStreamWaitEvent(io, c->ev_post, 0));
+            if (!side_tail) {                                    // (side_tail: io already waits for the step kernel)
+                PF_CUDA(cudaEventRecord(c->ev_post, st));
+                PF_CUDA(cudaStreamWaitEvent(io, c->ev_post, 0));
+            }
             pf_host_io_kernel<<<io_grid(sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs), out.nseg), 256, 0, io>>>(out);
             PF_CUDA(cudaGetLastError());
             PF_CUDA(cudaEventRecord(c->ev_out, io));
             c->out_pending = 1;
-            if (join) { PF_CUDA(cudaStreamWaitEvent(st, c->ev_out, 0)); c->out_pending = 0; }
+            if (join) { PF_CUDA(cudaStreamWaitEvent(st, c->ev_out, 0)); c->out_pending = 0; c->fin_pending = 0; }
         } else {
+            if (c->fin_pending) { PF_CUDA(cudaStreamWaitEvent(st, c->ev_fin, 0)); c->fin_pending = 0; }
             PF_CUDA(cudaMemcpyAsync(obs_host, bufs->obs_buf, sizeof(float) * N * P.num_obs, D2H, st));
             if (priv_obs_host && bufs->priv_obs_buf)
                 PF_CUDA(cudaMemcpyAsync(priv_obs_host, bufs->priv_obs_buf, sizeof(float) * N * P.num_priv_obs, D2H, st));
@@ -827,6 +900,10 @@ extern "C" int pf_step_host_join(pf_ctx* c, void* stream) {
     if (c->out_pending) {
         PF_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->ev_out, 0));
         c->out_pending = 0;
+    }
+    if (c->fin_pending) {
+        PF_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, c->ev_fin, 0));
+        c->fin_pending = 0;
     }
     return 0;
 }

@@ -450,55 +450,77 @@ PF_HD float pf_reward_term(const pf_params& P, const PfRewTab& T, const int id, 
     return r;
 }
 
+// Everything the step reads from env-owned global buffers, as one bundle of independent loads: issued together (and,
+// in the kernel, BEFORE the wait for the staged PhysX rows, so the two round trips to memory overlap).  Left where
+// the values are used, each load sits behind an earlier store the compiler must assume aliases it, and the step pays
+// ~60 memory latencies one after another.  Loops run to the compile-time maxima under a guard so that every array
+// lives in registers.
+struct PfEnvPre {
+    float es[PF_REW_COUNT];           // episode sums by term id (kMask != GENERIC)
+    float es_term;
+    float tq[PF_MAX_DOF], ldv[PF_MAX_DOF], la[PF_MAX_DOF], ac[PF_MAX_DOF];
+    bool fc_old[PF_NUM_FEET], cfilt_old[PF_NUM_FEET], lc_old[PF_NUM_FEET];
+    float fat_old[PF_NUM_FEET], lfat_old[PF_NUM_FEET], lmfh_old[PF_NUM_FEET], cmfh_old[PF_NUM_FEET];
+    float cmd_old[4];
+    long long ep_len_old;
+};
+
+template <uint32_t kMask>
+PF_HD void pf_env_preload(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, PfEnvPre& pre) {
+    constexpr bool kFast = kMask != PF_MASK_GENERIC;
+    const int D = kFast ? PF_MAX_DOF : P.num_dof;
+    const int N = P.num_envs;
+    if (kFast) {
+        const float* es_in = B.episode_sums + e;
+#define PF_X(ID) pre.es[ID] = pf_term_on<kMask, ID>(T) ? es_in[pf_term_off<kMask, ID>(T, N)] : 0.0f;
+        PF_REWARD_CANON(PF_X)
+#undef PF_X
+    }
+    pre.es_term = P.has_termination_term ? B.episode_sums[(size_t)P.num_reward_terms * N + e] : 0.0f;
+#pragma unroll
+    for (int d = 0; d < PF_MAX_DOF; ++d) {
+        const bool ok = d < D;
+        pre.tq[d] = ok ? B.torques[e * D + d] : 0.0f; pre.ldv[d] = ok ? B.last_dof_vel[e * D + d] : 0.0f;
+        pre.la[d] = ok ? B.last_actions[e * D + d] : 0.0f; pre.ac[d] = ok ? B.actions[e * D + d] : 0.0f;
+    }
+#pragma unroll
+    for (int f = 0; f < PF_NUM_FEET; ++f) {
+        const int k = e * PF_NUM_FEET + f;
+        pre.fc_old[f] = B.first_contact[k] != 0; pre.cfilt_old[f] = B.contact_filt[k] != 0; pre.lc_old[f] = B.last_contacts[k] != 0;
+        pre.fat_old[f] = B.feet_air_time[k]; pre.lfat_old[f] = B.last_feet_air_time[k];
+        pre.lmfh_old[f] = B.last_max_feet_height[k];
+        pre.cmfh_old[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pre.cmd_old[i] = i < P.num_commands ? B.commands[e * P.num_commands + i] : 0.0f;
+    pre.ep_len_old = B.episode_length_buf[e];
+}
+
 // post_physics_step up to (and including) reset_idx: PF:204-222.  `e` = local env index, writes go to B.
 // kMask: PF_MASK_GENERIC, PF_MASK_TABLE or a literal term mask (see pf_canon_pos).  Everything but GENERIC is the
 // common shape -- P.num_dof == PF_MAX_DOF and P.reward_ids in canonical order (pf_build_reward_table returned true
 // for T) -> straight-line reward sum, no guards.
 template <uint32_t kMask>
 PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
-                         uint32_t step, float* sums_out /* [R] scaled reward terms of this step or NULL */,
-                         PfEnvOut& out) {
+                         const PfEnvPre& pre, uint32_t step,
+                         float* sums_out /* [R] scaled reward terms of this step or NULL */, PfEnvOut& out) {
     constexpr bool kFast = kMask != PF_MASK_GENERIC;
     constexpr bool kCanon = kFast;
     constexpr int kD = kFast ? PF_MAX_DOF : 0;
     const int D = kFast ? PF_MAX_DOF : P.num_dof;
     const float dt = P.dt;
     const int N = P.num_envs;
-    // Everything the step reads from env-owned global buffers, loaded up front: the loads are independent of each
-    // other, so they are all in flight together.  Left where they are used, each one sits behind an earlier store
-    // the compiler must assume aliases it, and the step pays ~60 memory latencies one after another.
-    // Loops run to the compile-time maxima under a guard so that every array below lives in registers.
     const int R_terms = P.num_reward_terms;
-    float es[PF_REW_COUNT];                       // indexed by term id (a compile-time constant where it is used)
-    if (kCanon) {
-        const float* es_in = B.episode_sums + e;
-#define PF_X(ID) es[ID] = pf_term_on<kMask, ID>(T) ? es_in[pf_term_off<kMask, ID>(T, N)] : 0.0f;
-        PF_REWARD_CANON(PF_X)
-#undef PF_X
-    }
-    const float es_term = P.has_termination_term ? B.episode_sums[(size_t)R_terms * N + e] : 0.0f;
-    float tq_[PF_MAX_DOF], ldv_[PF_MAX_DOF], la_[PF_MAX_DOF];
+    const float* es = pre.es;
+    const float es_term = pre.es_term;
+    const float *tq_ = pre.tq, *ldv_ = pre.ldv, *la_ = pre.la;
 #pragma unroll
-    for (int d = 0; d < PF_MAX_DOF; ++d) {
-        const bool ok = d < D;
-        tq_[d] = ok ? B.torques[e * D + d] : 0.0f; ldv_[d] = ok ? B.last_dof_vel[e * D + d] : 0.0f;
-        la_[d] = ok ? B.last_actions[e * D + d] : 0.0f; out.actions[d] = ok ? B.actions[e * D + d] : 0.0f;
-    }
-    bool fc_old_[PF_NUM_FEET], cfilt_old_[PF_NUM_FEET], lc_old_[PF_NUM_FEET];
-    float fat_old_[PF_NUM_FEET], lfat_old_[PF_NUM_FEET], lmfh_old_[PF_NUM_FEET], cmfh_old_[PF_NUM_FEET];
-#pragma unroll
-    for (int f = 0; f < PF_NUM_FEET; ++f) {
-        const int k = e * PF_NUM_FEET + f;
-        fc_old_[f] = B.first_contact[k] != 0; cfilt_old_[f] = B.contact_filt[k] != 0; lc_old_[f] = B.last_contacts[k] != 0;
-        fat_old_[f] = B.feet_air_time[k]; lfat_old_[f] = B.last_feet_air_time[k];
-        lmfh_old_[f] = B.last_max_feet_height[k];
-        cmfh_old_[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
-    }
-    float cmd_old_[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) cmd_old_[i] = i < P.num_commands ? B.commands[e * P.num_commands + i] : 0.0f;
+    for (int d = 0; d < PF_MAX_DOF; ++d) out.actions[d] = pre.ac[d];
+    const bool *fc_old_ = pre.fc_old, *cfilt_old_ = pre.cfilt_old, *lc_old_ = pre.lc_old;
+    const float *fat_old_ = pre.fat_old, *lfat_old_ = pre.lfat_old, *lmfh_old_ = pre.lmfh_old, *cmfh_old_ = pre.cmfh_old;
+    const float* cmd_old_ = pre.cmd_old;
     // ---- PF:204 ----
-    const long long ep_len = B.episode_length_buf[e] + 1;
+    const long long ep_len = pre.ep_len_old + 1;
 
     // ---- PF:208-211 base quantities ----
     const float* q = in.root + 3;
@@ -646,9 +668,10 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
 // `mode`: 0 generic, 1 table, 2 the literal pointfoot mask (the caller checked that it applies)
 PF_HD void pf_env_step(const pf_params& P, const pf_env_buffers& B, const PfRewTab& T, int e, const PfEnvIn& in,
                        uint32_t step, float* sums_out, PfEnvOut& out, int mode) {
-    if (mode == 2) pf_env_step_t<PF_MASK_POINTFOOT>(P, B, T, e, in, step, sums_out, out);
-    else if (mode == 1) pf_env_step_t<PF_MASK_TABLE>(P, B, T, e, in, step, sums_out, out);
-    else pf_env_step_t<PF_MASK_GENERIC>(P, B, T, e, in, step, sums_out, out);
+    PfEnvPre pre;
+    if (mode == 2) { pf_env_preload<PF_MASK_POINTFOOT>(P, B, T, e, pre); pf_env_step_t<PF_MASK_POINTFOOT>(P, B, T, e, in, pre, step, sums_out, out); }
+    else if (mode == 1) { pf_env_preload<PF_MASK_TABLE>(P, B, T, e, pre); pf_env_step_t<PF_MASK_TABLE>(P, B, T, e, in, pre, step, sums_out, out); }
+    else { pf_env_preload<PF_MASK_GENERIC>(P, B, T, e, pre); pf_env_step_t<PF_MASK_GENERIC>(P, B, T, e, in, pre, step, sums_out, out); }
 }
 
 // which statement of the step applies to P (and env overrides for tests: force the table / the generic one)

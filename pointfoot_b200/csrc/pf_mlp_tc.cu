@@ -99,6 +99,7 @@ struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_byt
 static inline int pad16(int x) { return (x + 15) & ~15; }
 
 #include "pf_tc_ptx.cuh"
+#include "pf_launch.h"
 
 // ------------------------------------------------------------------------------------------------ kernel
 enum { TC_OUT_PLAIN = 0, TC_OUT_SAMPLE = 1, TC_OUT_VALUE = 2 };
@@ -269,6 +270,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + TC_NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int items = a.nnets * a.tiles;
+    pf_grid_dep_launch();       // the prologue below (barriers, TMEM, ones operand) runs under the predecessor's tail
 
     if (warp == TC_LOAD_WARP && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
@@ -287,6 +289,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pf_grid_dep_wait();         // first global access (observations, packed weights) comes after this
 
     if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
@@ -795,8 +798,8 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     const int items = a.nnets * a.tiles;
     if (items == 0) return 0;
     const int grid = items < c->num_sms ? items : c->num_sms;
-    pf_mlp_tc_kernel<<<grid, TC_THREADS, t->smem_bytes[variant], st>>>(a);
-    return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
+    return pf_launch_pdl(pf_mlp_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
+               ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }
 
 int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x, long long ldx, int rows, float* out,

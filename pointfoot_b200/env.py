@@ -258,9 +258,19 @@ class PointFoot:
         st = self._stream()
         if self.cfg.domain_rand.push_robots and self.common_step_counter % self.push_interval == 0:
             self._push_robots(st)
+        if getattr(self, "_defer_tail", False):
+            # GraphedStep with a policy: the step's tail (reset id list, count, extras["episode"]) runs on the context's
+            # side stream beside the policy kernel; join_tail() makes this stream wait for it
+            capi.check(self._lib.pf_post_physics_step_begin(self._ctx, C.byref(self._bufs), C.c_int64(self.common_step_counter), st),
+                       "pf_post_physics_step_begin")
+            return
         capi.check(self._lib.pf_post_physics_step(self._ctx, C.byref(self._bufs), C.c_int64(self.common_step_counter), st),
                    "pf_post_physics_step")
         self._notify_gym_of_resets()
+
+    def join_tail(self):
+        """make the current stream wait for a deferred step tail (pf_post_physics_step_begin / _join)"""
+        capi.check(self._lib.pf_post_physics_step_join(self._ctx, self._stream()), "pf_post_physics_step_join")
 
     def _push_robots(self, st):
         """point_foot.py:590-611."""
@@ -333,9 +343,17 @@ class GraphedStep:
         self.launches_per_step = None
 
     def _eager(self):
-        out = self.env.step(self.actions)
-        if self.extra is not None:
+        if self.extra is None:
+            return self.env.step(self.actions)
+        # step + policy: the policy's act kernel needs the observations only, so the step's tail (reset ids, count,
+        # episode statistics) is left running beside it and joined before the graph ends
+        self.env._defer_tail = True
+        try:
+            out = self.env.step(self.actions)
             self.extra()
+            self.env.join_tail()
+        finally:
+            self.env._defer_tail = False
         return out
 
     def _push_due(self):

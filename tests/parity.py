@@ -64,8 +64,14 @@ class EnvUnderTest:
                                                   stream), "pf_pd_torques")
                 if physics is not None:
                     physics(self)
-            capi.check(self.lib.pf_post_physics_step(self.ctx, C.byref(self.b), C.c_int64(self.step_counter), stream),
-                       "pf_post_physics_step")
+            if getattr(self, "split_tail", False):     # tail on the context's side stream, other work queued beside it
+                capi.check(self.lib.pf_post_physics_step_begin(self.ctx, C.byref(self.b), C.c_int64(self.step_counter), stream),
+                           "pf_post_physics_step_begin")
+                self.t["obs_buf"].sum()
+                capi.check(self.lib.pf_post_physics_step_join(self.ctx, stream), "pf_post_physics_step_join")
+            else:
+                capi.check(self.lib.pf_post_physics_step(self.ctx, C.byref(self.b), C.c_int64(self.step_counter), stream),
+                           "pf_post_physics_step")
             torch.cuda.synchronize()
         else:
             for i in range(self.P.decimation):

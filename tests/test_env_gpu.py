@@ -85,6 +85,29 @@ def test_reward_statements_and_cta_sizes_agree_bit_for_bit(monkeypatch):
             assert torch.equal(v, outs[0][k]), k
 
 
+def test_split_tail_equals_plain_step():
+    """pf_post_physics_step_begin / _join (reset ids, count, episode statistics on the context's side stream, beside
+    whatever the caller queues next) leaves exactly what pf_post_physics_step leaves, over several steps."""
+    from pointfoot_b200 import synth
+    state = synth.make_state(5000, "pointfoot_rough", seed=9)
+    envs = []
+    for split in (False, True):
+        e = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=9)
+        e.split_tail = split
+        for k in range(4):
+            e.step(state["actions"] * (1.0 - 0.2 * k))
+        envs.append(e)
+    n = int(envs[0].t["reset_count"])
+    assert n > 0 and n == int(envs[1].t["reset_count"])
+    for name in ("obs_buf", "priv_obs_buf", "rew_buf", "reset_buf", "episode_sums", "episode_stats", "root_states",
+                 "terrain_levels", "extras_time_outs"):
+        if name in envs[0].t and envs[0].t[name] is not None:
+            assert torch.equal(envs[0].t[name], envs[1].t[name]), name
+    assert torch.equal(envs[0].t["reset_ids"][:n], envs[1].t["reset_ids"][:n])
+    for e in envs:
+        e.close()
+
+
 def test_sharded_equals_unsharded():
     """env_id_offset: RNG draws are functions of the global env id, so two half shards == one full run."""
     import common
