@@ -282,7 +282,7 @@ def kernel_roofline(env, steps, flush, peaks, task):
             traffic = json.load(f).get(f"{task}:{env.num_envs}", {}).get("bytes")
     except (OSError, ValueError):
         pass
-    return {"bound": "hbm", "kernel": "pf_post_physics_kernel(+pf_finalize_kernel)", "achieved": achieved,
+    return {"bound": "hbm", "kernel": "pf_post_physics_kernel(+pf_finalize_kernel" + (", pf_height_scan_kernel" if env._P.num_height_points > 0 else "") + ")", "achieved": achieved,
             "peak": peak, "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "us_per_launch": ms * 1e3,
             "algorithmic_bytes_per_launch": nbytes}
@@ -382,7 +382,9 @@ def run_b200(args):
     policy = make_policy(env, train_cfg, args)
     actions = policy.actions if policy is not None else torch.zeros(env.num_envs, env.num_actions, device=device)
     extra = (lambda: policy.act_into(env, actions)) if policy is not None else None
-    launches_per_step = cfg.control.decimation + 2 + (policy.launches_per_act if policy is not None else 0)
+    # decimation x pf_pd_torques, [pf_height_scan_kernel when the task measures heights], pf_post_physics_kernel, pf_finalize_kernel
+    launches_per_step = (cfg.control.decimation + 2 + (1 if env._P.num_height_points > 0 else 0)
+                         + (policy.launches_per_act if policy is not None else 0))
     env.reset()
     if args.no_graph:
         def step_fn():

@@ -10,6 +10,7 @@ struct PfCtxScratch {
     int* blk_count;        // [num_slabs] resets in the warp slab (envs_per_warp consecutive envs)
     long long* blk_level;  // [num_slabs] sum of terrain levels in the slab
     double* blk_sums;      // [num_slabs][PF_MAX_REWARD_TERMS] episode sums of the slab's reset envs (valid iff count > 0)
+    float* height_mean;    // [num_envs] mean_p (root_z - measured_heights[p]): pf_height_scan_kernel -> step kernel
     const float* noise_vec;       // [max(num_obs, num_priv_obs)]
     const float* height_points;   // [P][2]
     PfRewTab rew;                 // reward terms by id (row, scale): constant-bank operands of the step kernel

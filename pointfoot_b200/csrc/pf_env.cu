@@ -128,6 +128,52 @@ __device__ __forceinline__ double pf_scan_env(const pf_params& P, const pf_env_b
     return want_sum ? pf_warp_sum(acc) : 0.0;
 }
 
+__device__ __forceinline__ void pf_scan_lane_load(const pf_params& P, const PfCtxScratch& S, int lane, PfScanLane& L) {
+    const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
+#pragma unroll
+    for (int k = 0; k < PF_MAX_HEIGHT_POINTS / 32; ++k) {
+        const int p = lane + 32 * k;
+        const bool ok = p < Pn;
+        const float2 g = ok ? reinterpret_cast<const float2*>(S.height_points)[p] : make_float2(0.f, 0.f);
+        L.gx[k] = g.x; L.gy[k] = g.y;
+        L.ns[k] = ok ? S.noise_vec[base_w + p] : 0.0f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K2a
+// _get_heights (PF:1048-1075, 1100-1112) + the height columns of both observation buffers (PF:367-369, 328-338,
+// 189-192) + the base-height mean of _reward_base_height (PF:1144-1147), for every env: one WARP per env, lanes =
+// scan points.  A kernel of its own because it wants the opposite of the step kernel: few registers, every warp
+// slot of the SM filled, tens of thousands of independent gathers in flight against the L2-resident heightfield.
+// The step kernel (launched behind it) only reads height_mean[e].
+template <bool kFast>
+__global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params P, const pf_env_buffers B,
+                                                             const PfCtxScratch S, const uint32_t step_arg) {
+    const int lane = threadIdx.x & 31;
+    const int gw = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), nw = (int)((gridDim.x * blockDim.x) >> 5);
+    pf_grid_dep_launch();
+    PfScanLane L;
+    pf_scan_lane_load(P, S, lane, L);                   // constants of the context: not written by any kernel
+    pf_grid_dep_wait();
+    const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
+    const uint32_t key0 = pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE);
+    const double inv_n = (double)P.num_height_points;
+    for (int e = gw; e < P.num_envs; e += nw) {
+        const float* g = B.root_states + (size_t)e * 13;
+        const float mine = lane < 7 ? g[lane] : 0.0f;    // pos xyz + quat xyzw: one coalesced 28-byte read
+        float r3[3], q[4];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) r3[i] = __shfl_sync(0xffffffffu, mine, i);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) q[i] = __shfl_sync(0xffffffffu, mine, 3 + i);
+        float zn, wn;
+        pf_yaw_quat(q, zn, wn);
+        const uint32_t nkey = pf_rng_env_key(key0, (uint32_t)(P.env_id_offset + e));
+        const double sum = pf_scan_env<true, kFast>(P, B, L, r3, zn, wn, r3[2], nkey, e, lane, true, &S.rew);
+        if (lane == 0) S.height_mean[e] = (float)(sum / inv_n);
+    }
+}
+
 // Warp partials for extras["episode"] (PF:276-288): count, terrain-level sum, per-term episode sums of the
 // warp's reset envs (read back BEFORE pf_env_reset zeroes them).  Entry index = global warp-slab index.
 __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_env_buffers& B, const PfCtxScratch& S,
@@ -167,9 +213,8 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 // kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
 // spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r2_step_kernel_sweeps.txt):
 // the spills cost more than the extra resident warps hide.
-// kScan: the task measures terrain heights (num_height_points > 0).  The plane task's kernel carries no scan code
-// and issues the per-env loads in front of the wait for the staged rows; the scan task issues them behind the scan,
-// which would otherwise hold ~70 registers across it.
+// kScan: the task measures terrain heights (num_height_points > 0): pf_height_scan_kernel ran in front of this
+// kernel and left height_mean[e]; only the envs that reset redo their scan here (phase 4).
 template <uint32_t kMask, int kMinB, bool kScan>
 __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
@@ -225,7 +270,7 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     float feet[6];
     PfEnvPre pre;
     if (active) {
-        if (!kScan) pf_env_preload<kMask>(P, B, S.rew, e, pre);       // in flight together with the staging above
+        pf_env_preload<kMask>(P, B, S.rew, e, pre);       // in flight together with the staging above
         for (int f = 0; f < PF_NUM_FEET; ++f) {
             const float* g = B.rigid_body_states + ((size_t)e * NB + P.feet_indices[f]) * 13;
             feet[3 * f] = __ldg(g); feet[3 * f + 1] = __ldg(g + 1); feet[3 * f + 2] = __ldg(g + 2);
@@ -235,41 +280,13 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     __syncwarp();
     if (bulk) mbar_wait(smem_u32(s.bar), 0);
 
-    // ---- phase 1: height scan ----
-    float height_mean = 0.0f;
-    PfScanLane L;
-    if (kScan) {
-#pragma unroll
-        for (int k = 0; k < PF_MAX_HEIGHT_POINTS / 32; ++k) {
-            const int p = lane + 32 * k;
-            const bool ok = p < Pn;
-            const float2 g = ok ? reinterpret_cast<const float2*>(S.height_points)[p] : make_float2(0.f, 0.f);
-            L.gx[k] = g.x; L.gy[k] = g.y;
-            L.ns[k] = ok ? S.noise_vec[base_w + p] : 0.0f;
-        }
-        if (active) {
-            float zn, wn;
-            pf_yaw_quat(s.root + lane * 13 + 3, zn, wn);
-            s.misc[4 * lane] = zn; s.misc[4 * lane + 1] = wn;
-            s.misc[4 * lane + 3] = __uint_as_float(nkey);
-        }
-        __syncwarp();
-        const bool want_sum = true;
-        double hsum = 0.0;
-        for (int i = 0; i < nenv; ++i) {
-            const float* r = s.root + i * 13;
-            const double sum = pf_scan_env<true, kFast>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], r[2],
-                                                        __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, want_sum, &S.rew);
-            if (lane == i) hsum = sum;
-        }
-        height_mean = (float)(hsum / (double)Pn);          // one division per lane, after the loop
-    }
+    // ---- phase 1 (height scan) is pf_height_scan_kernel, launched in front of this kernel ----
+    const float height_mean = (kScan && active) ? S.height_mean[e] : 0.0f;
 
     // ---- phase 2: one lane per env ----
     bool is_reset = false;
     PfEnvOut out;
     if (active) {
-        if (kScan) pf_env_preload<kMask>(P, B, S.rew, e, pre);
         PfEnvIn in;
         in.root = s.root + lane * 13;
         in.dof = s.dof + lane * 2 * D;
@@ -360,12 +377,18 @@ __global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(cons
     // ---- phase 4: height columns of the envs that reset ----
     if (kScan && (P.measure_heights_actor || P.measure_heights_critic)) {
         unsigned m = __ballot_sync(0xffffffffu, is_reset);
-        while (m) {
-            const int i = __ffs(m) - 1;
-            m &= m - 1;
-            const float* r = s.root + i * 13;
-            pf_scan_env<true, kFast>(P, B, L, r, s.misc[4 * i], s.misc[4 * i + 1], s.misc[4 * i + 2],
-                                     __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane, false, &S.rew);
+        if (m) {
+            PfScanLane L;
+            pf_scan_lane_load(P, S, lane, L);
+            while (m) {
+                const int i = __ffs(m) - 1;
+                m &= m - 1;
+                const float* r = s.root + i * 13;
+                float zn, wn;
+                pf_yaw_quat(r + 3, zn, wn);
+                pf_scan_env<true, kFast>(P, B, L, r, zn, wn, s.misc[4 * i + 2], __float_as_uint(s.misc[4 * i + 3]), e0 + i,
+                                         lane, false, &S.rew);
+            }
         }
     }
 }
@@ -589,6 +612,7 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
         if (!height_points_xy_host) { delete c; return pf_fail(1, "pf_ctx_create: %s", "height points missing"); }
         PF_CUDA(cudaMemcpy(d_pts, height_points_xy_host, sizeof(float) * 2 * P.num_height_points, cudaMemcpyHostToDevice));
     }
+    PF_CUDA(cudaMalloc(&c->S.height_mean, sizeof(float) * (size_t)P.num_envs));
     c->S.noise_vec = d_noise;
     c->S.height_points = d_pts;
     PF_CUDA(cudaMalloc(&c->S.blk_count, sizeof(int) * c->max_blocks));
@@ -607,7 +631,7 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
 extern "C" int pf_ctx_destroy(pf_ctx* c) {
     if (!c) return 0;
     cudaFree((void*)c->S.noise_vec); cudaFree((void*)c->S.height_points);
-    cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
+    cudaFree(c->S.height_mean); cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
     if (c->io_stream) cudaStreamDestroy(c->io_stream);
     for (cudaEvent_t e : {c->ev_fork, c->ev_in, c->ev_post, c->ev_out, c->ev_fin}) if (e) cudaEventDestroy(e);
     delete c;
@@ -653,6 +677,13 @@ static int pf_post_physics_impl(pf_ctx* c, const pf_env_buffers* bufs, int64_t c
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     const uint32_t step32 = (uint32_t)common_step_counter;
     const dim3 g(c->num_blocks), b(c->threads);
+    if (c->P.num_height_points > 0) {
+        const int warps = c->P.num_envs;
+        int blocks = (warps + 7) / 8;
+        if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
+        if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, step32));
+        else PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<false>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, step32));
+    }
     PF_CUDA(pf_launch_pdl(c->step_kernel, g, b, c->smem_bytes, st, c->P, *bufs, c->S, c->envs_per_warp, step32));
     if (!side) return pf_launch_finalize(c, bufs, st, 1);
     PF_CUDA(cudaEventRecord(c->ev_post, st));
