@@ -212,7 +212,8 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
 // kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
 // spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r2_step_kernel_sweeps.txt):
-// the spills cost more than the extra resident warps hide.
+// the spills cost more than the extra resident warps hide.  A larger shared-memory carve-out is slower as well: the
+// per-env loads of the [N,6] / [N,2] state arrays (24- and 8-byte strides per lane) live off L1 sector reuse.
 // kScan: the task measures terrain heights (num_height_points > 0): pf_height_scan_kernel ran in front of this
 // kernel and left height_mean[e]; only the envs that reset redo their scan here (phase 4).
 template <uint32_t kMask, int kMinB, bool kScan>
@@ -591,7 +592,7 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->envs_per_warp = pf_pick_epw(P.num_envs, c->num_sms);
     c->num_slabs = (P.num_envs + c->envs_per_warp - 1) / c->envs_per_warp;
     // CTA size of the step kernel: warps are independent, so a small batch is cut into small CTAs that reach every SM
-    c->threads = PF_THREADS;
+    c->threads = 128;          // measured: 128-thread CTAs beat 256 at large batches too (finer-grained SM fill)
     while (c->threads > 32 && (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32) < 2 * c->num_sms) c->threads >>= 1;
     if (const char* e = getenv("PF_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128 || v == 256) c->threads = v; }
     c->num_blocks = (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32);
