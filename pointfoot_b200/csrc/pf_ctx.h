@@ -10,6 +10,9 @@ struct PfCtxScratch {
     int* blk_count;        // [num_slabs] resets in the warp slab (envs_per_warp consecutive envs)
     long long* blk_level;  // [num_slabs] sum of terrain levels in the slab
     double* blk_sums;      // [num_slabs][PF_MAX_REWARD_TERMS] episode sums of the slab's reset envs (valid iff count > 0)
+    double* cta_sums;      // [finalize CTAs][PF_MAX_REWARD_TERMS] per-CTA partials of the episode statistics
+    long long* cta_lvl;    // [finalize CTAs]
+    int* ticket;           // last-CTA-done counter of the finalize kernel (left at 0)
     float* height_mean;    // [num_envs] mean_p (root_z - measured_heights[p]): pf_height_scan_kernel -> step kernel
     const float* noise_vec;       // [max(num_obs, num_priv_obs)]
     const float* height_points;   // [P][2]

@@ -437,16 +437,30 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
                                                            const PfCtxScratch S, const int epw,
                                                            const int num_slabs, const int count_step) {
     __shared__ int s_before[32], s_total[32], s_flags[32];
+    __shared__ double s_stat[32][PF_MAX_REWARD_TERMS];
+    __shared__ long long s_lvl[32];
+    __shared__ int s_last;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     pf_grid_dep_launch();
     pf_grid_dep_wait();
 
-    // One pass over the step kernel's per-slab counts gives both the number of resets in front of this CTA's envs
-    // and the total; one barrier; every warp then reduces the 32 per-warp partials itself (no serial loops).
-    const int before = (int)(((long long)blockIdx.x * 1024) / epw);
+    // One pass over the step kernel's per-slab counts (128-bit loads: `before` is a multiple of 32) gives both the
+    // number of resets in front of this CTA's envs and the total; one barrier; every warp then reduces the 32
+    // per-warp partials itself (no serial loops).
+    const int spc = 1024 / epw;                             // slabs per CTA
+    const int before = blockIdx.x * spc;
     int part_b = 0, part_t = 0;
-    for (int i = tid; i < num_slabs; i += 1024) {
+    const int n4 = num_slabs >> 2;
+    const int4* c4 = reinterpret_cast<const int4*>(S.blk_count);
+#pragma unroll 2
+    for (int i = tid; i < n4; i += 1024) {
+        const int4 c = c4[i];
+        const int sum = (c.x + c.y) + (c.z + c.w);
+        part_t += sum;
+        part_b += 4 * i < before ? sum : 0;
+    }
+    for (int i = 4 * n4 + tid; i < num_slabs; i += 1024) {
         const int c = S.blk_count[i];
         part_t += c;
         part_b += i < before ? c : 0;
@@ -454,6 +468,13 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int e = blockIdx.x * 1024 + tid;
     const bool flag = e < P.num_envs && B.reset_buf[e] != 0;
     const bool tmo = e < P.num_envs && B.time_out_buf[e] != 0;
+    // this CTA's own slabs, for the episode statistics: thread t < spc owns slab before + t
+    // (solo: few enough slabs for CTA 0 to own them all -- small batches skip the ticket round trip)
+    const bool solo = num_slabs <= 1024;
+    const int my_slab = solo ? tid : before + tid;
+    const bool own = solo ? (blockIdx.x == 0 && tid < num_slabs) : (tid < spc && my_slab < num_slabs);
+    const int my_count = own ? S.blk_count[my_slab] : 0;
+    long long lvl = own ? S.blk_level[my_slab] : 0;
     const unsigned m = __ballot_sync(0xffffffffu, flag);
     part_b = __reduce_add_sync(0xffffffffu, part_b);
     part_t = __reduce_add_sync(0xffffffffu, part_t);
@@ -463,52 +484,68 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int off = __reduce_add_sync(0xffffffffu, s_before[lane] + (lane < warp ? s_flags[lane] : 0));
     if (B.extras_time_outs && total > 0 && e < P.num_envs) B.extras_time_outs[e] = tmo;
     if (flag) B.reset_ids[off + __popc(m & ((1u << lane) - 1u))] = e;
+    if (blockIdx.x == 0 && tid == 0) {
+        *B.reset_count = total;
+        if (B.step_counter && count_step) *B.step_counter += 1;
+    }
+    if (total == 0) return;                       // PF:259: extras rebuilt only when >= 1 env resets (uniform over the grid)
+    if (solo && blockIdx.x != 0) return;
 
-    if (blockIdx.x == 0) {
-        if (tid == 0) {
-            *B.reset_count = total;
-            if (B.step_counter && count_step) *B.step_counter += 1;
+    // extras["episode"] (PF:276-288): every CTA reduces the partials of its own slabs in a fixed order and publishes
+    // them; the CTA that draws the last ticket adds the CTA partials up in CTA order.  Deterministic for a geometry,
+    // no float atomics, no CTA that walks every slab.
+    const int nw = solo ? 32 : (spc + 31) >> 5;   // warps that own slabs
+    if (warp < nw) {
+        const bool any = __any_sync(0xffffffffu, my_count > 0);
+        const double* row = S.blk_sums + (size_t)my_slab * PF_MAX_REWARD_TERMS;
+        for (int k = 0; k < R; ++k) {
+            double v = 0.0;
+            if (any) v = pf_warp_sum(my_count > 0 ? row[k] : 0.0);
+            if (lane == 0) s_stat[warp][k] = v;
         }
-        if (total > 0) {                          // PF:259: extras rebuilt only when >= 1 env resets
-            // thread t owns slabs t, t + 1024, ...: the (few) slabs with resets fetch their R partial sums in one
-            // go, warps without any skip the reduction; fixed order throughout (deterministic for a geometry)
-            __shared__ double s_stat[32][PF_MAX_REWARD_TERMS];
-            __shared__ long long s_lvl[32];
-            double acc[PF_MAX_REWARD_TERMS];
-#pragma unroll
-            for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) acc[k] = 0.0;
-            long long lvl = 0;
-            bool any = false;
-            for (int i = tid; i < num_slabs; i += 1024) {
-                lvl += S.blk_level[i];
-                if (S.blk_count[i] > 0) {
-                    any = true;
-                    const double* row = S.blk_sums + (size_t)i * PF_MAX_REWARD_TERMS;
-#pragma unroll
-                    for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) if (k < R) acc[k] += row[k];
-                }
+        for (int o = 16; o > 0; o >>= 1) lvl += __shfl_xor_sync(0xffffffffu, lvl, o);
+        if (lane == 0) s_lvl[warp] = lvl;
+    }
+    __syncthreads();
+    if (warp < R) {
+        const double t = pf_warp_sum(lane < nw ? s_stat[lane][warp] : 0.0);
+        if (lane == 0) {
+            if (solo) B.episode_stats[warp] = (float)(t / (double)total) / P.max_episode_length_s;
+            else S.cta_sums[(size_t)blockIdx.x * PF_MAX_REWARD_TERMS + warp] = t;
+        }
+    } else if (warp == R) {
+        long long t = lane < nw ? s_lvl[lane] : 0;
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0) {
+            if (solo) {
+                B.episode_stats[R] = (float)((double)t / (double)P.num_envs);
+                B.episode_stats[R + 1] = (float)total;
+            } else {
+                S.cta_lvl[blockIdx.x] = t;
             }
-            const bool warp_any = __any_sync(0xffffffffu, any);
-#pragma unroll
-            for (int k = 0; k < PF_MAX_REWARD_TERMS; ++k) {
-                double v = 0.0;
-                if (warp_any && k < R) v = pf_warp_sum(acc[k]);
-                if (lane == 0) s_stat[warp][k] = v;
-            }
-            for (int o = 16; o > 0; o >>= 1) lvl += __shfl_xor_sync(0xffffffffu, lvl, o);
-            if (lane == 0) s_lvl[warp] = lvl;
-            __syncthreads();
-            if (warp < R) {
-                const double t = pf_warp_sum(s_stat[lane][warp]);
-                if (lane == 0) B.episode_stats[warp] = (float)(t / (double)total) / P.max_episode_length_s;
-            } else if (warp == R) {
-                long long t = s_lvl[lane];
-                for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-                if (lane == 0) {
-                    B.episode_stats[R] = (float)((double)t / (double)P.num_envs);
-                    B.episode_stats[R + 1] = (float)total;
-                }
-            }
+        }
+    }
+    if (solo) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(S.ticket, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int nc = (int)gridDim.x;
+    if (warp < R) {
+        double acc = 0.0;
+        for (int c = lane; c < nc; c += 32) acc += __ldcg(S.cta_sums + (size_t)c * PF_MAX_REWARD_TERMS + warp);
+        acc = pf_warp_sum(acc);
+        if (lane == 0) B.episode_stats[warp] = (float)(acc / (double)total) / P.max_episode_length_s;
+    } else if (warp == R) {
+        long long acc = 0;
+        for (int c = lane; c < nc; c += 32) acc += __ldcg(S.cta_lvl + c);
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) {
+            B.episode_stats[R] = (float)((double)acc / (double)P.num_envs);
+            B.episode_stats[R + 1] = (float)total;
+            *S.ticket = 0;
         }
     }
 }
@@ -620,6 +657,11 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     PF_CUDA(cudaMalloc(&c->S.blk_level, sizeof(long long) * c->max_blocks));
     PF_CUDA(cudaMalloc(&c->S.blk_sums, sizeof(double) * PF_MAX_REWARD_TERMS * c->max_blocks));
     PF_CUDA(cudaMemset(c->S.blk_count, 0, sizeof(int) * c->max_blocks));
+    const int fin_ctas = (P.num_envs + 1023) / 1024;
+    PF_CUDA(cudaMalloc(&c->S.cta_sums, sizeof(double) * PF_MAX_REWARD_TERMS * fin_ctas));
+    PF_CUDA(cudaMalloc(&c->S.cta_lvl, sizeof(long long) * fin_ctas));
+    PF_CUDA(cudaMalloc(&c->S.ticket, sizeof(int)));
+    PF_CUDA(cudaMemset(c->S.ticket, 0, sizeof(int)));
     PF_CUDA(cudaMalloc(&c->d_actions_in, sizeof(float) * (size_t)P.num_envs * P.num_dof));
     PF_CUDA(cudaStreamCreateWithFlags(&c->io_stream, cudaStreamNonBlocking));
     for (cudaEvent_t* e : {&c->ev_fork, &c->ev_in, &c->ev_post, &c->ev_out, &c->ev_fin}) PF_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -632,7 +674,7 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
 extern "C" int pf_ctx_destroy(pf_ctx* c) {
     if (!c) return 0;
     cudaFree((void*)c->S.noise_vec); cudaFree((void*)c->S.height_points);
-    cudaFree(c->S.height_mean); cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
+    cudaFree(c->S.height_mean); cudaFree(c->S.cta_sums); cudaFree(c->S.cta_lvl); cudaFree(c->S.ticket); cudaFree(c->S.blk_count); cudaFree(c->S.blk_level); cudaFree(c->S.blk_sums); cudaFree(c->d_actions_in);
     if (c->io_stream) cudaStreamDestroy(c->io_stream);
     for (cudaEvent_t e : {c->ev_fork, c->ev_in, c->ev_post, c->ev_out, c->ev_fin}) if (e) cudaEventDestroy(e);
     delete c;
