@@ -211,7 +211,7 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
 // kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
-// spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r2_step_kernel_sweeps.txt):
+// spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r1h_step_kernel_sweeps.txt):
 // the spills cost more than the extra resident warps hide.  A larger shared-memory carve-out is slower as well: the
 // per-env loads of the [N,6] / [N,2] state arrays (24- and 8-byte strides per lane) live off L1 sector reuse.
 // kScan: the task measures terrain heights (num_height_points > 0): pf_height_scan_kernel ran in front of this
@@ -498,10 +498,24 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     if (warp < nw) {
         const bool any = __any_sync(0xffffffffu, my_count > 0);
         const double* row = S.blk_sums + (size_t)my_slab * PF_MAX_REWARD_TERMS;
-        for (int k = 0; k < R; ++k) {
-            double v = 0.0;
-            if (any) v = pf_warp_sum(my_count > 0 ? row[k] : 0.0);
-            if (lane == 0) s_stat[warp][k] = v;
+        for (int k0 = 0; k0 < R; k0 += 8) {       // 8 independent reduction chains at a time (ILP without a register blow-up)
+            double v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {          // loaded whether or not the slab had a reset (stale rows are masked):
+                const double x = (own && k0 + j < R) ? row[k0 + j] : 0.0;      // no load waits for the count
+                v[j] = my_count > 0 ? x : 0.0;
+            }
+            if (any) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
+                }
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) if (k0 + j < PF_MAX_REWARD_TERMS) s_stat[warp][k0 + j] = v[j];
+            }
         }
         for (int o = 16; o > 0; o >>= 1) lvl += __shfl_xor_sync(0xffffffffu, lvl, o);
         if (lane == 0) s_lvl[warp] = lvl;
@@ -535,6 +549,7 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int nc = (int)gridDim.x;
     if (warp < R) {
         double acc = 0.0;
+#pragma unroll 8
         for (int c = lane; c < nc; c += 32) acc += __ldcg(S.cta_sums + (size_t)c * PF_MAX_REWARD_TERMS + warp);
         acc = pf_warp_sum(acc);
         if (lane == 0) B.episode_stats[warp] = (float)(acc / (double)total) / P.max_episode_length_s;
