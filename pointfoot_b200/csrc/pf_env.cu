@@ -148,7 +148,8 @@ __device__ __forceinline__ void pf_scan_lane_load(const pf_params& P, const PfCt
 // The step kernel (launched behind it) only reads height_mean[e].
 template <bool kFast>
 __global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params P, const pf_env_buffers B,
-                                                             const PfCtxScratch S, const uint32_t step_arg) {
+                                                                const PfCtxScratch S, const int epw,
+                                                                const uint32_t step_arg) {
     const int lane = threadIdx.x & 31;
     const int gw = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), nw = (int)((gridDim.x * blockDim.x) >> 5);
     pf_grid_dep_launch();
@@ -157,20 +158,31 @@ __global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params 
     pf_grid_dep_wait();
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     const uint32_t key0 = pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE);
-    const double inv_n = (double)P.num_height_points;
-    for (int e = gw; e < P.num_envs; e += nw) {
-        const float* g = B.root_states + (size_t)e * 13;
-        const float mine = lane < 7 ? g[lane] : 0.0f;    // pos xyz + quat xyzw: one coalesced 28-byte read
-        float r3[3], q[4];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) r3[i] = __shfl_sync(0xffffffffu, mine, i);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) q[i] = __shfl_sync(0xffffffffu, mine, 3 + i);
-        float zn, wn;
-        pf_yaw_quat(q, zn, wn);
-        const uint32_t nkey = pf_rng_env_key(key0, (uint32_t)(P.env_id_offset + e));
-        const double sum = pf_scan_env<true, kFast>(P, B, L, r3, zn, wn, r3[2], nkey, e, lane, true, &S.rew);
-        if (lane == 0) S.height_mean[e] = (float)(sum / inv_n);
+    const double pn = (double)P.num_height_points;
+    // A warp takes `epw` (1..32) consecutive envs at a time: what is per env rather than per point -- the root row,
+    // the yaw quaternion (a square root and two divisions), the noise key, the final division of the mean -- is done
+    // once per batch with lane = env and handed to the scan by shuffles.  epw = 1 for small batches (one env per
+    // warp: maximum parallelism), 32 for large ones (minimum instructions).
+    for (int base = gw * epw; base < P.num_envs; base += nw * epw) {
+        const int nb = min(epw, P.num_envs - base);
+        float x = 0.0f, y = 0.0f, z = 0.0f, zn = 0.0f, wn = 1.0f;
+        uint32_t nkey = 0;
+        if (lane < nb) {
+            const float* g = B.root_states + (size_t)(base + lane) * 13;
+            x = g[0]; y = g[1]; z = g[2];
+            pf_yaw_quat(g + 3, zn, wn);
+            nkey = pf_rng_env_key(key0, (uint32_t)(P.env_id_offset + base + lane));
+        }
+        double hs = 0.0;
+        for (int j = 0; j < nb; ++j) {
+            float r3[3];
+            r3[0] = __shfl_sync(0xffffffffu, x, j); r3[1] = __shfl_sync(0xffffffffu, y, j); r3[2] = __shfl_sync(0xffffffffu, z, j);
+            const float zj = __shfl_sync(0xffffffffu, zn, j), wj = __shfl_sync(0xffffffffu, wn, j);
+            const uint32_t kj = __shfl_sync(0xffffffffu, nkey, j);
+            const double sum = pf_scan_env<true, kFast>(P, B, L, r3, zj, wj, r3[2], kj, base + j, lane, true, &S.rew);
+            if (lane == j) hs = sum;
+        }
+        if (lane < nb) S.height_mean[base + lane] = (float)(hs / pn);
     }
 }
 
@@ -736,11 +748,15 @@ static int pf_post_physics_impl(pf_ctx* c, const pf_env_buffers* bufs, int64_t c
     const uint32_t step32 = (uint32_t)common_step_counter;
     const dim3 g(c->num_blocks), b(c->threads);
     if (c->P.num_height_points > 0) {
-        const int warps = c->P.num_envs;
+        // envs per warp of the scan: as many as keep >= 8 warps per SM sub-partition busy, 1..16 (32 measured no better)
+        int sepw = 1;
+        while (sepw < 16 && c->P.num_envs / (sepw * 2) >= c->num_sms * 4 * 8) sepw *= 2;
+        if (const char* e = getenv("PF_SCAN_EPW")) { const int v = atoi(e); if (v >= 1 && v <= 32) sepw = v; }
+        const int warps = (c->P.num_envs + sepw - 1) / sepw;
         int blocks = (warps + 7) / 8;
         if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
-        if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, step32));
-        else PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<false>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, step32));
+        if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
+        else PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<false>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
     }
     PF_CUDA(pf_launch_pdl(c->step_kernel, g, b, c->smem_bytes, st, c->P, *bufs, c->S, c->envs_per_warp, step32));
     if (!side) return pf_launch_finalize(c, bufs, st, 1);

@@ -22,8 +22,16 @@
 #define PF_CE constexpr
 #endif
 
+// min / max as the select the reference's clip ops amount to for ordinary numbers.  On the device they are the
+// single-instruction FMNMX (fminf / fmaxf): identical for every pair of non-NaN operands except the sign of a zero
+// result when both operands are zeros of opposite sign, and NaN in the FIRST operand yields the second either way.
+#ifdef __CUDA_ARCH__
+PF_HD float pf_minf(float a, float b) { return fminf(a, b); }
+PF_HD float pf_maxf(float a, float b) { return fmaxf(a, b); }
+#else
 PF_HD float pf_minf(float a, float b) { return a < b ? a : b; }
 PF_HD float pf_maxf(float a, float b) { return a > b ? a : b; }
+#endif
 PF_HD float pf_clipf(float x, float lo, float hi) { return pf_minf(pf_maxf(x, lo), hi); }
 PF_HD float pf_sq(float x) { return x * x; }
 
@@ -51,6 +59,7 @@ struct PfRewTab {
     float rdt;                        // RN(1 / dt)
     int32_t dt_div_exact;             // pf_div_by(x, dt, rdt) == x / dt for every x (checked exhaustively on the host)
     float r_hscale;                   // RN(1 / horizontal_scale)
+    float rows_m2, cols_m2;           // (float)(hf_rows - 2), (float)(hf_cols - 2): index clamps of PF:1104-1105
     int32_t index_div_kind;           // PF:1102 (x / horizontal_scale): 0 IEEE division, 1 x * r_hscale (CUDA eager),
                                       // 2 pf_div_by (bit-identical to the division, checked exhaustively on the host)
 };
@@ -154,8 +163,8 @@ PF_HD int16_t pf_terrain_min3_fast(const pf_params& P, const PfRewTab& T, const 
     if (T.index_div_kind == 2) { x = pf_div_by(x, P.horizontal_scale, T.r_hscale); y = pf_div_by(y, P.horizontal_scale, T.r_hscale); }
     else if (T.index_div_kind == 1) { x = x * T.r_hscale; y = y * T.r_hscale; }
     else { x = x / P.horizontal_scale; y = y / P.horizontal_scale; }
-    const int px = (int)pf_minf(pf_maxf(x, 0.0f), (float)(P.hf_rows - 2));
-    const int py = (int)pf_minf(pf_maxf(y, 0.0f), (float)(P.hf_cols - 2));
+    const int px = (int)pf_minf(pf_maxf(x, 0.0f), T.rows_m2);
+    const int py = (int)pf_minf(pf_maxf(y, 0.0f), T.cols_m2);
     const int16_t* r = hs + (px * P.hf_cols + py);
 #ifdef __CUDA_ARCH__
     const int16_t h1 = __ldg(r), h2 = __ldg(r + P.hf_cols), h3 = __ldg(r + 1);
@@ -308,6 +317,7 @@ static inline bool pf_build_reward_table(const pf_params& P, PfRewTab& T) {
     T.rdt = 1.0f / P.dt;
     T.dt_div_exact = pf_div_by_is_exact(P.dt) ? 1 : 0;
     T.r_hscale = 1.0f / P.horizontal_scale;
+    T.rows_m2 = (float)(P.hf_rows - 2); T.cols_m2 = (float)(P.hf_cols - 2);
     T.index_div_kind = P.index_div_mode == PF_DIV_RECIPROCAL ? 1 : (pf_div_by_is_exact(P.horizontal_scale) ? 2 : 0);
     if ((long long)P.num_envs * (PF_MAX_REWARD_TERMS + 1) > 0x7fffffffLL) return false;
     for (int k = 0; k < P.num_reward_terms; ++k) {
