@@ -96,3 +96,54 @@ def parse_sim_params(args, cfg):
     if getattr(args, "num_threads", 0):
         out.setdefault("physx", {})["num_threads"] = args.num_threads
     return out
+
+
+# ---------------------------------------------------------------------------------------------------- export
+def actor_module_from_state_dict(state_dict, activation="elu"):
+    """A plain ``torch.nn.Sequential`` (Linear, ELU, ..., Linear) holding the ``actor.*`` entries of an rsl_rl
+    ``ActorCritic`` state dict -- the module the reference deep-copies out of ``actor_critic.actor`` (helpers.py:180-190,
+    export_policy_as_onnx.py:13-46).  Works for checkpoints of either stack (same keys: ``actor.{0,2,4,..}.{weight,bias}``)."""
+    import torch
+    if activation != "elu":
+        raise NotImplementedError("only the 'elu' activation of the pointfoot configs is implemented")
+    idx = sorted({int(k.split(".")[1]) for k in state_dict if k.startswith("actor.") and k.endswith(".weight")})
+    if not idx:
+        raise KeyError("state dict has no actor.*.weight entries")
+    layers = []
+    for n, i in enumerate(idx):
+        w = state_dict[f"actor.{i}.weight"].detach().to("cpu", torch.float)
+        b = state_dict[f"actor.{i}.bias"].detach().to("cpu", torch.float)
+        lin = torch.nn.Linear(w.shape[1], w.shape[0])
+        with torch.no_grad():
+            lin.weight.copy_(w); lin.bias.copy_(b)
+        layers.append(lin)
+        if n + 1 < len(idx):
+            layers.append(torch.nn.ELU())
+    return torch.nn.Sequential(*layers)
+
+
+def export_policy_as_jit(actor_critic, path):
+    """helpers.py:180-190 of the reference: TorchScript file ``<path>/policy_1.pt`` of the actor on the CPU.  The policy
+    deployed on the robot is this file, so it is plain torch (no dependency on the CUDA library)."""
+    import os
+    import torch
+    if getattr(actor_critic, "is_recurrent", False) or hasattr(actor_critic, "memory_a"):
+        raise NotImplementedError("recurrent policies are not used by the pointfoot configs (DESIGN.md section 6)")
+    os.makedirs(path, exist_ok=True)
+    file = os.path.join(path, "policy_1.pt")
+    model = actor_module_from_state_dict(actor_critic.state_dict())
+    torch.jit.script(model).save(file)
+    return file
+
+
+def export_policy_as_onnx(actor_critic, path, num_obs=None, file_name="policy.onnx"):
+    """export_policy_as_onnx.py:13-46 of the reference (``torch.onnx.export`` of the actor with a [1, num_obs] dummy input).
+    Needs the ``onnx`` package at call time; raises ImportError otherwise (it is not in this image)."""
+    import os
+    import torch
+    model = actor_module_from_state_dict(actor_critic.state_dict()).eval()
+    n = num_obs if num_obs is not None else model[0].in_features
+    os.makedirs(path, exist_ok=True)
+    file = os.path.join(path, file_name)
+    torch.onnx.export(model, torch.zeros(1, n), file, input_names=["obs"], output_names=["actions"], opset_version=13)
+    return file

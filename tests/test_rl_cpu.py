@@ -83,3 +83,22 @@ def test_tensor_core_mlp_schedule_is_built_and_dry_run_on_the_host():
     assert [e[5] for e in epis][-1] == "-1" and all(e[5] in "01" for e in epis[:-1])
     blob = int(re.search(r"blob_bytes=(\d+)", text).group(1))
     assert blob == 2 * ((160 + 16) * 512 + (512 + 16) * 256 + (256 + 16) * 128 + (128 + 16) * 16)
+
+
+def test_export_policy_as_jit_from_a_reference_style_checkpoint(tmp_path):
+    """a state dict with the upstream keys (here: the oracle's ActorCritic) exports to the TorchScript
+    actor the reference writes (helpers.py:180-190), and the file reproduces act_inference."""
+    import torch
+    from oracle import rsl_rl_ref
+    from pointfoot_b200 import helpers
+    torch.manual_seed(3)
+    ac = rsl_rl_ref.ActorCritic(27, 148, 6, [64, 32, 16], [64, 32, 16])
+
+    class Shim:                      # what export needs from either stack's ActorCritic
+        is_recurrent = False
+        def state_dict(self):
+            return ac.state_dict()
+    file = helpers.export_policy_as_jit(Shim(), str(tmp_path))
+    m = torch.jit.load(file)
+    x = torch.randn(5, 27)
+    assert torch.equal(m(x), ac.act_inference(x))

@@ -100,3 +100,27 @@ def test_closed_loop_config_c1_against_oracle():
         assert (q1 - p1).norm() <= 0.1 * (p1 - p0).norm(), ((q1 - p1).norm(), (p1 - p0).norm())
     finally:
         ppo.close(); env.close()
+
+
+def test_play_loop_and_jit_export(tmp_path):
+    """scripts/play.py (reference play.py:42-114, headless): closed loop with the inference policy, TorchScript export of
+    the actor (helpers.py:180-190); the exported CPU module agrees with the CUDA act_inference on the same weights."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("pf_play", os.path.join(common.ROOT, "scripts", "play.py"))
+    play = importlib.util.module_from_spec(spec); spec.loader.exec_module(play)
+    args = _args("pointfoot_rough", 32)
+    file = play.play(args, steps=8, export_dir=str(tmp_path))
+    assert file and os.path.isfile(file)
+    m = torch.jit.load(file)
+    from pointfoot_b200.task_registry import task_registry
+    env, _ = task_registry.make_env(name="pointfoot_rough", args=args)
+    runner, _ = task_registry.make_alg_runner(env=env, name="pointfoot_rough", args=args, log_root=None)
+    ac = runner.alg.actor_critic
+    x = torch.randn(7, 27)
+    from pointfoot_b200 import helpers as h
+    want = h.actor_module_from_state_dict(ac.state_dict())(x)
+    got = ac.act_inference(x.to(env.device)).cpu()
+    prec = parity_rl.BF16 if os.environ.get("PF_RL_PRECISION", "") == "bf16" else dict(rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(got, want, **prec)
+    assert m(x).shape == (7, 6)
+    runner.alg.close(); env.close()
