@@ -222,14 +222,15 @@ __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_en
 //   phase 3  the 27 leading observation columns, flattened over the warp's envs -> coalesced row writes
 //   phase 4  (rare) envs that reset: height columns rewritten with the post-reset root z (PF:223 runs
 //            after reset_idx) -- the scan itself stays on the pre-reset pose (PF:212-213)
-// kMinB = resident CTAs of 256 threads per SM the register allocation aims for.  2 = 128 registers, nothing
-// spilled; 3 (80 registers) and 4 (64) were measured slower at every batch size (profiles/r1h_step_kernel_sweeps.txt):
-// the spills cost more than the extra resident warps hide.  A larger shared-memory carve-out is slower as well: the
+// kMinB: the register allocation aims at 2 * kMinB resident CTAs of 128 threads per SM.  2 = 128 registers, nothing
+// spilled; 80- and 64-register builds were measured slower at every batch size, a 96-register build (5 CTAs, 20 bytes
+// spilled) no faster (profiles/r1h_step_kernel_sweeps.txt): ncu shows no unit saturated (DRAM 48 %, L1 39 %, LSU 21 %,
+// issue 37 % at 262,144 envs) -- the kernel is bound by how well 16 warps per SM overlap their memory round trips.  A larger shared-memory carve-out is slower as well: the
 // per-env loads of the [N,6] / [N,2] state arrays (24- and 8-byte strides per lane) live off L1 sector reuse.
 // kScan: the task measures terrain heights (num_height_points > 0): pf_height_scan_kernel ran in front of this
 // kernel and left height_mean[e]; only the envs that reset redo their scan here (phase 4).
 template <uint32_t kMask, int kMinB, bool kScan>
-__global__ void __launch_bounds__(PF_THREADS, kMinB) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
+__global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const pf_params P, const pf_env_buffers B,
                                                                         const PfCtxScratch S, const int epw,
                                                                         const uint32_t step_arg) {
     extern __shared__ __align__(16) float smem_f[];
