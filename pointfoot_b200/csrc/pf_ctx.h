@@ -24,6 +24,7 @@ typedef void (*pf_step_kernel_t)(const pf_params, const pf_env_buffers, const Pf
 struct pf_ctx {
     pf_params P;
     pf_step_kernel_t step_kernel;   // instantiation of pf_post_physics_kernel picked at pf_ctx_create
+    pf_step_kernel_t generic_kernel;   // the order-agnostic instantiation: also taken when a state tensor is not 8-byte aligned
     PfCtxScratch S;
     int device;
     int num_sms;

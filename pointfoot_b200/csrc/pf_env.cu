@@ -321,14 +321,23 @@ __global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const p
         s.misc[4 * lane + 2] = out.root_z;
         s.misc[4 * lane + 3] = __uint_as_float(nkey);
         // PF:225-227
+        if (kFast) {
 #pragma unroll
-        for (int d = 0; d < PF_MAX_DOF; ++d)
-            if (d < D) {
-                B.last_actions[(size_t)e * D + d] = out.actions[d];
-                B.last_dof_vel[(size_t)e * D + d] = out.dof_vel[d];
+            for (int d = 0; d < 6; d += 2) {
+                pf_st2(B.last_actions + (size_t)e * 6 + d, out.actions[d], out.actions[d + 1]);
+                pf_st2(B.last_dof_vel + (size_t)e * 6 + d, out.dof_vel[d], out.dof_vel[d + 1]);
+                pf_st2(B.last_root_vel + (size_t)e * 6 + d, out.root_vel[d], out.root_vel[d + 1]);
             }
+        } else {
 #pragma unroll
-        for (int i = 0; i < 6; ++i) B.last_root_vel[(size_t)e * 6 + i] = out.root_vel[i];
+            for (int d = 0; d < PF_MAX_DOF; ++d)
+                if (d < D) {
+                    B.last_actions[(size_t)e * D + d] = out.actions[d];
+                    B.last_dof_vel[(size_t)e * D + d] = out.dof_vel[d];
+                }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) B.last_root_vel[(size_t)e * 6 + i] = out.root_vel[i];
+        }
     }
     {
         const unsigned lv = __reduce_add_sync(0xffffffffu, (unsigned)lvl);   // levels are small and >= 0: exact
@@ -659,14 +668,16 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     // CTA size of the step kernel: warps are independent, so a small batch is cut into small CTAs that reach every SM
     c->threads = 128;          // measured: 128-thread CTAs beat 256 at large batches too (finer-grained SM fill)
     while (c->threads > 32 && (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32) < 2 * c->num_sms) c->threads >>= 1;
-    if (const char* e = getenv("PF_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128 || v == 256) c->threads = v; }
+    if (const char* e = getenv("PF_BLOCK")) { const int v = atoi(e); if (v == 32 || v == 64 || v == 128) c->threads = v; }
     c->num_blocks = (c->num_slabs + c->threads / 32 - 1) / (c->threads / 32);
     c->max_blocks = c->num_slabs;
     c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
     c->canonical = pf_step_mode(P, c->S.rew, getenv("PF_GENERIC_REWARDS") != nullptr, getenv("PF_TABLE_REWARDS") != nullptr);
     if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
     c->step_kernel = pf_pick_step_kernel(c->canonical, P.num_height_points > 0);
+    c->generic_kernel = pf_pick_step_kernel(0, P.num_height_points > 0);
     PF_CUDA(cudaFuncSetAttribute(c->step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
+    PF_CUDA(cudaFuncSetAttribute(c->generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
 
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
@@ -759,7 +770,16 @@ static int pf_post_physics_impl(pf_ctx* c, const pf_env_buffers* bufs, int64_t c
         if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
         else PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<false>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
     }
-    PF_CUDA(pf_launch_pdl(c->step_kernel, g, b, c->smem_bytes, st, c->P, *bufs, c->S, c->envs_per_warp, step32));
+    // the specialised kernels read / write pairs of the per-env state as 64-bit words: 8-byte aligned tensors only
+    const uintptr_t al = reinterpret_cast<uintptr_t>(bufs->torques) | reinterpret_cast<uintptr_t>(bufs->last_dof_vel) |
+                         reinterpret_cast<uintptr_t>(bufs->last_actions) | reinterpret_cast<uintptr_t>(bufs->actions) |
+                         reinterpret_cast<uintptr_t>(bufs->last_root_vel) | reinterpret_cast<uintptr_t>(bufs->feet_air_time) |
+                         reinterpret_cast<uintptr_t>(bufs->last_feet_air_time) | reinterpret_cast<uintptr_t>(bufs->feet_height) |
+                         reinterpret_cast<uintptr_t>(bufs->current_max_feet_height) | reinterpret_cast<uintptr_t>(bufs->last_max_feet_height) |
+                         ((reinterpret_cast<uintptr_t>(bufs->contact_filt) | reinterpret_cast<uintptr_t>(bufs->first_contact) |
+                           reinterpret_cast<uintptr_t>(bufs->last_contacts)) << 2);
+    const pf_step_kernel_t kern = (al & 7) == 0 ? c->step_kernel : c->generic_kernel;
+    PF_CUDA(pf_launch_pdl(kern, g, b, c->smem_bytes, st, c->P, *bufs, c->S, c->envs_per_warp, step32));
     if (!side) return pf_launch_finalize(c, bufs, st, 1);
     PF_CUDA(cudaEventRecord(c->ev_post, st));
     PF_CUDA(cudaStreamWaitEvent(c->io_stream, c->ev_post, 0));

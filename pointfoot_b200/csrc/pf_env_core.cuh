@@ -32,6 +32,22 @@ PF_HD float pf_maxf(float a, float b) { return fmaxf(a, b); }
 PF_HD float pf_minf(float a, float b) { return a < b ? a : b; }
 PF_HD float pf_maxf(float a, float b) { return a > b ? a : b; }
 #endif
+// Pairs of neighbouring values of one env ([N,2] feet arrays, the three (x, y) pairs of an [N,6] row) as ONE 64-bit
+// (16-bit for bool pairs) access on the device: half the load / store instructions and L1 lookups of the per-env state.
+// The kernels take this path only when every such tensor is 8-byte aligned (pf_post_physics_impl checks).
+#ifdef __CUDA_ARCH__
+struct alignas(8) PfF2 { float x, y; };
+PF_HD void pf_ld2(const float* p, float& a, float& b) { const PfF2 v = *reinterpret_cast<const PfF2*>(p); a = v.x; b = v.y; }
+PF_HD void pf_st2(float* p, float a, float b) { PfF2 v; v.x = a; v.y = b; *reinterpret_cast<PfF2*>(p) = v; }
+PF_HD void pf_ldb2(const uint8_t* p, bool& a, bool& b) { const uint16_t v = *reinterpret_cast<const uint16_t*>(p); a = (v & 0xffu) != 0; b = (v >> 8) != 0; }
+PF_HD void pf_stb2(uint8_t* p, bool a, bool b) { *reinterpret_cast<uint16_t*>(p) = (uint16_t)((a ? 1u : 0u) | ((b ? 1u : 0u) << 8)); }
+#else
+PF_HD void pf_ld2(const float* p, float& a, float& b) { a = p[0]; b = p[1]; }
+PF_HD void pf_st2(float* p, float a, float b) { p[0] = a; p[1] = b; }
+PF_HD void pf_ldb2(const uint8_t* p, bool& a, bool& b) { a = p[0] != 0; b = p[1] != 0; }
+PF_HD void pf_stb2(uint8_t* p, bool a, bool b) { p[0] = a; p[1] = b; }
+#endif
+
 PF_HD float pf_clipf(float x, float lo, float hi) { return pf_minf(pf_maxf(x, lo), hi); }
 PF_HD float pf_sq(float x) { return x * x; }
 
@@ -487,19 +503,37 @@ PF_HD void pf_env_preload(const pf_params& P, const pf_env_buffers& B, const PfR
 #undef PF_X
     }
     pre.es_term = P.has_termination_term ? B.episode_sums[(size_t)P.num_reward_terms * N + e] : 0.0f;
+    if (kFast && PF_MAX_DOF == 6 && PF_NUM_FEET == 2) {
 #pragma unroll
-    for (int d = 0; d < PF_MAX_DOF; ++d) {
-        const bool ok = d < D;
-        pre.tq[d] = ok ? B.torques[e * D + d] : 0.0f; pre.ldv[d] = ok ? B.last_dof_vel[e * D + d] : 0.0f;
-        pre.la[d] = ok ? B.last_actions[e * D + d] : 0.0f; pre.ac[d] = ok ? B.actions[e * D + d] : 0.0f;
-    }
+        for (int d = 0; d < 6; d += 2) {
+            pf_ld2(B.torques + e * 6 + d, pre.tq[d], pre.tq[d + 1]);
+            pf_ld2(B.last_dof_vel + e * 6 + d, pre.ldv[d], pre.ldv[d + 1]);
+            pf_ld2(B.last_actions + e * 6 + d, pre.la[d], pre.la[d + 1]);
+            pf_ld2(B.actions + e * 6 + d, pre.ac[d], pre.ac[d + 1]);
+        }
+        pf_ldb2(B.first_contact + e * 2, pre.fc_old[0], pre.fc_old[1]);
+        pf_ldb2(B.contact_filt + e * 2, pre.cfilt_old[0], pre.cfilt_old[1]);
+        pf_ldb2(B.last_contacts + e * 2, pre.lc_old[0], pre.lc_old[1]);
+        pf_ld2(B.feet_air_time + e * 2, pre.fat_old[0], pre.fat_old[1]);
+        pf_ld2(B.last_feet_air_time + e * 2, pre.lfat_old[0], pre.lfat_old[1]);
+        pf_ld2(B.last_max_feet_height + e * 2, pre.lmfh_old[0], pre.lmfh_old[1]);
+        pre.cmfh_old[0] = pre.cmfh_old[1] = 0.0f;
+        if (P.include_feet_height_rewards) pf_ld2(B.current_max_feet_height + e * 2, pre.cmfh_old[0], pre.cmfh_old[1]);
+    } else {
 #pragma unroll
-    for (int f = 0; f < PF_NUM_FEET; ++f) {
-        const int k = e * PF_NUM_FEET + f;
-        pre.fc_old[f] = B.first_contact[k] != 0; pre.cfilt_old[f] = B.contact_filt[k] != 0; pre.lc_old[f] = B.last_contacts[k] != 0;
-        pre.fat_old[f] = B.feet_air_time[k]; pre.lfat_old[f] = B.last_feet_air_time[k];
-        pre.lmfh_old[f] = B.last_max_feet_height[k];
-        pre.cmfh_old[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
+        for (int d = 0; d < PF_MAX_DOF; ++d) {
+            const bool ok = d < D;
+            pre.tq[d] = ok ? B.torques[e * D + d] : 0.0f; pre.ldv[d] = ok ? B.last_dof_vel[e * D + d] : 0.0f;
+            pre.la[d] = ok ? B.last_actions[e * D + d] : 0.0f; pre.ac[d] = ok ? B.actions[e * D + d] : 0.0f;
+        }
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const int k = e * PF_NUM_FEET + f;
+            pre.fc_old[f] = B.first_contact[k] != 0; pre.cfilt_old[f] = B.contact_filt[k] != 0; pre.lc_old[f] = B.last_contacts[k] != 0;
+            pre.fat_old[f] = B.feet_air_time[k]; pre.lfat_old[f] = B.last_feet_air_time[k];
+            pre.lmfh_old[f] = B.last_max_feet_height[k];
+            pre.cmfh_old[f] = P.include_feet_height_rewards ? B.current_max_feet_height[k] : 0.0f;
+        }
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) pre.cmd_old[i] = i < P.num_commands ? B.commands[e * P.num_commands + i] : 0.0f;
@@ -548,10 +582,10 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
 
     // ---- PF:1114-1129 feet state machine ----
     float fat[PF_NUM_FEET], lfat[PF_NUM_FEET], lmfh[PF_NUM_FEET];
-    bool first_contact[PF_NUM_FEET];
+    float fh_[PF_NUM_FEET], cm_[PF_NUM_FEET];
+    bool first_contact[PF_NUM_FEET], cfilt_[PF_NUM_FEET], contact_[PF_NUM_FEET];
 #pragma unroll
     for (int f = 0; f < PF_NUM_FEET; ++f) {
-        const int k = e * PF_NUM_FEET + f;
         const bool fc_old = fc_old_[f];
         const bool cfilt_old = cfilt_old_[f];
         float fat_f = fat_old_[f];
@@ -569,17 +603,36 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
                         * P.vertical_scale;
             const float fh = in.feet_pos[f][2] - below;
             cm = pf_maxf(cm, fh);
-            B.feet_height[k] = fh;
-            B.current_max_feet_height[k] = cm;
-            B.last_max_feet_height[k] = lmfh[f];
+            fh_[f] = fh; cm_[f] = cm;
         }
         const bool contact = in.cf[P.feet_indices[f] * 3 + 2] > 1.0f;
         const bool cfilt = contact || lc_old_[f];
         first_contact[f] = (fat_f > 0.0f) && cfilt;
         fat_f = fat_f + dt;
         fat[f] = fat_f;
-        B.contact_filt[k] = cfilt; B.last_contacts[k] = contact; B.first_contact[k] = first_contact[f];
-        B.feet_air_time[k] = fat_f; B.last_feet_air_time[k] = lfat[f];
+        cfilt_[f] = cfilt; contact_[f] = contact;
+    }
+    if (kFast && PF_NUM_FEET == 2) {
+        if (P.include_feet_height_rewards) {
+            pf_st2(B.feet_height + e * 2, fh_[0], fh_[1]);
+            pf_st2(B.current_max_feet_height + e * 2, cm_[0], cm_[1]);
+            pf_st2(B.last_max_feet_height + e * 2, lmfh[0], lmfh[1]);
+        }
+        pf_stb2(B.contact_filt + e * 2, cfilt_[0], cfilt_[1]);
+        pf_stb2(B.last_contacts + e * 2, contact_[0], contact_[1]);
+        pf_stb2(B.first_contact + e * 2, first_contact[0], first_contact[1]);
+        pf_st2(B.feet_air_time + e * 2, fat[0], fat[1]);
+        pf_st2(B.last_feet_air_time + e * 2, lfat[0], lfat[1]);
+    } else {
+#pragma unroll
+        for (int f = 0; f < PF_NUM_FEET; ++f) {
+            const int k = e * PF_NUM_FEET + f;
+            if (P.include_feet_height_rewards) {
+                B.feet_height[k] = fh_[f]; B.current_max_feet_height[k] = cm_[f]; B.last_max_feet_height[k] = lmfh[f];
+            }
+            B.contact_filt[k] = cfilt_[f]; B.last_contacts[k] = contact_[f]; B.first_contact[k] = first_contact[f];
+            B.feet_air_time[k] = fat[f]; B.last_feet_air_time[k] = lfat[f];
+        }
     }
 
     // ---- PF:479-493 callback: commands ----

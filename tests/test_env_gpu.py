@@ -69,7 +69,7 @@ def test_reward_statements_and_cta_sizes_agree_bit_for_bit(monkeypatch):
     from pointfoot_b200 import synth
     state = synth.make_state(3000, "pointfoot_rough", seed=5)
     outs = []
-    for env in ({}, {"PF_GENERIC_REWARDS": "1"}, {"PF_TABLE_REWARDS": "1"}, {"PF_BLOCK": "32"}, {"PF_BLOCK": "256", "PF_EPW": "4"}):
+    for env in ({}, {"PF_GENERIC_REWARDS": "1"}, {"PF_TABLE_REWARDS": "1"}, {"PF_BLOCK": "32"}, {"PF_BLOCK": "128", "PF_EPW": "4"}):
         for k in ("PF_GENERIC_REWARDS", "PF_TABLE_REWARDS", "PF_BLOCK", "PF_EPW"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
@@ -83,6 +83,25 @@ def test_reward_statements_and_cta_sizes_agree_bit_for_bit(monkeypatch):
     for o in outs[1:]:
         for k, v in o.items():
             assert torch.equal(v, outs[0][k]), k
+
+
+def test_unaligned_state_tensor_takes_the_generic_kernel():
+    """The specialised kernels read pairs of the per-env state as 64-bit words; a caller-owned tensor that is only
+    4-byte aligned (a slice) must still work: the launch falls back to the generic kernel, same bits."""
+    from pointfoot_b200 import synth
+    state = synth.make_state(777, "pointfoot_flat", seed=13)
+    a = parity.EnvUnderTest("pointfoot_flat", state, "cuda", seed=13)
+    b = parity.EnvUnderTest("pointfoot_flat", state, "cuda", seed=13)
+    odd = torch.zeros(b.t["last_actions"].numel() + 1, device="cuda")[1:].view_as(b.t["last_actions"])
+    assert odd.data_ptr() % 8 == 4
+    odd.copy_(b.t["last_actions"])
+    b.t["last_actions"] = odd
+    b.b.last_actions = odd.data_ptr()
+    for k in range(3):
+        a.step(state["actions"] * (1.0 - 0.3 * k)); b.step(state["actions"] * (1.0 - 0.3 * k))
+    for name in ("obs_buf", "rew_buf", "reset_buf", "episode_sums", "last_actions", "feet_air_time", "contact_filt", "root_states"):
+        assert torch.equal(a.t[name], b.t[name]), name
+    a.close(); b.close()
 
 
 def test_split_tail_equals_plain_step():
