@@ -550,24 +550,23 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     if (warp < nw) {
         const bool any = __any_sync(0xffffffffu, my_count > 0);
         const double* row = S.blk_sums + (size_t)my_slab * PF_MAX_REWARD_TERMS;
-        for (int k0 = 0; k0 < R; k0 += 8) {       // 8 independent reduction chains at a time (ILP without a register blow-up)
-            double v[8];
+        if (any) {
+            for (int k0 = 0; k0 < R; k0 += 8) {   // 8 independent loads / reduction chains at a time (ILP without a register blow-up)
+                double v[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {          // loaded whether or not the slab had a reset (stale rows are masked):
-                const double x = (own && k0 + j < R) ? row[k0 + j] : 0.0;      // no load waits for the count
-                v[j] = my_count > 0 ? x : 0.0;
-            }
-            if (any) {
+                for (int j = 0; j < 8; ++j) v[j] = (my_count > 0 && k0 + j < R) ? row[k0 + j] : 0.0;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
                 }
-            }
-            if (lane == 0) {
+                if (lane == 0) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) if (k0 + j < PF_MAX_REWARD_TERMS) s_stat[warp][k0 + j] = v[j];
+                    for (int j = 0; j < 8; ++j) if (k0 + j < PF_MAX_REWARD_TERMS) s_stat[warp][k0 + j] = v[j];
+                }
             }
+        } else if (lane < R) {
+            s_stat[warp][lane] = 0.0;             // no reset in this warp's slabs: nothing to load or reduce
         }
         for (int o = 16; o > 0; o >>= 1) lvl += __shfl_xor_sync(0xffffffffu, lvl, o);
         if (lane == 0) s_lvl[warp] = lvl;
