@@ -180,6 +180,11 @@ int pf_post_physics_step(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common
 int pf_post_physics_step_begin(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t common_step_counter, void* stream);
 int pf_post_physics_step_join(pf_ctx* ctx, void* stream);
 
+/* Diagnostic (tools/step_timeline.py): install a DEVICE log of 4096 uint64 (log[0] = record count, records =
+ * tag << 48 | globaltimer ns) that thread 0 of CTA 0 of the env kernels / the fused act kernel append to; NULL removes it. */
+int pf_debug_timeline(unsigned long long* device_log);
+int pf_rl_debug_timeline(unsigned long long* device_log);
+
 /* PF:590-611: random push forces into forces[N,B,3] (body 0 rows; everything else zeroed).
  * max_push_force = base_mass.mean() * max_push_vel_xy / sim_dt, evaluated by the host in double (PF:592-596). */
 int pf_push_forces(pf_ctx* ctx, const pf_env_buffers* bufs, float* forces, float max_push_force,

@@ -47,7 +47,9 @@ __global__ void __launch_bounds__(256) pf_pd_torques2_kernel(const pf_params P, 
     const int half = P.num_dof >> 1;
     const int n = P.num_envs * half;
     pf_grid_dep_launch();
+    pf_timeline(0x10);
     pf_grid_dep_wait();
+    pf_timeline(0x11);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int d = 2 * (i % half);
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(256) pf_pd_torques2_kernel(const pf_params P, 
     t.x = pf_pd_torque(P, d, a.x, s.x, s.y, lq.x);
     t.y = pf_pd_torque(P, d + 1, a.y, s.z, s.w, lq.y);
     reinterpret_cast<float2*>(B.torques)[i] = t;
+    pf_timeline(0x12);
 }
 
 // ------------------------------------------------------------------------------------------------ helpers
@@ -185,7 +188,9 @@ __global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params 
     pf_grid_dep_launch();
     PfScanLane L;
     pf_scan_lane_load(P, S, lane, L);                   // constants of the context: not written by any kernel
+    pf_timeline(0x40);
     pf_grid_dep_wait();
+    pf_timeline(0x41);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     const uint32_t key0 = pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE);
     const double pn = (double)P.num_height_points;
@@ -214,6 +219,7 @@ __global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params 
         }
         if (lane < nb) S.height_mean[base + lane] = (float)(hs / pn);
     }
+    pf_timeline(0x42);
 }
 
 // Warp partials for extras["episode"] (PF:276-288): count, terrain-level sum, per-term episode sums of the
@@ -271,7 +277,9 @@ __global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const p
     if (e0 >= P.num_envs) return;
     const PfWarpSmem s = pf_carve_warp(P, epw, smem_f + (size_t)warp * pf_warp_smem_floats(P, epw));
     const int nenv = min(epw, P.num_envs - e0);
+    pf_timeline(0x20);
     pf_grid_dep_wait();
+    pf_timeline(0x21);
     const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
     constexpr bool kFast = kMask != PF_MASK_GENERIC;
     constexpr int kD = kFast ? PF_MAX_DOF : 0;
@@ -443,7 +451,7 @@ __global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const p
                                          lane, false, &S.rew);
             }
         }
-    }
+    }    pf_timeline(0x22);
 }
 
 // the instantiation of the step kernel for a context: statement of the step (pf_step_mode) x with / without height scan
@@ -495,7 +503,9 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
     pf_grid_dep_launch();
+    pf_timeline(0x30);
     pf_grid_dep_wait();
+    pf_timeline(0x31);
 
     // One pass over the step kernel's per-slab counts (128-bit loads: `before` is a multiple of 32) gives both the
     // number of resets in front of this CTA's envs and the total; one barrier; every warp then reduces the 32
@@ -536,6 +546,7 @@ __global__ void __launch_bounds__(1024) pf_finalize_kernel(const pf_params P, co
     const int off = __reduce_add_sync(0xffffffffu, s_before[lane] + (lane < warp ? s_flags[lane] : 0));
     if (B.extras_time_outs && total > 0 && e < P.num_envs) B.extras_time_outs[e] = tmo;
     if (flag) B.reset_ids[off + __popc(m & ((1u << lane) - 1u))] = e;
+    pf_timeline(0x32);
     if (blockIdx.x == 0 && tid == 0) {
         *B.reset_count = total;
         if (B.step_counter && count_step) *B.step_counter += 1;
@@ -650,6 +661,10 @@ static int pf_fail(int code, const char* fmt, const char* detail) {
 
 extern "C" const char* pf_last_error(void) { return g_err; }
 void pf_set_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }   // used by pf_rl.cu / pf_mlp_tc.cu
+// diagnostic: install (or with NULL remove) a device log of 4096 uint64 that the env kernels append timeline records to
+extern "C" int pf_debug_timeline(unsigned long long* device_log) {
+    return pf_timeline_install(device_log) == cudaSuccess ? 0 : pf_fail(2, "%s", "pf_debug_timeline: cudaMemcpyToSymbol failed");
+}
 extern "C" int pf_abi_version(void) { return PF_ABI_VERSION; }
 extern "C" int pf_sizeof_params(void) { return (int)sizeof(pf_params); }
 extern "C" int pf_sizeof_env_buffers(void) { return (int)sizeof(pf_env_buffers); }

@@ -271,6 +271,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int items = a.nnets * a.tiles;
     pf_grid_dep_launch();       // the prologue below (barriers, TMEM, ones operand) runs under the predecessor's tail
+    pf_timeline(0x50);
 
     if (warp == TC_LOAD_WARP && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
@@ -289,7 +290,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pf_timeline(0x51);
     pf_grid_dep_wait();         // first global access (observations, packed weights) comes after this
+    pf_timeline(0x52);
 
     if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
@@ -507,6 +510,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     }
     tc_fence_before();
     __syncthreads();
+    pf_timeline(0x53);
     if (warp == TC_MMA_WARP) {
         __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC_TMEM_COLS) : "memory");
@@ -702,6 +706,10 @@ static int check_program(const TcProgram& P) {
 
 // Diagnostic: device buffer of 3 * TC_TRACE_CAP uint64 that CTA 0 of every following launch fills with its role
 // timelines (tools/tc_trace.py); NULL switches it off.
+extern "C" int pf_rl_debug_timeline(unsigned long long* device_log) {
+    return pf_timeline_install(device_log) == cudaSuccess ? 0 : 1;
+}
+
 extern "C" int pf_rl_tc_trace(pf_rl_ctx* c, unsigned long long* device_buf) {
     if (!c || !c->tc) return 1;
     static_cast<TcState*>(c->tc)->trace = device_buf;
