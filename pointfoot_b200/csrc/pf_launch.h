@@ -15,16 +15,17 @@
 // CTA 0 of every kernel appends (tag << 48 | globaltimer ns) records -- log[0] is the record count.  One global
 // load of a NULL pointer per kernel otherwise.  Each translation unit has its own copy of the pointer.
 static __device__ unsigned long long* g_pf_timeline = nullptr;
-__device__ __forceinline__ void pf_timeline(unsigned tag) {
-    if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
-        unsigned long long* p = g_pf_timeline;
-        if (p) {
-            unsigned long long t;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            const unsigned long long i = atomicAdd(p, 1ull);
-            if (i < 4094) p[1 + i] = ((unsigned long long)tag << 48) | (t & 0xFFFFFFFFFFFFull);
-        }
+__device__ __forceinline__ void pf_timeline_raw(unsigned tag) {      // the calling thread appends a record
+    unsigned long long* p = g_pf_timeline;
+    if (p) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const unsigned long long i = atomicAdd(p, 1ull);
+        if (i < 4094) p[1 + i] = ((unsigned long long)tag << 48) | (t & 0xFFFFFFFFFFFFull);
     }
+}
+__device__ __forceinline__ void pf_timeline(unsigned tag) {
+    if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) pf_timeline_raw(tag);
 }
 static inline cudaError_t pf_timeline_install(unsigned long long* device_log) {
     return cudaMemcpyToSymbol(g_pf_timeline, &device_log, sizeof(device_log));

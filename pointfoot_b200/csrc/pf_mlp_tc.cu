@@ -124,10 +124,14 @@ struct TcArgs {
     unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
+__device__ __forceinline__ void pf_timeline_raw(unsigned tag);
 struct TcTrace {
-    unsigned long long* p; int n;
-    __device__ __forceinline__ void init(unsigned long long* base, int role, bool on) { p = on && base ? base + role * TC_TRACE_CAP : nullptr; n = 0; }
-    __device__ __forceinline__ void ev(unsigned tag) { if (p && n < TC_TRACE_CAP) p[n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); }
+    unsigned long long* p; int n; bool on_;
+    __device__ __forceinline__ void init(unsigned long long* base, int role, bool on) { p = on && base ? base + role * TC_TRACE_CAP : nullptr; n = 0; on_ = on; }
+    __device__ __forceinline__ void ev(unsigned tag) {
+        if (p && n < TC_TRACE_CAP) p[n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull);
+        if (on_) pf_timeline_raw(0x1000u + tag);          // step timeline (pf_rl_debug_timeline), if installed
+    }
 };
 
 // branch-free ELU: the exponential is evaluated unconditionally (one MUFU) and selected, so that 32 of them schedule

@@ -44,4 +44,13 @@ for i in range(1, len(ev)):
         cut = i
 t0 = ev[cut][0]
 for t, tag in ev[cut:]:
-    print(f"{(t - t0) / 1000:8.2f} us  {NAMES.get(tag, hex(tag))}")
+    TC = {0x1: "loader: group", 0x2: "mma: reached group", 0x3: "mma: issue group", 0x4: "mma: group done", 0x5: "stage", 0x6: "epilogue: reached", 0x7: "epilogue: accumulator ready",
+          0x8: "epilogue: written", 0x9: "epilogue: done", 0xA: "mma: tile wait", 0xB: "mma: tile got", 0xC: "epi: tmem ld", 0xD: "epi: tmem got"}
+    name = NAMES.get(tag)
+    if name is None and tag >= 0x1000:
+        k, sub = (tag - 0x1000) >> 8, (tag - 0x1000) & 0xFF
+        if k in (0xC, 0xD):
+            continue
+        name = "   act " + TC.get(k, hex(k)) + " " + ({0: "begin", 2: "arrived", 3: "loaded", 4: "padded", 5: "signalled"}.get(sub, str(sub)) if k == 5 else str(sub))
+    name = name or hex(tag)
+    print(f"{(t - t0) / 1000:8.2f} us  {name}")
