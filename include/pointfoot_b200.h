@@ -181,7 +181,8 @@ int pf_post_physics_step_begin(pf_ctx* ctx, const pf_env_buffers* bufs, int64_t 
 int pf_post_physics_step_join(pf_ctx* ctx, void* stream);
 
 /* Diagnostic (tools/step_timeline.py): install a DEVICE log of 4096 uint64 (log[0] = record count, records =
- * tag << 48 | globaltimer ns) that thread 0 of CTA 0 of the env kernels / the fused act kernel append to; NULL removes it. */
+ * tag << 48 | globaltimer ns) that thread 0 of CTA 0 of the env kernels / the fused act kernel append to; NULL removes it.
+ * The marks are compiled in only with -DPF_TIMELINE (PF_BUILD_TIMELINE=1 at build time); otherwise installing a log fails. */
 int pf_debug_timeline(unsigned long long* device_log);
 int pf_rl_debug_timeline(unsigned long long* device_log);
 
@@ -303,6 +304,10 @@ int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, int32_t cap);
 /* Diagnostic: CTA 0 of every following tensor-core launch writes its role timelines (4 x 512 uint64, tag << 48 |
  * SM clock) into `device_buf`; NULL switches it off (tools/tc_trace.py). */
 int pf_rl_tc_trace(pf_rl_ctx* ctx, unsigned long long* device_buf);
+/* Opt-in (PF_RL_BF16_TC): the fused kernel processes one DRY item (zeros for the input rows, no outputs) before its
+ * programmatic-dependency wait, so that the code of all its roles has been executed once while the predecessor kernel
+ * (the env step) is still running.  For chains launched back to back (a CUDA-graphed step + act); off by default. */
+int pf_rl_tc_rehearse(pf_rl_ctx* ctx, int on);
 
 /* PPO.act (ppo.py act) fused with RolloutStorage.add_transitions' copies: actor forward -> Normal(mean, std)
  * sample (RNG contract, purpose POLICY, step = policy_step) -> log-prob; critic forward; writes row `t` of the

@@ -663,7 +663,7 @@ extern "C" const char* pf_last_error(void) { return g_err; }
 void pf_set_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }   // used by pf_rl.cu / pf_mlp_tc.cu
 // diagnostic: install (or with NULL remove) a device log of 4096 uint64 that the env kernels append timeline records to
 extern "C" int pf_debug_timeline(unsigned long long* device_log) {
-    return pf_timeline_install(device_log) == cudaSuccess ? 0 : pf_fail(2, "%s", "pf_debug_timeline: cudaMemcpyToSymbol failed");
+    return pf_timeline_install(device_log) == cudaSuccess ? 0 : pf_fail(7, "%s", "pf_debug_timeline: not compiled in (build with PF_BUILD_TIMELINE=1) or cudaMemcpyToSymbol failed");
 }
 extern "C" int pf_abi_version(void) { return PF_ABI_VERSION; }
 extern "C" int pf_sizeof_params(void) { return (int)sizeof(pf_params); }

@@ -11,11 +11,16 @@
 #include <utility>
 
 #ifdef __CUDACC__
-// Optional device timeline (tools/step_timeline.py): when a log buffer is installed (pf_debug_timeline), thread 0 of
-// CTA 0 of every kernel appends (tag << 48 | globaltimer ns) records -- log[0] is the record count.  One global
-// load of a NULL pointer per kernel otherwise.  Each translation unit has its own copy of the pointer.
+// Optional device timeline (tools/step_timeline.py), compiled in with -DPF_TIMELINE (PF_BUILD_TIMELINE=1 python
+// __graft_entry__.py --force): when a log buffer is installed (pf_debug_timeline), thread 0 of CTA 0 of every kernel
+// appends (tag << 48 | globaltimer ns) records -- log[0] is the record count.  Each translation unit has its own copy
+// of the pointer.  Without the define every mark is an empty function.
 static __device__ unsigned long long* g_pf_timeline = nullptr;
 __device__ __forceinline__ void pf_timeline_raw(unsigned tag) {      // the calling thread appends a record
+#ifndef PF_TIMELINE
+    (void)tag; return;          // compiled out of the product build: even the NULL test of the log pointer (a global load
+                                // per mark on the critical thread) was measured at ~4 us per policy step
+#endif
     unsigned long long* p = g_pf_timeline;
     if (p) {
         unsigned long long t;
@@ -24,11 +29,16 @@ __device__ __forceinline__ void pf_timeline_raw(unsigned tag) {      // the call
         if (i < 4094) p[1 + i] = ((unsigned long long)tag << 48) | (t & 0xFFFFFFFFFFFFull);
     }
 }
+__device__ __forceinline__ void pf_timeline_raw_if(bool on, unsigned tag) { if (on) pf_timeline_raw(tag); }
 __device__ __forceinline__ void pf_timeline(unsigned tag) {
     if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) pf_timeline_raw(tag);
 }
 static inline cudaError_t pf_timeline_install(unsigned long long* device_log) {
+#ifdef PF_TIMELINE
     return cudaMemcpyToSymbol(g_pf_timeline, &device_log, sizeof(device_log));
+#else
+    return device_log ? cudaErrorNotSupported : cudaSuccess;
+#endif
 }
 __device__ __forceinline__ void pf_grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pf_grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

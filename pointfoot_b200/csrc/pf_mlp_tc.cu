@@ -94,7 +94,7 @@ struct TcProgram {
     TcEpi e[TC_MAX_EPIS];
 };
 
-struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; unsigned long long* trace; };   // [actor only, critic only, both]
+struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; unsigned long long* trace; int rehearse; };   // [actor only, critic only, both]
 
 static inline int pad16(int x) { return (x + 15) & ~15; }
 
@@ -120,17 +120,30 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
+    int rehearse;                // run one DRY item (no input loads, no outputs) before the dependency wait: see pf_rl_tc_rehearse
     int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs
     unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
-__device__ __forceinline__ void pf_timeline_raw(unsigned tag);
 struct TcTrace {
-    unsigned long long* p; int n; bool on_;
-    __device__ __forceinline__ void init(unsigned long long* base, int role, bool on) { p = on && base ? base + role * TC_TRACE_CAP : nullptr; n = 0; on_ = on; }
+    unsigned long long* p; int n;
+    unsigned long long* tl;            // step timeline log (pf_rl_debug_timeline), read ONCE: events cost nothing when it is off
+    __device__ __forceinline__ void init(unsigned long long* base, int role, bool on) {
+        p = on && base ? base + role * TC_TRACE_CAP : nullptr; n = 0;
+#ifdef PF_TIMELINE
+        tl = on ? g_pf_timeline : nullptr;
+#else
+        tl = nullptr;
+#endif
+    }
     __device__ __forceinline__ void ev(unsigned tag) {
         if (p && n < TC_TRACE_CAP) p[n++] = ((unsigned long long)tag << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull);
-        if (on_) pf_timeline_raw(0x1000u + tag);          // step timeline (pf_rl_debug_timeline), if installed
+        if (tl) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            const unsigned long long i = atomicAdd(tl, 1ull);
+            if (i < 4094) tl[1 + i] = ((unsigned long long)(0x1000u + tag) << 48) | (t & 0xFFFFFFFFFFFFull);
+        }
     }
 };
 
@@ -148,7 +161,7 @@ __device__ __forceinline__ float elu_fast(float x) {
 // shared store; consecutive lanes hold consecutive 8-column blocks, which is why the staged operand uses a PADDED
 // leading byte offset (TC_X0_LBO = 2048 + 16): with the natural 2048 every lane of the warp would hit the same
 // bank.  Out of line so that the loads in flight do not add to the epilogue's register pressure.
-__device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid, TcTrace& tr) {
+__device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid, TcTrace& tr, bool dry) {
     const int lane = tid & 31;
     const int k = w / a.tiles, tile = w - k * a.tiles;
     const TcProgram& P = a.prog[k];
@@ -158,7 +171,8 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     const int K0 = P.dims[0], Kp = P.pdims[0];
     const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)K0 - 1) / (uint32_t)K0);
     const float* xb = N.x + (long long)row0 * N.ldx;
-    float* cb = (N.copy_to && !(a.debug & 1)) ? N.copy_to + (long long)row0 * K0 : nullptr;
+    float* cb = (N.copy_to && !(a.debug & 1) && !dry) ? N.copy_to + (long long)row0 * K0 : nullptr;
+    const bool noload = (a.debug & 2) || dry;       // dry item: same code, zeros instead of the rows
     const int total = nrows * K0;
     auto put = [&](int e, float v) {            // element e of the contiguous tile -> (row, column)
         const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
@@ -174,7 +188,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int idx = base + u * TC_STG_THREADS;
-                if (idx < n4) v[u] = (a.debug & 2) ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
+                if (idx < n4) v[u] = noload ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -193,14 +207,14 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
             }
         }
         for (int e = n4 * 4 + tid; e < total; e += TC_STG_THREADS) {
-            const float v = __ldg(xb + e);
+            const float v = noload ? 0.0f : __ldg(xb + e);
             if (cb) cb[e] = v;
             put(e, v);
         }
     } else {
         for (int e = tid; e < total; e += TC_STG_THREADS) {
             const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
-            const float v = __ldg(xb + (long long)r * N.ldx + kx);
+            const float v = noload ? 0.0f : __ldg(xb + (long long)r * N.ldx + kx);
             if (cb) cb[e] = v;
             put(e, v);
         }
@@ -225,7 +239,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     // hit HBM in the same instant one item later and sit out the burst inside its critical path; the prefetch spreads
     // that traffic under a whole item of MMAs and turns the next staging pass into L2 hits.
     const int w2 = w + (int)gridDim.x;
-    if (w2 < a.nnets * a.tiles) {
+    if (!dry && w2 < a.nnets * a.tiles) {
         const int k2 = w2 / a.tiles, tile2 = w2 - k2 * a.tiles;
         const TcNetArgs& N2 = a.net[k2];
         const int rows2 = min(TC_ROWS, a.rows - tile2 * TC_ROWS);
@@ -295,15 +309,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pf_timeline(0x51);
-    pf_grid_dep_wait();         // first global access (observations, packed weights) comes after this
-    pf_timeline(0x52);
+    // Every role below walks the items j = -reh, 0, 1, ...: with a.rehearse the first pass (j = -1) is a DRY copy of the
+    // CTA's first item -- zeros instead of the input rows, no outputs, every barrier used exactly as by a real item --
+    // executed BEFORE the dependency wait: launched as a programmatic dependent, the CTA would otherwise sit idle at
+    // that wait while its predecessor runs, and then execute every role's code for the first time (instruction
+    // fetches all the way from DRAM after an L2 flush) on the critical path.  Each role passes the wait at j = 0.
+    const int reh = a.rehearse ? 1 : 0;
+#define TC_ITEM_LOOP(j, w, dry)                                                                  \
+    for (int j = -reh, w = (int)blockIdx.x; w < items; ++j, w = (int)blockIdx.x + (j < 0 ? 0 : j) * (int)gridDim.x) \
+        if (const bool dry = j < 0; true)
 
     if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
         {
             uint32_t slot = 0, round = 0;           // ring position: slot index and how many times the ring wrapped
             TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0 && lane == 0);
-            for (int w = blockIdx.x; w < items; w += gridDim.x) {
+            TC_ITEM_LOOP(j, w, dry) {
+                if (j == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
+                (void)dry;
                 const int k = w / a.tiles;
                 const TcProgram& P = a.prog[k];
                 const unsigned char* blob = a.net[k].blob;
@@ -344,7 +367,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 full_bar += 8; empty_bar += 8; ring_desc += TC_SLOT_BYTES >> 4;
                 if (++slot == (uint32_t)S) { slot = 0; ++round; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
             };
-            for (int w = blockIdx.x; w < items; w += gridDim.x) {
+            TC_ITEM_LOOP(j, w, dry) {
+                if (j == 0) pf_grid_dep_wait();
+                (void)dry;
                 const TcProgram& P = a.prog[w / a.tiles];
                 for (int gi = 0; gi < P.ngroups; ++gi) {
                     const TcGroup& G = P.g[gi];
@@ -414,11 +439,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
         // item i + 1 are staged right then, under the MMAs and epilogues of the remaining layers.
         TcTrace tr; tr.init(a.trace, 3, blockIdx.x == 0 && tid == TC_EPI_THREADS);
         uint32_t it = 0;
-        for (int w = blockIdx.x; w < items; w += gridDim.x, ++it) {
+        TC_ITEM_LOOP(j, w, dry) {
+            if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(tid == TC_EPI_THREADS && blockIdx.x == 0, 0x52); }
             if (it) mbar_wait(pb0 + 8 * BAR_XFREE, (it - 1u) & 1u);
             tr.ev(0x500);
-            tc_stage_item(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr);
+            tc_stage_item(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr, dry);
             tr.ev(0x502);
+            ++it;
         }
     } else {
         // ================================================================ epilogues: 8 warps
@@ -441,12 +468,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 }
             }
         };
-        for (int w = blockIdx.x; w < items; w += gridDim.x) {
+        TC_ITEM_LOOP(j, w, dry) {
+            if (j == 0) pf_grid_dep_wait();
             const int k = w / a.tiles, tile = w - k * a.tiles;
             const TcProgram& P = a.prog[k];
             const TcNetArgs& N = a.net[k];
             const int row0 = tile * TC_ROWS;
-            const int nrows = min(TC_ROWS, a.rows - row0);
+            const int nrows = dry ? 0 : min(TC_ROWS, a.rows - row0);      // dry item: no row is written
             const int L = P.layers;
             for (int ei = 0; ei < P.nepis; ++ei) {
                 const TcEpi& E = P.e[ei];
@@ -512,6 +540,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
             pbits ^= P.parity_mask;
         }
     }
+#undef TC_ITEM_LOOP
     tc_fence_before();
     __syncthreads();
     pf_timeline(0x53);
@@ -710,6 +739,15 @@ static int check_program(const TcProgram& P) {
 
 // Diagnostic: device buffer of 3 * TC_TRACE_CAP uint64 that CTA 0 of every following launch fills with its role
 // timelines (tools/tc_trace.py); NULL switches it off.
+// Opt-in: the fused act / MLP kernel runs one dry item before its dependency wait (see the kernel).  Worth it when the
+// kernel is launched right behind a kernel that still runs for a few microseconds (a CUDA-graphed env step + act
+// chain); without such a predecessor it adds one item's latency, hence off by default.
+extern "C" int pf_rl_tc_rehearse(pf_rl_ctx* c, int on) {
+    if (!c || !c->tc) return 1;
+    static_cast<TcState*>(c->tc)->rehearse = on ? 1 : 0;
+    return 0;
+}
+
 extern "C" int pf_rl_debug_timeline(unsigned long long* device_log) {
     return pf_timeline_install(device_log) == cudaSuccess ? 0 : 1;
 }
@@ -806,10 +844,14 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.stages = t->stages[variant];
     a.x0_bytes = t->x0_bytes[variant];
     a.trace = t->trace;
+    a.rehearse = 0;
     { const char* e = getenv("PF_TC_DEBUG"); a.debug = e ? atoi(e) : 0; }
     const int items = a.nnets * a.tiles;
     if (items == 0) return 0;
     const int grid = items < c->num_sms ? items : c->num_sms;
+    // the dry item pays off only while a CTA has a single item (its whole latency is exposed) -- measured: -5 us at
+    // 4,096 envs, +3 us at 16,384 (two items per CTA, a shorter wait to hide it in)
+    a.rehearse = t->rehearse && items <= c->num_sms;
     return pf_launch_pdl(pf_mlp_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
                ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }

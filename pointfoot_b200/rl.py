@@ -488,6 +488,10 @@ class BenchPolicy:
         self.launches_per_act = 1 if precision == "bf16" else n_layers + 3      # bf16: ONE fused tcgen05 launch
         self.t = 0
         self.actions = self.alg._actions          # pf_rl_act writes the sampled actions here: step them directly
+        # the act kernel is launched right behind the env step's kernels (one CUDA graph): let it run its dry item under
+        # their tail (pf_rl_tc_rehearse).  PF_RL_REHEARSE=0 switches it off.
+        if precision == "bf16" and os.environ.get("PF_RL_REHEARSE", "1") != "0":
+            self.alg._lib.pf_rl_tc_rehearse(self.alg._ctx, 1)
 
     def describe(self):
         return (f"ActorCritic actor {self.ac.actor_dims} critic {self.ac.critic_dims} ELU, {self.precision}; "

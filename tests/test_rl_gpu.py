@@ -56,3 +56,33 @@ def test_rollout_buffer_overflow_raises():
             ppo.act(torch.zeros(8, 27, device="cuda"), torch.zeros(8, 27, device="cuda"))
     finally:
         ppo.close()
+
+
+@pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 300), ((512, 256, 128), 148, 4096), ((128, 64, 32), 27, 50001)])
+def test_rehearsed_act_is_bit_identical(hidden, nc, n):
+    """pf_rl_tc_rehearse: the dry item the fused kernel runs before its dependency wait changes no output bit
+    (actions, values, log-probs, storage rows), with one item per CTA and with several."""
+    import torch
+    from pointfoot_b200 import rl
+    outs = []
+    for on in (0, 1):
+        torch.manual_seed(11)
+        ac = rl.ActorCritic(27, nc, 6, hidden, hidden)
+        ppo = rl.PPO(ac, precision="bf16", num_mini_batches=4, num_learning_epochs=1)
+        ppo.init_storage(n, 3, [27], [nc], [6])
+        assert ppo._lib.pf_rl_tc_rehearse(ppo._ctx, on) == 0
+        g = torch.Generator(device="cuda").manual_seed(5)
+        res = []
+        for t in range(3):
+            obs = torch.randn(n, 27, device="cuda", generator=g)
+            cobs = torch.randn(n, nc, device="cuda", generator=g)
+            a = ppo.act(obs, cobs).clone()
+            ppo.storage.step += 1 if ppo.storage.step == t else 0
+            res.append(a)
+        torch.cuda.synchronize()
+        st = ppo.storage
+        outs.append([torch.stack(res)] + [getattr(st, k).clone() for k in ("observations", "privileged_observations", "actions", "values",
+                                                                           "actions_log_prob", "mu", "sigma")])
+        ppo.close()
+    for x, y in zip(*outs):
+        assert torch.equal(x, y)

@@ -1,5 +1,6 @@
 """Device timeline of one CUDA-graphed policy step (pf_debug_timeline / pf_rl_debug_timeline): when each kernel's CTA 0
-starts, passes its griddepcontrol.wait and ends, in ns of the GPU's global timer.
+starts, passes its griddepcontrol.wait and ends, in ns of the GPU's global timer.  Needs the diagnostic build:
+    PF_BUILD_TIMELINE=1 python __graft_entry__.py --force      (the marks are compiled out of the product build)
 usage: python tools/step_timeline.py [task] [num_envs]"""
 import argparse
 import ctypes as C
@@ -27,7 +28,8 @@ lib = env._lib
 for _ in range(5):
     flush.fill_(1); step()
 torch.cuda.synchronize()
-assert lib.pf_debug_timeline(C.c_void_p(log.data_ptr())) == 0 and lib.pf_rl_debug_timeline(C.c_void_p(log.data_ptr())) == 0
+if lib.pf_debug_timeline(C.c_void_p(log.data_ptr())) != 0 or lib.pf_rl_debug_timeline(C.c_void_p(log.data_ptr())) != 0:
+    sys.exit("timeline marks are not compiled in: PF_BUILD_TIMELINE=1 python __graft_entry__.py --force")
 for _ in range(3):
     flush.fill_(1); step()
 torch.cuda.synchronize()
