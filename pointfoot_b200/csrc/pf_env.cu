@@ -452,6 +452,17 @@ __global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const p
             }
         }
     }    pf_timeline(0x22);
+#ifdef PF_TIMELINE
+    {   // latest end time over all warps, kept apart for warps with / without a reset env: log[4000], log[4001]
+        unsigned long long* p = g_pf_timeline;
+        const bool had_reset = __any_sync(0xffffffffu, is_reset);
+        if (p && lane == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            atomicMax(p + 4000 + (had_reset ? 1 : 0), t);
+        }
+    }
+#endif
 }
 
 // the instantiation of the step kernel for a context: statement of the step (pf_step_mode) x with / without height scan

@@ -31,6 +31,7 @@ torch.cuda.synchronize()
 if lib.pf_debug_timeline(C.c_void_p(log.data_ptr())) != 0 or lib.pf_rl_debug_timeline(C.c_void_p(log.data_ptr())) != 0:
     sys.exit("timeline marks are not compiled in: PF_BUILD_TIMELINE=1 python __graft_entry__.py --force")
 for _ in range(3):
+    log[4000:4002] = 0                 # per-step maxima (the last step's survive)
     flush.fill_(1); step()
 torch.cuda.synchronize()
 lib.pf_debug_timeline(None); lib.pf_rl_debug_timeline(None)
@@ -56,3 +57,5 @@ for t, tag in ev[cut:]:
         name = "   act " + TC.get(k, hex(k)) + " " + ({0: "begin", 2: "arrived", 3: "loaded", 4: "padded", 5: "signalled"}.get(sub, str(sub)) if k == 5 else str(sub))
     name = name or hex(tag)
     print(f"{(t - t0) / 1000:8.2f} us  {name}")
+if raw[4000] or raw[4001]:
+    print(f"step kernel, last warp to finish: without a reset env {(raw[4000] - t0) / 1000:8.2f} us, with one {(raw[4001] - t0) / 1000:8.2f} us")
