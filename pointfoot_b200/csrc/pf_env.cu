@@ -161,6 +161,38 @@ __device__ __forceinline__ double pf_scan_env(const pf_params& P, const pf_env_b
     return want_sum ? pf_warp_sum(acc) : 0.0;
 }
 
+// The same scan for the rare caller (phase 4 of the step kernel: envs that reset), ROLLED: one copy of the point's code
+// instead of eight, the grid point and noise scale read inside the loop.  The few warps that take this path are the
+// last of the launch to retire and execute it exactly once, so what counts is how many cold instruction lines they
+// have to fetch, not instructions per point (same arithmetic, same results).
+template <bool kFast>
+__device__ __forceinline__ void pf_scan_env_rolled(const pf_params& P, const pf_env_buffers& B, const PfCtxScratch& S,
+                                                const float* __restrict__ root, float zn, float wn, float root_z_obs,
+                                                uint32_t nkey, int e, int lane) {
+    const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
+    const bool rough = P.terrain_kind == PF_TERRAIN_HEIGHTFIELD;
+    const float bx = root[0], by = root[1];
+    float* mh = B.measured_heights ? B.measured_heights + (size_t)e * Pn : nullptr;
+    float* oh = P.measure_heights_actor ? B.obs_buf + (size_t)e * P.num_obs + base_w : nullptr;
+    float* ph = (P.measure_heights_critic && B.priv_obs_buf) ? B.priv_obs_buf + (size_t)e * P.num_priv_obs + base_w : nullptr;
+#pragma unroll 1
+    for (int p = lane; p < Pn; p += 32) {
+        const float2 g = reinterpret_cast<const float2*>(S.height_points)[p];
+        const float ns = S.noise_vec[base_w + p];
+        int16_t r = 0;
+        if (rough) r = pf_scan_point(P, B.height_samples, zn, wn, g.x, g.y, bx, by, kFast ? &S.rew : nullptr);
+        const float h = (float)r * P.vertical_scale;
+        if (mh) mh[p] = h;
+        if (oh || ph) {
+            float v = pf_clipf((root_z_obs - 0.5f) - h, -1.0f, 1.0f) * P.obs_scale_height;
+            if (P.add_noise && ns != 0.0f) v = v + (2.0f * pf_rng_uniform(nkey, (uint32_t)(base_w + p)) - 1.0f) * ns;
+            v = pf_clipf(v, -P.clip_obs, P.clip_obs);
+            if (oh) oh[p] = v;
+            if (ph) ph[p] = v;
+        }
+    }
+}
+
 __device__ __forceinline__ void pf_scan_lane_load(const pf_params& P, const PfCtxScratch& S, int lane, PfScanLane& L) {
     const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
 #pragma unroll
@@ -438,20 +470,16 @@ __global__ void __launch_bounds__(128, 2 * kMinB) pf_post_physics_kernel(const p
     // ---- phase 4: height columns of the envs that reset ----
     if (kScan && (P.measure_heights_actor || P.measure_heights_critic)) {
         unsigned m = __ballot_sync(0xffffffffu, is_reset);
-        if (m) {
-            PfScanLane L;
-            pf_scan_lane_load(P, S, lane, L);
-            while (m) {
-                const int i = __ffs(m) - 1;
-                m &= m - 1;
-                const float* r = s.root + i * 13;
-                float zn, wn;
-                pf_yaw_quat(r + 3, zn, wn);
-                pf_scan_env<true, kFast>(P, B, L, r, zn, wn, s.misc[4 * i + 2], __float_as_uint(s.misc[4 * i + 3]), e0 + i,
-                                         lane, false, &S.rew);
-            }
+        while (m) {
+            const int i = __ffs(m) - 1;
+            m &= m - 1;
+            const float* r = s.root + i * 13;
+            float zn, wn;
+            pf_yaw_quat(r + 3, zn, wn);
+            pf_scan_env_rolled<kFast>(P, B, S, r, zn, wn, s.misc[4 * i + 2], __float_as_uint(s.misc[4 * i + 3]), e0 + i, lane);
         }
-    }    pf_timeline(0x22);
+    }
+    pf_timeline(0x22);
 #ifdef PF_TIMELINE
     {   // latest end time over all warps, kept apart for warps with / without a reset env: log[4000], log[4001]
         unsigned long long* p = g_pf_timeline;
