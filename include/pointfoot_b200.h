@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-#define PF_ABI_VERSION 1
+#define PF_ABI_VERSION 2
 #define PF_MAX_DOF 6
 #define PF_MAX_BODIES 9
 #define PF_NUM_FEET 2
@@ -163,6 +163,10 @@ int pf_sizeof_env_buffers(void);
 int pf_ctx_create(const pf_params* params, const float* noise_scale_vec_host,
                   const float* height_points_xy_host, pf_ctx** out);
 int pf_ctx_destroy(pf_ctx* ctx);
+/* update_command_curriculum (PF:638-650, LR:443-453) widens command_ranges["lin_vel_x"] on the host; ranges[4][2] =
+ * lin_vel_x, lin_vel_y, ang_vel_yaw, heading replaces pf_params.cmd_range for every later launch of this ctx (a step
+ * captured in a CUDA graph keeps the old values: re-capture). */
+int pf_set_command_ranges(pf_ctx* ctx, const float* ranges_host);
 
 /* PF:176-177 + PF:523-547 (LR:353-375).  If actions_in != NULL it is clipped to +-clip_actions into
  * bufs->actions first (the step() prologue); torques written to bufs->torques. */
@@ -316,10 +320,11 @@ int pf_rl_tc_rehearse(pf_rl_ctx* ctx, int on);
 int pf_rl_act(pf_rl_ctx* ctx, const float* params, const float* obs, const float* critic_obs, int32_t t,
               const pf_rl_storage* storage, int64_t policy_step, float* actions_out, float* values_out,
               float* logp_out, void* stream);
-/* ActorCritic.act_inference: actions_out = actor(obs) */
-int pf_rl_act_inference(pf_rl_ctx* ctx, const float* params, const float* obs, float* actions_out, void* stream);
-/* ActorCritic.evaluate: values_out[N] = critic(critic_obs) */
-int pf_rl_evaluate(pf_rl_ctx* ctx, const float* params, const float* critic_obs, float* values_out, void* stream);
+/* ActorCritic.act_inference: actions_out[rows, A] = actor(obs[rows, num_obs]); any row count (upstream accepts any
+ * batch: one row in play / export checks), processed in chunks of the workspace size */
+int pf_rl_act_inference(pf_rl_ctx* ctx, const float* params, const float* obs, int32_t rows, float* actions_out, void* stream);
+/* ActorCritic.evaluate: values_out[rows] = critic(critic_obs[rows, num_critic_obs]) */
+int pf_rl_evaluate(pf_rl_ctx* ctx, const float* params, const float* critic_obs, int32_t rows, float* values_out, void* stream);
 /* PPO.process_env_step: rewards[t] = rew + gamma * values[t] * time_outs (time_outs may be NULL), dones[t] = dones */
 int pf_rl_process_env_step(pf_rl_ctx* ctx, const pf_rl_storage* storage, int32_t t, const float* rew,
                            const uint8_t* dones, const uint8_t* time_outs, void* stream);

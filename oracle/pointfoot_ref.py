@@ -117,6 +117,10 @@ class RefEnv:
         self.reset_ids = torch.zeros(0, dtype=torch.int32)
         self.push_forces = z(N, B, 3)
         self.extras_time_outs = z(N, dt=torch.bool)
+        # PF:492-493, 1009: 0 = never (the caller sets it from cfg.domain_rand; it is host-side state, not a kernel parameter)
+        self.push_interval = 0
+        self.sim_dt_py = None           # cfg.sim.dt as the python float the reference divides by (PF:595)
+        self.max_push_vel_xy_py = None
 
     # -------------------------------------------------------------------------------- PF:523-547
     def compute_torques(self):
@@ -236,6 +240,8 @@ class RefEnv:
             ang %= 2 * np.pi
             ang -= 2 * np.pi * (ang > np.pi)
             self.commands[:, 2] = torch.clip(0.5 * ang, -1., 1.)
+        if self.push_interval and self.common_step_counter % self.push_interval == 0:      # PF:492-493
+            self.push_robots(self.base_mass.mean().item() * self.max_push_vel_xy_py / self.sim_dt_py)
 
     # -------------------------------------------------------------------------------- PF:590-611
     def push_robots(self, max_push_force):
@@ -402,3 +408,25 @@ class RefEnv:
             if P.num_priv_obs:
                 extra = (2 * torch.from_numpy(ctx.uniform((self.N, P.num_priv_obs - n_obs))) - 1) * self.noise_vec[n_obs:]
                 self.priv_obs_buf += torch.cat((noise, extra), dim=1)
+
+
+def heights_native_eager(orc, device):
+    """``_get_heights`` (PF:1048-1075, 1100-1112) of a RefEnv with the tensors on ``device`` and the division of PF:1102
+    left to torch's own ``/`` operator there: ATen's CPU kernel divides, its CUDA kernel multiplies by the reciprocal of
+    the scalar.  Used by the GPU tests to pin PF_DIV_RECIPROCAL to what the reference does on a CUDA device."""
+    P = orc.P
+    root = orc.root_states.to(device)
+    pts0 = orc.height_points.to(device)
+    hs_t = orc.height_samples.to(device)
+    quat = root[:, 3:7].repeat(1, orc.num_height_points)
+    qy = quat.clone().view(-1, 4)
+    qy[:, :2] = 0.
+    qy = normalize(qy)
+    points = quat_apply(qy, pts0) + (root[:, :3]).unsqueeze(1)
+    points = points + _f(P.border_size)
+    points = (points / _f(np.float32(P.horizontal_scale))).long()
+    px = torch.clip(points[:, :, 0].view(-1), 0, hs_t.shape[0] - 2)
+    py = torch.clip(points[:, :, 1].view(-1), 0, hs_t.shape[1] - 2)
+    h = torch.min(hs_t[px, py], hs_t[px + 1, py])
+    h = torch.min(h, hs_t[px, py + 1])
+    return h.view(orc.N, -1) * _f(np.float32(P.vertical_scale))

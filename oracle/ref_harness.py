@@ -277,8 +277,10 @@ def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0):
               "first_contact", "last_contacts", "current_max_feet_height", "last_max_feet_height"):
         if k in state:
             getattr(env, k)[:] = state[k]
-    if "episode_sums" in state:
-        for i, name in enumerate(env.episode_sums.keys()):
+    if "episode_sums" in state:      # rows in the C-ABI's order: summation order, 'termination' last (include/pointfoot_b200.h)
+        keys = [k for k in env.episode_sums.keys() if k != "termination"]
+        keys += ["termination"] if "termination" in env.episode_sums else []
+        for i, name in enumerate(keys):
             env.episode_sums[name][:] = state["episode_sums"][i]
     env.common_step_counter = int(state.get("common_step_counter", 0))
     return env

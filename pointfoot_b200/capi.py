@@ -6,7 +6,7 @@ product path raises.  Build with ``python -c "import __graft_entry__ as g; g.bui
 import ctypes as C
 import os
 
-PF_ABI_VERSION = 1
+PF_ABI_VERSION = 2
 MAX_DOF, MAX_BODIES, NUM_FEET, MAX_REWARD_TERMS, MAX_HEIGHT_POINTS = 6, 9, 2, 24, 256
 
 REWARD_IDS = {name: i for i, name in enumerate((

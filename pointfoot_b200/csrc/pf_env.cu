@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <stdlib.h>
 #include <stdio.h>
+#include <string.h>
 #include "pf_env_core.cuh"
 #include "pf_ctx.h"
 #include "pf_tc_ptx.cuh"      // mbarrier + bulk-copy wrappers
@@ -717,6 +718,8 @@ static int pf_pick_epw(int num_envs, int num_sms) {
     return 32;
 }
 
+static int pf_ctx_init(pf_ctx* c, const float* noise_scale_vec_host, const float* height_points_xy_host);
+
 extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_vec_host,
                              const float* height_points_xy_host, pf_ctx** out) {
     if (!params || !out) return pf_fail(1, "pf_ctx_create: %s", "null argument");
@@ -743,7 +746,18 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
         return pf_fail(2, "pf_ctx_create: no CUDA device (%s); there is no CPU fallback", cudaGetErrorString(e));
 
     pf_ctx* c = new pf_ctx();
+    memset(&c->S, 0, sizeof(c->S));
+    c->d_actions_in = nullptr; c->io_stream = nullptr;
+    c->ev_fork = c->ev_in = c->ev_post = c->ev_out = c->ev_fin = nullptr;
     c->P = P;
+    if (int rc = pf_ctx_init(c, noise_scale_vec_host, height_points_xy_host)) { pf_ctx_destroy(c); return rc; }
+    *out = c;
+    return 0;
+}
+
+// everything of pf_ctx_create that can fail after the context object exists (the caller destroys it on a non-zero return)
+static int pf_ctx_init(pf_ctx* c, const float* noise_scale_vec_host, const float* height_points_xy_host) {
+    const pf_params& P = c->P;
     PF_CUDA(cudaGetDevice(&c->device));
     PF_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device));
     c->envs_per_warp = pf_pick_epw(P.num_envs, c->num_sms);
@@ -756,7 +770,7 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     c->max_blocks = c->num_slabs;
     c->smem_bytes = (size_t)(c->threads / 32) * pf_warp_smem_floats(P, c->envs_per_warp) * sizeof(float);
     c->canonical = pf_step_mode(P, c->S.rew, getenv("PF_GENERIC_REWARDS") != nullptr, getenv("PF_TABLE_REWARDS") != nullptr);
-    if (c->smem_bytes > 200 * 1024) { delete c; return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded"); }
+    if (c->smem_bytes > 200 * 1024) return pf_fail(1, "pf_ctx_create: %s", "shared memory budget exceeded");
     c->step_kernel = pf_pick_step_kernel(c->canonical, P.num_height_points > 0);
     c->generic_kernel = pf_pick_step_kernel(0, P.num_height_points > 0);
     PF_CUDA(cudaFuncSetAttribute(c->step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c->smem_bytes));
@@ -765,16 +779,16 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     const int nv = P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs;
     float* d_noise = nullptr; float* d_pts = nullptr;
     PF_CUDA(cudaMalloc(&d_noise, sizeof(float) * nv));
+    c->S.noise_vec = d_noise;
     if (noise_scale_vec_host) PF_CUDA(cudaMemcpy(d_noise, noise_scale_vec_host, sizeof(float) * nv, cudaMemcpyHostToDevice));
     else PF_CUDA(cudaMemset(d_noise, 0, sizeof(float) * nv));
     PF_CUDA(cudaMalloc(&d_pts, sizeof(float) * 2 * (P.num_height_points > 0 ? P.num_height_points : 1)));
+    c->S.height_points = d_pts;
     if (P.num_height_points > 0) {
-        if (!height_points_xy_host) { delete c; return pf_fail(1, "pf_ctx_create: %s", "height points missing"); }
+        if (!height_points_xy_host) return pf_fail(1, "pf_ctx_create: %s", "height points missing");
         PF_CUDA(cudaMemcpy(d_pts, height_points_xy_host, sizeof(float) * 2 * P.num_height_points, cudaMemcpyHostToDevice));
     }
     PF_CUDA(cudaMalloc(&c->S.height_mean, sizeof(float) * (size_t)P.num_envs));
-    c->S.noise_vec = d_noise;
-    c->S.height_points = d_pts;
     PF_CUDA(cudaMalloc(&c->S.blk_count, sizeof(int) * c->max_blocks));
     PF_CUDA(cudaMalloc(&c->S.blk_level, sizeof(long long) * c->max_blocks));
     PF_CUDA(cudaMalloc(&c->S.blk_sums, sizeof(double) * PF_MAX_REWARD_TERMS * c->max_blocks));
@@ -789,7 +803,12 @@ extern "C" int pf_ctx_create(const pf_params* params, const float* noise_scale_v
     for (cudaEvent_t* e : {&c->ev_fork, &c->ev_in, &c->ev_post, &c->ev_out, &c->ev_fin}) PF_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     c->out_pending = 0;
     c->fin_pending = 0;
-    *out = c;
+    return 0;
+}
+
+extern "C" int pf_set_command_ranges(pf_ctx* c, const float* ranges_host) {
+    if (!c || !ranges_host) return pf_fail(1, "%s", "pf_set_command_ranges: null argument");
+    for (int i = 0; i < 4; ++i) { c->P.cmd_range[i][0] = ranges_host[2 * i]; c->P.cmd_range[i][1] = ranges_host[2 * i + 1]; }
     return 0;
 }
 

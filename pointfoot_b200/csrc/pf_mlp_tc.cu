@@ -821,7 +821,7 @@ int pf_tc_create(pf_rl_ctx* c) {
 }
 
 void pf_tc_destroy(pf_rl_ctx* c) {
-    for (int k = 0; k < 2; ++k) cudaFree(c->net[k].tc_weights);
+    for (int k = 0; k < 2; ++k) { cudaFree(c->net[k].tc_weights); c->net[k].tc_weights = nullptr; }
     delete static_cast<TcState*>(c->tc);
     c->tc = nullptr;
 }

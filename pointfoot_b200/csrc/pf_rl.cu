@@ -156,6 +156,8 @@ static int setup_net(PfNet& n, int layers, const int32_t* dims, long long& off) 
     return 0;
 }
 
+static int rl_ctx_init(pf_rl_ctx* c);
+
 extern "C" int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out) {
     if (!params || !out) return rl_fail(1, "pf_rl_create", "null argument");
     const pf_rl_params& P = *params;
@@ -168,16 +170,22 @@ extern "C" int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out) {
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return rl_fail(2, "pf_rl_create: no CUDA device; there is no CPU fallback", cudaGetErrorString(e));
-    pf_rl_ctx* c = new pf_rl_ctx();
+    pf_rl_ctx* c = new pf_rl_ctx();      // value-initialised: every pointer starts NULL, so a failed create can be destroyed
     c->P = P;
+    if (int rc = rl_ctx_init(c)) { pf_rl_destroy(c); return rc; }
+    *out = c;
+    return 0;
+}
+
+// the part of pf_rl_create that can fail once the context exists (the caller destroys it on a non-zero return)
+static int rl_ctx_init(pf_rl_ctx* c) {
+    const pf_rl_params& P = c->P;
     RL_CUDA(cudaGetDevice(&c->device));
     RL_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, c->device));
     long long off = 0;
     c->std_off = off; off += P.num_actions;                       // ActorCritic.parameters(): std first
-    if (setup_net(c->net[0], P.actor_layers, P.actor_dims, off) || setup_net(c->net[1], P.critic_layers, P.critic_dims, off)) {
-        delete c;
+    if (setup_net(c->net[0], P.actor_layers, P.actor_dims, off) || setup_net(c->net[1], P.critic_layers, P.critic_dims, off))
         return rl_fail(1, "pf_rl_create", "bad MLP description");
-    }
     c->n_params = off;
     const long long total = (long long)P.num_envs * P.num_steps;
     c->mb_size = (int)(total / P.num_mini_batches);
@@ -212,18 +220,18 @@ extern "C" int pf_rl_create(const pf_rl_params* params, pf_rl_ctx** out) {
     RL_CUDA(cudaMalloc(&c->norm_part, sizeof(double) * (size_t)(c->norm_blocks + 8)));
     c->tc = nullptr;
     if (P.precision == PF_RL_BF16_TC) {
-        if (int rc = pf_tc_create(c)) { return rc; }
-        if (int rc = pf_tc_gemm_create(c)) { return rc; }
+        if (int rc = pf_tc_create(c)) return rc;
+        if (int rc = pf_tc_gemm_create(c)) return rc;
     } else if (P.precision != PF_RL_FP32) {
         return rl_fail(1, "pf_rl_create", "unknown precision");
     }
-    *out = c;
     return 0;
 }
 
 extern "C" int pf_rl_destroy(pf_rl_ctx* c) {
     if (!c) return 0;
     if (c->tc) pf_tc_destroy(c);
+    for (int k = 0; k < 2; ++k) cudaFree(c->net[k].tc_weights);       // (a pf_tc_create that failed half-way)
     pf_tc_gemm_destroy(c);
     for (int k = 0; k < 2; ++k)
         for (int l = 0; l < c->net[k].layers; ++l) cudaFree(c->net[k].act[l]);
@@ -353,27 +361,36 @@ extern "C" int pf_rl_act(pf_rl_ctx* c, const float* params, const float* obs, co
     return 0;
 }
 
-extern "C" int pf_rl_act_inference(pf_rl_ctx* c, const float* params, const float* obs, float* actions_out, void* stream) {
-    if (int rc = check_rl(c, params, obs, "pf_rl_act_inference")) return rc;
-    if (!actions_out) return rl_fail(1, "pf_rl_act_inference", "null output");
-    cudaStream_t st = (cudaStream_t)stream;
-    float* mean = nullptr;
-    if (int rc = mlp_forward(c, 0, params, obs, c->P.num_envs, actions_out, nullptr, st, &mean)) return rc;
-    if (mean != actions_out)
-        RL_CUDA(cudaMemcpyAsync(actions_out, mean, sizeof(float) * (size_t)c->P.num_envs * c->P.num_actions,
-                                cudaMemcpyDeviceToDevice, st));
+// ActorCritic.act_inference / evaluate accept any batch size upstream (a single observation row in play / export
+// checks, a whole rollout in analysis scripts): `rows` rows are processed in chunks of at most rows_cap, the size
+// the activation workspace was allocated for.
+static int mlp_rows(pf_rl_ctx* c, int k, const float* params, const float* x, int rows, float* out, cudaStream_t st) {
+    const int in_w = c->net[k].dims[0], out_w = c->net[k].dims[c->net[k].layers];
+    for (int r0 = 0; r0 < rows; r0 += c->rows_cap) {
+        const int n = rows - r0 < c->rows_cap ? rows - r0 : c->rows_cap;
+        float* dst = out + (size_t)r0 * out_w;
+        float* res = nullptr;
+        if (int rc = mlp_forward(c, k, params, x + (size_t)r0 * in_w, n, dst, nullptr, st, &res)) return rc;
+        if (res != dst)
+            RL_CUDA(cudaMemcpyAsync(dst, res, sizeof(float) * (size_t)n * out_w, cudaMemcpyDeviceToDevice, st));
+    }
     return 0;
 }
 
-extern "C" int pf_rl_evaluate(pf_rl_ctx* c, const float* params, const float* critic_obs, float* values_out, void* stream) {
+extern "C" int pf_rl_act_inference(pf_rl_ctx* c, const float* params, const float* obs, int32_t rows, float* actions_out,
+                                   void* stream) {
+    if (int rc = check_rl(c, params, obs, "pf_rl_act_inference")) return rc;
+    if (!actions_out) return rl_fail(1, "pf_rl_act_inference", "null output");
+    if (rows < 0) return rl_fail(1, "pf_rl_act_inference", "negative row count");
+    return mlp_rows(c, 0, params, obs, rows, actions_out, (cudaStream_t)stream);
+}
+
+extern "C" int pf_rl_evaluate(pf_rl_ctx* c, const float* params, const float* critic_obs, int32_t rows, float* values_out,
+                              void* stream) {
     if (int rc = check_rl(c, params, critic_obs, "pf_rl_evaluate")) return rc;
     if (!values_out) return rl_fail(1, "pf_rl_evaluate", "null output");
-    cudaStream_t st = (cudaStream_t)stream;
-    float* val = nullptr;
-    if (int rc = mlp_forward(c, 1, params, critic_obs, c->P.num_envs, values_out, nullptr, st, &val)) return rc;
-    if (val != values_out)
-        RL_CUDA(cudaMemcpyAsync(values_out, val, sizeof(float) * (size_t)c->P.num_envs, cudaMemcpyDeviceToDevice, st));
-    return 0;
+    if (rows < 0) return rl_fail(1, "pf_rl_evaluate", "negative row count");
+    return mlp_rows(c, 1, params, critic_obs, rows, values_out, (cudaStream_t)stream);
 }
 
 // PPO.process_env_step (ppo.py): rewards = rew.clone(); rewards += gamma * squeeze(values * time_outs)

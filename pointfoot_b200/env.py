@@ -72,6 +72,9 @@ class PointFoot:
         if self.device.type != "cuda" or not torch.cuda.is_available():
             raise RuntimeError("pointfoot_b200.PointFoot needs a CUDA device (no CPU fallback); got " + str(sim_device))
         self._lib = capi.load()
+        # multi-GPU block sharding: global id of local env 0 (the RNG contract keys on global ids; the runner hands the
+        # same offset to the policy's sampling kernel) and the contract's seed
+        self.env_id_offset, self.seed = int(env_id_offset), int(seed)
         N = self.num_envs = cfg.env.num_envs
         self.num_obs = cfg.env.num_propriceptive_obs
         self.num_privileged_obs = cfg.env.num_privileged_obs
@@ -158,6 +161,7 @@ class PointFoot:
         self.d_gains = torch.tensor([P.d_gains[i] for i in range(D)], device=dev)
         self.torque_limits = torch.tensor([P.torque_limits[i] for i in range(D)], device=dev)
         self.base_mass = self._state.get("base_mass", torch.full((N,), pf_params.RobotModel.base_mass, device=dev))
+        self._refresh_max_push_force()
         self.measured_heights = z(N, P.num_height_points) if P.num_height_points else 0
         R = P.num_reward_terms + P.has_termination_term
         self._episode_sums = z(R, N)
@@ -267,14 +271,30 @@ class PointFoot:
         capi.check(self._lib.pf_post_physics_step(self._ctx, C.byref(self._bufs), C.c_int64(self.common_step_counter), st),
                    "pf_post_physics_step")
         self._notify_gym_of_resets()
+        self._maybe_command_curriculum()
+
+    def _maybe_command_curriculum(self):
+        if self._command_curriculum_due() and int(self._reset_count.item()) > 0:   # reset_idx returns early without resets (PF:259)
+            self.update_command_curriculum()
+
+    def _command_curriculum_due(self):
+        """point_foot.py:265: only on steps where common_step_counter % max_episode_length == 0 (every 1000 steps)"""
+        return bool(self.cfg.commands.curriculum) and self.common_step_counter % self.max_episode_length == 0
 
     def join_tail(self):
         """make the current stream wait for a deferred step tail (pf_post_physics_step_begin / _join)"""
         capi.check(self._lib.pf_post_physics_step_join(self._ctx, self._stream()), "pf_post_physics_step_join")
 
+    def _refresh_max_push_force(self):
+        """point_foot.py:592-596 evaluates base_mass.mean().item() * max_push_vel_xy / dt on every push; base_mass only
+        changes through update_added_mass_and_base_com, so the python double is kept (no host sync on the step path,
+        and a push step can sit inside a stream capture)."""
+        self._max_push_force = (float(self.base_mass.mean().item()) * self.cfg.domain_rand.max_push_vel_xy
+                                / self.cfg.sim.dt)
+
     def _push_robots(self, st):
         """point_foot.py:590-611."""
-        m = float(self.base_mass.mean().item()) * self.cfg.domain_rand.max_push_vel_xy / self.cfg.sim.dt
+        m = self._max_push_force
         capi.check(self._lib.pf_push_forces(self._ctx, C.byref(self._bufs),
                                             C.c_void_p(self.rigid_body_external_forces.data_ptr()), C.c_float(m),
                                             C.c_int64(self.common_step_counter), st), "pf_push_forces")
@@ -300,6 +320,48 @@ class PointFoot:
     def update_cmd(self, cmd):
         """point_foot.py:123-129 (sys-id scripts drive env 0 by hand)."""
         self.commands[0, :3] = torch.as_tensor(cmd[:3], dtype=torch.float, device=self.device)
+
+    def update_frictions(self, fric, env_handle, actor_handle):
+        """point_foot.py:103-108: a pass-through to the physics backend (nothing on the per-step path reads it)."""
+        dof_props = self.gym.get_actor_dof_properties(env_handle, actor_handle)
+        for i in range(len(dof_props["friction"])):
+            dof_props["friction"][i] = fric[i]
+        self.gym.set_actor_dof_properties(env_handle, actor_handle, dof_props)
+
+    def update_added_mass_and_base_com(self, added_mass, added_com, env_handle, actor_handle):
+        """point_foot.py:110-121: pass-through to the physics backend; ``base_mass`` becomes the 0-d tensor the
+        reference leaves behind (so the push force scale follows, point_foot.py:592-596)."""
+        body_props = self.gym.get_actor_rigid_body_properties(env_handle, actor_handle)
+        body_props[0].mass += added_mass
+        self.base_mass = torch.tensor(body_props[0].mass, dtype=torch.float)
+        body_props[0].com.x += added_com[0]
+        body_props[0].com.y += added_com[1]
+        body_props[0].com.z += added_com[2]
+        self.gym.set_actor_rigid_body_properties(env_handle, actor_handle, body_props, recomputeInertia=True)
+        self._refresh_max_push_force()
+
+    def update_command_curriculum(self, env_ids=None):
+        """point_foot.py:638-650: widen the lin_vel_x command range when the mean tracking reward of the envs that just
+        reset exceeds 80 % of its maximum.  ``extras["episode"]["rew_tracking_lin_vel"]`` already holds that mean
+        (divided by max_episode_length_s, point_foot.py:279-280).  The new range goes into the context (the LR
+        command resampling of LR:337-351 draws from it) and into ``command_ranges``."""
+        if "tracking_lin_vel" not in self.reward_names:
+            raise KeyError("tracking_lin_vel")           # the reference indexes episode_sums / reward_scales by that name
+        k = self.reward_names.index("tracking_lin_vel")
+        mean = float(self._episode_stats[k].item()) * self.max_episode_length_s
+        if mean / self.max_episode_length > 0.8 * self.reward_scales["tracking_lin_vel"]:
+            r, mx = self.command_ranges["lin_vel_x"], self.cfg.commands.max_curriculum
+            r[0] = float(np.clip(r[0] - 0.5, -mx, 0.))
+            r[1] = float(np.clip(r[1] + 0.5, 0., mx))
+            self._push_command_ranges()
+
+    def _push_command_ranges(self):
+        cr = self.command_ranges
+        arr = (C.c_float * 8)(*[float(v) for key in ("lin_vel_x", "lin_vel_y", "ang_vel_yaw", "heading") for v in cr[key]])
+        capi.check(self._lib.pf_set_command_ranges(self._ctx, arr), "pf_set_command_ranges")
+        for i, key in enumerate(("lin_vel_x", "lin_vel_y", "ang_vel_yaw", "heading")):
+            self._P.cmd_range[i][0], self._P.cmd_range[i][1] = cr[key]
+        self.graph_epoch = getattr(self, "graph_epoch", 0) + 1      # constants changed: a captured step must be re-captured
 
     @property
     def reset_env_ids(self):
@@ -335,12 +397,21 @@ class GraphedStep:
             self._eager()                      # warm-up on the side stream (lazy module loads, allocator)
         torch.cuda.current_stream(env.device).wait_stream(side)
         torch.cuda.synchronize(env.device)
+        self._capture()
+        self.launches_per_step = None
+
+    def _capture(self):
+        env = self.env
         self.graph = torch.cuda.CUDAGraph()
         host_counter = env.common_step_counter
-        with torch.cuda.graph(self.graph):
-            self._eager()
+        self._capturing = True
+        try:
+            with torch.cuda.graph(self.graph):
+                self._eager()
+        finally:
+            self._capturing = False
         env.common_step_counter = host_counter     # capture does not execute
-        self.launches_per_step = None
+        self._epoch = getattr(env, "graph_epoch", 0)
 
     def _eager(self):
         if self.extra is None:
@@ -354,16 +425,24 @@ class GraphedStep:
             self.env.join_tail()
         finally:
             self.env._defer_tail = False
+        if not getattr(self, "_capturing", False):
+            self.env._maybe_command_curriculum()
         return out
 
     def _push_due(self):
+        """steps with host-side work (a push, point_foot.py:492-493; the command curriculum, :265) run eagerly"""
         env = self.env
-        return env.cfg.domain_rand.push_robots and (env.common_step_counter + 1) % env.push_interval == 0
+        nxt = env.common_step_counter + 1
+        return ((env.cfg.domain_rand.push_robots and nxt % env.push_interval == 0)
+                or (bool(env.cfg.commands.curriculum) and nxt % env.max_episode_length == 0))
 
     def __call__(self):
         env = self.env
         if self._push_due():
             self._eager()
+            if getattr(env, "graph_epoch", 0) != self._epoch:      # kernel constants changed (command ranges): re-capture
+                torch.cuda.synchronize(env.device)
+                self._capture()
         else:
             self.graph.replay()
             env.common_step_counter += 1

@@ -30,6 +30,22 @@ def _stream(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+def _checked(t, device, cols, what, rows=None, dtype=torch.float32):
+    """The kernels are handed raw pointers: refuse anything that is not the dense tensor they index.  Returns ``t``
+    (made contiguous if it is a strided view of the right dtype / device)."""
+    if not torch.is_tensor(t):
+        raise TypeError(f"{what}: expected a torch tensor, got {type(t).__name__}")
+    if t.device != device:
+        raise RuntimeError(f"{what}: tensor is on {t.device}, the policy lives on {device}")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{what}: dtype {t.dtype}, expected {dtype}")
+    if cols is not None and (t.dim() < 1 or t.numel() != t.shape[0] * cols):
+        raise RuntimeError(f"{what}: shape {tuple(t.shape)} does not have {cols} columns")
+    if rows is not None and t.shape[0] != rows:
+        raise RuntimeError(f"{what}: {t.shape[0]} rows, expected {rows}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
 class ActorCritic:
     """modules/actor_critic.py.  Parameters live in ONE flat fp32 device buffer in ``parameters()`` order
     (std, actor.*, critic.*); ``state_dict()`` exposes the upstream key names as views of it."""
@@ -119,14 +135,17 @@ class ActorCritic:
 
     # -- inference ---------------------------------------------------------------------------------
     def act_inference(self, observations):
-        out = torch.empty(observations.shape[0], self.num_actions, device=self.device)
-        capi.check(self._lib.pf_rl_act_inference(self._ctx, _ptr(self.flat), _ptr(observations.contiguous()), _ptr(out),
+        """actor(observations) for ANY number of rows (upstream: a plain nn.Sequential call)"""
+        obs = _checked(observations, self.flat.device, self.num_actor_obs, "act_inference(observations)")
+        out = torch.empty(obs.shape[0], self.num_actions, device=self.device)
+        capi.check(self._lib.pf_rl_act_inference(self._ctx, _ptr(self.flat), _ptr(obs), C.c_int32(obs.shape[0]), _ptr(out),
                                                  _stream(self.device)), "pf_rl_act_inference")
         return out
 
     def evaluate(self, critic_observations, **kwargs):
-        out = torch.empty(critic_observations.shape[0], 1, device=self.device)
-        capi.check(self._lib.pf_rl_evaluate(self._ctx, _ptr(self.flat), _ptr(critic_observations.contiguous()), _ptr(out),
+        cobs = _checked(critic_observations, self.flat.device, self.num_critic_obs, "evaluate(critic_observations)")
+        out = torch.empty(cobs.shape[0], 1, device=self.device)
+        capi.check(self._lib.pf_rl_evaluate(self._ctx, _ptr(self.flat), _ptr(cobs), C.c_int32(cobs.shape[0]), _ptr(out),
                                             _stream(self.device)), "pf_rl_evaluate")
         return out
 
@@ -248,6 +267,9 @@ class PPO:
         """ppo.py act + the storage copies of add_transitions; returns the sampled actions [N, A]."""
         if self.storage.step >= self.storage.num_transitions_per_env:
             raise AssertionError("Rollout buffer overflow")
+        ac, N = self.actor_critic, self.storage.num_envs
+        obs = _checked(obs, ac.flat.device, ac.num_actor_obs, "PPO.act(obs)", N)
+        critic_obs = _checked(critic_obs, ac.flat.device, ac.num_critic_obs, "PPO.act(critic_obs)", N)
         self.policy_step += 1
         capi.check(self._lib.pf_rl_act(self._ctx, _ptr(self.actor_critic.flat), _ptr(obs), _ptr(critic_obs),
                                        C.c_int32(self.storage.step), C.byref(self.storage.c), C.c_int64(self.policy_step),
@@ -256,13 +278,22 @@ class PPO:
 
     def process_env_step(self, rewards, dones, infos):
         to = infos.get("time_outs") if isinstance(infos, dict) else None
+        dev, N = self.actor_critic.flat.device, self.storage.num_envs
+        rewards = _checked(rewards, dev, 1, "process_env_step(rewards)", N)
+        if dones.dtype not in (torch.bool, torch.uint8):
+            raise RuntimeError(f"process_env_step(dones): dtype {dones.dtype}, expected torch.bool / uint8")
+        dones = _checked(dones, dev, 1, "process_env_step(dones)", N, dones.dtype)
+        if to is not None:
+            to = _checked(to, dev, 1, "process_env_step(time_outs)", N, torch.bool if to.dtype == torch.bool else torch.uint8)
         capi.check(self._lib.pf_rl_process_env_step(self._ctx, C.byref(self.storage.c), C.c_int32(self.storage.step),
                                                     _ptr(rewards), _ptr(dones), _ptr(to), self._st()), "pf_rl_process_env_step")
         self.storage.step += 1
 
     def compute_returns(self, last_critic_obs):
         lib, st = self._lib, self._st()
-        capi.check(lib.pf_rl_evaluate(self._ctx, _ptr(self.actor_critic.flat), _ptr(last_critic_obs), _ptr(self._last_values), st),
+        ac, N = self.actor_critic, self.storage.num_envs
+        last_critic_obs = _checked(last_critic_obs, ac.flat.device, ac.num_critic_obs, "compute_returns(last_critic_obs)", N)
+        capi.check(lib.pf_rl_evaluate(self._ctx, _ptr(ac.flat), _ptr(last_critic_obs), C.c_int32(N), _ptr(self._last_values), st),
                    "pf_rl_evaluate")
         capi.check(lib.pf_rl_gae(self._ctx, C.byref(self.storage.c), _ptr(self._last_values), _ptr(self._gae_stats), st), "pf_rl_gae")
         shard.allreduce_sum_(self._gae_stats)              # advantage mean / std span all shards

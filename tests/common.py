@@ -34,6 +34,37 @@ def grid187(cfg):
     cfg.env.num_privileged_obs = 27 + 187
 
 
+def all_reward_terms(cfg):
+    """Every optional branch of compute_reward (PF:301-318): the five terms both pointfoot cfgs leave at -0.0
+    (PF:1153 dof_vel, :1170 termination, :1174 dof_pos_limits, :1180 dof_vel_limits, :1226 stumble) get non-zero scales
+    and ``only_positive_rewards`` is switched on (the clip of PF:312-313 and the post-clip termination add of
+    PF:315-318).  The cfg key is ``stumble``: ``feet_stumble`` has no ``_reward_feet_stumble``."""
+    sc = cfg.rewards.scales
+    sc.dof_vel = -2.e-4
+    sc.termination = -4.0
+    sc.dof_pos_limits = -3.0
+    sc.dof_vel_limits = -0.7
+    sc.stumble = -1.5
+    sc.feet_stumble = 0.0
+    # tracking terms dominate less than half of the envs, so the clip hits some envs and not others
+    sc.tracking_lin_vel = 12.0
+    cfg.rewards.only_positive_rewards = True
+
+
+def control_v(cfg):
+    cfg.control.control_type = "V"          # PF:540-542
+
+
+def control_t(cfg):
+    cfg.control.control_type = "T"          # PF:543-544
+
+
+def push_every_step_2(cfg):
+    """push at common_step_counter 2 (and 4): push_interval = ceil(push_interval_s / dt) = 2 (PF:1009, 492-493)"""
+    cfg.domain_rand.push_robots = True
+    cfg.domain_rand.push_interval_s = 0.04
+
+
 def clone_state(state):
     return {k: (v.clone() if torch.is_tensor(v) else copy.deepcopy(v)) for k, v in state.items()}
 
@@ -103,4 +134,13 @@ def host_emu():
 def oracle_env(task, state, mutate=None, **kw):
     from oracle.pointfoot_ref import RefEnv
     cfg, P, noise, pts, names = make_params(task, state, mutate, **kw)
-    return RefEnv(P, noise, pts, clone_state(state)), (cfg, P, noise, pts, names)
+    orc = RefEnv(P, noise, pts, clone_state(state))
+    orc.push_interval, orc.sim_dt_py, orc.max_push_vel_xy_py = push_schedule(cfg)
+    return orc, (cfg, P, noise, pts, names)
+
+
+def push_schedule(cfg):
+    """(push_interval in policy steps or 0, sim dt, max_push_vel_xy) as the reference holds them (PF:492-493, 592-596, 1009)"""
+    dt = cfg.control.decimation * cfg.sim.dt
+    interval = int(np.ceil(cfg.domain_rand.push_interval_s / dt)) if cfg.domain_rand.push_robots else 0
+    return interval, cfg.sim.dt, cfg.domain_rand.max_push_vel_xy

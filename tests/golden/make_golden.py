@@ -35,9 +35,12 @@ def hf_checksum(hf):
     return hashlib.sha256(hf.numpy().tobytes()).hexdigest()
 
 
-def generate(task, seed=1, mutate=None, tag=""):
-    state = synth.make_state(N, task, seed=seed, adversarial=True)
-    out = {}
+def generate(fname, task, mutate=None, start_step=0, seed=1):
+    # (19 rows of episode sums unless the cfg mutation enables more terms; kept so the older files' inputs stay as they were)
+    state = synth.make_state(N, task, seed=seed, adversarial=True,
+                             num_reward_terms=24 if mutate is common.all_reward_terms else 19)
+    state["common_step_counter"] = start_step
+    out = {"start_step": np.int64(start_step)}
     for k, v in state.items():
         if k == "height_samples":
             out["hf_sha256"] = np.frombuffer(hf_checksum(v).encode(), dtype=np.uint8)
@@ -64,7 +67,8 @@ def generate(task, seed=1, mutate=None, tag=""):
         ep = extras.get("episode", {})
         out[p + "extras_episode"] = np.array([float(ep["rew_" + n]) for n in names] if ep else [], np.float32)
         out[p + "time_outs"] = extras["time_outs"].numpy().copy()
-    path = os.path.join(HERE, f"{task}{tag}_n{N}.npz")
+        out[p + "push_forces"] = env.rigid_body_external_forces.numpy().copy()      # PF:590-611 (zeros until a push step)
+    path = os.path.join(HERE, fname)
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes")
 
@@ -72,6 +76,9 @@ def generate(task, seed=1, mutate=None, tag=""):
 if __name__ == "__main__":
     if not ref_harness.reference_available():
         raise SystemExit("reference not available here; golden files can only be regenerated in the build container")
-    generate("pointfoot_flat")
-    generate("pointfoot_rough")
-    generate("pointfoot_rough", mutate=common.grid187, tag="_p187")
+    import parity
+    only = sys.argv[1:]
+    for fname, (task, mutate, start_step) in parity.GOLDEN.items():
+        if only and fname not in only:
+            continue
+        generate(fname, task, mutate, start_step)

@@ -18,6 +18,19 @@ extern "C" int pf_emu_pd_torques(const pf_params* Pp, const pf_env_buffers* Bp, 
     return 0;
 }
 
+// _push_robots, PF:590-611 (pf_push_kernel's loop, serial)
+extern "C" int pf_emu_push_forces(const pf_params* Pp, const pf_env_buffers* Bp, float* forces, float max_push_force,
+                                  long long common_step_counter) {
+    const pf_params& P = *Pp; const pf_env_buffers& B = *Bp;
+    const int row = 3 * P.num_bodies;
+    for (int e = 0; e < P.num_envs; ++e) {
+        for (int c = 0; c < row; ++c) forces[(size_t)e * row + c] = 0.0f;
+        pf_push_force(P, e, B.root_states + (size_t)e * 13 + 3, max_push_force, (uint32_t)common_step_counter,
+                      forces + (size_t)e * row);
+    }
+    return 0;
+}
+
 extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffers* Bp, const float* noise_vec,
                                         const float* height_points_xy, long long common_step_counter) {
     const pf_params& P = *Pp; const pf_env_buffers& B = *Bp;

@@ -15,6 +15,10 @@ from pointfoot_b200 import rl
 
 FP32 = dict(rtol=1e-4, atol=1e-5)
 BF16 = dict(rtol=2e-2, atol=2e-2)
+# bf16 tensor-core PPO.update (PF_RL_BF16_TC): operands rounded to bf16 (2^-9 relative), fp32 accumulation.  Per parameter
+# tensor the first-minibatch gradient must be within 2e-2 relative L2 of torch autograd with cosine >= 0.999; the parameters
+# after the 20 Adam steps within 5 % of the update's own L2 movement.
+GRAD_REL_L2_BF16, GRAD_COS_BF16, PARAM_ERR_BF16 = 2e-2, 0.999, 0.05
 ALG = dict(value_loss_coef=1.0, use_clipped_value_loss=True, clip_param=0.2, entropy_coef=0.01, num_learning_epochs=5,
            num_mini_batches=4, learning_rate=1.e-3, schedule="adaptive", gamma=0.99, lam=0.95, desired_kl=0.01,
            max_grad_norm=1.)
@@ -191,8 +195,27 @@ def run_update(num_envs=512, num_obs=27, num_critic_obs=148, hidden=(512, 256, 1
         oc.optimizer.step = grab
         oc.update()
         scale = first["g"].abs().max().item()
-        torch.testing.assert_close(g_cuda, first["g"], rtol=tol["rtol"] * 10, atol=max(tol["atol"], tol["rtol"] * scale),
-                                   msg=lambda m: f"first-minibatch gradient: {m}")
+        if precision == "fp32":
+            torch.testing.assert_close(g_cuda, first["g"], rtol=tol["rtol"] * 10, atol=max(tol["atol"], tol["rtol"] * scale),
+                                       msg=lambda m: f"first-minibatch gradient: {m}")
+        # per parameter tensor (std, every weight, every bias): relative L2 error and cosine against autograd -- a wrong
+        # dgrad / wgrad of ONE small layer cannot hide behind the large ones
+        rel_bar, cos_bar = (1e-3, 0.999999) if precision == "fp32" else (GRAD_REL_L2_BF16, GRAD_COS_BF16)
+        lay, _ = ppo.actor_critic.layout()
+        worst = (0.0, 1.0, "")
+        for key, off, shape in lay:
+            n = int(torch.Size(shape).numel())
+            a, b = g_cuda[off:off + n].double(), first["g"][off:off + n].double()
+            nb = b.norm().item()
+            if nb < 1e-12:
+                assert a.norm().item() < 1e-9, key
+                continue
+            rel = (a - b).norm().item() / nb
+            cos = (a @ b).item() / (a.norm().item() * nb + 1e-300)
+            if rel > worst[0]:
+                worst = (rel, cos, key)
+            assert rel <= rel_bar and cos >= cos_bar, f"gradient of {key}: rel-L2 {rel:.3e} (bar {rel_bar}), cosine {cos:.6f} (bar {cos_bar})"
+        print(f"[{precision}] first-minibatch gradient, worst tensor {worst[2]}: rel-L2 {worst[0]:.3e} cosine {worst[1]:.6f}")
         kl_cuda = (stats[3] / stats[4]).item()
         assert abs(kl_cuda - first["kl"]) <= 1e-4 + 1e-3 * abs(first["kl"]), (kl_cuda, first["kl"])
         if first_minibatch_only:
@@ -206,7 +229,8 @@ def run_update(num_envs=512, num_obs=27, num_critic_obs=148, hidden=(512, 256, 1
         # update as a whole (relative L2), not per element
         moved = (p_ref - p0).norm().item()
         err = (p_cuda - p_ref).norm().item()
-        assert err <= (0.02 if precision == "fp32" else 0.25) * moved, f"parameters after update: |err| {err:.3e} vs |movement| {moved:.3e}"
+        print(f"[{precision}] parameters after the update: |err| {err:.3e} = {err / moved:.4f} of the movement {moved:.3e}")
+        assert err <= (0.02 if precision == "fp32" else PARAM_ERR_BF16) * moved, f"parameters after update: |err| {err:.3e} vs |movement| {moved:.3e}"
         assert abs(ppo.learning_rate - oppo.learning_rate) <= 1e-12 + 1e-9 * oppo.learning_rate, (ppo.learning_rate, oppo.learning_rate)
         lr_, la_ = (1e-3, 1e-5) if precision == "fp32" else (2e-2, 2e-4)      # mean losses: bf16 operands move them by ~1 %
         assert abs(vl - ovl) <= lr_ * abs(ovl) + la_ and abs(sl - osl) <= lr_ * abs(osl) + la_, (vl, ovl, sl, osl)
@@ -219,3 +243,7 @@ def smoke_check():
     run_act_and_gae(num_envs=64, T=4)
     run_gae_exact(num_envs=64, T=8)
     print("rl parity: act / storage / GAE ok")
+    # the tensor-core kernels (tcgen05): the fused act kernel and one minibatch of PPO.update on the bf16 GEMMs
+    run_act_and_gae(num_envs=256, num_critic_obs=148, hidden=(512, 256, 128), T=2, precision="bf16")
+    run_update(num_envs=128, num_critic_obs=148, hidden=(512, 256, 128), T=8, precision="bf16", first_minibatch_only=True)
+    print("rl parity: tcgen05 act + tcgen05 minibatch gradient ok")

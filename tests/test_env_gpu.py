@@ -203,3 +203,116 @@ def test_host_buffer_step_equals_device_step(pinned, split):
     for k in ("root_states", "dof_state", "episode_sums", "reset_ids"):
         assert torch.equal(host.t[k], dev.t[k]), k
     dev.close(); host.close()
+
+
+# ------------------------------------------------------------------------------------------------ optional branches
+@pytest.mark.parametrize("task", ["pointfoot_flat", "pointfoot_rough"])
+@pytest.mark.parametrize("n", [33, 4096])
+def test_cuda_all_24_reward_terms_positive_clip_and_termination_add(task, n):
+    """PF:1153 dof_vel, :1170 termination, :1174 dof_pos_limits, :1180 dof_vel_limits, :1226 stumble enabled together
+    with only_positive_rewards (PF:312-313) and the post-clip termination add (PF:315-318): the table-driven statement
+    of the step (PF_MASK_TABLE) against the oracle; pinned to the unmodified reference by the *_allterms golden files."""
+    import common
+    out = parity.run(task, n, steps=3, mutate=common.all_reward_terms, num_reward_terms=24)
+    assert n < 4096 or out[-1]["num_resets"] > 0
+
+
+def test_all_terms_generic_statement_matches_too(monkeypatch):
+    import common
+    monkeypatch.setenv("PF_GENERIC_REWARDS", "1")
+    parity.run("pointfoot_rough", 1000, steps=2, mutate=common.all_reward_terms, num_reward_terms=24)
+
+
+@pytest.mark.parametrize("task", ["pointfoot_flat", "pointfoot_rough"])
+def test_cuda_push_step_matches_oracle(task):
+    """_push_robots (PF:590-611) on the step where common_step_counter % 350 == 0: pf_push_kernel against the oracle
+    (bit-exact: quat_rotate is the same op sequence); the *_push349 golden files pin the same to the reference."""
+    out = parity.run(task, 5000, steps=3, start_step=348)
+    assert out[1]["push_forces"] == 0.0
+
+
+@pytest.mark.parametrize("mut", ["control_v", "control_t"])
+@pytest.mark.parametrize("n", [31, 4096])
+def test_cuda_control_types_v_and_t(mut, n):
+    """PF:540-545: velocity-target and direct-torque control laws (both the paired and the scalar torque kernel run:
+    4096 * 6 is even, the 64-bit path; the scalar kernel is taken for unaligned tensors, see below)"""
+    import common
+    parity.run("pointfoot_flat", n, steps=3, mutate=getattr(common, mut))
+
+
+def test_scalar_torque_kernel_control_v_unaligned():
+    """pf_pd_torques_kernel (one thread per DOF) is what runs when a tensor is only 4-byte aligned: same bits."""
+    import common
+    from pointfoot_b200 import synth
+    state = synth.make_state(515, "pointfoot_flat", seed=21)
+    a = parity.EnvUnderTest("pointfoot_flat", state, "cuda", common.control_v, seed=21)
+    b = parity.EnvUnderTest("pointfoot_flat", state, "cuda", common.control_v, seed=21)
+    odd = torch.zeros(b.t["torques"].numel() + 1, device="cuda")[1:].view_as(b.t["torques"])
+    b.t["torques"] = odd
+    b.b.torques = odd.data_ptr()
+    for k in range(2):
+        a.step(state["actions"] * (1.0 + k)); b.step(state["actions"] * (1.0 + k))
+    assert torch.equal(a.t["torques"], b.t["torques"]) and torch.equal(a.t["rew_buf"], b.t["rew_buf"])
+    a.close(); b.close()
+
+
+def test_reciprocal_index_division_is_what_cuda_eager_does():
+    """PF:1102 ``(points / horizontal_scale).long()``: ATen's CPU kernel divides, its CUDA kernel multiplies by the
+    fp32 reciprocal of the python scalar.  PF_DIV_RECIPROCAL must reproduce the reference run with its tensors on THIS
+    device (the oracle-of-record for the index path on a GPU box), PF_DIV_TRUE the CPU run; the two
+    differ for a few samples per million, which is counted here, not hidden."""
+    import common
+    from oracle import pointfoot_ref
+    from pointfoot_b200 import capi, synth
+    N = 20000
+    state = synth.make_state(N, "pointfoot_rough", seed=17)
+    want = {}
+    for dev in ("cpu", "cuda"):
+        orc, _ = common.oracle_env("pointfoot_rough", state, seed=17)
+        want[dev] = pointfoot_ref.heights_native_eager(orc, dev).cpu()
+    got = {}
+    for mode in (capi.DIV_TRUE, capi.DIV_RECIPROCAL):
+        e = parity.EnvUnderTest("pointfoot_rough", state, "cuda", seed=17, index_div_mode=mode)
+        e.step(state["actions"])
+        got[mode] = e.t["measured_heights"].cpu().clone()
+        e.close()
+    assert torch.equal(got[capi.DIV_TRUE], want["cpu"]), "PF_DIV_TRUE differs from the CPU-eager reference"
+    assert torch.equal(got[capi.DIV_RECIPROCAL], want["cuda"]), "PF_DIV_RECIPROCAL differs from the CUDA-eager reference"
+    n_diff = int((want["cpu"] != want["cuda"]).sum())
+    print(f"CPU-eager vs CUDA-eager height samples that differ: {n_diff} of {want['cpu'].numel()}")
+    # the oracle's own statement of the reciprocal mode agrees with the device run as well
+    orc, _ = common.oracle_env("pointfoot_rough", state, seed=17, index_div_mode=capi.DIV_RECIPROCAL)
+    assert torch.equal(orc.get_heights(), want["cuda"])
+
+
+def test_pointfoot_class_pushes_without_a_host_sync_and_inside_a_graph():
+    """env.py PointFoot._push_robots on step 350 through the public class (eager and GraphedStep) == the oracle"""
+    import common
+    from pointfoot_b200 import synth
+    from pointfoot_b200.env import PointFoot, GraphedStep
+    N, task = 300, "pointfoot_flat"
+    state = synth.make_state(N, task, seed=4)
+    cfg = common.make_cfg(task, N)
+    orc, _ = common.oracle_env(task, state, seed=1)
+    orc.common_step_counter = 348
+    env = PointFoot(cfg, None, None, "cuda:0", True, state=common.clone_state(state), seed=1)
+    env.common_step_counter = 348
+    env._step_counter.fill_(348)
+    a = torch.zeros(N, 6, device="cuda")
+    step = GraphedStep(env, a)
+    for k in ("episode_length_buf", "last_actions", "last_dof_vel", "feet_air_time", "last_feet_air_time", "contact_filt",
+              "first_contact", "last_contacts"):
+        getattr(env, k).copy_(state[k].view(getattr(env, k).shape))
+    for k in ("root_states", "dof_state"):
+        getattr(env, k).copy_(state[k].view(getattr(env, k).shape))
+    env.common_step_counter = 348
+    env._step_counter.fill_(348)
+    for i in range(3):
+        step()
+        orc.step(torch.zeros(N, 6))
+        if i == 0:
+            assert float(env.rigid_body_external_forces.abs().max()) == 0.0
+    assert env.common_step_counter == 351 == orc.common_step_counter
+    assert torch.equal(env.rigid_body_external_forces.cpu(), orc.push_forces)
+    assert float(orc.push_forces.abs().max()) > 0
+    env.close()
