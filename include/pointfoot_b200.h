@@ -188,6 +188,9 @@ int pf_post_physics_step_join(pf_ctx* ctx, void* stream);
  * tag << 48 | globaltimer ns) that thread 0 of CTA 0 of the env kernels / the fused act kernel append to; NULL removes it.
  * The marks are compiled in only with -DPF_TIMELINE (PF_BUILD_TIMELINE=1 at build time); otherwise installing a log fails. */
 int pf_debug_timeline(unsigned long long* device_log);
+/* Diagnostic: number of kernel launches this library has issued in this process so far (a launch recorded during a stream
+ * capture counts once; replays are the caller's to multiply).  bench.py's `gpu_launches` is measured with it. */
+unsigned long long pf_debug_launch_count(void);
 int pf_rl_debug_timeline(unsigned long long* device_log);
 
 /* PF:590-611: random push forces into forces[N,B,3] (body 0 rows; everything else zeroed).

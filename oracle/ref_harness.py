@@ -22,7 +22,22 @@ import torch
 from . import rng
 from . import isaacgym_torch_utils as _tu
 
-REFERENCE_ROOT = os.environ.get("POINTFOOT_REFERENCE_ROOT", "/root/reference")
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _default_root():
+    """$POINTFOOT_REFERENCE_ROOT, else the reference tree of the build container, else the offline install that travels
+    with the repo snapshot (baseline/_ref, made by baseline/install_reference.py)."""
+    env = os.environ.get("POINTFOOT_REFERENCE_ROOT")
+    if env:
+        return env
+    for root in ("/root/reference", os.path.join(_REPO, "baseline", "_ref")):
+        if os.path.isfile(os.path.join(root, "legged_gym/envs/pointfoot/point_foot.py")):
+            return root
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _default_root()
 
 
 def reference_available():
@@ -140,6 +155,22 @@ def _patched(obj, name, value):
         setattr(obj, name, old)
 
 
+def _make_plain_class():
+    """The reference PointFoot with torch's own generators (``torch.rand_like`` ...): what bench.py TIMES (on the host
+    cores and, as the torch-eager bar, on the CUDA device).  The one change: the ``torch.save`` of the noise tensor that
+    point_foot.py:334 does on every step (a leftover debug dump) is skipped -- timing disk writes
+    would only flatter the comparison."""
+    install_stubs()
+    from legged_gym.envs.pointfoot.point_foot import PointFoot
+
+    class TimedPointFoot(PointFoot):
+        def _add_noise_to_obs(self):
+            with _patched(torch, "save", lambda *a, **k: None):
+                super()._add_noise_to_obs()
+
+    return TimedPointFoot
+
+
 def _make_class():
     """Subclass of the reference PointFoot whose only additions route RNG draws to the contract."""
     install_stubs()
@@ -193,12 +224,17 @@ def make_cfg(task, num_envs, mutate=None):
     return cfg
 
 
-def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0):
+def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0, device="cpu", contract_rng=True):
     """Build the reference ``PointFoot`` over the synthetic tensors in ``state`` (a dict of CPU torch tensors,
     see pointfoot_b200.synth.make_state).  The four PhysX-owned tensors are used in place (the reference
-    writes reset rows into them, point_foot.py:557-588)."""
-    cls = _make_class()
+    writes reset rows into them, point_foot.py:557-588).  ``device``: where the reference's tensors live ('cpu' is what
+    the fork hard-codes, point_foot.py:41,50; 'cuda' is upstream legged_gym's default pipeline).  ``contract_rng=False``
+    leaves torch's own generators in place (timing runs)."""
+    cls = _make_class() if contract_rng else _make_plain_class()
     from types import SimpleNamespace
+    if str(device) != "cpu":
+        assert not contract_rng, "the counter-based RNG contract is a CPU (numpy) statement"
+        state = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in state.items()}
     N = int(state["root_states"].shape[0])
     cfg = make_cfg(task, N, mutate_cfg)
     env = object.__new__(cls)
@@ -215,18 +251,18 @@ def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0):
     env.gym = FakeGym(state)
     env.sim = None
     env.physics_engine = None
-    env.sim_device = env.device = 'cpu'
+    env.sim_device = env.device = str(device)
     env.headless = True
     env.num_envs = N
     env.num_obs = cfg.env.num_propriceptive_obs
     env.num_privileged_obs = cfg.env.num_privileged_obs
     env.num_actions = cfg.env.num_actions
-    env.proprioceptive_obs_buf = torch.zeros(N, env.num_obs)
-    env.rew_buf = torch.zeros(N)
-    env.reset_buf = torch.ones(N, dtype=torch.long)
-    env.episode_length_buf = torch.zeros(N, dtype=torch.long)
-    env.time_out_buf = torch.zeros(N, dtype=torch.bool)
-    env.privileged_obs_buf = (torch.zeros(N, env.num_privileged_obs)
+    env.proprioceptive_obs_buf = torch.zeros(N, env.num_obs, device=device)
+    env.rew_buf = torch.zeros(N, device=device)
+    env.reset_buf = torch.ones(N, dtype=torch.long, device=device)
+    env.episode_length_buf = torch.zeros(N, dtype=torch.long, device=device)
+    env.time_out_buf = torch.zeros(N, dtype=torch.bool, device=device)
+    env.privileged_obs_buf = (torch.zeros(N, env.num_privileged_obs, device=device)
                               if env.num_privileged_obs is not None else None)
     env.extras = {}
     env.enable_viewer_sync = True
@@ -246,16 +282,16 @@ def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0):
         out = []
         for n in names:
             out.extend(i for i, s in enumerate(BODY_NAMES) if n in s)
-        return torch.tensor(out, dtype=torch.long)
-    env.feet_indices = torch.tensor([i for i, s in enumerate(BODY_NAMES) if cfg.asset.foot_name in s])
+        return torch.tensor(out, dtype=torch.long, device=device)
+    env.feet_indices = torch.tensor([i for i, s in enumerate(BODY_NAMES) if cfg.asset.foot_name in s], device=device)
     env.penalised_contact_indices = idx(cfg.asset.penalize_contacts_on)
     env.termination_contact_indices = idx(cfg.asset.terminate_after_contacts_on)
     isl = cfg.init_state
-    env.base_init_state = _tu.to_torch(isl.pos + isl.rot + isl.lin_vel + isl.ang_vel)
+    env.base_init_state = _tu.to_torch(isl.pos + isl.rot + isl.lin_vel + isl.ang_vel, device=device)
     env.base_mass = state["base_mass"].clone()
     if cfg.terrain.mesh_type in ("heightfield", "trimesh"):
         env.terrain = SimpleNamespace(cfg=cfg.terrain, env_length=cfg.terrain.terrain_length,
-                                      env_origins=state["terrain_origins"].numpy())
+                                      env_origins=state["terrain_origins"].cpu().numpy())
         env.height_samples = state["height_samples"]
     env._get_env_origins()                                   # reference code, point_foot.py:970-997
     if env.custom_origins:

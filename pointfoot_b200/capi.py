@@ -94,6 +94,7 @@ def load():
     lib = C.CDLL(path)
     lib.pf_last_error.restype = C.c_char_p
     lib.pf_abi_version.restype = C.c_int
+    lib.pf_debug_launch_count.restype = C.c_ulonglong
     if lib.pf_abi_version() != PF_ABI_VERSION:
         raise RuntimeError("pointfoot_b200: ABI version mismatch between capi.py and the built library")
     if lib.pf_sizeof_params() != C.sizeof(PfParams) or lib.pf_sizeof_env_buffers() != C.sizeof(PfEnvBuffers):

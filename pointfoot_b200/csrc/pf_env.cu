@@ -705,6 +705,8 @@ void pf_set_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); 
 extern "C" int pf_debug_timeline(unsigned long long* device_log) {
     return pf_timeline_install(device_log) == cudaSuccess ? 0 : pf_fail(7, "%s", "pf_debug_timeline: not compiled in (build with PF_BUILD_TIMELINE=1) or cudaMemcpyToSymbol failed");
 }
+unsigned long long g_pf_launch_count = 0;
+extern "C" unsigned long long pf_debug_launch_count(void) { return g_pf_launch_count; }
 extern "C" int pf_abi_version(void) { return PF_ABI_VERSION; }
 extern "C" int pf_sizeof_params(void) { return (int)sizeof(pf_params); }
 extern "C" int pf_sizeof_env_buffers(void) { return (int)sizeof(pf_env_buffers); }
@@ -924,7 +926,7 @@ extern "C" int pf_reset_all(pf_ctx* c, const pf_env_buffers* bufs, int64_t commo
     if (int rc = pf_check_bufs(c, bufs)) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     PF_CUDA(cudaMemsetAsync(bufs->reset_buf, 1, (size_t)c->P.num_envs, st));
-    pf_reset_all_kernel<<<c->num_blocks, c->threads, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
+    PF_LAUNCHED(), pf_reset_all_kernel<<<c->num_blocks, c->threads, 0, st>>>(c->P, *bufs, c->S, c->envs_per_warp,
                                                                           (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return pf_launch_finalize(c, bufs, st, 0);
@@ -937,7 +939,7 @@ extern "C" int pf_push_forces(pf_ctx* c, const pf_env_buffers* bufs, float* forc
     const int n = c->P.num_envs * c->P.num_bodies * 3;
     int blocks = (n + 255) / 256;
     if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
-    pf_push_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(c->P, *bufs, forces, max_push_force,
+    PF_LAUNCHED(), pf_push_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(c->P, *bufs, forces, max_push_force,
                                                              (uint32_t)common_step_counter);
     PF_CUDA(cudaGetLastError());
     return 0;
@@ -1038,12 +1040,12 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
         }
         add(in, actions_host, c->d_actions_in, sizeof(float) * N * P.num_dof, true);
         if (mapped) {
-            pf_host_io_kernel<<<io_grid(4 * N * P.num_dof * 2, in.nseg), 256, 0, st>>>(in);
+            PF_LAUNCHED(), pf_host_io_kernel<<<io_grid(4 * N * P.num_dof * 2, in.nseg), 256, 0, st>>>(in);
             PF_CUDA(cudaGetLastError());
             if (in2.nseg || in2.rbs_src) {           // forked behind the first gather: the bus is not shared with it
                 PF_CUDA(cudaEventRecord(c->ev_fork, st));
                 PF_CUDA(cudaStreamWaitEvent(io, c->ev_fork, 0));
-                pf_host_io_kernel<<<io_grid(4 * N * P.num_bodies * 3, in2.nseg + (in2.rbs_src ? 1 : 0)), 256, 0, io>>>(in2);
+                PF_LAUNCHED(), pf_host_io_kernel<<<io_grid(4 * N * P.num_bodies * 3, in2.nseg + (in2.rbs_src ? 1 : 0)), 256, 0, io>>>(in2);
                 PF_CUDA(cudaGetLastError());
                 PF_CUDA(cudaEventRecord(c->ev_in, io));
                 forked = true;
@@ -1086,7 +1088,7 @@ static int pf_step_host_impl(pf_ctx* c, const pf_env_buffers* bufs, const pf_hos
                 PF_CUDA(cudaEventRecord(c->ev_post, st));
                 PF_CUDA(cudaStreamWaitEvent(io, c->ev_post, 0));
             }
-            pf_host_io_kernel<<<io_grid(sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs), out.nseg), 256, 0, io>>>(out);
+            PF_LAUNCHED(), pf_host_io_kernel<<<io_grid(sizeof(float) * N * (P.num_priv_obs > P.num_obs ? P.num_priv_obs : P.num_obs), out.nseg), 256, 0, io>>>(out);
             PF_CUDA(cudaGetLastError());
             PF_CUDA(cudaEventRecord(c->ev_out, io));
             c->out_pending = 1;

@@ -18,6 +18,7 @@
 #include <string.h>
 #include "pf_rl_internal.h"
 #include "pf_tc_ptx.cuh"
+#include "pf_launch.h"
 
 void pf_set_error(const char* msg);
 
@@ -257,10 +258,10 @@ int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& d, int splits, cudaStream_t st) {
     const int mtiles = (d.M + GT_ROWS - 1) / GT_ROWS, ntiles = (d.N + NT - 1) / NT;
     const long long a_slots = (long long)mtiles * kblocks * GT_ROWS, b_slots = (long long)ntiles * kblocks * NT;
     if ((size_t)a_slots * 16 > t->ap_bytes || (size_t)b_slots * 16 > t->bp_bytes) return gt_fail(1, "pf_tc_gemm: operand larger than the packing workspace");
-    pf_tc_pack_operand_kernel<<<(unsigned)((a_slots + 255) / 256), 256, 0, st>>>(d.A, d.sam, d.sak, d.a_rows, nullptr, d.M, d.K, GT_ROWS,
+    PF_LAUNCHED(), pf_tc_pack_operand_kernel<<<(unsigned)((a_slots + 255) / 256), 256, 0, st>>>(d.A, d.sam, d.sak, d.a_rows, nullptr, d.M, d.K, GT_ROWS,
                                                                                  kblocks, a_slots, reinterpret_cast<uint4*>(t->ap));
     // B(k, n) = B[krow(k) * sbk + n * sbn]: the packed operand is B^T, rows = n, columns = k
-    pf_tc_pack_operand_kernel<<<(unsigned)((b_slots + 255) / 256), 256, 0, st>>>(d.B, d.sbn, d.sbk, nullptr, d.b_rows, d.N, d.K, NT,
+    PF_LAUNCHED(), pf_tc_pack_operand_kernel<<<(unsigned)((b_slots + 255) / 256), 256, 0, st>>>(d.B, d.sbn, d.sbk, nullptr, d.b_rows, d.N, d.K, NT,
                                                                                  kblocks, b_slots, reinterpret_cast<uint4*>(t->bp));
     TcGemmArgs g;
     memset(&g, 0, sizeof(g));
@@ -272,6 +273,6 @@ int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& d, int splits, cudaStream_t st) {
     g.stages = per_split < 2 ? 2 : per_split > GT_STAGES ? GT_STAGES : per_split;
     if (NT == 256 && g.stages == 3) g.stages = 2;         // 2 x 48 KB stages: two CTAs per SM; 3 would only fit one
     const int smem = g.stages * (GT_ROWS * GT_KSTEP * 2 + NT * GT_KSTEP * 2) + 256;
-    pf_tc_gemm_kernel<<<dim3(ntiles, mtiles, splits), GT_THREADS, smem, st>>>(g);
+    PF_LAUNCHED(), pf_tc_gemm_kernel<<<dim3(ntiles, mtiles, splits), GT_THREADS, smem, st>>>(g);
     return cudaGetLastError() == cudaSuccess ? 0 : gt_fail(2, "pf_tc_gemm: launch failed");
 }

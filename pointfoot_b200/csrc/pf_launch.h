@@ -44,6 +44,12 @@ __device__ __forceinline__ void pf_grid_dep_wait() { asm volatile("griddepcontro
 __device__ __forceinline__ void pf_grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #endif
 
+// Launch counter behind bench.py's `gpu_launches`: every kernel launch of the library (pf_launch_pdl and the plain <<<>>> sites,
+// through PF_LAUNCHED()) bumps it on the host; pf_debug_launch_count() reads it.  Launches recorded during a stream
+// capture count once, at capture; a graph replay is counted by the caller as that many launches per replay.
+extern unsigned long long g_pf_launch_count;
+#define PF_LAUNCHED() ((void)++g_pf_launch_count)
+
 static inline bool pf_pdl_enabled() {
     static const bool on = [] { const char* e = getenv("PF_NO_PDL"); return !(e && atoi(e) != 0); }();
     return on;
@@ -58,5 +64,6 @@ static inline cudaError_t pf_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pf_pdl_enabled() ? 1 : 0;
+    PF_LAUNCHED();
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }

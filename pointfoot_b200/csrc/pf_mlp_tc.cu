@@ -834,7 +834,7 @@ int pf_tc_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st) {
         a.blob[k] = static_cast<unsigned char*>(c->net[k].tc_weights);
         for (int l = 0; l < PF_MAX_MLP_LAYERS; ++l) { a.w_off[k][l] = c->net[k].w_off[l]; a.b_off[k][l] = c->net[k].b_off[l]; }
     }
-    pf_tc_pack_kernel<<<dim3(16, (unsigned)(t->prog[0].ngroups + t->prog[1].ngroups)), 256, 0, st>>>(a, params);
+    PF_LAUNCHED(), pf_tc_pack_kernel<<<dim3(16, (unsigned)(t->prog[0].ngroups + t->prog[1].ngroups)), 256, 0, st>>>(a, params);
     return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_tc_pack_weights: launch failed");
 }
 

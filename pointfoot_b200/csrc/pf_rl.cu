@@ -9,6 +9,7 @@
 #include <math.h>
 #include "pf_rl_internal.h"
 #include "pf_rng.cuh"
+#include "pf_launch.h"
 
 static thread_local char g_rl_err[512] = "";
 extern "C" const char* pf_last_error(void);
@@ -134,7 +135,7 @@ __global__ void pf_colsum_kernel(const float* __restrict__ dY, long long ld, int
 static int launch_gemm(pf_rl_ctx* c, const GemmArgs& g, int splits, cudaStream_t st) {
     if (pf_tc_gemm_supported(c, g.M, g.N, g.K)) return pf_tc_gemm(c, g, splits, st);
     dim3 grid((g.N + GT - 1) / GT, (g.M + GT - 1) / GT, splits);
-    pf_sgemm_kernel<<<grid, 256, 0, st>>>(g);
+    PF_LAUNCHED(), pf_sgemm_kernel<<<grid, 256, 0, st>>>(g);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
@@ -355,7 +356,7 @@ extern "C" int pf_rl_act(pf_rl_ctx* c, const float* params, const float* obs, co
     if (int rc = mlp_forward(c, 1, params, critic_obs, P.num_envs, c->val, copy_priv, st, &val)) return rc;
     pf_rl_storage S = {};
     if (storage) S = *storage;
-    pf_act_sample_kernel<<<(P.num_envs + 127) / 128, 128, 0, st>>>(P, mean, params + c->std_off, val, S, storage != nullptr,
+    PF_LAUNCHED(), pf_act_sample_kernel<<<(P.num_envs + 127) / 128, 128, 0, st>>>(P, mean, params + c->std_off, val, S, storage != nullptr,
                                                                    t, (uint32_t)policy_step, actions_out, values_out, logp_out);
     RL_CUDA(cudaGetLastError());
     return 0;
@@ -410,7 +411,7 @@ extern "C" int pf_rl_process_env_step(pf_rl_ctx* c, const pf_rl_storage* storage
     if (int rc = check_rl(c, storage, rew, "pf_rl_process_env_step")) return rc;
     if (!dones) return rl_fail(1, "pf_rl_process_env_step", "null dones");
     if (t < 0 || t >= c->P.num_steps) return rl_fail(5, "pf_rl_process_env_step", "Rollout buffer overflow");
-    pf_process_env_step_kernel<<<(c->P.num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c->P, *storage, t, rew, dones, time_outs);
+    PF_LAUNCHED(), pf_process_env_step_kernel<<<(c->P.num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c->P, *storage, t, rew, dones, time_outs);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
@@ -482,9 +483,9 @@ extern "C" int pf_rl_gae(pf_rl_ctx* c, const pf_rl_storage* storage, const float
     if (int rc = check_rl(c, storage, last_values, "pf_rl_gae")) return rc;
     if (!stats) return rl_fail(1, "pf_rl_gae", "null stats");
     cudaStream_t st = (cudaStream_t)stream;
-    pf_gae_kernel<<<c->gae_blocks, 256, 0, st>>>(c->P, *storage, last_values, c->gae_part);
+    PF_LAUNCHED(), pf_gae_kernel<<<c->gae_blocks, 256, 0, st>>>(c->P, *storage, last_values, c->gae_part);
     RL_CUDA(cudaGetLastError());
-    pf_gae_stats_kernel<<<1, 256, 0, st>>>(c->gae_part, c->gae_blocks, (double)c->P.num_envs * c->P.num_steps, stats);
+    PF_LAUNCHED(), pf_gae_stats_kernel<<<1, 256, 0, st>>>(c->gae_part, c->gae_blocks, (double)c->P.num_envs * c->P.num_steps, stats);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
@@ -492,7 +493,7 @@ extern "C" int pf_rl_gae(pf_rl_ctx* c, const pf_rl_storage* storage, const float
 extern "C" int pf_rl_normalize_advantages(pf_rl_ctx* c, const pf_rl_storage* storage, const double* stats, void* stream) {
     if (int rc = check_rl(c, storage, stats, "pf_rl_normalize_advantages")) return rc;
     const long long n = (long long)c->P.num_envs * c->P.num_steps;
-    pf_norm_adv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(storage->advantages, n, stats);
+    PF_LAUNCHED(), pf_norm_adv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(storage->advantages, n, stats);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
@@ -528,7 +529,7 @@ extern "C" int pf_rl_make_permutation(pf_rl_ctx* c, int64_t iteration, void* str
     if (bits < 2) bits = 2;
     bits += bits & 1;
     const uint32_t ek = pf_rng_env_key(pf_rng_key(c->P.seed, (uint32_t)iteration, 7u), 0u);
-    pf_permutation_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c->perm, n, bits / 2, pf_rng_u32(ek, 0), pf_rng_u32(ek, 1),
+    PF_LAUNCHED(), pf_permutation_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c->perm, n, bits / 2, pf_rng_u32(ek, 0), pf_rng_u32(ek, 1),
                                                                            pf_rng_u32(ek, 2), pf_rng_u32(ek, 3));
     RL_CUDA(cudaGetLastError());
     return 0;
@@ -664,13 +665,13 @@ static int backward_fp32(pf_rl_ctx* c, int k, const pf_rl_learner* L, const floa
         g.split_stride = (long long)out * in;
         if (int rc = launch_gemm(c, g, splits, st)) return rc;
         const long long wn = (long long)out * in;
-        pf_reduce_partials_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, st>>>(c->part, splits, wn, L->grads + n.w_off[l], wn);
+        PF_LAUNCHED(), pf_reduce_partials_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, st>>>(c->part, splits, wn, L->grads + n.w_off[l], wn);
         RL_CUDA(cudaGetLastError());
         // ---- bias grad: column sums of dY ----
         dim3 cg((out + 31) / 32, splits), cb(32, 8);
-        pf_colsum_kernel<<<cg, cb, 0, st>>>(dY, out, rows, out, kps, c->part, out);
+        PF_LAUNCHED(), pf_colsum_kernel<<<cg, cb, 0, st>>>(dY, out, rows, out, kps, c->part, out);
         RL_CUDA(cudaGetLastError());
-        pf_reduce_partials_kernel<<<(out + 255) / 256, 256, 0, st>>>(c->part, splits, out, L->grads + n.b_off[l], out);
+        PF_LAUNCHED(), pf_reduce_partials_kernel<<<(out + 255) / 256, 256, 0, st>>>(c->part, splits, out, L->grads + n.b_off[l], out);
         RL_CUDA(cudaGetLastError());
         // ---- dgrad: dH = dY W, times ELU'(saved activation) ----
         if (l > 0) {
@@ -700,10 +701,10 @@ extern "C" int pf_rl_minibatch_grad(pf_rl_ctx* c, const pf_rl_storage* storage, 
     // forward (activations kept for the backward pass); the minibatch rows are gathered on the fly
     if (int rc = forward_fp32(c, 0, L->params, storage->observations, P.num_obs, idx, MB, st)) return rc;
     if (int rc = forward_fp32(c, 1, L->params, cobs, P.num_critic_obs, idx, MB, st)) return rc;
-    pf_ppo_loss_kernel<<<c->loss_blocks, LOSS_THREADS, 0, st>>>(P, *storage, idx, MB, net_out(c, 0), net_out(c, 1),
+    PF_LAUNCHED(), pf_ppo_loss_kernel<<<c->loss_blocks, LOSS_THREADS, 0, st>>>(P, *storage, idx, MB, net_out(c, 0), net_out(c, 1),
                                                                  L->params + c->std_off, c->dmu, c->dval, c->loss_part);
     RL_CUDA(cudaGetLastError());
-    pf_ppo_loss_final_kernel<<<1, 64, 0, st>>>(c->loss_part, c->loss_blocks, P.num_actions, L->loss_stats, L->grads + c->std_off);
+    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 64, 0, st>>>(c->loss_part, c->loss_blocks, P.num_actions, L->loss_stats, L->grads + c->std_off);
     RL_CUDA(cudaGetLastError());
     if (int rc = backward_fp32(c, 0, L, storage->observations, P.num_obs, idx, c->dmu, MB, st)) return rc;
     if (int rc = backward_fp32(c, 1, L, cobs, P.num_critic_obs, idx, c->dval, MB, st)) return rc;
@@ -787,13 +788,13 @@ extern "C" int pf_rl_adam_step(pf_rl_ctx* c, const pf_rl_learner* L, void* strea
     int blocks = (int)((n + 255) / 256);
     if (blocks > c->norm_blocks) blocks = c->norm_blocks;
     AdamScalars* sc = reinterpret_cast<AdamScalars*>(c->norm_part + c->norm_blocks);
-    pf_gradnorm_kernel<<<blocks, 256, 0, st>>>(L->grads, n, c->norm_part);
+    PF_LAUNCHED(), pf_gradnorm_kernel<<<blocks, 256, 0, st>>>(L->grads, n, c->norm_part);
     RL_CUDA(cudaGetLastError());
-    pf_adam_scalars_kernel<<<1, 32, 0, st>>>(c->P, c->norm_part, blocks, *L, sc);
+    PF_LAUNCHED(), pf_adam_scalars_kernel<<<1, 32, 0, st>>>(c->P, c->norm_part, blocks, *L, sc);
     RL_CUDA(cudaGetLastError());
     int ublocks = (int)((n + 255) / 256);
     if (ublocks > c->num_sms * 8) ublocks = c->num_sms * 8;
-    pf_adam_kernel<<<ublocks, 256, 0, st>>>(n, *L, sc);
+    PF_LAUNCHED(), pf_adam_kernel<<<ublocks, 256, 0, st>>>(n, *L, sc);
     RL_CUDA(cudaGetLastError());
     if (c->tc) return pf_tc_pack_weights(c, L->params, st);
     return 0;

@@ -113,6 +113,8 @@ class PointFoot:
         self._include_feet_height_rewards = bool(P.include_feet_height_rewards)
         self._init_buffers(names)
 
+        # what pf_post_physics_step launches besides the step kernel (bench.py names them in its roofline block)
+        self.tail_kernel_name = " + pf_finalize_kernel"
         self._ctx = C.c_void_p()
         pts = pts.contiguous()
         capi.check(self._lib.pf_ctx_create(C.byref(P), C.c_void_p(noise.contiguous().data_ptr()),
@@ -289,7 +291,9 @@ class PointFoot:
         """point_foot.py:592-596 evaluates base_mass.mean().item() * max_push_vel_xy / dt on every push; base_mass only
         changes through update_added_mass_and_base_com, so the python double is kept (no host sync on the step path,
         and a push step can sit inside a stream capture)."""
-        self._max_push_force = (float(self.base_mass.mean().item()) * self.cfg.domain_rand.max_push_vel_xy
+        # (the mean is taken where the reference takes it: on the host, point_foot.py:41,50 -- ATen's CPU and CUDA
+        # reductions round differently from a few thousand envs on)
+        self._max_push_force = (float(self.base_mass.detach().cpu().mean().item()) * self.cfg.domain_rand.max_push_vel_xy
                                 / self.cfg.sim.dt)
 
     def _push_robots(self, st):
@@ -398,18 +402,19 @@ class GraphedStep:
         torch.cuda.current_stream(env.device).wait_stream(side)
         torch.cuda.synchronize(env.device)
         self._capture()
-        self.launches_per_step = None
 
     def _capture(self):
         env = self.env
         self.graph = torch.cuda.CUDAGraph()
         host_counter = env.common_step_counter
         self._capturing = True
+        n0 = env._lib.pf_debug_launch_count()
         try:
             with torch.cuda.graph(self.graph):
                 self._eager()
         finally:
             self._capturing = False
+        self.launches_per_step = int(env._lib.pf_debug_launch_count() - n0)     # kernels of this library per replay
         env.common_step_counter = host_counter     # capture does not execute
         self._epoch = getattr(env, "graph_epoch", 0)
 

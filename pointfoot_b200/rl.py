@@ -195,6 +195,7 @@ class PPO:
         self.precision = {"fp32": capi.RL_FP32, "bf16": capi.RL_BF16_TC}[precision]
         self.storage, self._ctx, self._t = None, None, 0
         self._update_graph, self._graph_updates = None, os.environ.get("PF_RL_UPDATE_GRAPH", "1") != "0"
+        self.launches_per_optimizer_step = None          # measured (library launch counter) by the first update()
         self._lib = capi.load_rl()
 
     # learning_rate mirrors the device scalar the adaptive schedule updates (one sync when read)
@@ -322,16 +323,21 @@ class PPO:
         # All optimizer steps of one update are a fixed sequence of ~2,000 small launches on fixed buffers (learning
         # rate, Adam state and the permutation live on the device): captured once, replayed as ONE graph launch.
         # With more than one rank the NCCL all-reduces stay outside a graph, so the steps are launched one by one.
+        n_steps = self.num_learning_epochs * self.num_mini_batches
         if self._graph_updates and shard.dist_or_none() is None:
             if self._update_graph is None:
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
+                n0 = self._lib.pf_debug_launch_count()
                 with torch.cuda.graph(g):
                     self._update_steps()
+                self.launches_per_optimizer_step = (self._lib.pf_debug_launch_count() - n0) / n_steps
                 self._update_graph = g
             self._update_graph.replay()
         else:
+            n0 = self._lib.pf_debug_launch_count()
             self._update_steps()
+            self.launches_per_optimizer_step = (self._lib.pf_debug_launch_count() - n0) / n_steps
         acc = self._loss_acc.tolist()                      # the one host sync of update(), like upstream's .item()
         self.storage.clear()
         self.iteration += 1

@@ -68,7 +68,7 @@ class EnvUnderTest:
                 if physics is not None:
                     physics(self)
             if self.push_interval and self.step_counter % self.push_interval == 0:      # PF:492-493, 590-611
-                m = float(self.t["base_mass"].mean().item()) * self.max_push_vel_xy_py / self.sim_dt_py
+                m = float(self.t["base_mass"].cpu().mean().item()) * self.max_push_vel_xy_py / self.sim_dt_py
                 capi.check(self.lib.pf_push_forces(self.ctx, C.byref(self.b), C.c_void_p(self.t["push_forces"].data_ptr()),
                                                    C.c_float(m), C.c_int64(self.step_counter), stream), "pf_push_forces")
             if getattr(self, "split_tail", False):     # tail on the context's side stream, other work queued beside it
@@ -86,7 +86,7 @@ class EnvUnderTest:
                 if physics is not None:
                     physics(self)
             if self.push_interval and self.step_counter % self.push_interval == 0:
-                m = float(self.t["base_mass"].mean().item()) * self.max_push_vel_xy_py / self.sim_dt_py
+                m = float(self.t["base_mass"].cpu().mean().item()) * self.max_push_vel_xy_py / self.sim_dt_py
                 self.lib.pf_emu_push_forces(C.byref(self.P), C.byref(self.b), C.c_void_p(self.t["push_forces"].data_ptr()),
                                             C.c_float(m), C.c_longlong(self.step_counter))
             self.lib.pf_emu_post_physics_step(C.byref(self.P), C.byref(self.b), C.c_void_p(self.noise.data_ptr()),
