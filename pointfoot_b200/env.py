@@ -262,7 +262,9 @@ class PointFoot:
         gym.refresh_rigid_body_state_tensor(sim)
         self.common_step_counter += 1
         st = self._stream()
-        if self.cfg.domain_rand.push_robots and self.common_step_counter % self.push_interval == 0:
+        # (a step being captured into a CUDA graph never carries the push: GraphedStep runs push steps eagerly)
+        if (self.cfg.domain_rand.push_robots and self.common_step_counter % self.push_interval == 0
+                and not getattr(self, "_in_capture", False)):
             self._push_robots(st)
         if getattr(self, "_defer_tail", False):
             # GraphedStep with a policy: the step's tail (reset id list, count, extras["episode"]) runs on the context's
@@ -407,13 +409,13 @@ class GraphedStep:
         env = self.env
         self.graph = torch.cuda.CUDAGraph()
         host_counter = env.common_step_counter
-        self._capturing = True
+        self._capturing = env._in_capture = True
         n0 = env._lib.pf_debug_launch_count()
         try:
             with torch.cuda.graph(self.graph):
                 self._eager()
         finally:
-            self._capturing = False
+            self._capturing = env._in_capture = False
         self.launches_per_step = int(env._lib.pf_debug_launch_count() - n0)     # kernels of this library per replay
         env.common_step_counter = host_counter     # capture does not execute
         self._epoch = getattr(env, "graph_epoch", 0)
