@@ -133,7 +133,7 @@ __global__ void pf_colsum_kernel(const float* __restrict__ dY, long long ld, int
 }
 
 static int launch_gemm(pf_rl_ctx* c, const GemmArgs& g, int splits, cudaStream_t st) {
-    if (pf_tc_gemm_supported(c, g.M, g.N, g.K)) return pf_tc_gemm(c, g, splits, st);
+    (void)c;
     dim3 grid((g.N + GT - 1) / GT, (g.M + GT - 1) / GT, splits);
     PF_LAUNCHED(), pf_sgemm_kernel<<<grid, 256, 0, st>>>(g);
     RL_CUDA(cudaGetLastError());
@@ -222,7 +222,7 @@ static int rl_ctx_init(pf_rl_ctx* c) {
     c->tc = nullptr;
     if (P.precision == PF_RL_BF16_TC) {
         if (int rc = pf_tc_create(c)) return rc;
-        if (int rc = pf_tc_gemm_create(c)) return rc;
+        if (int rc = pf_tt_create(c)) return rc;
     } else if (P.precision != PF_RL_FP32) {
         return rl_fail(1, "pf_rl_create", "unknown precision");
     }
@@ -233,7 +233,7 @@ extern "C" int pf_rl_destroy(pf_rl_ctx* c) {
     if (!c) return 0;
     if (c->tc) pf_tc_destroy(c);
     for (int k = 0; k < 2; ++k) cudaFree(c->net[k].tc_weights);       // (a pf_tc_create that failed half-way)
-    pf_tc_gemm_destroy(c);
+    pf_tt_destroy(c);
     for (int k = 0; k < 2; ++k)
         for (int l = 0; l < c->net[k].layers; ++l) cudaFree(c->net[k].act[l]);
     cudaFree(c->perm); cudaFree(c->dbuf[0]); cudaFree(c->dbuf[1]); cudaFree(c->part);
@@ -254,7 +254,8 @@ extern "C" int64_t pf_rl_param_offset(const pf_rl_ctx* c, int net, int layer, in
 
 extern "C" int pf_rl_params_changed(pf_rl_ctx* c, const float* params, void* stream) {
     if (!c || !params) return rl_fail(1, "pf_rl_params_changed", "null argument");
-    if (c->tc) return pf_tc_pack_weights(c, params, (cudaStream_t)stream);
+    if (c->tc) { if (int rc = pf_tc_pack_weights(c, params, (cudaStream_t)stream)) return rc; }
+    if (c->tc_gemm) return pf_tt_pack_weights(c, params, (cudaStream_t)stream);
     return 0;
 }
 
@@ -655,7 +656,7 @@ static int backward_fp32(pf_rl_ctx* c, int k, const pf_rl_learner* L, const floa
         // ---- wgrad: dW[out,in] = dY^T X, split over the batch ----
         int splits = c->wgrad_splits;
         int kps = (rows + splits - 1) / splits;
-        const int kq = c->tc_gemm ? 64 : GK;            // split granularity: one pipeline stage of the tensor-core GEMM
+        const int kq = GK;
         kps = (kps + kq - 1) / kq * kq;
         splits = (rows + kps - 1) / kps;
         GemmArgs g = {};
@@ -688,6 +689,17 @@ static int backward_fp32(pf_rl_ctx* c, int k, const pf_rl_learner* L, const floa
     return 0;
 }
 
+// pf_ppo_loss_kernel over the outputs in c->mu / c->val (the tensor-core forward's fp32 results): fills c->dmu / c->dval,
+// loss_stats and the gradient of std
+static int loss_on_ctx_outputs(pf_rl_ctx* c, const pf_rl_storage* storage, const pf_rl_learner* L, const int* idx, cudaStream_t st) {
+    PF_LAUNCHED(), pf_ppo_loss_kernel<<<c->loss_blocks, LOSS_THREADS, 0, st>>>(c->P, *storage, idx, c->mb_size, c->mu, c->val,
+                                                                                L->params + c->std_off, c->dmu, c->dval, c->loss_part);
+    RL_CUDA(cudaGetLastError());
+    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 64, 0, st>>>(c->loss_part, c->loss_blocks, c->P.num_actions, L->loss_stats, L->grads + c->std_off);
+    RL_CUDA(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int pf_rl_minibatch_grad(pf_rl_ctx* c, const pf_rl_storage* storage, const pf_rl_learner* L,
                                     int32_t minibatch, void* stream) {
     if (int rc = check_rl(c, storage, L, "pf_rl_minibatch_grad")) return rc;
@@ -698,6 +710,7 @@ extern "C" int pf_rl_minibatch_grad(pf_rl_ctx* c, const pf_rl_storage* storage, 
     const int MB = c->mb_size;
     const int* idx = c->perm + (long long)minibatch * MB;
     const float* cobs = storage->privileged_observations ? storage->privileged_observations : storage->observations;
+    if (c->tc_gemm) return pf_tt_minibatch(c, storage, L, idx, st, loss_on_ctx_outputs);      // PF_RL_BF16_TC: tcgen05 GEMMs
     // forward (activations kept for the backward pass); the minibatch rows are gathered on the fly
     if (int rc = forward_fp32(c, 0, L->params, storage->observations, P.num_obs, idx, MB, st)) return rc;
     if (int rc = forward_fp32(c, 1, L->params, cobs, P.num_critic_obs, idx, MB, st)) return rc;
@@ -796,6 +809,7 @@ extern "C" int pf_rl_adam_step(pf_rl_ctx* c, const pf_rl_learner* L, void* strea
     if (ublocks > c->num_sms * 8) ublocks = c->num_sms * 8;
     PF_LAUNCHED(), pf_adam_kernel<<<ublocks, 256, 0, st>>>(n, *L, sc);
     RL_CUDA(cudaGetLastError());
-    if (c->tc) return pf_tc_pack_weights(c, L->params, st);
+    if (c->tc) { if (int rc = pf_tc_pack_weights(c, L->params, st)) return rc; }
+    if (c->tc_gemm) return pf_tt_pack_weights(c, L->params, st);
     return 0;
 }

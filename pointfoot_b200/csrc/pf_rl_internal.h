@@ -53,7 +53,7 @@ int pf_tc_act_fusable(const pf_rl_ctx* c);
 int pf_tc_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
               int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st);
 
-// ---- GEMM contract shared by the fp32 kernel (pf_rl.cu) and the tensor-core kernel (pf_gemm_tc.cu) ----
+// ---- GEMM contract of the fp32 kernel (pf_rl.cu) ----
 struct GemmArgs {
     const float* A; long long sam, sak; const int* a_rows;   // a_rows gathers the m index (forward)
     const float* B; long long sbk, sbn; const int* b_rows;   // b_rows gathers the k index (wgrad)
@@ -67,8 +67,10 @@ struct GemmArgs {
     long long ld_elu;
 };
 
-
-int pf_tc_gemm_create(pf_rl_ctx* c);
-void pf_tc_gemm_destroy(pf_rl_ctx* c);
-int pf_tc_gemm_supported(const pf_rl_ctx* c, int M, int N, int K);
-int pf_tc_gemm(pf_rl_ctx* c, const GemmArgs& g, int splits, cudaStream_t st);
+// ---- tensor-core PPO.update (pf_train_tc.cu): state hangs off pf_rl_ctx::tc_gemm ----
+int pf_tt_create(pf_rl_ctx* c);
+void pf_tt_destroy(pf_rl_ctx* c);
+int pf_tt_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st);
+// gather + forward of both nets + `loss` (fills c->dmu / c->dval from c->mu / c->val, and the std gradient) + backward
+int pf_tt_minibatch(pf_rl_ctx* c, const pf_rl_storage* storage, const pf_rl_learner* L, const int* idx, cudaStream_t st,
+                    int (*loss)(pf_rl_ctx*, const pf_rl_storage*, const pf_rl_learner*, const int*, cudaStream_t));

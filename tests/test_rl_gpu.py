@@ -43,8 +43,16 @@ def test_ppo_update_rough_net():
 def test_ppo_update_tensor_core_gemms_bf16(hidden, nc, n):
     """PF_RL_BF16_TC: forward / dgrad / wgrad of PPO.update on the tcgen05 GEMM (bf16 operands, fp32 accumulate);
     first-minibatch gradient of EVERY parameter tensor within 2e-2 relative L2 of torch autograd, cosine >= 0.999;
-    parameters after the whole update within 5 % of the update's own L2 movement (bars in parity_rl.py)."""
+    parameters after the whole update within 8 % of the update's own L2 movement (bars and measured values in parity_rl.py)."""
     parity_rl.run_update(num_envs=n, num_critic_obs=nc, hidden=hidden, T=24, precision="bf16")
+
+
+@pytest.mark.parametrize("hidden,nc,n,t", [((256, 128), 48, 129, 8), ((64, 64, 64, 64), 235, 67, 12), ((200, 48), 27, 300, 4),
+                                            ((512, 256, 128), 148, 4096, 24)])
+def test_tensor_core_minibatch_gradient_shapes(hidden, nc, n, t):
+    """the tcgen05 training GEMMs on other layer shapes (widths that are not multiples of 128, four hidden layers, a ragged
+    last row tile, the full 24 x 4,096 minibatch): first-minibatch gradient per parameter tensor against torch autograd"""
+    parity_rl.run_update(num_envs=n, num_critic_obs=nc, hidden=hidden, T=t, precision="bf16", first_minibatch_only=True)
 
 
 def test_rollout_buffer_overflow_raises():
