@@ -632,15 +632,23 @@ __global__ void __launch_bounds__(LOSS_THREADS) pf_ppo_loss_kernel(const pf_rl_p
     }
 }
 
-// partials -> loss_stats[0..4] and the gradient of std
-__global__ void pf_ppo_loss_final_kernel(const double* __restrict__ part, int blocks, int A, double* loss_stats,
-                                         float* grad_std) {
-    const int k = threadIdx.x;                   // one thread per slot, fixed order over CTAs
-    if (k >= LOSS_SLOTS) return;
-    double v = 0.0;
-    for (int i = 0; i < blocks; ++i) v += part[(long long)i * LOSS_SLOTS + k];
-    if (k < 5) loss_stats[k] = v;
-    if (k >= 8 && k < 8 + A) grad_std[k - 8] = (float)v;
+// partials -> loss_stats[0..4] and the gradient of std.  One warp per slot (lanes stride over the CTAs, fixed shuffle
+// tree: deterministic), instead of one thread walking every CTA's partial.
+__global__ void __launch_bounds__(1024) pf_ppo_loss_final_kernel(const double* __restrict__ part, int blocks, int A, double* loss_stats,
+                                                                 float* grad_std) {
+    pf_grid_dep_launch();
+    pf_grid_dep_wait();
+    const int lane = threadIdx.x & 31;
+    for (int k = threadIdx.x >> 5; k < LOSS_SLOTS; k += (int)(blockDim.x >> 5)) {
+        if (!(k < 5 || (k >= 8 && k < 8 + A))) continue;
+        double v = 0.0;
+        for (int i = lane; i < blocks; i += 32) v += part[(long long)i * LOSS_SLOTS + k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) {
+            if (k < 5) loss_stats[k] = v;
+            else grad_std[k - 8] = (float)v;
+        }
+    }
 }
 
 // ================================================================================================ backward
@@ -695,7 +703,7 @@ static int loss_on_ctx_outputs(pf_rl_ctx* c, const pf_rl_storage* storage, const
     PF_LAUNCHED(), pf_ppo_loss_kernel<<<c->loss_blocks, LOSS_THREADS, 0, st>>>(c->P, *storage, idx, c->mb_size, c->mu, c->val,
                                                                                 L->params + c->std_off, c->dmu, c->dval, c->loss_part);
     RL_CUDA(cudaGetLastError());
-    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 64, 0, st>>>(c->loss_part, c->loss_blocks, c->P.num_actions, L->loss_stats, L->grads + c->std_off);
+    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 1024, 0, st>>>(c->loss_part, c->loss_blocks, c->P.num_actions, L->loss_stats, L->grads + c->std_off);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
@@ -717,7 +725,7 @@ extern "C" int pf_rl_minibatch_grad(pf_rl_ctx* c, const pf_rl_storage* storage, 
     PF_LAUNCHED(), pf_ppo_loss_kernel<<<c->loss_blocks, LOSS_THREADS, 0, st>>>(P, *storage, idx, MB, net_out(c, 0), net_out(c, 1),
                                                                  L->params + c->std_off, c->dmu, c->dval, c->loss_part);
     RL_CUDA(cudaGetLastError());
-    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 64, 0, st>>>(c->loss_part, c->loss_blocks, P.num_actions, L->loss_stats, L->grads + c->std_off);
+    PF_LAUNCHED(), pf_ppo_loss_final_kernel<<<1, 1024, 0, st>>>(c->loss_part, c->loss_blocks, P.num_actions, L->loss_stats, L->grads + c->std_off);
     RL_CUDA(cudaGetLastError());
     if (int rc = backward_fp32(c, 0, L, storage->observations, P.num_obs, idx, c->dmu, MB, st)) return rc;
     if (int rc = backward_fp32(c, 1, L, cobs, P.num_critic_obs, idx, c->dval, MB, st)) return rc;
@@ -748,11 +756,17 @@ __global__ void __launch_bounds__(256) pf_gradnorm_kernel(const float* __restric
 
 struct AdamScalars { float clip_coef, w1, beta2, w2, bc2_sqrt, eps, neg_step_size, pad; };
 
-__global__ void pf_adam_scalars_kernel(const pf_rl_params P, const double* __restrict__ part, int blocks,
-                                       pf_rl_learner L, AdamScalars* out) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    double n2 = 0.0;
-    for (int i = 0; i < blocks; ++i) n2 += part[i];
+__global__ void __launch_bounds__(256) pf_adam_scalars_kernel(const pf_rl_params P, const double* __restrict__ part, int blocks,
+                                                              pf_rl_learner L, AdamScalars* out) {
+    // grad-norm^2: the <= 256 CTA partials summed by a fixed tree (one load per thread instead of a serial walk)
+    __shared__ double red[8];
+    double n2 = (int)threadIdx.x < blocks ? part[threadIdx.x] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = n2;
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    n2 = 0.0;
+    for (int w = 0; w < 8; ++w) n2 += red[w];
     L.loss_stats[5] = n2;
     double lr = *L.lr;
     if (P.adaptive_schedule && P.desired_kl > 0.0) {
@@ -803,7 +817,7 @@ extern "C" int pf_rl_adam_step(pf_rl_ctx* c, const pf_rl_learner* L, void* strea
     AdamScalars* sc = reinterpret_cast<AdamScalars*>(c->norm_part + c->norm_blocks);
     PF_LAUNCHED(), pf_gradnorm_kernel<<<blocks, 256, 0, st>>>(L->grads, n, c->norm_part);
     RL_CUDA(cudaGetLastError());
-    PF_LAUNCHED(), pf_adam_scalars_kernel<<<1, 32, 0, st>>>(c->P, c->norm_part, blocks, *L, sc);
+    PF_LAUNCHED(), pf_adam_scalars_kernel<<<1, 256, 0, st>>>(c->P, c->norm_part, blocks, *L, sc);
     RL_CUDA(cudaGetLastError());
     int ublocks = (int)((n + 255) / 256);
     if (ublocks > c->num_sms * 8) ublocks = c->num_sms * 8;

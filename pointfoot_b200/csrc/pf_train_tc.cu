@@ -35,32 +35,37 @@ void pf_set_error(const char* msg);
 
 #define TT_TH 128                      // rows per tile of every activation / gradient tensor (= UMMA M)
 #define TT_KS 64                       // K elements per pipeline stage
-#define TT_OPER_BYTES 16384            // one staged operand tile: 128 x 64 bf16 in either orientation
+#define TT_A_BYTES 16384               // staged A tile: 128 x 64 bf16 in either orientation
+#define TT_B_BYTES 32768               // staged B tile: up to 256 x 64 bf16
+#define TT_STAGE_BYTES (TT_A_BYTES + TT_B_BYTES)
+#define TT_STAGES 4
 #define TT_MAXPROB 4
-#define TT_EPI_WARPS 4
+#define TT_EPI_WARPS 8                 // 4 TMEM lane quarters x 2 column halves
+#define TT_MMA_WARP TT_EPI_WARPS
+#define TT_LOAD_WARP (TT_EPI_WARPS + 1)
 #define TT_THREADS ((TT_EPI_WARPS + 2) * 32)
-#define TT_MAX_STAGES 4
+#define TT_SMEM (TT_STAGES * TT_STAGE_BYTES + 256)
 enum { TT_FWD = 0, TT_DGRAD = 1, TT_WGRAD = 2 };
 
 static inline int pad16i(int x) { return (x + 15) & ~15; }
 
-// one GEMM of a launch
+// one GEMM of a launch.  Its output is cut into tiles of 128 rows x up to 256 columns (x split-K slices for wgrad); the
+// launch's tiles are numbered problem after problem and dealt round-robin to the persistent CTAs.
 struct TtProb {
     const unsigned char* a; const unsigned char* b;
     int a_cbs, b_cbs, b_th;            // col blocks per tile of the A / B source tensors; tile height of the B source
     int mode;
-    int m_tiles, n_groups, nb;         // CTA grid: m_tiles x n_groups (x splits); nb = 128-wide N tiles per CTA (1 or 2)
-    int n_tiles;                       // N tiles of this problem (128 wide, the last one may be narrower)
-    int n_cbs_total;                   // dgrad / wgrad: N extent in col blocks
+    int m_tiles, n_tiles;              // output tiles: m_tiles x n_tiles (x splits)
+    int n_cbs_total;                   // dgrad / wgrad: N extent in col blocks (a tile takes up to 32 of them)
     int k_stages, k_last;              // K stages of TT_KS elements; elements in the last one (multiple of 16)
     int splits, stages_per_split;      // wgrad: split-K over the batch
-    int cta0, ctas;
+    int tile0, tiles;
     unsigned char* out_pk; int out_cbs; int n_valid; int ones; int elu;     // packed bf16 output (fwd hidden, dgrad)
     const unsigned char* y_pk; int y_cbs;                                   // dgrad: saved activation for ELU'
     float* out_f32; int ld_f32; int rows_valid;                             // fwd, last layer: plain fp32 [rows, n_valid]
-    float* part;                       // wgrad: partials [split][m_tile][n_tile][128][128] fp32
+    float* part;                       // wgrad: partials [split][m_tile][n_tile][128][256] fp32
 };
-struct TtArgs { TtProb p[TT_MAXPROB]; int nprob; int stages; };
+struct TtArgs { TtProb p[TT_MAXPROB]; int nprob; int total_tiles; };
 
 __device__ __forceinline__ uint32_t tt_idesc(int n, int a_mn, int b_mn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
@@ -76,36 +81,43 @@ __device__ __forceinline__ uint32_t tt_pack2(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&p);
 }
 
-__global__ void __launch_bounds__(TT_THREADS, 2) pf_train_gemm_kernel(const __grid_constant__ TtArgs g) {
+// what a CTA needs to know about one tile
+struct TtTile { int pi, mt, jn, z, s_beg, nst, w; };
+__device__ __forceinline__ TtTile tt_tile(const TtArgs& g, int t) {
+    TtTile T;
+    T.pi = 0;
+#pragma unroll
+    for (int i = 1; i < TT_MAXPROB; ++i) if (i < g.nprob && t >= g.p[i].tile0) T.pi = i;
+    const TtProb& P = g.p[T.pi];
+    int idx = t - P.tile0;
+    T.mt = idx % P.m_tiles; idx /= P.m_tiles;
+    T.jn = idx % P.n_tiles;
+    T.z = idx / P.n_tiles;
+    T.s_beg = T.z * P.stages_per_split;
+    T.nst = min(P.k_stages, T.s_beg + P.stages_per_split) - T.s_beg;
+    if (P.mode == TT_FWD) T.w = P.b_th;                                       // a tile of the weight tensor's rows
+    else { const int cb = P.n_cbs_total - T.jn * 32; T.w = (cb < 32 ? cb : 32) * 8; }
+    return T;
+}
+
+// Persistent: one CTA per SM walks its tiles.  Loader warp -> 4-stage shared-memory ring -> MMA warp -> two 256-column TMEM
+// accumulators -> 8 epilogue warps, so that the epilogue of tile i runs under the loads and MMAs of tile i + 1.
+__global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __grid_constant__ TtArgs g) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     pf_grid_dep_launch();
-    // ---- which problem, which tile ----
-    int pi = 0;
-#pragma unroll
-    for (int i = 1; i < TT_MAXPROB; ++i) if (i < g.nprob && (int)blockIdx.x >= g.p[i].cta0) pi = i;
-    const TtProb& P = g.p[pi];
-    int idx = (int)blockIdx.x - P.cta0;
-    const int mt = idx % P.m_tiles; idx /= P.m_tiles;
-    const int ng = idx % P.n_groups;
-    const int z = idx / P.n_groups;
-    const int NB = P.nb, S = g.stages;
-    const uint32_t stage_bytes = TT_OPER_BYTES * (1 + NB);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * stage_bytes);
-    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TT_MAX_STAGES), acc_bar = smem_u32(bars + 2 * TT_MAX_STAGES);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TT_MAX_STAGES + 1);
-    const int s_beg = z * P.stages_per_split;
-    const int s_end = min(P.k_stages, s_beg + P.stages_per_split);
-    const int nst = s_end - s_beg;
-    const uint32_t tmem_cols = NB == 2 ? 256u : 128u;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TT_STAGES * TT_STAGE_BYTES);
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TT_STAGES);
+    const uint32_t accf0 = smem_u32(bars + 2 * TT_STAGES), acce0 = smem_u32(bars + 2 * TT_STAGES + 2);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TT_STAGES + 4);
 
-    if (warp == TT_EPI_WARPS + 1 && lane == 0) {
-        for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        mbar_init(acc_bar, 1);
+    if (warp == TT_LOAD_WARP && lane == 0) {
+        for (int s = 0; s < TT_STAGES; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(accf0 + 8 * b, 1); mbar_init(acce0 + 8 * b, TT_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == TT_EPI_WARPS) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols) : "memory");
+    if (warp == TT_MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -114,142 +126,142 @@ __global__ void __launch_bounds__(TT_THREADS, 2) pf_train_gemm_kernel(const __gr
     const uint32_t tmem_base = *tmem_slot;
     pf_grid_dep_wait();              // everything above ran under the predecessor's tail; its outputs are visible from here on
 
-    // N tiles of this CTA: global tile index jn = ng * NB + nbi; width in columns
-    const int mode = P.mode;
-    auto n_width = [&](int jn) -> int {
-        if (jn >= P.n_tiles) return 0;
-        if (mode == TT_FWD) return P.b_th;                                 // a tile of the weight tensor's rows
-        const int cb = P.n_cbs_total - jn * 16;
-        return (cb < 16 ? cb : 16) * 8;
-    };
-
-    if (warp == TT_EPI_WARPS + 1) {
-        // ================================================================ loader: the whole warp issues the stage's copies
-        for (int s = 0; s < nst; ++s) {
-            const int slot = s % S, gs = s_beg + s;
-            const int kthis = gs == P.k_stages - 1 ? P.k_last : TT_KS;
-            if (s >= S) mbar_wait(empty0 + 8 * slot, (uint32_t)((s / S) - 1) & 1u);
-            const uint32_t fb = full0 + 8 * slot;
-            const uint32_t a_dst = smem_u32(smem + slot * stage_bytes);
-            // bytes of the stage (every lane computes them: warp-uniform)
-            uint32_t total = 0;
-            const int a_ncb = mode == TT_WGRAD ? min(16, P.a_cbs - mt * 16) : kthis >> 3;
-            total += mode == TT_WGRAD ? (uint32_t)a_ncb * (uint32_t)kthis * 16u : (uint32_t)a_ncb * TT_TH * 16u;
-            for (int nbi = 0; nbi < NB; ++nbi) {
-                const int w = n_width(ng * NB + nbi);
-                if (w == 0) continue;
-                total += mode == TT_FWD ? (uint32_t)(kthis >> 3) * (uint32_t)P.b_th * 16u : (uint32_t)(w >> 3) * (uint32_t)kthis * 16u;
-            }
-            if (lane == 0) mbar_expect_tx(fb, total);
-            __syncwarp();
-            // ---- A ----
-            if (mode != TT_WGRAD) {           // K-major rows of X / dY: the stage's col blocks are contiguous
-                if (lane == 0)
-                    bulk_g2s(a_dst, P.a + ((size_t)mt * P.a_cbs + (size_t)gs * 8) * (TT_TH * 16), (uint32_t)a_ncb * TT_TH * 16u, fb);
-            } else {                          // MN-major: 64 batch rows of each of the M tile's col blocks
-                const int rt = gs >> 1, r0 = (gs & 1) * TT_KS;
-                for (int cb = lane; cb < a_ncb; cb += 32)
-                    bulk_g2s(a_dst + cb * 1024, P.a + ((size_t)rt * P.a_cbs + (size_t)mt * 16 + cb) * (TT_TH * 16) + r0 * 16,
-                             (uint32_t)kthis * 16u, fb);
-            }
-            // ---- B ----
-            for (int nbi = 0; nbi < NB; ++nbi) {
-                const int jn = ng * NB + nbi, w = n_width(jn);
-                if (w == 0) continue;
-                const uint32_t b_dst = a_dst + TT_OPER_BYTES * (1 + nbi);
-                if (mode == TT_FWD) {         // K-major rows of W: tile jn, the stage's col blocks
-                    if (lane == 0)
-                        bulk_g2s(b_dst, P.b + ((size_t)jn * P.b_cbs + (size_t)gs * 8) * ((size_t)P.b_th * 16),
-                                 (uint32_t)(kthis >> 3) * (uint32_t)P.b_th * 16u, fb);
+    if (warp == TT_LOAD_WARP) {
+        // ================================================================ loader: the whole warp issues a stage's copies
+        uint32_t it = 0;                                             // stages issued so far by this CTA (ring position)
+        for (int t = (int)blockIdx.x; t < g.total_tiles; t += (int)gridDim.x) {
+            const TtTile T = tt_tile(g, t);
+            const TtProb& P = g.p[T.pi];
+            const int mode = P.mode;
+            for (int s = 0; s < T.nst; ++s, ++it) {
+                const uint32_t slot = it % TT_STAGES, gs = T.s_beg + s;
+                const int kthis = (int)gs == P.k_stages - 1 ? P.k_last : TT_KS;
+                if (it >= TT_STAGES) mbar_wait(empty0 + 8 * slot, ((it / TT_STAGES) - 1u) & 1u);
+                const uint32_t fb = full0 + 8 * slot;
+                const uint32_t a_dst = smem_u32(smem + slot * TT_STAGE_BYTES), b_dst = a_dst + TT_A_BYTES;
+                const int a_ncb = mode == TT_WGRAD ? min(16, P.a_cbs - T.mt * 16) : kthis >> 3;
+                const uint32_t a_bytes = mode == TT_WGRAD ? (uint32_t)a_ncb * (uint32_t)kthis * 16u : (uint32_t)a_ncb * TT_TH * 16u;
+                const uint32_t b_bytes = mode == TT_FWD ? (uint32_t)(kthis >> 3) * (uint32_t)P.b_th * 16u : (uint32_t)(T.w >> 3) * (uint32_t)kthis * 16u;
+                if (lane == 0) mbar_expect_tx(fb, a_bytes + b_bytes);
+                __syncwarp();
+                // ---- A ----
+                if (mode != TT_WGRAD) {           // K-major rows of X / dY: the stage's col blocks are contiguous
+                    if (lane == 0) bulk_g2s(a_dst, P.a + ((size_t)T.mt * P.a_cbs + (size_t)gs * 8) * (TT_TH * 16), a_bytes, fb);
+                } else {                          // MN-major: 64 batch rows of each of the M tile's col blocks
+                    const int rt = gs >> 1, r0 = (gs & 1) * TT_KS;
+                    for (int cb = lane; cb < a_ncb; cb += 32)
+                        bulk_g2s(a_dst + cb * 1024, P.a + ((size_t)rt * P.a_cbs + (size_t)T.mt * 16 + cb) * (TT_TH * 16) + r0 * 16,
+                                 (uint32_t)kthis * 16u, fb);
+                }
+                // ---- B ----
+                if (mode == TT_FWD) {             // K-major rows of W: tile jn, the stage's col blocks
+                    if (lane == 0) bulk_g2s(b_dst, P.b + ((size_t)T.jn * P.b_cbs + (size_t)gs * 8) * ((size_t)P.b_th * 16), b_bytes, fb);
                 } else {
                     // MN-major: rows [gs*64, +kthis) of the source (W rows for dgrad, batch rows of X for wgrad), col blocks of tile jn
                     const int th = mode == TT_DGRAD ? P.b_th : TT_TH;
                     const int row = gs * TT_KS, rt = row / th, r0 = row - rt * th;
-                    for (int cb = lane; cb < (w >> 3); cb += 32)
-                        bulk_g2s(b_dst + cb * 1024, P.b + ((size_t)rt * P.b_cbs + (size_t)jn * 16 + cb) * ((size_t)th * 16) + r0 * 16,
+                    for (int cb = lane; cb < (T.w >> 3); cb += 32)
+                        bulk_g2s(b_dst + cb * 1024, P.b + ((size_t)rt * P.b_cbs + (size_t)T.jn * 32 + cb) * ((size_t)th * 16) + r0 * 16,
                                  (uint32_t)kthis * 16u, fb);
                 }
             }
         }
-    } else if (warp == TT_EPI_WARPS) {
+    } else if (warp == TT_MMA_WARP) {
         // ================================================================ MMA issue
-        const bool a_mn = mode == TT_WGRAD, b_mn = mode != TT_FWD;
-        uint32_t idesc[2]; int wv[2];
-        for (int nbi = 0; nbi < 2; ++nbi) { wv[nbi] = nbi < NB ? n_width(ng * NB + nbi) : 0; idesc[nbi] = tt_idesc(wv[nbi] > 0 ? wv[nbi] : 16, a_mn, b_mn); }
-        // descriptor strides (bytes): K-major = (LBO: next 8 K columns, SBO: next 8 rows); MN-major = (LBO: next 8 K rows, SBO: next 8 MN)
-        const uint32_t a_lbo = a_mn ? 128u : TT_TH * 16u, a_sbo = a_mn ? 1024u : 128u;
-        const uint32_t b_lbo = b_mn ? 128u : (uint32_t)P.b_th * 16u, b_sbo = b_mn ? 1024u : 128u;
-        const uint64_t a_step = a_mn ? 16u : (2u * TT_TH * 16u) >> 4;            // K = 16 further, in 16-byte units
-        const uint64_t b_step = b_mn ? 16u : (2u * (uint32_t)P.b_th * 16u) >> 4;
-        for (int s = 0; s < nst; ++s) {
-            const int slot = s % S, gs = s_beg + s;
-            const int nk16 = (gs == P.k_stages - 1 ? P.k_last : TT_KS) >> 4;
-            mbar_wait(full0 + 8 * slot, (uint32_t)(s / S) & 1u);
+        uint32_t it = 0, j = 0;
+        for (int t = (int)blockIdx.x; t < g.total_tiles; t += (int)gridDim.x, ++j) {
+            const TtTile T = tt_tile(g, t);
+            const TtProb& P = g.p[T.pi];
+            const bool a_mn = P.mode == TT_WGRAD, b_mn = P.mode != TT_FWD;
+            const uint32_t idesc = tt_idesc(T.w, a_mn, b_mn);
+            // descriptor strides (bytes): K-major = (LBO: next 8 K columns, SBO: next 8 rows); MN-major = (LBO: next 8 K rows, SBO: next 8 MN)
+            const uint32_t a_lbo = a_mn ? 128u : TT_TH * 16u, a_sbo = a_mn ? 1024u : 128u;
+            const uint32_t b_lbo = b_mn ? 128u : (uint32_t)P.b_th * 16u, b_sbo = b_mn ? 1024u : 128u;
+            const uint64_t a_step = a_mn ? 16u : (2u * TT_TH * 16u) >> 4;            // K = 16 further, in 16-byte units
+            const uint64_t b_step = b_mn ? 16u : (2u * (uint32_t)P.b_th * 16u) >> 4;
+            const uint32_t acc = j & 1u, td = tmem_base + acc * 256u;
+            if (j >= 2) mbar_wait(acce0 + 8 * acc, ((j >> 1) - 1u) & 1u);            // the epilogue has drained this accumulator
             tc_fence_after();
-            if (elect_one()) {
-                const uint32_t base = smem_u32(smem + slot * stage_bytes);
-                const uint64_t ad = make_desc(base, a_lbo, a_sbo);
-#pragma unroll
-                for (int nbi = 0; nbi < 2; ++nbi) {
-                    if (wv[nbi] == 0) continue;
-                    const uint64_t bd = make_desc(base + TT_OPER_BYTES * (1 + nbi), b_lbo, b_sbo);
-                    const uint32_t td = tmem_base + nbi * 128;
-                    for (int k = 0; k < nk16; ++k) {
-                        if (s == 0 && k == 0) umma_bf16(td, ad, bd, idesc[nbi], 0u);
-                        else umma_bf16_acc(td, ad + k * a_step, bd + k * b_step, idesc[nbi]);
-                    }
+            for (int s = 0; s < T.nst; ++s, ++it) {
+                const uint32_t slot = it % TT_STAGES;
+                const int nk16 = (T.s_beg + s == P.k_stages - 1 ? P.k_last : TT_KS) >> 4;
+                mbar_wait(full0 + 8 * slot, (it / TT_STAGES) & 1u);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t base = smem_u32(smem + slot * TT_STAGE_BYTES);
+                    const uint64_t ad = make_desc(base, a_lbo, a_sbo), bd = make_desc(base + TT_A_BYTES, b_lbo, b_sbo);
+                    if (s == 0) umma_bf16(td, ad, bd, idesc, 0u); else umma_bf16_acc(td, ad, bd, idesc);
+                    for (int k = 1; k < nk16; ++k) umma_bf16_acc(td, ad + k * a_step, bd + k * b_step, idesc);
+                    umma_commit(empty0 + 8 * slot);
+                    if (s == T.nst - 1) umma_commit(accf0 + 8 * acc);
                 }
-                umma_commit(empty0 + 8 * slot);
-                if (s == nst - 1) umma_commit(acc_bar);
+                __syncwarp();
             }
-            __syncwarp();
         }
     } else {
-        // ================================================================ epilogue: warp q owns TMEM lanes [32q, 32q + 32) = tile rows
-        const int row = warp * 32 + lane;
-        if (nst > 0) { mbar_wait(acc_bar, 0u); tc_fence_after(); }
-        const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
-        for (int nbi = 0; nbi < NB; ++nbi) {
-            const int jn = ng * NB + nbi, w = n_width(jn);
-            if (w == 0) continue;
-            const int n0 = jn * (mode == TT_FWD ? P.b_th : 128);
+        // ================================================================ epilogue: warp (q, h) owns TMEM lanes [32q, 32q + 32) = tile rows,
+        // column half h of the accumulator
+        const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
+        uint32_t j = 0;
+        for (int t = (int)blockIdx.x; t < g.total_tiles; t += (int)gridDim.x, ++j) {
+            const TtTile T = tt_tile(g, t);
+            const TtProb& P = g.p[T.pi];
+            const int mode = P.mode, mt = T.mt, w = T.w;
+            const uint32_t acc = j & 1u;
+            mbar_wait(accf0 + 8 * acc, (j >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t trow = tmem_base + acc * 256u + ((uint32_t)(q * 32) << 16);
+            const int n0 = T.jn * (mode == TT_FWD ? P.b_th : 256);
             // forward into a packed tensor: the last N tile also writes the columns behind the real ones (ones, zero padding)
-            const int cols_end = (mode == TT_FWD && P.out_pk && jn == P.n_tiles - 1) ? P.out_cbs * 8 - n0 : w;
-            for (int c0 = 0; c0 < cols_end; c0 += 32) {
+            const int cols_end = (mode == TT_FWD && P.out_pk && T.jn == P.n_tiles - 1) ? P.out_cbs * 8 - n0 : w;
+            // this warp's column range: groups of 32 columns, alternating between the two halves
+            const int ngroups = (cols_end + 31) >> 5;
+            bool released = false;
+            for (int gi = h; gi < ngroups || !released; gi += 2) {
+                const int c0 = gi * 32;
                 uint32_t v[32];
-                if (c0 < w && nst > 0) {
-                    if (w - c0 >= 32) tmem_ld32(trow + nbi * 128 + c0, v);
-                    else { tmem_ld16(trow + nbi * 128 + c0, v);
+                const bool real = gi < ngroups && c0 < w;
+                if (real) {
+                    if (w - c0 >= 32) tmem_ld32(trow + c0, v);
+                    else { tmem_ld16(trow + c0, v);
 #pragma unroll
-                        for (int j = 16; j < 32; ++j) v[j] = 0u; }
+                        for (int jj = 16; jj < 32; ++jj) v[jj] = 0u; }
                     tmem_ld_wait();
                 } else {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = 0u;
+                    for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
                 }
+                // the accumulator is free once this warp's last real group sits in registers
+                if (!released && (gi + 2) * 32 >= w) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acce0 + 8 * acc);
+                    released = true;
+                }
+                if (gi >= ngroups) break;
                 if (mode == TT_WGRAD) {
-                    float4* dst = reinterpret_cast<float4*>(P.part + ((((size_t)z * P.m_tiles + mt) * P.n_tiles + jn) * 128 + row) * 128 + c0);
+                    float4* dst = reinterpret_cast<float4*>(P.part + ((((size_t)T.z * P.m_tiles + mt) * P.n_tiles + T.jn) * 128 + row) * 256 + c0);
                     const int nq = min(32, w - c0) >> 2;
 #pragma unroll
-                    for (int q = 0; q < 8; ++q)
-                        if (q < nq) dst[q] = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+                    for (int qq = 0; qq < 8; ++qq)
+                        if (qq < nq) dst[qq] = make_float4(__uint_as_float(v[4 * qq]), __uint_as_float(v[4 * qq + 1]), __uint_as_float(v[4 * qq + 2]), __uint_as_float(v[4 * qq + 3]));
                 } else if (P.out_f32) {       // forward, last layer: plain fp32 rows (mu / value)
                     const int grow = mt * TT_TH + row;
                     if (grow < P.rows_valid) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (n0 + c0 + j < P.n_valid) P.out_f32[(size_t)grow * P.ld_f32 + n0 + c0 + j] = __uint_as_float(v[j]);
+                        for (int jj = 0; jj < 32; ++jj)
+                            if (n0 + c0 + jj < P.n_valid) P.out_f32[(size_t)grow * P.ld_f32 + n0 + c0 + jj] = __uint_as_float(v[jj]);
                     }
                 } else {
                     const int ncb = min(4, (cols_end - c0 + 7) >> 3);
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        if (q >= ncb) continue;
-                        const int cb = (n0 + c0) / 8 + q;
+                    for (int qq = 0; qq < 4; ++qq) {
+                        if (qq >= ncb) continue;
+                        const int cb = (n0 + c0) / 8 + qq;
                         if (cb >= P.out_cbs) continue;
                         float x[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(v[8 * q + i]);
+                        for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(v[8 * qq + i]);
                         if (mode == TT_FWD) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
@@ -275,9 +287,9 @@ __global__ void __launch_bounds__(TT_THREADS, 2) pf_train_gemm_kernel(const __gr
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == TT_EPI_WARPS) {
+    if (warp == TT_MMA_WARP) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -388,8 +400,8 @@ __global__ void __launch_bounds__(256) pf_tt_reduce_kernel(const __grid_constant
     const TtReduceTab::E& L = t.e[li];
     const long long lu = u - L.elem0;
     const int o = (int)(lu / (L.in + 1)), i = (int)(lu % (L.in + 1));          // i == in: the bias column
-    const size_t tile = ((size_t)(o >> 7) * L.n_tiles + (i >> 7)) * 16384 + (size_t)(o & 127) * 128 + (i & 127);
-    const size_t stride = (size_t)L.m_tiles * L.n_tiles * 16384;
+    const size_t tile = ((size_t)(o >> 7) * L.n_tiles + (i >> 8)) * 32768 + (size_t)(o & 127) * 256 + (i & 255);
+    const size_t stride = (size_t)L.m_tiles * L.n_tiles * 32768;
     float s = 0.0f;
     for (int z = 0; z < L.splits; ++z) s += L.part[(size_t)z * stride + tile];
     if (i < L.in) grads[L.w_off + (long long)o * L.in + i] = s;
@@ -434,6 +446,7 @@ int pf_tt_create(pf_rl_ctx* c) {
     c->tc_gemm = t;                          // (pf_rl_destroy -> pf_tt_destroy frees whatever was allocated if we fail below)
     t->rows = c->mb_size;
     t->row_tiles = (c->mb_size + TT_TH - 1) / TT_TH;
+    if (t->row_tiles < 1) t->row_tiles = 1;          // (a storage smaller than num_mini_batches: empty minibatches, as upstream)
     t->rows_p = t->row_tiles * TT_TH;
     t->num_sms = c->num_sms;
     const int k_stages_batch = 2 * t->row_tiles;
@@ -445,27 +458,27 @@ int pf_tt_create(pf_rl_ctx* c) {
         for (int l = 0; l < n.L; ++l) {
             n.in[l] = c->net[k].dims[l]; n.out[l] = c->net[k].dims[l + 1];
             const int in_p = pad16i(n.in[l] + 2), out_p = pad16i(n.out[l]);
-            if (tt_alloc(n.W[l], out_p, in_p, out_p < 128 ? out_p : 128) || tt_alloc(n.X[l], t->rows_p, in_p, TT_TH) ||
+            // weights: tile height = the N of one forward MMA (<= 128: the whole layer; wider: 256-row tiles)
+            if (tt_alloc(n.W[l], out_p, in_p, out_p <= 128 ? out_p : 256) || tt_alloc(n.X[l], t->rows_p, in_p, TT_TH) ||
                 tt_alloc(n.dY[l], t->rows_p, out_p, TT_TH))
                 return tt_fail(2, "pf_rl_create: cudaMalloc of the packed training tensors failed");
-            n.mt_w[l] = (out_p + 127) / 128; n.nt_w[l] = (in_p + 127) / 128;
+            n.mt_w[l] = (out_p + 127) / 128; n.nt_w[l] = (in_p + 255) / 256;
             tiles_at[l] += n.mt_w[l] * n.nt_w[l];
         }
     }
     for (int k = 0; k < 2; ++k) {
         TtNet& n = t->net[k];
         for (int l = 0; l < n.L; ++l) {
-            int splits = (2 * t->num_sms + tiles_at[l] - 1) / tiles_at[l];
+            int splits = (t->num_sms + tiles_at[l] - 1) / tiles_at[l];
             if (splits > k_stages_batch / 2) splits = k_stages_batch / 2;       // at least two stages per split
             if (splits < 1) splits = 1;
             const int sps = (k_stages_batch + splits - 1) / splits;
             n.sps[l] = sps; n.splits[l] = (k_stages_batch + sps - 1) / sps;
-            if (cudaMalloc(&n.part[l], sizeof(float) * (size_t)n.splits[l] * n.mt_w[l] * n.nt_w[l] * 16384) != cudaSuccess)
+            if (cudaMalloc(&n.part[l], sizeof(float) * (size_t)n.splits[l] * n.mt_w[l] * n.nt_w[l] * 32768) != cudaSuccess)
                 return tt_fail(2, "pf_rl_create: cudaMalloc of the wgrad partials failed");
         }
     }
-    const int smem = 96 * 1024 + 256;
-    if (cudaFuncSetAttribute(pf_train_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+    if (cudaFuncSetAttribute(pf_train_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM) != cudaSuccess)
         return tt_fail(2, "pf_rl_create: cannot reserve shared memory for the tensor-core training GEMM");
     return 0;
 }
@@ -490,15 +503,12 @@ int pf_tt_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st) {
 }
 
 static int tt_launch(TtState* t, TtArgs& a, cudaStream_t st) {
-    int ctas = 0, nb = 1;
-    for (int i = 0; i < a.nprob; ++i) { a.p[i].cta0 = ctas; ctas += a.p[i].ctas; if (a.p[i].nb > nb) nb = a.p[i].nb; }
-    if (ctas == 0) return 0;
-    // 96 KB of stages per CTA (two CTAs per SM: one's epilogue runs under the other's MMAs): 3 x 32 KB or 2 x 48 KB
-    a.stages = nb == 2 ? 2 : 3;
-    for (int i = 0; i < a.nprob; ++i) if (a.p[i].nb != nb) a.stages = 2;      // mixed launch: the ring is sized for the larger stage
-    const int smem = 96 * 1024 + 256;
-    (void)t;
-    return pf_launch_pdl(pf_train_gemm_kernel, dim3(ctas), dim3(TT_THREADS), (size_t)smem, st, a) == cudaSuccess
+    int tiles = 0;
+    for (int i = 0; i < a.nprob; ++i) { a.p[i].tile0 = tiles; tiles += a.p[i].tiles; }
+    if (tiles == 0) return 0;
+    a.total_tiles = tiles;
+    const int grid = tiles < t->num_sms ? tiles : t->num_sms;         // persistent: one CTA per SM
+    return pf_launch_pdl(pf_train_gemm_kernel, dim3(grid), dim3(TT_THREADS), (size_t)TT_SMEM, st, a) == cudaSuccess
                ? 0 : tt_fail(2, "pf_train_gemm_kernel: launch failed");
 }
 
@@ -510,9 +520,8 @@ static TtProb tt_fwd(TtState* t, TtNet& n, int l, float* out_f32) {
     const TtTensor &X = n.X[l], &W = n.W[l];
     p.mode = TT_FWD; p.a = X.p; p.a_cbs = X.cbs; p.b = W.p; p.b_cbs = W.cbs; p.b_th = W.th;
     p.m_tiles = t->row_tiles; p.n_tiles = W.rows_p / W.th;
-    p.nb = p.n_tiles >= 2 ? 2 : 1; p.n_groups = (p.n_tiles + p.nb - 1) / p.nb;
     tt_k(p, X.cbs * 8);
-    p.ctas = p.m_tiles * p.n_groups;
+    p.tiles = p.m_tiles * p.n_tiles;
     p.n_valid = n.out[l];
     if (l < n.L - 1) { p.out_pk = n.X[l + 1].p; p.out_cbs = n.X[l + 1].cbs; p.ones = 1; p.elu = 1; }
     else { p.out_f32 = out_f32; p.ld_f32 = n.out[l]; p.rows_valid = t->rows; }
@@ -525,10 +534,9 @@ static TtProb tt_dgrad(TtState* t, TtNet& n, int l) {
     p.mode = TT_DGRAD; p.a = G.p; p.a_cbs = G.cbs; p.b = W.p; p.b_cbs = W.cbs; p.b_th = W.th;
     p.m_tiles = t->row_tiles;
     p.n_cbs_total = D.cbs;                       // the real inputs of layer l (the bias columns of W are not propagated)
-    p.n_tiles = (D.cbs + 15) / 16;
-    p.nb = p.n_tiles >= 2 ? 2 : 1; p.n_groups = (p.n_tiles + p.nb - 1) / p.nb;
+    p.n_tiles = (D.cbs + 31) / 32;
     tt_k(p, G.cbs * 8);
-    p.ctas = p.m_tiles * p.n_groups;
+    p.tiles = p.m_tiles * p.n_tiles;
     p.out_pk = D.p; p.out_cbs = D.cbs; p.n_valid = n.in[l];
     p.y_pk = n.X[l].p; p.y_cbs = n.X[l].cbs;
     return p;
@@ -539,10 +547,9 @@ static TtProb tt_wgrad(TtState* t, TtNet& n, int l) {
     const TtTensor &G = n.dY[l], &X = n.X[l];
     p.mode = TT_WGRAD; p.a = G.p; p.a_cbs = G.cbs; p.b = X.p; p.b_cbs = X.cbs; p.b_th = TT_TH;
     p.m_tiles = n.mt_w[l]; p.n_tiles = n.nt_w[l]; p.n_cbs_total = X.cbs;
-    p.nb = 1; p.n_groups = p.n_tiles;
     tt_k(p, t->rows_p);
     p.splits = n.splits[l]; p.stages_per_split = n.sps[l];
-    p.ctas = p.m_tiles * p.n_groups * p.splits;
+    p.tiles = p.m_tiles * p.n_tiles * p.splits;
     p.part = n.part[l];
     return p;
 }
