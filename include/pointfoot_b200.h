@@ -335,6 +335,21 @@ int pf_rl_process_env_step(pf_rl_ctx* ctx, const pf_rl_storage* storage, int32_t
  * stats[3] (device, double) = sum, sum of squares, count of the raw advantages on THIS device.  Multi-GPU:
  * all-reduce `stats` (sum) between the two calls. */
 int pf_rl_gae(pf_rl_ctx* ctx, const pf_rl_storage* storage, const float* last_values, double* stats, void* stream);
+/* pf_rl_gae for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Needs no pf_rl_ctx and calls no cudaMalloc / cudaFree / allocating library routine: the per-CTA partials of the reduction
+ * live in a static 64 KB device array inside the library (held by every GPU that loads it until the process exits).
+ * Inputs / outputs are the rollout_storage.py tensors, [T,N,1] contiguous DEVICE memory owned by the caller: rewards, dones
+ * (uint8), values in; returns and raw advantages (returns - values) out; last_values[N]; stats[3] (device, double) = sum, sum
+ * of squares, count of the raw advantages, exactly what pf_rl_gae writes (feed it to pf_rl_normalize_advantages or to the
+ * caller's own normalisation).  Same kernels, same bits as pf_rl_gae.
+ * num_envs > PF_GAE_NOALLOC_MAX_ENVS is rejected (code 8, message in pf_last_error()).  All calls on a device share the
+ * array: it keeps the previous call's contents (none of which a later call reads), and calls that OVERLAP on the GPU --
+ * different streams with no ordering between them -- race; order them on one stream or with events. */
+#define PF_GAE_NOALLOC_MAX_ENVS 1048576
+int pf_rl_gae_noalloc(const float* rewards, const uint8_t* dones, const float* values, const float* last_values,
+                      int32_t num_envs, int32_t num_steps, float gamma, float lam, float* returns, float* advantages,
+                      double* stats, void* stream);
 /* second half: advantages = (adv - mean) / (std_unbiased + 1e-8) from stats */
 int pf_rl_normalize_advantages(pf_rl_ctx* ctx, const pf_rl_storage* storage, const double* stats, void* stream);
 /* mini_batch_generator's shuffle: the Feistel permutation contract (oracle/rsl_rl_ref.py feistel_permutation)

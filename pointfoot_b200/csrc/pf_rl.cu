@@ -6,6 +6,7 @@
 // third party).
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <string.h>
 #include <math.h>
 #include "pf_rl_internal.h"
 #include "pf_rng.cuh"
@@ -487,6 +488,74 @@ extern "C" int pf_rl_gae(pf_rl_ctx* c, const pf_rl_storage* storage, const float
     PF_LAUNCHED(), pf_gae_kernel<<<c->gae_blocks, 256, 0, st>>>(c->P, *storage, last_values, c->gae_part);
     RL_CUDA(cudaGetLastError());
     PF_LAUNCHED(), pf_gae_stats_kernel<<<1, 256, 0, st>>>(c->gae_part, c->gae_blocks, (double)c->P.num_envs * c->P.num_steps, stats);
+    RL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ GAE without allocation
+// pf_rl_gae_noalloc: the same two kernels as pf_rl_gae (pf_gae_kernel + pf_gae_stats_kernel, unchanged), for callers that
+// cannot allocate device memory: no pf_rl_ctx (pf_rl_create calls cudaMalloc), the per-CTA partials live in a file-scope
+// device array instead of the context's gae_part.  No counterpart in the
+// reference.
+//   * the array is PF_GAE_NOALLOC_MAX_ENVS / 256 CTAs x 2 doubles = 64 KB; every GPU that loads the library holds it until
+//     the process exits;
+//   * in HOST code the array's name is only a host-side stand-in for the symbol, not a device address: the device address
+//     is looked up once per device (with that device current) by cudaGetSymbolAddress and that pointer is what the
+//     kernels are handed;
+//   * every call on a device shares the array.  Nothing in it has to start at zero -- every CTA of pf_gae_kernel overwrites
+//     its own two partials and pf_gae_stats_kernel reads exactly the CTAs of this call -- so a call does not depend on what
+//     the previous one left; but two calls that OVERLAP on the GPU (different streams, no ordering between them) race
+//     on it.  Calls on one stream, or ordered by events, are safe.
+#define PF_GAE_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) double g_pf_gae_noalloc_part[2 * (PF_GAE_NOALLOC_MAX_ENVS / 256)];
+static double* g_pf_gae_noalloc_ptr[PF_GAE_NOALLOC_MAX_DEVICES] = {nullptr};      // device address of the array, per device
+
+// device address of the scratch array on the CURRENT device (looked up on the first call there); NULL + error on failure
+static double* gae_noalloc_scratch(void) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= PF_GAE_NOALLOC_MAX_DEVICES) {
+        rl_fail(2, "pf_rl_gae_noalloc", "no current CUDA device (or device ordinal >= 64)");
+        return nullptr;
+    }
+    double* p = __atomic_load_n(&g_pf_gae_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p) return p;
+    void* sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_pf_gae_noalloc_part);
+    if (e != cudaSuccess || !sym) {
+        rl_fail(2, "pf_rl_gae_noalloc: cudaGetSymbolAddress", cudaGetErrorString(e));
+        return nullptr;
+    }
+    // (two threads racing here store the same address: the symbol has one address per device)
+    __atomic_store_n(&g_pf_gae_noalloc_ptr[dev], static_cast<double*>(sym), __ATOMIC_RELEASE);
+    return static_cast<double*>(sym);
+}
+
+extern "C" int pf_rl_gae_noalloc(const float* rewards, const uint8_t* dones, const float* values, const float* last_values,
+                                 int32_t num_envs, int32_t num_steps, float gamma, float lam, float* returns,
+                                 float* advantages, double* stats, void* stream) {
+    if (!rewards || !dones || !values || !last_values || !returns || !advantages || !stats)
+        return rl_fail(1, "pf_rl_gae_noalloc", "null argument");
+    if (num_envs <= 0 || num_steps <= 0) return rl_fail(1, "pf_rl_gae_noalloc", "num_envs and num_steps must be positive");
+    if (num_envs > PF_GAE_NOALLOC_MAX_ENVS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "num_envs = %d exceeds PF_GAE_NOALLOC_MAX_ENVS = %d (the static scratch array holds no more); "
+                 "use pf_rl_gae with a pf_rl_ctx for larger batches", (int)num_envs, (int)PF_GAE_NOALLOC_MAX_ENVS);
+        return rl_fail(8, "pf_rl_gae_noalloc", msg);
+    }
+    double* part = gae_noalloc_scratch();
+    if (!part) return 2;
+    pf_rl_params P;
+    memset(&P, 0, sizeof(P));
+    P.abi_version = PF_ABI_VERSION; P.num_envs = num_envs; P.num_steps = num_steps; P.gamma = gamma; P.lam = lam;
+    pf_rl_storage S;
+    memset(&S, 0, sizeof(S));
+    S.rewards = const_cast<float*>(rewards); S.dones = const_cast<uint8_t*>(dones); S.values = const_cast<float*>(values);
+    S.returns = returns; S.advantages = advantages;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int blocks = (num_envs + 255) / 256;
+    PF_LAUNCHED(), pf_gae_kernel<<<blocks, 256, 0, st>>>(P, S, last_values, part);
+    RL_CUDA(cudaGetLastError());
+    PF_LAUNCHED(), pf_gae_stats_kernel<<<1, 256, 0, st>>>(part, blocks, (double)num_envs * num_steps, stats);
     RL_CUDA(cudaGetLastError());
     return 0;
 }
