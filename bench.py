@@ -723,9 +723,9 @@ def run_b200(args):
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)
-    barrier()
     if world > 1:
-        dist.destroy_process_group()
+        from pointfoot_b200 import shard
+        shard.shutdown()
 
 
 if __name__ == "__main__":

@@ -196,6 +196,7 @@ class PPO:
         self.storage, self._ctx, self._t = None, None, 0
         self._update_graph, self._graph_updates = None, os.environ.get("PF_RL_UPDATE_GRAPH", "1") != "0"
         self.launches_per_optimizer_step = None          # measured (library launch counter) by the first update()
+        self._graph_dist = os.environ.get("PF_RL_UPDATE_GRAPH_DIST", "1") != "0"
         self._lib = capi.load_rl()
 
     # learning_rate mirrors the device scalar the adaptive schedule updates (one sync when read)
@@ -324,15 +325,28 @@ class PPO:
         # rate, Adam state and the permutation live on the device): captured once, replayed as ONE graph launch.
         # With more than one rank the NCCL all-reduces stay outside a graph, so the steps are launched one by one.
         n_steps = self.num_learning_epochs * self.num_mini_batches
-        if self._graph_updates and shard.dist_or_none() is None:
-            if self._update_graph is None:
-                torch.cuda.synchronize(self.device)
-                g = torch.cuda.CUDAGraph()
-                n0 = self._lib.pf_debug_launch_count()
+        # More than one rank: the NCCL all-reduces of the flat gradient and of loss_stats are captured with the kernels (the
+        # communicator exists since init_storage's broadcast), so the multi-GPU update is ONE graph launch as well.
+        # PF_RL_UPDATE_GRAPH_DIST=0 (or a failed capture) falls back to launching the steps one by one.
+        use_graph = self._graph_updates and (shard.dist_or_none() is None or self._graph_dist)
+        if use_graph and self._update_graph is None:
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            n0 = self._lib.pf_debug_launch_count()
+            try:
                 with torch.cuda.graph(g):
                     self._update_steps()
-                self.launches_per_optimizer_step = (self._lib.pf_debug_launch_count() - n0) / n_steps
                 self._update_graph = g
+                self.launches_per_optimizer_step = (self._lib.pf_debug_launch_count() - n0) / n_steps
+            except Exception as ex:                    # capture of the collectives refused: eager from here on
+                if shard.dist_or_none() is None:
+                    raise
+                print(f"pointfoot_b200: PPO.update graph capture with collectives failed ({type(ex).__name__}: {ex}); "
+                      "launching the update steps eagerly")
+                self._graph_dist, use_graph = False, False
+                torch.cuda.synchronize(self.device)
+                self._loss_acc.zero_()
+        if use_graph:
             self._update_graph.replay()
         else:
             n0 = self._lib.pf_debug_launch_count()
@@ -345,6 +359,12 @@ class PPO:
         return acc[1] / cnt, acc[0] / cnt
 
     def close(self):
+        # the captured update holds this context's buffers and, on more than one rank, NCCL kernels: it has to go BEFORE the
+        # context and before torch.distributed.destroy_process_group() (a live graph with captured collectives makes the
+        # communicator's teardown wait forever)
+        if self._update_graph is not None:
+            torch.cuda.synchronize(self.device)
+            self._update_graph = None
         if self._ctx:
             self._lib.pf_rl_destroy(self._ctx)
             self._ctx = None
@@ -425,6 +445,7 @@ class OnPolicyRunner:
         cur_reward_sum = torch.zeros(env.num_envs, dtype=torch.float, device=dev)
         cur_episode_length = torch.zeros(env.num_envs, dtype=torch.float, device=dev)
         tot_iter = self.current_learning_iteration + num_learning_iterations
+        sharded = shard.dist_or_none() is not None
         for it in range(self.current_learning_iteration, tot_iter):
             start = time.time()
             for _ in range(self.num_steps_per_env):
@@ -432,8 +453,12 @@ class OnPolicyRunner:
                 obs, priv, rewards, dones, infos = env.step(actions)
                 critic_obs = priv if priv is not None else obs
                 alg.process_env_step(rewards, dones, infos)
+                if sharded and "episode" in infos:     # every rank: the merge after the rollout is a collective
+                    ep = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in infos["episode"].items()}
+                    ep["_count"] = env._reset_count.clone() if hasattr(env, "_reset_count") else (dones > 0).sum()
+                    ep_infos.append(ep)
                 if self.log_dir is not None:
-                    if "episode" in infos:
+                    if "episode" in infos and not sharded:
                         ep_infos.append({k: (v.clone() if torch.is_tensor(v) else v) for k, v in infos["episode"].items()})
                     cur_reward_sum += rewards
                     cur_episode_length += 1
@@ -443,6 +468,8 @@ class OnPolicyRunner:
                     cur_reward_sum[new_ids] = 0
                     cur_episode_length[new_ids] = 0
             alg.compute_returns(critic_obs)
+            if sharded:                                # Episode/* of the whole job, not of this rank's shard
+                ep_infos = [shard.allreduce_episode_infos(ep_infos, env.num_envs)] if ep_infos else []
             torch.cuda.synchronize(dev)
             stop = time.time()
             collection_time, start = stop - start, stop
@@ -454,7 +481,7 @@ class OnPolicyRunner:
                 self.log(locals())
                 if it % self.save_interval == 0:
                     self.save(os.path.join(self.log_dir, "model_{}.pt".format(it)))
-            ep_infos.clear()
+            ep_infos = []
         self.current_learning_iteration += num_learning_iterations
         if self.log_dir is not None:
             self.save(os.path.join(self.log_dir, "model_{}.pt".format(self.current_learning_iteration)))

@@ -29,11 +29,15 @@ def allreduce_sum_(t):
 
 def allreduce_mean_(t):
     """Gradient averaging of PPO.update: the minibatch loss is a mean over the rank's samples and shards are equal
-    sized, so the global-minibatch gradient is the mean of the rank gradients."""
+    sized, so the global-minibatch gradient is the mean of the rank gradients.  ONE collective (NCCL's AVG) where the
+    backend has it; gloo (the CPU tests) sums and divides."""
     d = dist_or_none()
     if d:
-        d.all_reduce(t)
-        t.div_(d.get_world_size())
+        if d.get_backend() == "nccl":
+            d.all_reduce(t, op=d.ReduceOp.AVG)
+        else:
+            d.all_reduce(t)
+            t.div_(d.get_world_size())
     return t
 
 
@@ -51,3 +55,66 @@ def merge_episode_stats(stats, counts):
     counts = counts.to(stats.dtype)
     tot = counts.sum().clamp_min(1.0)
     return (stats * counts[:, None]).sum(0) / tot
+
+
+def allreduce_episode_infos(ep_infos, num_envs):
+    """``extras["episode"]`` of the steps of one rollout, merged over all shards (BASELINE.json north_star: NCCL "for the
+    PPO gradient allreduce and the reward/episode statistics").  ``ep_infos``: one dict per step, the env's 0-d tensors
+    plus ``"_count"`` = the number of envs of THIS shard that reset on that step.  A ``rew_*`` entry is the mean over the
+    shard's reset envs (point_foot.py:276-280), so the job-wide value of a step is the count-weighted mean over shards;
+    ``terrain_level`` is a mean over all envs of the shard (point_foot.py:283): weighted by ``num_envs``.  Steps on which
+    no env of any shard reset carry no new information and are left out; the result is the plain mean over the other
+    steps, like the runner's mean over ``ep_infos`` upstream.  One all-reduce of (S x K) x 2 doubles.  Collective: every
+    rank calls it, with the same number of steps.  Returns {key: float}; non-tensor entries are passed through."""
+    import torch
+    if not ep_infos:
+        return {}
+    keys = [k for k, v in ep_infos[0].items() if k != "_count" and torch.is_tensor(v)]
+    out = {k: v for k, v in ep_infos[-1].items() if k != "_count" and not torch.is_tensor(v)}
+    if not keys:
+        return out
+    dev = ep_infos[0][keys[0]].device
+    S, K = len(ep_infos), len(keys)
+    vals = torch.stack([torch.stack([ep[k].reshape(()).to(torch.float64) for k in keys]) for ep in ep_infos])
+    cnt = torch.stack([torch.as_tensor(ep["_count"], device=dev).reshape(()).to(torch.float64) for ep in ep_infos])
+    w = cnt[:, None].expand(S, K).clone()
+    for j, k in enumerate(keys):
+        if k == "terrain_level":
+            w[:, j] = float(num_envs)
+    buf = torch.cat(((vals * w).flatten(), w.flatten()))
+    allreduce_sum_(buf)
+    num, den = buf[:S * K].view(S, K), buf[S * K:].view(S, K)
+    valid = (den > 0).to(torch.float64)
+    mean = (num / den.clamp_min(1.0) * valid).sum(0) / valid.sum(0).clamp_min(1.0)
+    mean = mean.cpu().tolist()
+    out.update({k: mean[j] for j, k in enumerate(keys)})
+    return out
+
+
+def shutdown(grace_s=20.0):
+    """``destroy_process_group()`` that cannot hang the job: callers close their PPO objects first (PPO.close drops the
+    CUDA graph that holds captured NCCL kernels); if the communicator's teardown still has not returned after ``grace_s``
+    seconds, the process exits with status 0 -- everything that had to be printed or saved was, before this call."""
+    import gc
+    import os
+    import sys
+    import threading
+    d = dist_or_none()
+    if d is None:
+        return
+    gc.collect()
+    torch.cuda.synchronize()
+    sys.stdout.flush(); sys.stderr.flush()
+
+    def bail():
+        sys.stderr.write("pointfoot_b200.shard.shutdown: destroy_process_group() did not return; exiting\n")
+        sys.stderr.flush()
+        os._exit(0)
+    t = threading.Timer(grace_s, bail)
+    t.daemon = True
+    t.start()
+    try:
+        d.barrier()
+        d.destroy_process_group()
+    finally:
+        t.cancel()

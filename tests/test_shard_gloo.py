@@ -135,6 +135,18 @@ def _ppo_worker(rank, world, port, q):
               and torch.allclose(loss, kl_all.sum(0)))
         merged = shard.merge_episode_stats(torch.tensor([[1.0, 2.0], [3.0, 6.0]]), torch.tensor([1, 3]))
         ok = ok and torch.allclose(merged, torch.tensor([2.5, 5.0]))
+        # extras["episode"] of a 3-step rollout merged over the two shards (what OnPolicyRunner.learn logs when sharded):
+        # step 0: rank 0 had 1 reset (mean 2.0), rank 1 had 3 (mean 6.0) -> 5.0; step 1: nobody reset -> left out;
+        # step 2: only rank 1 reset (mean 1.0; rank 0's entry is a stale 9.0 with count 0) -> 1.0.  Mean over steps: 3.0.
+        # terrain_level is a mean over ALL envs of a shard: weighted by num_envs (equal shards -> plain mean over ranks).
+        rew = ([2.0, 7.0, 9.0], [6.0, 6.0, 1.0])[rank]
+        cnt = ([1, 0, 0], [3, 0, 1])[rank]
+        lvl = ([1.0, 1.0, 2.0], [3.0, 3.0, 4.0])[rank]
+        infos = [{"rew_torques": torch.tensor(rew[i]), "terrain_level": torch.tensor(lvl[i]), "max_command_x": 1.0,
+                  "_count": torch.tensor(cnt[i], dtype=torch.int32)} for i in range(3)]
+        m = shard.allreduce_episode_infos(infos, num_envs=8)
+        ok = ok and abs(m["rew_torques"] - 3.0) < 1e-12 and abs(m["terrain_level"] - (2.0 + 2.0 + 3.0) / 3) < 1e-12
+        ok = ok and m["max_command_x"] == 1.0 and "_count" not in m
         if rank == 0:
             q.put(("ok", bool(ok)))
         dist.barrier()
