@@ -40,13 +40,10 @@ void pf_set_error(const char* msg);
 #define TC_SLOT_BYTES 16384                  // weight ring slot = largest tile (N x K x 2 B: 256x32, 128x64, 64x128 ...)
 #define TC_MAX_STAGES 16
 #define TC_X0_KSTEP ((2 * TC_X0_LBO) / 16)    // K = 16 further along the staged input, in descriptor units
-#define TC_EPI_WARPS 8                       // epilogue warps: 4 TMEM lane quarters x 2 column halves (the ELU is MUFU-bound: more warps do not help)
-#define TC_EPI_THREADS (TC_EPI_WARPS * 32)
-#define TC_STG_WARPS 8                       // staging warps: input rows of the NEXT item, under the tail of the current one
-#define TC_STG_THREADS (TC_STG_WARPS * 32)
-#define TC_MMA_WARP (TC_EPI_WARPS + TC_STG_WARPS)
-#define TC_LOAD_WARP (TC_MMA_WARP + 1)
-#define TC_THREADS ((TC_LOAD_WARP + 1) * 32)
+// Warp roles are template parameters of the kernel: kEpi epilogue warps (8 = 4 TMEM lane quarters x 2 column halves; the ELU is
+// MUFU-bound, more do not help; 4 in the compact variant), kStg staging warps (input rows of the NEXT item, under the tail of
+// the current one), then the MMA warp and the loader warp.
+#define TC_THREADS_OF(kEpi, kStg) (((kEpi) + (kStg) + 2) * 32)
 #define TC_MAX_GROUPS 24
 #define TC_MAX_EPIS 16
 #define TC_TMEM_COLS 512
@@ -83,6 +80,7 @@ struct TcEpi {
     int8_t pad[2];
 };
 struct TcProgram {
+    int odd_col;                         // TMEM column of the accumulators of odd layers: 256, or 128 in the compact variant
     int layers;
     int dims[PF_MAX_MLP_LAYERS + 1];     // true widths
     int pdims[PF_MAX_MLP_LAYERS + 1];    // padded to a multiple of 16
@@ -94,7 +92,13 @@ struct TcProgram {
     TcEpi e[TC_MAX_EPIS];
 };
 
-struct TcState { TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3]; unsigned long long* trace; int rehearse; };   // [actor only, critic only, both]
+// [actor only, critic only, both].  The COMPACT variant (progc, stages_c ...) exists when both nets are small enough for
+// TWO CTAs per SM: every accumulator within 256 TMEM columns, <= 113 KB of shared memory, 4 + 4 worker warps.
+struct TcState {
+    TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3];
+    int compact; TcProgram progc[2]; int stages_c[3]; int smem_bytes_c[3];
+    unsigned long long* trace; int rehearse;
+};
 
 static inline int pad16(int x) { return (x + 15) & ~15; }
 
@@ -115,6 +119,7 @@ struct TcArgs {
     TcProgram prog[2];
     TcNetArgs net[2];
     int nnets, rows, tiles, stages, x0_bytes;
+    int tmem_cols;               // 512, or 256 in the compact variant (two CTAs per SM)
     // PPO.act tail (TC_OUT_SAMPLE / TC_OUT_VALUE)
     uint32_t seed, policy_step; int env_id_offset, num_actions;
     const float* std;
@@ -161,6 +166,7 @@ __device__ __forceinline__ float elu_fast(float x) {
 // shared store; consecutive lanes hold consecutive 8-column blocks, which is why the staged operand uses a PADDED
 // leading byte offset (TC_X0_LBO = 2048 + 16): with the natural 2048 every lane of the warp would hit the same
 // bank.  Out of line so that the loads in flight do not add to the epilogue's register pressure.
+template <int TC_STG_THREADS>
 __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid, TcTrace& tr, bool dry) {
     const int lane = tid & 31;
     const int k = w / a.tiles, tile = w - k * a.tiles;
@@ -276,7 +282,10 @@ __device__ __noinline__ void tc_sample_row(const TcArgs& a, long long er, const 
     if (a.has_storage) a.S.actions_log_prob[srow] = logp;
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
+template <int TC_EPI_WARPS, int TC_STG_WARPS, int kCtasPerSm>
+__global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCtasPerSm) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
+    constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32, TC_STG_THREADS = TC_STG_WARPS * 32;
+    constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_STG_WARPS, TC_LOAD_WARP = TC_MMA_WARP + 1;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] bf16
     unsigned char* ach = smem + a.x0_bytes;                    // 2 activation chunk buffers [128 x 128] bf16
@@ -297,7 +306,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == TC_MMA_WARP) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"((uint32_t)a.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else if (warp < TC_EPI_WARPS) {
         for (int i = tid; i < TC_ROWS * 2; i += TC_EPI_THREADS)             // ones operand: 2 column blocks x 128 rows x 16 B
@@ -443,13 +452,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
             if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(tid == TC_EPI_THREADS && blockIdx.x == 0, 0x52); }
             if (it) mbar_wait(pb0 + 8 * BAR_XFREE, (it - 1u) & 1u);
             tr.ev(0x500);
-            tc_stage_item(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr, dry);
+            tc_stage_item<TC_STG_THREADS>(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr, dry);
             tr.ev(0x502);
             ++it;
         }
     } else {
         // ================================================================ epilogues: 8 warps
-        const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
+        const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;          // (h == 0 for every warp when TC_EPI_WARPS == 4)
         uint32_t pbits = 0;
         TcTrace tr; tr.init(a.trace, 0, blockIdx.x == 0 && tid == 0);
         // ELU + bf16 pack of 32 accumulator columns [g, g + 32) of this thread's row into a chunk buffer
@@ -483,7 +492,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
                 if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, ((pbits >> E.free_bar) ^ (uint32_t)E.free_k) & 1u);
                 tc_fence_after();
                 tr.ev(0x700 + ei);
-                const int nt = E.nt, units = nt >> 4, u0 = (units + 1) >> 1;               // 16-column units over the 2 column halves
+                const int nt = E.nt, units = nt >> 4, u0 = TC_EPI_WARPS == 4 ? units : (units + 1) >> 1;   // 16-column units over the column halves
                 const int c_lo = h == 0 ? 0 : u0 * 16, c_hi = h == 0 ? u0 * 16 : nt;
                 const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + E.tmem_col;
                 if (E.dst >= 0) {
@@ -546,9 +555,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) pf_mlp_tc_kernel(const __grid_c
     pf_timeline(0x53);
     if (warp == TC_MMA_WARP) {
         __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)a.tmem_cols) : "memory");
     }
 }
+
+// the two instantiations: 8 + 8 worker warps, one CTA per SM, all of TMEM; and the compact one (4 + 4 warps, two CTAs per SM)
+static const auto pf_mlp_tc_kernel_std = pf_mlp_tc_kernel<8, 8, 1>;
+static const auto pf_mlp_tc_kernel_compact = pf_mlp_tc_kernel<4, 4, 2>;
 
 // ------------------------------------------------------------------------------------------------ packing
 // fp32 nn.Linear weight [out, in] + bias -> bf16 tiles in consumption order.  Tiles of a group, contiguous: the BIAS
@@ -593,13 +606,18 @@ static int pick_kt(int nt, int kc) {
 }
 
 // Builds the static schedule of one net (see the header comment).  Returns non-zero if the shape does not fit.
-static int build_program(TcProgram& P, const PfNet& n) {
+static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256) {
     memset(&P, 0, sizeof(P));
     const int L = n.layers;
     P.layers = L;
+    P.odd_col = odd_col;
     for (int i = 0; i <= L; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
     if (P.pdims[0] > 256) return 1;                                   // staged input rows: <= 64 KB
     for (int l = 1; l < L; ++l) if (P.pdims[l + 1] > 256) return 1;    // accumulators of layers >= 1 live whole in half of TMEM
+    if (odd_col == 128) {          // compact: layer 0 in ONE chunk at columns [0, 128), every other accumulator <= 128 wide
+        if (P.pdims[1] > TC_CHUNK) return 1;
+        for (int l = 1; l < L; ++l) if (P.pdims[l + 1] > 128) return 1;
+    }
     const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK;
     if (nch0 > 8 || (L == 1 && nch0 > 2)) return 1;
     P.x0_bytes = (((P.pdims[0] >> 3) * TC_X0_LBO) + 127) & ~127;
@@ -620,7 +638,7 @@ static int build_program(TcProgram& P, const PfNet& n) {
         P.e[P.nepis++] = e;
         return 0;
     };
-    auto region_col = [](int l) { return (l & 1) ? 256 : 0; };
+    auto region_col = [odd_col](int l) { return (l & 1) ? odd_col : 0; };
     auto region_bar = [](int l) { return (l & 1) ? BAR_ACC2 : BAR_ACC0; };
 
     // ---- layer 0: chunk c accumulates in TMEM slot c & 1 from the staged input ----
@@ -782,10 +800,11 @@ extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, in
     return 0;
 }
 
-static int smem_layout(int x0_bytes, int* stages, int* smem_bytes) {
+// budget_kb: 227 (one CTA per SM), or 113 for the compact variant (two CTAs per SM: 2 x (113 + 1 KB reserved) = 228 KB)
+static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 3) {
     const int fixed = x0_bytes + 2 * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
-    int S = (227 * 1024 - fixed) / TC_SLOT_BYTES;
-    if (S < 3) return 1;
+    int S = (budget_kb * 1024 - fixed) / TC_SLOT_BYTES;
+    if (S < min_stages) return 1;
     *stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
     *smem_bytes = fixed + *stages * TC_SLOT_BYTES;
     return 0;
@@ -807,12 +826,26 @@ int pf_tc_create(pf_rl_ctx* c) {
         if (smem_layout(t->x0_bytes[v], &t->stages[v], &t->smem_bytes[v])) { delete t; return tc_fail(6, "pf_rl_create: shared memory layout does not fit"); }
         max_smem = t->smem_bytes[v] > max_smem ? t->smem_bytes[v] : max_smem;
     }
+    // compact variant (two CTAs per SM): both nets' accumulators within 256 TMEM columns, shared memory within 113 KB.  Same
+    // groups, tiles and blob offsets as the standard programs (only the accumulator columns differ): the packed weights are shared.
+    t->compact = getenv("PF_TC_NO_COMPACT") == nullptr;
+    for (int k = 0; k < 2 && t->compact; ++k)
+        if (build_program(t->progc[k], c->net[k], 128) || check_program(t->progc[k]) || t->progc[k].blob_bytes != t->prog[k].blob_bytes ||
+            t->progc[k].ngroups != t->prog[k].ngroups)
+            t->compact = 0;
+    for (int v = 0; v < 3 && t->compact; ++v)
+        if (smem_layout(t->x0_bytes[v], &t->stages_c[v], &t->smem_bytes_c[v], 113, 2)) t->compact = 0;
+    if (t->compact) {
+        int mc = 0;
+        for (int v = 0; v < 3; ++v) mc = t->smem_bytes_c[v] > mc ? t->smem_bytes_c[v] : mc;
+        if (cudaFuncSetAttribute(pf_mlp_tc_kernel_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, mc) != cudaSuccess) { cudaGetLastError(); t->compact = 0; }
+    }
     for (int k = 0; k < 2; ++k) {
         if (cudaMalloc(&c->net[k].tc_weights, (size_t)t->prog[k].blob_bytes) != cudaSuccess) { delete t; return tc_fail(2, "pf_rl_create: cudaMalloc of the packed weights failed"); }
         cudaMemset(c->net[k].tc_weights, 0, (size_t)t->prog[k].blob_bytes);      // padding columns of the bias tiles stay zero
         c->net[k].tc_weight_bytes = (size_t)t->prog[k].blob_bytes;
     }
-    if (cudaFuncSetAttribute(pf_mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess) {
+    if (cudaFuncSetAttribute(pf_mlp_tc_kernel_std, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess) {
         delete t;
         return tc_fail(2, "pf_rl_create: cannot reserve shared memory for the tensor-core kernel");
     }
@@ -848,11 +881,27 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     { const char* e = getenv("PF_TC_DEBUG"); a.debug = e ? atoi(e) : 0; }
     const int items = a.nnets * a.tiles;
     if (items == 0) return 0;
-    const int grid = items < c->num_sms ? items : c->num_sms;
     // the dry item pays off only while a CTA has a single item (its whole latency is exposed) -- measured: -5 us at
     // 4,096 envs, +3 us at 16,384 (two items per CTA, a shorter wait to hide it in)
     a.rehearse = t->rehearse && items <= c->num_sms;
-    return pf_launch_pdl(pf_mlp_tc_kernel, dim3(grid), dim3(TC_THREADS), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
+    // An item is a serial chain of MMA -> epilogue hand-offs (~10k cycles for the flat nets, the tensor pipe busy for a few
+    // percent of them): once a CTA would walk several items, two CTAs per SM (the compact variant) overlap two chains.
+    // With at most one item per SM the 8 + 8 warp variant has the shorter single-item latency.
+    static const int force = [] { const char* e = getenv("PF_TC_COMPACT"); return e ? atoi(e) : -1; }();    // experiments: 0 never, 1 always
+    const bool compact = t->compact && (force < 0 ? items > c->num_sms : force != 0);
+    if (compact) {
+        for (int i = 0; i < a.nnets; ++i)
+            for (int k = 0; k < 2; ++k)
+                if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progc[k];
+        a.stages = t->stages_c[variant];
+        a.tmem_cols = 256;
+        const int grid = items < 2 * c->num_sms ? items : 2 * c->num_sms;
+        return pf_launch_pdl(pf_mlp_tc_kernel_compact, dim3(grid), dim3(TC_THREADS_OF(4, 4)), (size_t)t->smem_bytes_c[variant], st, a) == cudaSuccess
+                   ? 0 : tc_fail(2, "pf_mlp_tc_kernel (compact): launch failed");
+    }
+    a.tmem_cols = TC_TMEM_COLS;
+    const int grid = items < c->num_sms ? items : c->num_sms;
+    return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
                ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }
 
