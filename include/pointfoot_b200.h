@@ -368,6 +368,31 @@ int pf_rl_minibatch_grad(pf_rl_ctx* ctx, const pf_rl_storage* storage, const pf_
  * the packed bf16 parameter copies. */
 int pf_rl_adam_step(pf_rl_ctx* ctx, const pf_rl_learner* learner, void* stream);
 
+/* ================================================================================================
+ * Actuator-network torques: legged_gym/envs/anymal_c/anymal.py:62-78, the only other
+ * _compute_torques of the reference (cfg.control.use_actuator_network, anymal_c_rough_config.py:68-69).
+ * ============================================================================================== */
+#define PF_ACTUATOR_MAX_DOF 12
+#define PF_ACTUATOR_NET_WEIGHTS 969     /* floats: the module's state_dict without in_scale / out_scale, in its order:
+                                            lstm.weight_ih_l0[32,2] weight_hh_l0[32,8] bias_ih_l0[32] bias_hh_l0[32]
+                                            weight_ih_l1[32,8] weight_hh_l1[32,8] bias_ih_l1[32] bias_hh_l1[32]
+                                            linear.weight[1,8] linear.bias[1] */
+typedef struct pf_actuator_net_params {
+    int32_t num_envs, num_dof;
+    float action_scale;                          /* cfg.control.action_scale (anymal.py:66) */
+    float in_scale[2], out_scale;                /* the module's buffers (anydrive_v3_lstm.pt: (2.0, 0.25), 20.0) */
+    float default_dof_pos[PF_ACTUATOR_MAX_DOF];
+} pf_actuator_net_params;
+/* anymal.py:62-72: torques[N,A] = out_scale * Linear(LSTM((action * action_scale + default - q, qd) * in_scale, (h, c))),
+ * h / c [2, N*A, 8] updated in place (anymal.py:48-49 sea_hidden_state / sea_cell_state).  weights: DEVICE float[969].
+ * Context-free: allocates nothing, retains nothing. */
+int pf_actuator_net_torques(const pf_actuator_net_params* params, const float* weights, const float* actions,
+                            const float* dof_state, float* hidden, float* cell, float* torques, void* stream);
+/* anymal.py:52-56 (reset_idx): zero the recurrent state of the envs in reset_ids[0 .. *reset_count) (both DEVICE, as
+ * pf_post_physics_step leaves them: no host sync). */
+int pf_actuator_net_reset(int32_t num_envs, int32_t num_dof, const int32_t* reset_ids, const int32_t* reset_count,
+                          float* hidden, float* cell, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -320,3 +320,31 @@ def build_reference_env(task, state, seed=1, mutate_cfg=None, env_id_offset=0, d
             env.episode_sums[name][:] = state["episode_sums"][i]
     env.common_step_counter = int(state.get("common_step_counter", 0))
     return env
+
+
+# --------------------------------------------------------------------------------------------
+def build_reference_anymal_torques(num_envs, device="cpu"):
+    """The UNMODIFIED ``Anymal._compute_torques`` (legged_gym/envs/anymal_c/anymal.py:62-78) with the reference's own
+    actuator network (resources/actuator_nets/anydrive_v3_lstm.pt), on an ``Anymal`` built with ``object.__new__``: only the
+    attributes that method and ``Anymal._init_buffers``' own lines (anymal.py:43-50) touch are set.  Needs the reference
+    SOURCE tree (the .pt file is a resource, not part of the installed package)."""
+    install_stubs()
+    from types import SimpleNamespace
+    from legged_gym.envs.anymal_c.anymal import Anymal
+    from legged_gym.envs.anymal_c.mixed_terrains.anymal_c_rough_config import AnymalCRoughCfg
+    cfg = AnymalCRoughCfg()
+    root = "/root/reference"
+    env = object.__new__(Anymal)
+    env.cfg, env.device, env.num_envs, env.num_actions = cfg, device, num_envs, 12
+    env.actuator_network = torch.jit.load(cfg.control.actuator_net_file.format(LEGGED_GYM_ROOT_DIR=root)).to(device)
+    env.default_dof_pos = torch.tensor([list(cfg.init_state.default_joint_angles.values())], dtype=torch.float, device=device)
+    env.dof_state = torch.zeros(num_envs * 12, 2, device=device)
+    env.dof_pos = env.dof_state.view(num_envs, 12, 2)[..., 0]
+    env.dof_vel = env.dof_state.view(num_envs, 12, 2)[..., 1]
+    # anymal.py:43-50, verbatim attribute set-up (super()._init_buffers() needs PhysX)
+    env.sea_input = torch.zeros(num_envs * 12, 1, 2, device=device, requires_grad=False)
+    env.sea_hidden_state = torch.zeros(2, num_envs * 12, 8, device=device, requires_grad=False)
+    env.sea_cell_state = torch.zeros(2, num_envs * 12, 8, device=device, requires_grad=False)
+    env.sea_hidden_state_per_env = env.sea_hidden_state.view(2, num_envs, 12, 8)
+    env.sea_cell_state_per_env = env.sea_cell_state.view(2, num_envs, 12, 8)
+    return env

@@ -164,3 +164,12 @@ def load_rl():
     lib.pf_rl_param_offset.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     lib._pf_rl_ready = True
     return lib
+
+
+# ------------------------------------------------------------------------------------------------ actuator network
+ACTUATOR_MAX_DOF, ACTUATOR_NET_WEIGHTS = 12, 969
+
+
+class PfActuatorNetParams(C.Structure):
+    _fields_ = [("num_envs", _i), ("num_dof", _i), ("action_scale", _f), ("in_scale", _f * 2), ("out_scale", _f),
+                ("default_dof_pos", _f * ACTUATOR_MAX_DOF)]

@@ -73,6 +73,39 @@ def generate(fname, task, mutate=None, start_step=0, seed=1):
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+ACTUATOR_FILE = "anymal_actuator_n64.npz"
+
+
+def generate_actuator(steps=6, seed=3):
+    """Anymal._compute_torques with the actuator network (anymal.py:62-78) over ``steps`` chained sub-steps, the recurrent
+    state of a few envs zeroed before step 3 as Anymal.reset_idx does (anymal.py:52-56)."""
+    env = ref_harness.build_reference_anymal_torques(N)
+    net = env.actuator_network
+    sd = net.state_dict()
+    keys = [k for k in sd if k not in ("in_scale", "out_scale")]
+    out = {"weights": torch.cat([sd[k].flatten() for k in keys]).numpy().copy(), "weight_keys": np.array(keys),
+           "in_scale": sd["in_scale"].flatten().numpy().copy(), "out_scale": sd["out_scale"].flatten().numpy().copy(),
+           "action_scale": np.float32(env.cfg.control.action_scale), "default_dof_pos": env.default_dof_pos.flatten().numpy().copy(),
+           "reset_ids": np.array([0, 5, 17, 63], np.int32), "reset_before_step": np.int64(3)}
+    g = torch.Generator().manual_seed(seed)
+    for i in range(steps):
+        if i == 3:
+            ids = torch.from_numpy(out["reset_ids"]).long()
+            env.sea_hidden_state_per_env[:, ids] = 0.          # anymal.py:55-56
+            env.sea_cell_state_per_env[:, ids] = 0.
+        actions = torch.randn(N, 12, generator=g) * (3.0 if i == 4 else 1.0)
+        env.dof_state[:, 0] = torch.randn(N * 12, generator=g) * 0.5
+        env.dof_state[:, 1] = torch.randn(N * 12, generator=g) * 4.0
+        t = env._compute_torques(actions)
+        p = f"s{i}_"
+        out[p + "actions"], out[p + "dof_state"] = actions.numpy().copy(), env.dof_state.numpy().copy()
+        out[p + "torques"] = t.numpy().copy().reshape(N, 12)
+        out[p + "hidden"], out[p + "cell"] = env.sea_hidden_state.numpy().copy(), env.sea_cell_state.numpy().copy()
+    path = os.path.join(HERE, ACTUATOR_FILE)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if not ref_harness.reference_available():
         raise SystemExit("reference not available here; golden files can only be regenerated in the build container")
@@ -82,3 +115,5 @@ if __name__ == "__main__":
         if only and fname not in only:
             continue
         generate(fname, task, mutate, start_step)
+    if not only or ACTUATOR_FILE in only:
+        generate_actuator()
