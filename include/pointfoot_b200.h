@@ -393,6 +393,92 @@ int pf_actuator_net_torques(const pf_actuator_net_params* params, const float* w
 int pf_actuator_net_reset(int32_t num_envs, int32_t num_dof, const int32_t* reset_ids, const int32_t* reset_count,
                           float* hidden, float* cell, void* stream);
 
+/* ================================================================================================
+ * LeggedRobot base class: legged_gym/envs/base/legged_robot.py (LR), the env of the a1 /
+ * anymal / cassie tasks.  Differences from PointFoot that matter on the step path: observations lead with base_lin_vel and
+ * put the commands in front of the joints (48 columns + the height scan in ONE buffer, LR:209-226); commands are really
+ * resampled (LR:337-351, from the callback and again in reset_idx); the push overwrites the root xy velocity (LR:414-419); no
+ * feet state machine in the step -- feet_air_time / last_contacts are updated inside _reward_feet_air_time (LR:882-893);
+ * _reward_stand_still is the joint-pose variant (LR:900-902); reset_idx zeroes fewer buffers (LR:168-173).
+ * Context-free entry points: parameters and buffers are passed on every call, nothing is allocated or retained.
+ * ============================================================================================== */
+#define PF_LR_MAX_DOF 12
+#define PF_LR_MAX_BODIES 24
+#define PF_LR_MAX_FEET 4
+
+typedef struct pf_lr_params {
+    int32_t abi_version, num_envs;
+    int64_t env_id_offset;
+    int32_t num_dof, num_bodies, num_feet, num_commands, num_obs;
+    uint32_t seed;
+    int32_t control_type, decimation;                                 /* LR:353-375 */
+    float action_scale, sim_dt, dt, clip_actions, clip_obs;
+    float p_gains[PF_LR_MAX_DOF], d_gains[PF_LR_MAX_DOF], torque_limits[PF_LR_MAX_DOF], default_dof_pos[PF_LR_MAX_DOF];
+    float dof_pos_limits[PF_LR_MAX_DOF][2], dof_vel_limits[PF_LR_MAX_DOF];   /* soft limits, LR:291-305 */
+    int32_t feet_indices[PF_LR_MAX_FEET];
+    int32_t num_termination, termination_indices[PF_LR_MAX_BODIES];
+    int32_t num_penalised, penalised_indices[PF_LR_MAX_BODIES];
+    float max_episode_length, max_episode_length_s;                  /* LR:735-736 */
+    int32_t resample_period, heading_command;                         /* LR:325-330 */
+    float cmd_range[4][2];                                            /* command_ranges: lin_vel_x, lin_vel_y, ang_vel_yaw, heading */
+    float obs_scale_lin_vel, obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel, obs_scale_height;
+    float commands_scale[3];
+    int32_t add_noise, measure_heights;
+    int32_t terrain_kind, index_div_mode, hf_rows, hf_cols;
+    float border_size, horizontal_scale, vertical_scale;
+    int32_t num_height_points;
+    int32_t custom_origins, terrain_curriculum, max_terrain_level, num_terrain_types;
+    float terrain_env_length;
+    float base_init_state[13];
+    int32_t send_timeouts;
+    int32_t num_reward_terms, reward_ids[PF_MAX_REWARD_TERMS];       /* enum pf_reward_id, in summation (dir()) order */
+    float reward_scales[PF_MAX_REWARD_TERMS];                        /* already * dt (LR:553) */
+    int32_t has_termination_term; float termination_scale;
+    int32_t only_positive_rewards;
+    float base_height_target, soft_dof_vel_limit, soft_torque_limit, tracking_sigma, max_contact_force;
+    float max_push_vel_xy;                                            /* LR:417 */
+} pf_lr_params;
+
+/* Device pointers; N = num_envs, D = num_dof, B = num_bodies, F = num_feet, P = num_height_points, R = reward rows. */
+typedef struct pf_lr_buffers {
+    float* root_states;               /* [N,13]  PhysX-owned: reset rows and the push are written in place */
+    float* dof_state;                 /* [N*D,2] */
+    const float* contact_forces;      /* [N*B,3] */
+    float* actions; float* torques;   /* [N,D] */
+    float* commands;                  /* [N,4] */
+    int64_t* episode_length_buf;      /* [N] */
+    float* base_lin_vel; float* base_ang_vel; float* projected_gravity;   /* [N,3] */
+    float* last_actions; float* last_dof_vel;                             /* [N,D] */
+    float* last_root_vel;             /* [N,6] */
+    float* feet_air_time;             /* [N,F] */
+    uint8_t* last_contacts;           /* [N,F] torch.bool */
+    float* episode_sums;              /* [R,N], termination last */
+    float* rew_buf;                   /* [N] */
+    uint8_t* reset_buf; uint8_t* time_out_buf;                            /* [N] torch.bool */
+    float* obs_buf;                   /* [N,num_obs] */
+    float* measured_heights;          /* [N,P]; required when measure_heights (LR:331-332 keeps it as an attribute) */
+    const int16_t* height_samples; const float* terrain_origins;
+    int64_t* terrain_levels; const int64_t* terrain_types;
+    float* env_origins;               /* [N,3] */
+    int32_t* reset_ids; int32_t* reset_count;                             /* ascending ids (LR:128), device count */
+    float* episode_stats;             /* [R+2]: term means / max_episode_length_s, terrain level mean, reset count (LR:175-184) */
+    uint8_t* extras_time_outs;        /* [N] or NULL (LR:186-187) */
+    const float* noise_scale_vec;     /* [num_obs] DEVICE: _get_noise_scale_vec, LR:455-478 */
+    const float* height_points_xy;    /* [P][2] DEVICE: _init_height_points, LR:761-775 */
+} pf_lr_buffers;
+
+int pf_lr_sizeof_params(void);
+int pf_lr_sizeof_buffers(void);
+/* LR:86-87 (action clip, when actions_in != NULL) + LR:353-375 _compute_torques */
+int pf_lr_pd_torques(const pf_lr_params* params, const pf_lr_buffers* bufs, const float* actions_in, void* stream);
+/* LR:105-136 post_physics_step between the gym refresh calls and the return of step(), + the obs clip of LR:99-102.
+ * `push` != 0: this is a step on which _push_robots fires (LR:333: common_step_counter % push_interval == 0; the host decides). */
+int pf_lr_post_physics_step(const pf_lr_params* params, const pf_lr_buffers* bufs, int64_t common_step_counter,
+                            int32_t push, void* stream);
+/* base_task.py:105-109 reset(): reset_idx over every env (LR:145-188; time_out_buf is read as it stands for
+ * extras["time_outs"]).  The zero-action step that follows is the caller's. */
+int pf_lr_reset_all(const pf_lr_params* params, const pf_lr_buffers* bufs, int64_t common_step_counter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -229,7 +229,7 @@ class RefEnv:
             self.commands[ids, 0] = (r[0][1] - r[0][0]) * u[:, 0] + r[0][0]
             self.commands[ids, 1] = (r[1][1] - r[1][0]) * u[:, 1] + r[1][0]
             if P.heading_command:
-                self.commands[ids, 3] = (r[3][1] - r[3][0]) * u[:, 3] + r[3][0]
+                self.commands[ids, 3] = (r[3][1] - r[3][0]) * u[:, 2] + r[3][0]     # third draw of LR:346-349 (heading OR yaw): lane 2
             else:
                 self.commands[ids, 2] = (r[2][1] - r[2][0]) * u[:, 2] + r[2][0]
             self.commands[ids, :2] *= (torch.norm(self.commands[ids, :2], dim=1) > 0.2).unsqueeze(1)

@@ -348,3 +348,154 @@ def build_reference_anymal_torques(num_envs, device="cpu"):
     env.sea_hidden_state_per_env = env.sea_hidden_state.view(2, num_envs, 12, 8)
     env.sea_cell_state_per_env = env.sea_cell_state.view(2, num_envs, 12, 8)
     return env
+
+
+# --------------------------------------------------------------------------------------------
+# LeggedRobot base class with the a1 asset: constants PhysX would have reported for
+# resources/robots/a1/urdf/a1.urdf after fixed-joint collapse (feet kept by dont_collapse, a1.urdf:187,309,431,553).
+A1_DOF_NAMES = [f"{leg}_{j}_joint" for leg in ("FR", "FL", "RR", "RL") for j in ("hip", "thigh", "calf")]
+A1_BODY_NAMES = ["base"] + [f"{leg}_{b}" for leg in ("FR", "FL", "RR", "RL") for b in ("hip", "thigh", "calf", "foot")]
+A1_DOF_LOWER = [-0.802851455917, -1.0471975512, -2.69653369433] * 4
+A1_DOF_UPPER = [0.802851455917, 4.18879020479, -0.916297857297] * 4
+A1_DOF_VELOCITY = [52.4, 28.6, 28.6] * 4
+A1_DOF_EFFORT = [20.0, 55.0, 55.0] * 4
+
+
+def _make_lr_class():
+    """Subclass of the reference LeggedRobot whose only additions route RNG draws to the contract (oracle.rng).
+    ``_resample_commands`` is called from the callback (LR:326) and from reset_idx (LR:166) on the same step: two purposes."""
+    install_stubs()
+    from legged_gym.envs.base.legged_robot import LeggedRobot
+
+    class RefLeggedRobot(LeggedRobot):
+        rng_seed = 1
+        env_id_offset = 0
+        _in_reset = False
+
+        def _ctx(self, purpose, env_ids, lane0=0):
+            ids = env_ids.cpu().numpy() if torch.is_tensor(env_ids) else np.asarray(env_ids)
+            return rng.draw(rng.DrawContext(self.rng_seed, int(self.common_step_counter), purpose, ids, self.env_id_offset, lane0))
+
+        def compute_observations(self):
+            def rand_like(t):
+                return rng.active_uniform(t.shape, t.device)
+            with self._ctx(rng.OBS_NOISE, np.arange(self.num_envs)), _patched(torch, "rand_like", rand_like):
+                super().compute_observations()
+
+        def reset_idx(self, env_ids):
+            self._in_reset = True
+            try:
+                super().reset_idx(env_ids)
+            finally:
+                self._in_reset = False
+
+        def _resample_commands(self, env_ids):
+            if len(env_ids) == 0:            # (torch_rand_float of an empty shape draws nothing)
+                return super()._resample_commands(env_ids)
+            with self._ctx(rng.RESAMPLE_RESET if self._in_reset else rng.RESAMPLE_CMD, env_ids):
+                super()._resample_commands(env_ids)
+
+        def _reset_dofs(self, env_ids):
+            with self._ctx(rng.RESET_DOF, env_ids):
+                super()._reset_dofs(env_ids)
+
+        def _reset_root_states(self, env_ids):
+            with self._ctx(rng.RESET_ROOT, env_ids, 0 if self.custom_origins else 2):
+                super()._reset_root_states(env_ids)
+
+        def _push_robots(self):
+            with self._ctx(rng.PUSH, np.arange(self.num_envs)):
+                super()._push_robots()
+
+        def _update_terrain_curriculum(self, env_ids):
+            def randint_like(t, high):
+                return rng.active_randint(t.shape, high, t.device).to(t.dtype)
+            with self._ctx(rng.CURRICULUM, env_ids), _patched(torch, "randint_like", randint_like):
+                super()._update_terrain_curriculum(env_ids)
+
+    return RefLeggedRobot
+
+
+def make_a1_cfg(num_envs, mutate=None):
+    install_stubs()
+    from legged_gym.envs.a1.a1_config import A1RoughCfg
+    cfg = A1RoughCfg()
+    cfg.env.num_envs = num_envs
+    if mutate is not None:
+        mutate(cfg)
+    return cfg
+
+
+def build_reference_legged_robot(state, seed=1, mutate_cfg=None, env_id_offset=0):
+    """The UNMODIFIED ``LeggedRobot`` (legged_gym/envs/base/legged_robot.py) with the a1 config over the synthetic tensors
+    of ``state`` (pointfoot_b200.synth.make_lr_state): built with ``object.__new__``, what BaseTask.__init__ / create_sim /
+    _create_envs would have set from PhysX is set from the URDF constants, then the reference's own ``_parse_cfg``,
+    ``_process_dof_props``, ``_get_env_origins``, ``_init_buffers`` and ``_prepare_reward_function`` run."""
+    cls = _make_lr_class()
+    from types import SimpleNamespace
+    N = int(state["root_states"].shape[0])
+    cfg = make_a1_cfg(N, mutate_cfg)
+    env = object.__new__(cls)
+    env.rng_seed, env.env_id_offset = seed, env_id_offset
+    # ---- LeggedRobot.__init__ (LR:65-70) + BaseTask.__init__ (base_task.py:40-85) ----
+    env.cfg = cfg
+    env.sim_params = SimpleNamespace(dt=cfg.sim.dt, use_gpu_pipeline=False)
+    env.height_samples = None
+    env.debug_viz = False
+    env.init_done = False
+    env._parse_cfg(cfg)
+    env.gym = FakeGym(state)
+    env.sim = env.physics_engine = None
+    env.sim_device = env.device = "cpu"
+    env.headless, env.viewer, env.enable_viewer_sync = True, None, True
+    env.num_envs, env.num_obs = N, cfg.env.num_observations
+    env.num_privileged_obs, env.num_actions = cfg.env.num_privileged_obs, cfg.env.num_actions
+    env.obs_buf = torch.zeros(N, env.num_obs)
+    env.rew_buf = torch.zeros(N)
+    env.reset_buf = torch.ones(N, dtype=torch.long)
+    env.episode_length_buf = torch.zeros(N, dtype=torch.long)
+    env.time_out_buf = torch.zeros(N, dtype=torch.bool)
+    env.privileged_obs_buf = None
+    env.extras = {}
+    # ---- create_sim / _create_envs (LR:228-244, 614-699) ----
+    env.up_axis_idx = 2
+    env.num_dof = env.num_dofs = 12
+    env.num_bodies = len(A1_BODY_NAMES)
+    env.dof_names = list(A1_DOF_NAMES)
+    props = np.zeros(12, dtype=[("lower", "f4"), ("upper", "f4"), ("velocity", "f4"), ("effort", "f4")])
+    props["lower"], props["upper"], props["velocity"], props["effort"] = A1_DOF_LOWER, A1_DOF_UPPER, A1_DOF_VELOCITY, A1_DOF_EFFORT
+    env._process_dof_props(props, 0)                         # reference code: soft limits, LR:279-305
+
+    def idx(names):
+        out = []
+        for n in names:
+            out.extend(i for i, s in enumerate(A1_BODY_NAMES) if n in s)
+        return torch.tensor(out, dtype=torch.long)
+    env.feet_indices = idx([cfg.asset.foot_name])
+    env.penalised_contact_indices = idx(cfg.asset.penalize_contacts_on)
+    env.termination_contact_indices = idx(cfg.asset.terminate_after_contacts_on)
+    isl = cfg.init_state
+    env.base_init_state = _tu.to_torch(isl.pos + isl.rot + isl.lin_vel + isl.ang_vel)
+    if cfg.terrain.mesh_type in ("heightfield", "trimesh"):
+        env.terrain = SimpleNamespace(cfg=cfg.terrain, env_length=cfg.terrain.terrain_length,
+                                      env_origins=state["terrain_origins"].cpu().numpy())
+        env.height_samples = state["height_samples"]
+    env._get_env_origins()                                   # reference code, LR:701-726 (its torch.randint levels are overwritten)
+    if env.custom_origins:
+        env.terrain_levels = state["terrain_levels"].clone()
+        env.terrain_types = state["terrain_types"].clone()
+        env.env_origins[:] = env.terrain_origins[env.terrain_levels, env.terrain_types]
+    env.envs, env.actor_handles = [None] * N, [None] * N
+    env._init_buffers()
+    env._prepare_reward_function()
+    env.init_done = True
+    # ---- internal state the synthetic generator randomises ----
+    env.commands[:] = state["commands"]
+    env.episode_length_buf[:] = state["episode_length_buf"]
+    for k in ("last_actions", "last_dof_vel", "feet_air_time", "last_contacts"):
+        getattr(env, k)[:] = state[k]
+    keys = [k for k in env.episode_sums if k != "termination"] + (["termination"] if "termination" in env.episode_sums else [])
+    for i, name in enumerate(keys):
+        env.episode_sums[name][:] = state["episode_sums"][i]
+    env.common_step_counter = int(state.get("common_step_counter", 0))
+    return env

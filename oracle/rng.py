@@ -19,7 +19,8 @@ RESET_DOF = 1       # point_foot.py:557, lanes 0..D-1
 RESET_ROOT = 2      # point_foot.py:577 xy offset = lanes 0..1 (custom origins only); :583 velocities = lanes 2..7
 CURRICULUM = 3      # point_foot.py:632 randint_like, lane 0
 PUSH = 4            # point_foot.py:598, lanes 0..2
-RESAMPLE_CMD = 5    # legged_robot.py:337-351, lanes 0..3
+RESAMPLE_CMD = 5    # legged_robot.py:337-351 called from the callback (LR:326): lanes 0, 1, and 2 = the third draw (heading OR yaw)
+RESAMPLE_RESET = 8  # the same method called from reset_idx (LR:166) on the same step: its own purpose, same lanes
 POLICY = 6          # rsl_rl ActorCritic.act: Normal.sample, lanes 0..A-1 (two u32 per lane)
 
 _M = np.uint64(0xFFFFFFFF)

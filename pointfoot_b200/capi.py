@@ -173,3 +173,67 @@ ACTUATOR_MAX_DOF, ACTUATOR_NET_WEIGHTS = 12, 969
 class PfActuatorNetParams(C.Structure):
     _fields_ = [("num_envs", _i), ("num_dof", _i), ("action_scale", _f), ("in_scale", _f * 2), ("out_scale", _f),
                 ("default_dof_pos", _f * ACTUATOR_MAX_DOF)]
+
+
+# ------------------------------------------------------------------------------------------------ LeggedRobot (N2)
+LR_MAX_DOF, LR_MAX_BODIES, LR_MAX_FEET = 12, 24, 4
+
+
+class PfLrParams(C.Structure):
+    _fields_ = [
+        ("abi_version", _i), ("num_envs", _i), ("env_id_offset", C.c_int64),
+        ("num_dof", _i), ("num_bodies", _i), ("num_feet", _i), ("num_commands", _i), ("num_obs", _i),
+        ("seed", _u),
+        ("control_type", _i), ("decimation", _i),
+        ("action_scale", _f), ("sim_dt", _f), ("dt", _f), ("clip_actions", _f), ("clip_obs", _f),
+        ("p_gains", _f * LR_MAX_DOF), ("d_gains", _f * LR_MAX_DOF), ("torque_limits", _f * LR_MAX_DOF),
+        ("default_dof_pos", _f * LR_MAX_DOF),
+        ("dof_pos_limits", (_f * 2) * LR_MAX_DOF), ("dof_vel_limits", _f * LR_MAX_DOF),
+        ("feet_indices", _i * LR_MAX_FEET),
+        ("num_termination", _i), ("termination_indices", _i * LR_MAX_BODIES),
+        ("num_penalised", _i), ("penalised_indices", _i * LR_MAX_BODIES),
+        ("max_episode_length", _f), ("max_episode_length_s", _f),
+        ("resample_period", _i), ("heading_command", _i),
+        ("cmd_range", (_f * 2) * 4),
+        ("obs_scale_lin_vel", _f), ("obs_scale_ang_vel", _f), ("obs_scale_dof_pos", _f), ("obs_scale_dof_vel", _f),
+        ("obs_scale_height", _f),
+        ("commands_scale", _f * 3),
+        ("add_noise", _i), ("measure_heights", _i),
+        ("terrain_kind", _i), ("index_div_mode", _i), ("hf_rows", _i), ("hf_cols", _i),
+        ("border_size", _f), ("horizontal_scale", _f), ("vertical_scale", _f),
+        ("num_height_points", _i),
+        ("custom_origins", _i), ("terrain_curriculum", _i), ("max_terrain_level", _i), ("num_terrain_types", _i),
+        ("terrain_env_length", _f), ("base_init_state", _f * 13), ("send_timeouts", _i),
+        ("num_reward_terms", _i), ("reward_ids", _i * MAX_REWARD_TERMS), ("reward_scales", _f * MAX_REWARD_TERMS),
+        ("has_termination_term", _i), ("termination_scale", _f),
+        ("only_positive_rewards", _i),
+        ("base_height_target", _f), ("soft_dof_vel_limit", _f), ("soft_torque_limit", _f),
+        ("tracking_sigma", _f), ("max_contact_force", _f),
+        ("max_push_vel_xy", _f),
+    ]
+
+
+LR_BUFFER_FIELDS = (
+    "root_states", "dof_state", "contact_forces", "actions", "torques", "commands", "episode_length_buf",
+    "base_lin_vel", "base_ang_vel", "projected_gravity", "last_actions", "last_dof_vel", "last_root_vel",
+    "feet_air_time", "last_contacts", "episode_sums", "rew_buf", "reset_buf", "time_out_buf", "obs_buf",
+    "measured_heights", "height_samples", "terrain_origins", "terrain_levels", "terrain_types", "env_origins",
+    "reset_ids", "reset_count", "episode_stats", "extras_time_outs", "noise_scale_vec", "height_points_xy",
+)
+
+
+class PfLrBuffers(C.Structure):
+    _fields_ = [(name, _P) for name in LR_BUFFER_FIELDS]
+
+
+def load_lr():
+    """The same library with the LeggedRobot struct layouts checked."""
+    lib = load()
+    if getattr(lib, "_pf_lr_ready", False):
+        return lib
+    if lib.pf_lr_sizeof_params() != C.sizeof(PfLrParams) or lib.pf_lr_sizeof_buffers() != C.sizeof(PfLrBuffers):
+        raise RuntimeError("pointfoot_b200: pf_lr_params / pf_lr_buffers layout mismatch between capi.py and the header")
+    lib.pf_lr_post_physics_step.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
+    lib.pf_lr_pd_torques.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib._pf_lr_ready = True
+    return lib

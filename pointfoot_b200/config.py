@@ -309,3 +309,159 @@ class PointFootFlatCfgPPO(PointFootRoughCfgPPO):
     class runner(PointFootRoughCfgPPO.runner):
         experiment_name = 'pointfoot_flat'
         max_iterations = 30000
+
+
+# ------------------------------------------------------------------------------------------------ LeggedRobot / a1
+# the base-class task family (legged_gym/envs/base/legged_robot_config.py:33-214) and its a1
+# instance (legged_gym/envs/a1/a1_config.py:33-86).  Only what the step path and the runner read is carried over; the
+# PhysX / viewer / asset-loading knobs stay with whoever owns the simulator.
+class LeggedRobotCfg(BaseConfig):
+    class env:
+        num_envs = 4096
+        num_observations = 235              # 48 + 17 x 11 height points (LR:209-224)
+        num_privileged_obs = None
+        num_actions = 12
+        env_spacing = 3.
+        send_timeouts = True
+        episode_length_s = 20
+
+    class terrain(PointFootRoughCfg.terrain):
+        static_friction = 1.0
+        dynamic_friction = 1.0
+        restitution = 0.
+        measure_heights = True
+        measured_points_x = [round(0.1 * i, 1) for i in range(-8, 9)]
+        measured_points_y = [round(0.1 * i, 1) for i in range(-5, 6)]
+
+    class commands(PointFootRoughCfg.commands):
+        class ranges:
+            lin_vel_x = [-1.0, 1.0]
+            lin_vel_y = [-1.0, 1.0]
+            ang_vel_yaw = [-1, 1]
+            heading = [-3.14, 3.14]
+
+    class init_state:
+        pos = [0.0, 0.0, 1.]
+        rot = [0.0, 0.0, 0.0, 1.0]
+        lin_vel = [0.0, 0.0, 0.0]
+        ang_vel = [0.0, 0.0, 0.0]
+        default_joint_angles = {"joint_a": 0., "joint_b": 0.}
+
+    class control:
+        control_type = 'P'
+        stiffness = {'joint_a': 10.0, 'joint_b': 15.}
+        damping = {'joint_a': 1.0, 'joint_b': 1.5}
+        action_scale = 0.5
+        decimation = 4
+
+    class asset:
+        file = ""
+        name = "legged_robot"
+        foot_name = "None"
+        penalize_contacts_on = []
+        terminate_after_contacts_on = []
+
+    class domain_rand:
+        randomize_friction = True
+        friction_range = [0.5, 1.25]
+        randomize_base_mass = False
+        added_mass_range = [-1., 1.]
+        push_robots = True
+        push_interval_s = 15
+        max_push_vel_xy = 1.
+
+    class rewards:
+        class scales:
+            termination = -0.0
+            tracking_lin_vel = 1.0
+            tracking_ang_vel = 0.5
+            lin_vel_z = -2.0
+            ang_vel_xy = -0.05
+            orientation = -0.
+            torques = -0.00001
+            dof_vel = -0.
+            dof_acc = -2.5e-7
+            base_height = -0.
+            feet_air_time = 1.0
+            collision = -1.
+            feet_stumble = -0.0
+            action_rate = -0.01
+            stand_still = -0.
+
+        only_positive_rewards = True
+        tracking_sigma = 0.25
+        soft_dof_pos_limit = 1.
+        soft_dof_vel_limit = 1.
+        soft_torque_limit = 1.
+        base_height_target = 1.
+        max_contact_force = 100.
+
+    class normalization:
+        class obs_scales:
+            lin_vel = 2.0
+            ang_vel = 0.25
+            dof_pos = 1.0
+            dof_vel = 0.05
+            height_measurements = 5.0
+
+        clip_observations = 100.
+        clip_actions = 100.
+
+    class noise:
+        add_noise = True
+        noise_level = 1.0
+
+        class noise_scales:
+            dof_pos = 0.01
+            dof_vel = 1.5
+            lin_vel = 0.1
+            ang_vel = 0.2
+            gravity = 0.05
+            height_measurements = 0.1
+
+    class sim:
+        dt = 0.005
+        substeps = 1
+        gravity = [0., 0., -9.81]
+        up_axis = 1
+
+
+class LeggedRobotCfgPPO(PointFootRoughCfgPPO):
+    class runner(PointFootRoughCfgPPO.runner):
+        max_iterations = 1500
+        experiment_name = 'test'
+        run_name = ''
+
+
+class A1RoughCfg(LeggedRobotCfg):
+    class init_state(LeggedRobotCfg.init_state):
+        pos = [0.0, 0.0, 0.42]
+        default_joint_angles = {f"{leg}_{j}_joint": a
+                                for j, front, rear in (("hip", 0.1, 0.1), ("thigh", 0.8, 1.0), ("calf", -1.5, -1.5))
+                                for leg, a in (("FL", front), ("RL", rear), ("FR", -front if j == "hip" else front),
+                                               ("RR", -rear if j == "hip" else rear))}
+
+    class control(LeggedRobotCfg.control):
+        stiffness = {'joint': 20.}
+        damping = {'joint': 0.5}
+        action_scale = 0.25
+
+    class asset(LeggedRobotCfg.asset):
+        file = '{LEGGED_GYM_ROOT_DIR}/resources/robots/a1/urdf/a1.urdf'
+        name = "a1"
+        foot_name = "foot"
+        penalize_contacts_on = ["thigh", "calf"]
+        terminate_after_contacts_on = ["base"]
+
+    class rewards(LeggedRobotCfg.rewards):
+        soft_dof_pos_limit = 0.9
+        base_height_target = 0.25
+
+        class scales(LeggedRobotCfg.rewards.scales):
+            torques = -0.0002
+            dof_pos_limits = -10.0
+
+
+class A1RoughCfgPPO(LeggedRobotCfgPPO):
+    class runner(LeggedRobotCfgPPO.runner):
+        experiment_name = 'rough_a1'

@@ -645,7 +645,7 @@ PF_HD void pf_env_step_t(const pf_params& P, const pf_env_buffers& B, const PfRe
         out.commands[0] = (P.cmd_range[0][1] - P.cmd_range[0][0]) * pf_rng_uniform(ek, 0) + P.cmd_range[0][0];
         out.commands[1] = (P.cmd_range[1][1] - P.cmd_range[1][0]) * pf_rng_uniform(ek, 1) + P.cmd_range[1][0];
         if (P.heading_command)
-            out.commands[3] = (P.cmd_range[3][1] - P.cmd_range[3][0]) * pf_rng_uniform(ek, 3) + P.cmd_range[3][0];
+            out.commands[3] = (P.cmd_range[3][1] - P.cmd_range[3][0]) * pf_rng_uniform(ek, 2) + P.cmd_range[3][0];   // the THIRD draw of LR:346-349, heading or yaw: lane 2 either way
         else
             out.commands[2] = (P.cmd_range[2][1] - P.cmd_range[2][0]) * pf_rng_uniform(ek, 2) + P.cmd_range[2][0];
         const float keep = pf_norm2(out.commands[0], out.commands[1]) > 0.2f ? 1.0f : 0.0f;

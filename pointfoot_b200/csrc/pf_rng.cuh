@@ -16,8 +16,9 @@ enum PfRngPurpose : uint32_t {
     PF_RNG_RESET_ROOT = 2,  // PF:577 (lanes 0..1), PF:583 (lanes 2..7)
     PF_RNG_CURRICULUM = 3,  // PF:632
     PF_RNG_PUSH = 4,        // PF:598
-    PF_RNG_RESAMPLE = 5,    // LR:337-351
-    PF_RNG_POLICY = 6       // rsl_rl ActorCritic.act (Normal.sample)
+    PF_RNG_RESAMPLE = 5,    // LR:337-351 from the callback (LR:326): lanes 0, 1, 2 (third draw: heading OR yaw)
+    PF_RNG_POLICY = 6,      // rsl_rl ActorCritic.act (Normal.sample)
+    PF_RNG_RESAMPLE_RESET = 8   // LR:337-351 from reset_idx (LR:166): same lanes, own purpose (7 is the minibatch shuffle)
 };
 
 PF_RNG_HD uint32_t pf_fmix32(uint32_t h) {

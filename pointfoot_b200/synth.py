@@ -154,3 +154,96 @@ def _inject_adversarial(s, N, rough):
         r = s["root_states"]
         r[:n, 0] = np.array([-30.0, -25.0, -24.95, 104.9, 105.0, 300.0, 0.0, 79.95] * 2)[:n]
         r[:n, 1] = np.array([-30.0, 184.9, 185.0, -24.99, 500.0, 0.05, 0.1, 159.9] * 2)[:n]
+
+
+# ------------------------------------------------------------------------------------------------ LeggedRobot / a1 (N2)
+LR_NUM_DOF, LR_NUM_BODIES, LR_FEET = 12, 17, (4, 8, 12, 16)
+LR_DOF_LOWER = np.array([-0.802851455917, -1.0471975512, -2.69653369433] * 4, np.float32)      # a1.urdf joint limits
+LR_DOF_UPPER = np.array([0.802851455917, 4.18879020479, -0.916297857297] * 4, np.float32)
+
+
+def make_lr_state(num_envs, seed=1, env_id_offset=0, adversarial=False, num_reward_terms=20, terrain=None):
+    """Seeded synthetic state for the LeggedRobot base class with the a1 asset (12 DOF, 17 bodies, 4 feet) on the rough
+    terrain (a1_config.py: trimesh, 187-point scan).  Same conventions as ``make_state``."""
+    N, D, B = num_envs, LR_NUM_DOF, LR_NUM_BODIES
+    g = np.random.default_rng(seed * 1000003 + env_id_offset + 77)
+    f32 = np.float32
+    s = {}
+    root = np.zeros((N, 13), f32)
+    root[:, 0] = g.uniform(0, 80, N)
+    root[:, 1] = g.uniform(0, 160, N)
+    root[:, 2] = 0.42 + g.normal(0, 0.05, N)
+    q = np.concatenate([g.normal(0, 0.15, (N, 3)), np.ones((N, 1))], 1)
+    root[:, 3:7] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    root[:, 7:13] = g.normal(0, 0.5, (N, 6))
+    s["root_states"] = root
+    dof = np.zeros((N, D, 2), f32)
+    # inside the soft limits (a1_config.py: soft_dof_pos_limit 0.9) except ~1.5 % of the joints, which sit beyond them so that
+    # dof_pos_limits (scale -10) fires for some envs and only_positive_rewards clips some totals and not others
+    mid, span = (LR_DOF_UPPER + LR_DOF_LOWER) / 2, LR_DOF_UPPER - LR_DOF_LOWER
+    u = g.uniform(-0.42, 0.42, (N, D))
+    out_ = g.random((N, D)) < 0.015
+    u = np.where(out_, np.sign(u) * g.uniform(0.455, 0.5, (N, D)), u)
+    dof[..., 0] = mid + u * span
+    dof[..., 1] = g.normal(0, 3, (N, D))
+    # 40 % of the envs "track well" (joints near the default pose, slow joints, base velocity near the command): small torque /
+    # acceleration penalties and large tracking rewards, so that the total is positive for them and the clip of
+    # only_positive_rewards (LR:198-199) bites for the others
+    good = g.random(N) < 0.4
+    dflt = np.array([-0.1, 0.8, -1.5, 0.1, 0.8, -1.5, -0.1, 1.0, -1.5, 0.1, 1.0, -1.5], f32)     # a1_config.py default_joint_angles, DOF order
+    dof[good, :, 0] = dflt + g.normal(0, 0.08, (int(good.sum()), D))
+    dof[good, :, 1] = g.normal(0, 0.4, (int(good.sum()), D))
+    s["_good"] = good
+    s["dof_state"] = dof.reshape(N * D, 2)
+    cf = np.zeros((N, B, 3), f32)
+    for f in LR_FEET:
+        cf[:, f, 2] = np.maximum(0, g.normal(20, 40, N))
+        cf[:, f, :2] = g.normal(0, 5, (N, 2))
+    hit = g.random((N, B)) < 0.004
+    hit[:, list(LR_FEET)] = False
+    d = g.normal(0, 1, (N, B, 3)); d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    cf += (hit[..., None] * d * 5.0).astype(f32)
+    s["contact_forces"] = cf.reshape(N * B, 3)
+    cmd = np.zeros((N, 4), f32)
+    cmd[:, 0] = g.uniform(-1, 1, N); cmd[:, 1] = g.uniform(-1, 1, N)
+    cmd[:, :2] *= (g.random((N, 1)) > 0.15)                   # some zero commands: feet_air_time's command gate
+    cmd[:, 2] = g.uniform(-1, 1, N); cmd[:, 3] = g.uniform(-3.14, 3.14, N)
+    s["commands"] = cmd
+    ep = g.integers(0, 1000, N)
+    late = g.random(N) < 1e-3
+    ep[late] = g.integers(1000, 1002, late.sum())
+    s["episode_length_buf"] = ep.astype(np.int64)
+    s["actions"] = g.normal(0, 1, (N, D)).astype(f32)
+    s["last_actions"] = g.normal(0, 1, (N, D)).astype(f32)
+    s["last_dof_vel"] = g.normal(0, 3, (N, D)).astype(f32)
+    good = s.pop("_good")
+    ng = int(good.sum())
+    s["last_dof_vel"][good] = dof[good, :, 1] + g.normal(0, 0.2, (ng, D)).astype(f32)
+    s["last_actions"][good] = s["actions"][good] + g.normal(0, 0.2, (ng, D)).astype(f32)
+    root[good, 7:9] = cmd[good, :2] + g.normal(0, 0.1, (ng, 2))          # (base frame ~ world frame: the quaternions are near identity)
+    root[good, 9] = g.normal(0, 0.05, ng)
+    root[good, 10:12] = g.normal(0, 0.1, (ng, 2))
+    root[good, 12] = cmd[good, 2] + g.normal(0, 0.1, ng)
+    s["feet_air_time"] = (g.uniform(0, 0.8, (N, 4)) * (g.random((N, 4)) < 0.7)).astype(f32)
+    s["last_contacts"] = g.random((N, 4)) < 0.5
+    s["episode_sums"] = g.normal(0, 1, (num_reward_terms, N)).astype(f32)
+    hf, origins = terrain if terrain is not None else make_heightfield(seed)
+    s["height_samples"], s["terrain_origins"] = hf, origins
+    s["terrain_levels"] = g.integers(0, 6, N).astype(np.int64)
+    s["terrain_types"] = np.floor(np.arange(N) / (N / TERRAIN_COLS)).astype(np.int64)
+    if adversarial:
+        n = min(N, 16)
+        c = s["contact_forces"].reshape(N, B, 3)
+        for i in range(n):
+            c[i, 0] = 0
+            c[i, 0, i % 3] = (1.0, np.nextafter(f32(1.0), f32(2.0)), 0.1, 0.10000001)[i % 4]      # termination body: ||F|| at 1.0
+            c[i, LR_FEET[i % 4], 2] = (1.0, 0.1, np.nextafter(f32(1.0), f32(2.0)), 0.0)[(i // 2) % 4]
+            c[i, 2 + 4 * (i % 4)] = 0
+            c[i, 2 + 4 * (i % 4), 0] = (0.1, 0.10000001)[i % 2]                                  # penalised body at 0.1
+        s["episode_length_buf"][:n] = np.array([999, 1000, 1001, 499, 500, 0, 1000, 500] * 2)[:n]   # resample period 500
+        r = s["root_states"]
+        r[:n, 0] = np.array([-30.0, -25.0, -24.95, 104.9, 105.0, 300.0, 0.0, 79.95] * 2)[:n]
+        r[:n, 1] = np.array([-30.0, 184.9, 185.0, -24.99, 500.0, 0.05, 0.1, 159.9] * 2)[:n]
+    out = {k: (torch.from_numpy(np.ascontiguousarray(v)) if isinstance(v, np.ndarray) else v) for k, v in s.items()}
+    out["common_step_counter"] = 0
+    return out

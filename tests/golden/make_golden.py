@@ -106,6 +106,57 @@ def generate_actuator(steps=6, seed=3):
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+LR_FIELDS = ("root_states", "dof_state", "commands", "episode_length_buf", "last_actions", "last_dof_vel", "last_root_vel",
+             "feet_air_time", "last_contacts", "base_lin_vel", "base_ang_vel", "projected_gravity", "torques", "time_out_buf")
+
+
+def generate_lr(fname, mutate=None, start_step=0, seed=1):
+    """The UNMODIFIED LeggedRobot (legged_gym/envs/base/legged_robot.py) with the a1 config, STEPS chained step() calls."""
+    import parity_lr
+    state = synth.make_lr_state(N, seed=seed, adversarial=True)
+    state["common_step_counter"] = start_step
+    out = {"start_step": np.int64(start_step)}
+    for k, v in state.items():
+        if k == "height_samples":
+            out["hf_sha256"] = np.frombuffer(hf_checksum(v).encode(), dtype=np.uint8)
+        elif torch.is_tensor(v):
+            out["in_" + k] = v.numpy().copy()
+    env = ref_harness.build_reference_legged_robot(common.clone_state(state), seed=seed, mutate_cfg=mutate)
+    names = list(env.episode_sums.keys())
+    out["reward_names"] = np.array(names)
+    out["num_obs"] = np.int64(env.num_obs)
+    cover = {"resets": 0, "resampled": 0, "pushes": 0, "clipped_rew": 0, "positive_rew": 0}
+    for i in range(STEPS):
+        a = parity_lr.actions_for(N, seed, i)
+        before = env.commands.clone()
+        obs, priv, rew, reset, extras = env.step(a.clone())
+        assert priv is None
+        p = f"s{i}_"
+        out[p + "obs"], out[p + "rew"], out[p + "reset"] = obs.numpy().copy(), rew.numpy().copy(), reset.numpy().copy()
+        for k in LR_FIELDS:
+            out[p + k] = getattr(env, k).numpy().copy()
+        out[p + "episode_sums"] = torch.stack([env.episode_sums[n] for n in names]).numpy().copy()
+        out[p + "reset_ids"] = reset.nonzero().flatten().to(torch.int32).numpy()
+        if env.custom_origins:
+            out[p + "terrain_levels"] = env.terrain_levels.numpy().copy()
+            out[p + "env_origins"] = env.env_origins.numpy().copy()
+        if torch.is_tensor(env.measured_heights):
+            out[p + "measured_heights"] = env.measured_heights.numpy().copy()
+        ep = extras.get("episode", {})
+        out[p + "extras_episode"] = np.array([float(ep["rew_" + n]) for n in names] if ep else [], np.float32)
+        if "terrain_level" in ep:
+            out[p + "extras_terrain_level"] = np.float32(float(ep["terrain_level"]))
+        out[p + "time_outs"] = extras["time_outs"].numpy().copy()
+        cover["resets"] += int(reset.sum())
+        cover["resampled"] += int(((env.commands[:, :2] != before[:, :2]).any(1) & ~reset.bool()).sum())
+        cover["pushes"] += int(env.common_step_counter % env.cfg.domain_rand.push_interval == 0 and env.cfg.domain_rand.push_robots)
+        cover["clipped_rew"] += int((rew == 0).sum())
+        cover["positive_rew"] += int((rew > 0).sum())
+    path = os.path.join(HERE, fname)
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes", cover)
+
+
 if __name__ == "__main__":
     if not ref_harness.reference_available():
         raise SystemExit("reference not available here; golden files can only be regenerated in the build container")
@@ -117,3 +168,7 @@ if __name__ == "__main__":
         generate(fname, task, mutate, start_step)
     if not only or ACTUATOR_FILE in only:
         generate_actuator()
+    import parity_lr
+    for fname, (mutate, start_step) in parity_lr.LR_GOLDEN.items():
+        if not only or fname in only:
+            generate_lr(fname, mutate, start_step)

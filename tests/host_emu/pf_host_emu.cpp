@@ -99,3 +99,54 @@ extern "C" int pf_emu_post_physics_step(const pf_params* Pp, const pf_env_buffer
     }
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------ LeggedRobot (N2)
+// The SAME pf_lr_core.cuh the pf_lr_* kernels use, driven serially; the finalize step is restated with serial loops
+// (the kernel's fixed-stride tree only changes the rounding of the double-precision sums).
+#include "../../pointfoot_b200/csrc/pf_lr_core.cuh"
+
+extern "C" int pf_emu_lr_pd_torques(const pf_lr_params* Pp, const pf_lr_buffers* Bp, const float* actions_in) {
+    for (int i = 0; i < Pp->num_envs * Pp->num_dof; ++i) lr_pd_torque_elem(*Pp, *Bp, actions_in, i);
+    return 0;
+}
+
+static void lr_emu_finalize(const pf_lr_params& P, const pf_lr_buffers& B) {
+    const int N = P.num_envs, R = P.num_reward_terms + (P.has_termination_term ? 1 : 0);
+    int count = 0;
+    for (int e = 0; e < N; ++e) if (B.reset_buf[e]) B.reset_ids[count++] = e;
+    *B.reset_count = count;
+    for (int k = 0; k < R; ++k) {
+        double t = 0.0;
+        for (int e = 0; e < N; ++e) if (B.reset_buf[e]) { t += (double)B.episode_sums[(size_t)k * N + e]; B.episode_sums[(size_t)k * N + e] = 0.0f; }
+        if (count) B.episode_stats[k] = (float)(t / (double)count) / P.max_episode_length_s;
+    }
+    if (count) {
+        double lv = 0.0;
+        if (B.terrain_levels) for (int e = 0; e < N; ++e) lv += (double)B.terrain_levels[e];
+        B.episode_stats[R] = (float)(lv / (double)N);
+        B.episode_stats[R + 1] = (float)count;
+        if (B.extras_time_outs) for (int e = 0; e < N; ++e) B.extras_time_outs[e] = B.time_out_buf[e];
+    }
+}
+
+extern "C" int pf_emu_lr_post_physics_step(const pf_lr_params* Pp, const pf_lr_buffers* Bp, long long common_step_counter, int push) {
+    const pf_lr_params& P = *Pp; const pf_lr_buffers& B = *Bp;
+    const uint32_t step = (uint32_t)common_step_counter;
+    if (P.measure_heights)
+        for (int e = 0; e < P.num_envs; ++e) {
+            const float* r = B.root_states + (size_t)e * 13;
+            float zn, wn; pf_yaw_quat(r + 3, zn, wn);
+            for (int p = 0; p < P.num_height_points; ++p) lr_scan_point(P, B, e, p, zn, wn, r[0], r[1]);
+        }
+    for (int e = 0; e < P.num_envs; ++e) lr_step_env(P, B, e, step, push);
+    if (P.measure_heights)
+        for (long long i = 0; i < (long long)P.num_envs * P.num_height_points; ++i) lr_obs_height(P, B, i, step);
+    lr_emu_finalize(P, B);
+    return 0;
+}
+
+extern "C" int pf_emu_lr_reset_all(const pf_lr_params* Pp, const pf_lr_buffers* Bp, long long common_step_counter) {
+    for (int e = 0; e < Pp->num_envs; ++e) lr_reset_all_env(*Pp, *Bp, e, (uint32_t)common_step_counter);
+    lr_emu_finalize(*Pp, *Bp);
+    return 0;
+}
