@@ -58,8 +58,10 @@ class _Wrap:
 
 class PointFoot:
     def __init__(self, cfg, sim_params=None, physics_engine=None, sim_device="cuda:0", headless=True,
-                 gym=None, gymtorch=None, state=None, seed=1, env_id_offset=0, resample_commands=False):
+                 gym=None, gymtorch=None, state=None, seed=1, env_id_offset=0, resample_commands=False,
+                 keep_measured_heights=False):
         self.cfg = cfg
+        self._keep_measured_heights = bool(keep_measured_heights)
         self.sim_params = sim_params
         self.physics_engine = physics_engine
         self.headless = headless
@@ -164,7 +166,10 @@ class PointFoot:
         self.torque_limits = torch.tensor([P.torque_limits[i] for i in range(D)], device=dev)
         self.base_mass = self._state.get("base_mass", torch.full((N,), pf_params.RobotModel.base_mass, device=dev))
         self._refresh_max_push_force()
-        self.measured_heights = z(N, P.num_height_points) if P.num_height_points else 0
+        # PF:775 / 212-213 keep the scan as an attribute, but its only readers on the step path (height observation columns,
+        # base-height reward) are fused into the kernels; the [N,P] fp32 copy (127 MB per step at 262,144 envs) is written
+        # only for a caller that asks (keep_measured_heights=True: debug drawing, parity tests)
+        self._measured_heights = z(N, P.num_height_points) if (P.num_height_points and self._keep_measured_heights) else None
         R = P.num_reward_terms + P.has_termination_term
         self._episode_sums = z(R, N)
         self.episode_sums = {n: self._episode_sums[i] for i, n in enumerate(names)}
@@ -200,7 +205,7 @@ class PointFoot:
             last_contacts=self.last_contacts, episode_sums=self._episode_sums, rew_buf=self.rew_buf,
             reset_buf=self.reset_buf, time_out_buf=self.time_out_buf, terminate=self.terminate,
             obs_buf=self.proprioceptive_obs_buf, priv_obs_buf=self.privileged_obs_buf,
-            measured_heights=self.measured_heights if torch.is_tensor(self.measured_heights) else None,
+            measured_heights=self._measured_heights,
             height_samples=self.height_samples, terrain_origins=self.terrain_origins,
             terrain_levels=self.terrain_levels, terrain_types=self.terrain_types, env_origins=self.env_origins,
             reset_ids=self._reset_ids, reset_count=self._reset_count, episode_stats=self._episode_stats,
@@ -220,6 +225,16 @@ class PointFoot:
         self.extras["episode"] = ep
         if self.cfg.env.send_timeouts:
             self.extras["time_outs"] = self._time_outs
+
+    @property
+    def measured_heights(self):
+        """PF:775 (the int 0 when the task measures nothing), PF:1054-1085"""
+        if not self._P.num_height_points:
+            return 0
+        if self._measured_heights is None:
+            raise AttributeError("measured_heights is not materialised on the step path by default; construct the env with "
+                                 "keep_measured_heights=True (the height observations and the base-height reward do not need it)")
+        return self._measured_heights
 
     # ------------------------------------------------------------------ VecEnv protocol
     def get_observations(self):

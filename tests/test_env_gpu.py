@@ -316,3 +316,29 @@ def test_pointfoot_class_pushes_without_a_host_sync_and_inside_a_graph():
     assert torch.equal(env.rigid_body_external_forces.cpu(), orc.push_forces)
     assert float(orc.push_forces.abs().max()) > 0
     env.close()
+
+
+def test_step_outputs_do_not_depend_on_materialising_measured_heights():
+    """measured_heights is written only for a caller that asks (PointFoot(keep_measured_heights=True)); observations,
+    rewards and the episode sums -- its readers on the step path -- are bit-identical either way"""
+    import common
+    from pointfoot_b200 import synth
+    from pointfoot_b200.env import PointFoot
+    N, task = 777, "pointfoot_rough"
+    state = synth.make_state(N, task, seed=6, adversarial=True)
+    envs = []
+    for keep in (False, True):
+        cfg = common.make_cfg(task, N)
+        envs.append(PointFoot(cfg, None, None, "cuda:0", True, state=common.clone_state(state), seed=1, keep_measured_heights=keep))
+    a = synth.make_state(N, task, seed=7)["actions"].cuda()
+    for _ in range(3):
+        outs = [e.step(a) for e in envs]
+        torch.cuda.synchronize()
+        for x, y in zip(outs[0][:4], outs[1][:4]):
+            assert torch.equal(x, y)
+        assert torch.equal(envs[0]._episode_sums, envs[1]._episode_sums)
+    assert envs[1].measured_heights.shape == (N, 121) and float(envs[1].measured_heights.abs().sum()) > 0
+    with pytest.raises(AttributeError, match="keep_measured_heights"):
+        envs[0].measured_heights
+    for e in envs:
+        e.close()
