@@ -479,6 +479,50 @@ int pf_lr_post_physics_step(const pf_lr_params* params, const pf_lr_buffers* buf
  * extras["time_outs"]).  The zero-action step that follows is the caller's. */
 int pf_lr_reset_all(const pf_lr_params* params, const pf_lr_buffers* bufs, int64_t common_step_counter, void* stream);
 
+/* ================================================================================================
+ * Terrain generation: legged_gym/utils/terrain.py::Terrain (terrain.py:38-187) + the sub-terrain
+ * primitives of isaacgym.terrain_utils it calls, as ONE raster kernel over the whole int16 height field (the field the
+ * height scan of the step path gathers from), a per-sub-terrain kernel for env_origins (terrain.py:160-167) and the
+ * height-field -> triangle-mesh conversion handed to PhysX for mesh_type 'trimesh' (terrain.py:66-70).
+ * The host reduces every sub-terrain to integers exactly as terrain_utils does (int(step_height / vertical_scale) ...,
+ * pointfoot_b200/terrain.py) and passes one pf_subterrain per map cell; random draws are evaluated per pixel from the
+ * counter-based contract (purpose PF_RNG_TERRAIN, "env" = row * num_cols + col, lanes as listed below).
+ * ============================================================================================== */
+enum pf_subterrain_kind {
+    PF_SUB_SLOPE = 0,        /* pyramid_sloped_terrain: p0 max_height (signed counts), p1 platform half size [px] */
+    PF_SUB_NOISY_SLOPE = 1,  /* + random_uniform_terrain: p2 lowest height, p3 number of heights, p4 step [counts], p5 / p6 coarse grid
+                                    nx / ny; draw lane a * ny + b for grid node (a, b) */
+    PF_SUB_STAIRS = 2,       /* pyramid_stairs_terrain: p0 step width [px], p1 step height (signed counts), p2 number of steps */
+    PF_SUB_OBSTACLES = 3,    /* discrete_obstacles_terrain: p0 max height, p1 / p2 min / max size [px], p3 number of rectangles,
+                                    p4..p7 platform x1 x2 y1 y2; lanes 5 r + {0 width, 1 length, 2 start_i, 3 start_j, 4 height} */
+    PF_SUB_STONES = 4,       /* stepping_stones_terrain: p0 stone size, p1 stone distance [px], p2 max height, p3 depth (counts),
+                                    p4..p7 platform x1 x2 y1 y2; lanes 128 band + {0 offset, 1 first piece, 2 + s stone s} */
+    PF_SUB_GAP = 5,          /* gap_terrain (terrain.py:169-181): p0..p3 outer x1 x2 y1 y2 (-1000), p4..p7 inner (0) */
+    PF_SUB_PIT = 6           /* pit_terrain (terrain.py:183-190): p0 height (= -depth counts), p4..p7 x1 x2 y1 y2 */
+};
+
+typedef struct pf_subterrain { int32_t kind; int32_t p[15]; } pf_subterrain;
+
+typedef struct pf_terrain_params {
+    int32_t abi_version;
+    int32_t num_rows, num_cols;        /* sub-terrains: levels x types */
+    int32_t cell_px;                   /* width_per_env_pixels = length_per_env_pixels (the reference builds square sub-terrains, terrain.py:110-114) */
+    int32_t border_px, tot_rows, tot_cols;
+    uint32_t seed;
+    int32_t origin_patch[4];           /* x1 x2 y1 y2 of the patch whose max is env_origin_z (terrain.py:163-166) */
+    double env_length, env_width, vertical_scale;
+} pf_terrain_params;
+
+int pf_terrain_sizeof_params(void);
+/* subs: DEVICE pf_subterrain[num_rows * num_cols] (row-major); height_field: DEVICE int16[tot_rows, tot_cols];
+ * env_origins: DEVICE double[num_rows, num_cols, 3] */
+int pf_terrain_generate(const pf_terrain_params* params, const pf_subterrain* subs, int16_t* height_field, double* env_origins,
+                        void* stream);
+/* isaacgym.terrain_utils.convert_heightfield_to_trimesh: vertices fp32[rows * cols, 3], triangles uint32[2 (rows-1)(cols-1), 3];
+ * slope_threshold < 0: no correction */
+int pf_terrain_trimesh(const int16_t* height_field, int32_t rows, int32_t cols, double horizontal_scale, double vertical_scale,
+                       double slope_threshold, float* vertices, uint32_t* triangles, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -499,3 +499,66 @@ def build_reference_legged_robot(state, seed=1, mutate_cfg=None, env_id_offset=0
         env.episode_sums[name][:] = state["episode_sums"][i]
     env.common_step_counter = int(state.get("common_step_counter", 0))
     return env
+
+
+# --------------------------------------------------------------------------------------------
+# Terrain generation: the UNMODIFIED legged_gym/utils/terrain.py::Terrain over the restated
+# isaacgym.terrain_utils (oracle/terrain_ref.py -- third-party, absent, parity unpinned for that part).
+def make_terrain_cfg(mutate=None):
+    install_stubs()
+    from legged_gym.envs.base.legged_robot_config import LeggedRobotCfg
+
+    class terrain(LeggedRobotCfg.terrain):
+        pass
+    cfg = terrain()
+    if mutate is not None:
+        mutate(cfg)
+    return cfg
+
+
+def build_reference_terrain(mutate=None, seed=1, num_robots=64):
+    """-> the reference's Terrain object (height_field_raw int16, env_origins float64[rows, cols, 3], ...).  Every random draw
+    -- the primitives' through terrain_ref.draw_index, Terrain.randomized_terrain's own np.random.uniform / np.random.choice
+    (terrain.py:78-79) -- is routed to the counter-based contract: purpose TERRAIN, 'env' = sub-terrain index
+    row * num_cols + col, step 0."""
+    install_stubs()
+    from oracle import terrain_ref
+    import legged_gym.envs.base.legged_robot_config                # (envs first: legged_gym.utils <-> envs import cycle)
+    import legged_gym.utils.terrain as ref_terrain
+    ref_terrain.terrain_utils = terrain_ref                  # the module global the reference's calls resolve through
+    cfg = make_terrain_cfg(mutate)
+    ctx = {"sub": 0, "made": 0, "layout": 0}
+
+    def sub_of(count):
+        if cfg.curriculum:                                   # terrain.py:85-92: for j: for i
+            j, i = divmod(count, cfg.num_rows)
+        else:                                                # terrain.py:73-82 / 94-107: k -> unravel_index
+            i, j = divmod(count, cfg.num_cols)
+        return i * cfg.num_cols + j
+
+    class RefTerrain(ref_terrain.Terrain):
+        def make_terrain(self, choice, difficulty):
+            ctx["sub"] = sub_of(ctx["made"])
+            ctx["made"] += 1
+            return super().make_terrain(choice, difficulty)
+
+    def hook(n, lane):
+        return int(rng.rand_u32(seed, 0, rng.TERRAIN, ctx["sub"], lane)) % n
+
+    def np_uniform(lo=0.0, hi=1.0, size=None):
+        assert size is None
+        sub = sub_of(ctx["layout"])
+        return lo + (hi - lo) * float(rng.uniform(seed, 0, rng.TERRAIN, sub, terrain_ref.LANE_LAYOUT))
+
+    def np_choice(a, size=None, **kw):
+        assert size is None and not kw
+        sub = sub_of(ctx["layout"])
+        ctx["layout"] += 1
+        return a[int(rng.rand_u32(seed, 0, rng.TERRAIN, sub, terrain_ref.LANE_LAYOUT + 1)) % len(a)]
+
+    terrain_ref.set_draw_hook(hook)
+    try:
+        with _patched(np.random, "uniform", np_uniform), _patched(np.random, "choice", np_choice):
+            return RefTerrain(cfg, num_robots)
+    finally:
+        terrain_ref.set_draw_hook(None)

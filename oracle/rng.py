@@ -21,6 +21,7 @@ CURRICULUM = 3      # point_foot.py:632 randint_like, lane 0
 PUSH = 4            # point_foot.py:598, lanes 0..2
 RESAMPLE_CMD = 5    # legged_robot.py:337-351 called from the callback (LR:326): lanes 0, 1, and 2 = the third draw (heading OR yaw)
 RESAMPLE_RESET = 8  # the same method called from reset_idx (LR:166) on the same step: its own purpose, same lanes
+TERRAIN = 9         # terrain generation (terrain.py + terrain_utils): 'env' = sub-terrain index, lanes = oracle/terrain_ref.py LANE_*; step 0
 POLICY = 6          # rsl_rl ActorCritic.act: Normal.sample, lanes 0..A-1 (two u32 per lane)
 
 _M = np.uint64(0xFFFFFFFF)

@@ -237,3 +237,20 @@ def load_lr():
     lib.pf_lr_pd_torques.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib._pf_lr_ready = True
     return lib
+
+
+# ------------------------------------------------------------------------------------------------ terrain generation (N1)
+class PfTerrainParams(C.Structure):
+    _fields_ = [("abi_version", _i), ("num_rows", _i), ("num_cols", _i), ("cell_px", _i), ("border_px", _i), ("tot_rows", _i),
+                ("tot_cols", _i), ("seed", _u), ("origin_patch", _i * 4), ("env_length", C.c_double), ("env_width", C.c_double),
+                ("vertical_scale", C.c_double)]
+
+
+def load_terrain():
+    lib = load()
+    if getattr(lib, "_pf_terrain_ready", False):
+        return lib
+    if lib.pf_terrain_sizeof_params() != C.sizeof(PfTerrainParams):
+        raise RuntimeError("pointfoot_b200: pf_terrain_params layout mismatch between capi.py and the header")
+    lib._pf_terrain_ready = True
+    return lib

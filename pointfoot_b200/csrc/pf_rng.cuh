@@ -18,6 +18,7 @@ enum PfRngPurpose : uint32_t {
     PF_RNG_PUSH = 4,        // PF:598
     PF_RNG_RESAMPLE = 5,    // LR:337-351 from the callback (LR:326): lanes 0, 1, 2 (third draw: heading OR yaw)
     PF_RNG_POLICY = 6,      // rsl_rl ActorCritic.act (Normal.sample)
+    PF_RNG_TERRAIN = 9,     // terrain generation: 'env' = sub-terrain index, lanes as in csrc/pf_terrain.cu; step 0
     PF_RNG_RESAMPLE_RESET = 8   // LR:337-351 from reset_idx (LR:166): same lanes, own purpose (7 is the minibatch shuffle)
 };
 

@@ -157,6 +157,30 @@ def generate_lr(fname, mutate=None, start_step=0, seed=1):
     print("wrote", path, os.path.getsize(path), "bytes", cover)
 
 
+def generate_terrain(fname, mutate, keep_field):
+    """The UNMODIFIED legged_gym/utils/terrain.py::Terrain over oracle/terrain_ref.py (restated isaacgym.terrain_utils)."""
+    from oracle import terrain_ref
+    import parity_terrain
+    t = ref_harness.build_reference_terrain(mutate, seed=1)
+    hf = t.height_field_raw
+    out = {"shape": np.array(hf.shape), "geometry": np.array([t.tot_rows, t.tot_cols, t.border, t.width_per_env_pixels]),
+           "hf_sha256": np.frombuffer(parity_terrain.sha(hf).encode(), np.uint8), "env_origins": t.env_origins.copy()}
+    if keep_field:
+        out["height_field"] = hf.copy()
+    else:
+        r0 = t.border + 3 * t.length_per_env_pixels - 40           # two rows of cells' edges, every column type
+        out["slab_rows"], out["slab"] = np.array([r0, r0 + 160]), hf[r0:r0 + 160].copy()
+    assert t.type == "trimesh"
+    moved = terrain_ref.convert_heightfield_to_trimesh(hf, t.cfg.horizontal_scale, t.cfg.vertical_scale, None)[0]
+    out["vertices_sha256"] = np.frombuffer(parity_terrain.sha(t.vertices).encode(), np.uint8)
+    out["triangles_sha256"] = np.frombuffer(parity_terrain.sha(t.triangles).encode(), np.uint8)
+    out["moved_vertices"] = np.int64((moved[:, :2] != t.vertices[:, :2]).any(1).sum())
+    path = os.path.join(HERE, fname)
+    np.savez_compressed(path, **out)
+    kinds = {}
+    print("wrote", path, os.path.getsize(path), "bytes; min/max", hf.min(), hf.max(), "moved vertices", int(out["moved_vertices"]))
+
+
 if __name__ == "__main__":
     if not ref_harness.reference_available():
         raise SystemExit("reference not available here; golden files can only be regenerated in the build container")
@@ -168,6 +192,10 @@ if __name__ == "__main__":
         generate(fname, task, mutate, start_step)
     if not only or ACTUATOR_FILE in only:
         generate_actuator()
+    import parity_terrain
+    for fname, (mutate, keep) in parity_terrain.TERRAIN_GOLDEN.items():
+        if not only or fname in only:
+            generate_terrain(fname, mutate, keep)
     import parity_lr
     for fname, (mutate, start_step) in parity_lr.LR_GOLDEN.items():
         if not only or fname in only:

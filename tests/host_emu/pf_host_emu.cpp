@@ -150,3 +150,38 @@ extern "C" int pf_emu_lr_reset_all(const pf_lr_params* Pp, const pf_lr_buffers* 
     lr_emu_finalize(*Pp, *Bp);
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------ terrain generation (N1)
+#include "../../pointfoot_b200/csrc/pf_terrain_core.cuh"
+
+extern "C" int pf_emu_terrain_generate(const pf_terrain_params* Pp, const pf_subterrain* subs, int16_t* hf, double* origins) {
+    const pf_terrain_params& P = *Pp;
+    for (int r = 0; r < P.tot_rows; ++r)
+        for (int c = 0; c < P.tot_cols; ++c) hf[(size_t)r * P.tot_cols + c] = pf_terrain_map_pixel(P, subs, r, c);
+    const int W = P.cell_px;
+    for (int i = 0; i < P.num_rows; ++i)
+        for (int j = 0; j < P.num_cols; ++j) {
+            int m = -32768;
+            for (int x = P.origin_patch[0]; x < P.origin_patch[1]; ++x)
+                for (int y = P.origin_patch[2]; y < P.origin_patch[3]; ++y) {
+                    const int v = hf[(size_t)(P.border_px + i * W + x) * P.tot_cols + (P.border_px + j * W + y)];
+                    m = v > m ? v : m;
+                }
+            double* o = origins + (size_t)(i * P.num_cols + j) * 3;
+            o[0] = ((double)i + 0.5) * P.env_length; o[1] = ((double)j + 0.5) * P.env_width; o[2] = (double)m * P.vertical_scale;
+        }
+    return 0;
+}
+
+extern "C" int pf_emu_terrain_trimesh(const int16_t* hf, int rows, int cols, double hs, double vs, double thr, float* vertices,
+                                      uint32_t* tri) {
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < cols; ++c) pf_terrain_vertex(hf, rows, cols, hs, vs, thr, r, c, vertices + ((size_t)r * cols + c) * 3);
+    for (int r = 0; r < rows - 1; ++r)
+        for (int c = 0; c < cols - 1; ++c) {
+            const uint32_t i0 = (uint32_t)(r * cols + c), i1 = i0 + 1, i2 = i0 + (uint32_t)cols, i3 = i2 + 1;
+            uint32_t* t = tri + ((size_t)r * (cols - 1) + c) * 6;
+            t[0] = i0; t[1] = i3; t[2] = i1; t[3] = i0; t[4] = i2; t[5] = i3;
+        }
+    return 0;
+}
