@@ -1,9 +1,9 @@
 // Terrain generation: legged_gym/utils/terrain.py::Terrain + the isaacgym.terrain_utils primitives
 // it calls, as raster kernels (include/pointfoot_b200.h, "Terrain generation").
-//   pf_terrain_raster_kernel   one thread per pixel of the WHOLE map: border / cell look-up, the sub-terrain's closed form
-//                              (pyramid, stairs, gap, pit) or its random structure re-derived per pixel from the counter-based
-//                              contract (noise grid nodes, the 20 rectangles, the stone bands) -- no sub-terrain buffers, no
-//                              paste step (terrain.py:147-158), int16 stores coalesced along the map's columns
+//   pf_terrain_cells_kernel    one CTA per (map cell, 16-row strip), one thread per pixel: the sub-terrain's closed form
+//                              (pyramid, stairs, gap, pit) or its random structure re-derived from the counter-based contract
+//                              (noise grid nodes and stone bands per pixel, the 20 rectangles once per CTA into shared memory)
+//                              -- no sub-terrain buffers, no paste step (terrain.py:147-158), int16 stores along the map's columns
 //   pf_terrain_origins_kernel  one warp per sub-terrain: max over the centre patch -> env_origins (terrain.py:160-167)
 //   pf_terrain_vertices_kernel / pf_terrain_triangles_kernel   convert_heightfield_to_trimesh (terrain.py:66-70)
 // Init-time work in the reference (numpy, ~2.4 s for the default 1300 x 2100 map); here HBM bound: 2 B written per pixel,
@@ -15,24 +15,49 @@
 
 void pf_set_error(const char* msg);
 
-__global__ void __launch_bounds__(256) pf_terrain_raster_kernel(const pf_terrain_params P, const pf_subterrain* __restrict__ subs,
-                                                                int16_t* __restrict__ hf) {
-    const long long n = (long long)P.tot_rows * P.tot_cols;
-    // two pixels per thread: one 32-bit store
-    const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 2;
-    if (i >= n) return;
-    const int r = (int)(i / P.tot_cols), c = (int)(i - (long long)r * P.tot_cols);
-    const int16_t a = pf_terrain_map_pixel(P, subs, r, c);
-    if (i + 1 < n && c + 1 < P.tot_cols && (P.tot_cols & 1) == 0) {
-        const int16_t b = pf_terrain_map_pixel(P, subs, r, c + 1);
-        *reinterpret_cast<uint32_t*>(hf + i) = (uint32_t)(uint16_t)a | ((uint32_t)(uint16_t)b << 16);
-    } else {
-        hf[i] = a;
-        if (i + 1 < n) {
-            const long long k = i + 1;
-            const int r1 = (int)(k / P.tot_cols), c1 = (int)(k - (long long)r1 * P.tot_cols);
-            hf[k] = pf_terrain_map_pixel(P, subs, r1, c1);
+#define PF_T_STRIP 16          // rows of a cell one CTA rasterises
+#define PF_T_MAX_RECTS 64     // rectangles of an obstacle cell staged in shared memory (the reference paints 20)
+
+// One CTA per (cell, strip of PF_T_STRIP rows).  The structure shared by the cell's pixels is derived ONCE per CTA: the
+// rectangles of an obstacle cell (5 draws each; a pixel then compares against <= 20 staged rectangles instead of re-deriving
+// 100 draws) -- everything else goes through the same pf_terrain_pixel the host emulation runs.
+__global__ void __launch_bounds__(256) pf_terrain_cells_kernel(const pf_terrain_params P, const pf_subterrain* __restrict__ subs,
+                                                               int16_t* __restrict__ hf, const int strips) {
+    __shared__ int s_rect[PF_T_MAX_RECTS][5];
+    __shared__ pf_subterrain s_sub;
+    const int sub = blockIdx.x / strips, strip = blockIdx.x - sub * strips, W = P.cell_px;
+    if (threadIdx.x < 16) reinterpret_cast<int32_t*>(&s_sub)[threadIdx.x] = reinterpret_cast<const int32_t*>(subs + sub)[threadIdx.x];
+    __syncthreads();
+    const pf_subterrain& S = s_sub;
+    const uint32_t ek = pf_rng_env_key(pf_rng_key(P.seed, 0u, PF_RNG_TERRAIN), (uint32_t)sub);
+    const bool staged = S.kind == PF_SUB_OBSTACLES && S.p[3] <= PF_T_MAX_RECTS;
+    if (staged && (int)threadIdx.x < S.p[3]) {
+        const int r = threadIdx.x, mh = S.p[0], nw = pf_t_ceil_div(S.p[2] - S.p[1], 4);
+        const uint32_t l = 5u * (uint32_t)r;
+        const int w = S.p[1] + 4 * pf_t_draw(ek, l, nw), len = S.p[1] + 4 * pf_t_draw(ek, l + 1, nw);
+        const int k = pf_t_draw(ek, l + 4, 4);
+        s_rect[r][0] = 4 * pf_t_draw(ek, l + 2, pf_t_ceil_div(W - w, 4));
+        s_rect[r][1] = 4 * pf_t_draw(ek, l + 3, pf_t_ceil_div(W - len, 4));
+        s_rect[r][2] = w; s_rect[r][3] = len;
+        s_rect[r][4] = k == 0 ? -mh : (k == 1 ? pf_t_floor_div2(-mh) : (k == 2 ? pf_t_floor_div2(mh) : mh));
+    }
+    __syncthreads();
+    const int i = sub / P.num_cols, j = sub - i * P.num_cols;
+    const int x0 = strip * PF_T_STRIP, nx = min(PF_T_STRIP, W - x0);
+    int16_t* base = hf + (size_t)(P.border_px + i * W) * P.tot_cols + (P.border_px + j * W);
+    for (int k = threadIdx.x; k < nx * W; k += blockDim.x) {
+        const int x = x0 + k / W, y = k % W;
+        int16_t h;
+        if (staged) {
+            int v = 0;
+            for (int r = S.p[3] - 1; r >= 0; --r)
+                if (x >= s_rect[r][0] && x < s_rect[r][0] + s_rect[r][2] && y >= s_rect[r][1] && y < s_rect[r][1] + s_rect[r][3]) { v = s_rect[r][4]; break; }
+            if (pf_t_in(x, y, S.p + 4)) v = 0;
+            h = (int16_t)v;
+        } else {
+            h = pf_terrain_pixel(S, ek, W, x, y);
         }
+        base[(size_t)x * P.tot_cols + y] = h;
     }
 }
 
@@ -94,12 +119,12 @@ extern "C" int pf_terrain_generate(const pf_terrain_params* p, const pf_subterra
     const int* o = p->origin_patch;
     if (o[0] < 0 || o[1] > p->cell_px || o[0] >= o[1] || o[2] < 0 || o[3] > p->cell_px || o[2] >= o[3])
         return t_fail(1, "pf_terrain_generate: origin patch outside the sub-terrain");
-    if (reinterpret_cast<uintptr_t>(height_field) & 3) return t_fail(1, "pf_terrain_generate: height_field must be 4-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    const long long n = (long long)p->tot_rows * p->tot_cols, pairs = (n + 1) / 2;
-    PF_LAUNCHED(), pf_terrain_raster_kernel<<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>(*p, subs, height_field);
+    const int nsub = p->num_rows * p->num_cols, strips = (p->cell_px + PF_T_STRIP - 1) / PF_T_STRIP;
+    // the border (terrain.py:62 np.zeros) and then the cells
+    T_CUDA(cudaMemsetAsync(height_field, 0, sizeof(int16_t) * (size_t)p->tot_rows * p->tot_cols, st));
+    PF_LAUNCHED(), pf_terrain_cells_kernel<<<nsub * strips, 256, 0, st>>>(*p, subs, height_field, strips);
     T_CUDA(cudaGetLastError());
-    const int nsub = p->num_rows * p->num_cols;
     PF_LAUNCHED(), pf_terrain_origins_kernel<<<(nsub * 32 + 255) / 256, 256, 0, st>>>(*p, height_field, env_origins);
     T_CUDA(cudaGetLastError());
     return 0;
