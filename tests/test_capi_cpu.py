@@ -60,3 +60,23 @@ def test_bad_params_are_rejected(lib):
     P.num_obs = 30            # reference: RuntimeError at point_foot.py:363-365
     rc = lib.pf_ctx_create(C.byref(P), C.c_void_p(noise.data_ptr()), None, C.byref(ctx))
     assert rc == 3 and b"observation width" in lib.pf_last_error()
+
+
+def test_redzone_helper_detects_overruns_on_either_side():
+    """tests/common.py::RedZone is the memcheck stand-in of tests/test_redzone_gpu.py: it must flag a byte written before or
+    after a wrapped buffer and accept writes inside it"""
+    import pytest
+    import torch
+    import common
+    rz = common.RedZone()
+    t = rz.wrap(torch.arange(10, dtype=torch.float32), "t")
+    t += 1
+    assert rz.check() == 1 and float(t[9]) == 10.0
+    name, raw, n = rz.guards[0]
+    raw[rz.PAD + n] = 0
+    with pytest.raises(AssertionError, match="ABOVE buffer t"):
+        rz.check()
+    raw[rz.PAD + n] = 0xA5
+    raw[rz.PAD - 1] = 1
+    with pytest.raises(AssertionError, match="BELOW buffer t"):
+        rz.check()
