@@ -438,8 +438,8 @@ def rooflines(w, flush, peaks, n=20):
         tf_peak = peaks.get("bf16_tflops_sustained", 1381.4)
         hbm_frac = abytes / (ms_a * 1e-3) / 1e9 / hbm
         tc_frac = flops / (ms_a * 1e-3) / 1e12 / tf_peak
-        act_r = {"kernel": "pf_mlp_tc_kernel (PPO.act: both nets + sample + log-prob + storage row)" if w.policy.precision == "bf16"
-                 else "pf_sgemm_kernel chain + pf_act_sample_kernel", "us_per_launch": ms_a * 1e3,
+        act_r = {"kernel": w.policy.kernel_name + (" (PPO.act: both nets + sample + log-prob + storage row)" if w.policy.precision == "bf16" else ""),
+                 "us_per_launch": ms_a * 1e3,
                  "bound": "tensor" if tc_frac > hbm_frac else "hbm", "hbm_frac": hbm_frac, "tensor_frac": tc_frac,
                  "achieved_gbs": abytes / (ms_a * 1e-3) / 1e9, "achieved_tflops": flops / (ms_a * 1e-3) / 1e12,
                  "peak_tflops": tf_peak, "algorithmic_bytes_per_launch": abytes, "algorithmic_flops_per_launch": flops}

@@ -315,6 +315,10 @@ int pf_rl_tc_trace(pf_rl_ctx* ctx, unsigned long long* device_buf);
  * programmatic-dependency wait, so that the code of all its roles has been executed once while the predecessor kernel
  * (the env step) is still running.  For chains launched back to back (a CUDA-graphed step + act); off by default. */
 int pf_rl_tc_rehearse(pf_rl_ctx* ctx, int on);
+/* Which kernels serve act / act_inference / evaluate of this context: 0 = fp32 SIMT chain (PF_RL_FP32), 1 = fused tcgen05
+ * kernel (pf_mlp_tc.cu), 2 = register-resident warp-MMA kernel for small nets (pf_mlp_wm.cu: every hidden width a multiple of
+ * 16 and <= 128, inputs <= 128, outputs <= 8 -- the pointfoot_flat policy; PF_RL_WM=0 in the environment disables it). */
+int pf_rl_inference_path(const pf_rl_ctx* ctx);
 
 /* PPO.act (ppo.py act) fused with RolloutStorage.add_transitions' copies: actor forward -> Normal(mean, std)
  * sample (RNG contract, purpose POLICY, step = policy_step) -> log-prob; critic forward; writes row `t` of the

@@ -761,6 +761,7 @@ static int check_program(const TcProgram& P) {
 // kernel is launched right behind a kernel that still runs for a few microseconds (a CUDA-graphed env step + act
 // chain); without such a predecessor it adds one item's latency, hence off by default.
 extern "C" int pf_rl_tc_rehearse(pf_rl_ctx* c, int on) {
+    if (c && c->wm) return 0;                    // the small-net path has no chain to rehearse
     if (!c || !c->tc) return 1;
     static_cast<TcState*>(c->tc)->rehearse = on ? 1 : 0;
     return 0;

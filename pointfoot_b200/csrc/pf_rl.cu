@@ -221,8 +221,11 @@ static int rl_ctx_init(pf_rl_ctx* c) {
     c->norm_blocks = 256;
     RL_CUDA(cudaMalloc(&c->norm_part, sizeof(double) * (size_t)(c->norm_blocks + 8)));
     c->tc = nullptr;
+    c->wm = nullptr;
     if (P.precision == PF_RL_BF16_TC) {
-        if (int rc = pf_tc_create(c)) return rc;
+        // inference side: small nets (the flat policy) run register-resident on warp-level MMAs, everything else on tcgen05
+        if (int rc = pf_wm_create(c)) return rc;
+        if (!c->wm) { if (int rc = pf_tc_create(c)) return rc; }
         if (int rc = pf_tt_create(c)) return rc;
     } else if (P.precision != PF_RL_FP32) {
         return rl_fail(1, "pf_rl_create", "unknown precision");
@@ -233,6 +236,7 @@ static int rl_ctx_init(pf_rl_ctx* c) {
 extern "C" int pf_rl_destroy(pf_rl_ctx* c) {
     if (!c) return 0;
     if (c->tc) pf_tc_destroy(c);
+    pf_wm_destroy(c);
     for (int k = 0; k < 2; ++k) cudaFree(c->net[k].tc_weights);       // (a pf_tc_create that failed half-way)
     pf_tt_destroy(c);
     for (int k = 0; k < 2; ++k)
@@ -243,6 +247,8 @@ extern "C" int pf_rl_destroy(pf_rl_ctx* c) {
     delete c;
     return 0;
 }
+
+extern "C" int pf_rl_inference_path(const pf_rl_ctx* c) { return !c ? -1 : (c->wm ? 2 : (c->tc ? 1 : 0)); }
 
 extern "C" int64_t pf_rl_param_count(const pf_rl_ctx* c) { return c ? c->n_params : -1; }
 
@@ -256,6 +262,7 @@ extern "C" int64_t pf_rl_param_offset(const pf_rl_ctx* c, int net, int layer, in
 extern "C" int pf_rl_params_changed(pf_rl_ctx* c, const float* params, void* stream) {
     if (!c || !params) return rl_fail(1, "pf_rl_params_changed", "null argument");
     if (c->tc) { if (int rc = pf_tc_pack_weights(c, params, (cudaStream_t)stream)) return rc; }
+    if (c->wm) { if (int rc = pf_wm_pack_weights(c, params, (cudaStream_t)stream)) return rc; }
     if (c->tc_gemm) return pf_tt_pack_weights(c, params, (cudaStream_t)stream);
     return 0;
 }
@@ -327,6 +334,11 @@ static int check_rl(pf_rl_ctx* c, const void* a, const void* b, const char* what
 static int mlp_forward(pf_rl_ctx* c, int k, const float* params, const float* x, int rows, float* out_tc,
                        float* copy_to, cudaStream_t st, float** out) {
     PfNet& n = c->net[k];
+    if (c->wm) {
+        if (int rc = pf_wm_mlp_forward(c, k, x, n.dims[0], rows, out_tc, copy_to, st)) return rc;
+        *out = out_tc;
+        return 0;
+    }
     if (c->tc) {
         if (int rc = pf_tc_mlp_forward(c, k, params, x, n.dims[0], rows, out_tc, copy_to, st)) return rc;
         *out = out_tc;
@@ -347,6 +359,8 @@ extern "C" int pf_rl_act(pf_rl_ctx* c, const float* params, const float* obs, co
     cudaStream_t st = (cudaStream_t)stream;
     if (storage && (t < 0 || t >= P.num_steps)) return rl_fail(5, "pf_rl_act", "Rollout buffer overflow");
     if (!critic_obs) critic_obs = obs;
+    if (c->wm)
+        return pf_wm_act(c, params, obs, critic_obs, storage, storage ? t : 0, policy_step, actions_out, values_out, logp_out, st);
     if (c->tc && pf_tc_act_fusable(c))
         return pf_tc_act(c, params, obs, critic_obs, storage, storage ? t : 0, policy_step, actions_out, values_out, logp_out, st);
     const long long row0 = (long long)t * P.num_envs;
@@ -893,6 +907,7 @@ extern "C" int pf_rl_adam_step(pf_rl_ctx* c, const pf_rl_learner* L, void* strea
     PF_LAUNCHED(), pf_adam_kernel<<<ublocks, 256, 0, st>>>(n, *L, sc);
     RL_CUDA(cudaGetLastError());
     if (c->tc) { if (int rc = pf_tc_pack_weights(c, L->params, st)) return rc; }
+    if (c->wm) { if (int rc = pf_wm_pack_weights(c, L->params, st)) return rc; }
     if (c->tc_gemm) return pf_tt_pack_weights(c, L->params, st);
     return 0;
 }

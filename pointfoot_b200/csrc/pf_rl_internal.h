@@ -37,6 +37,7 @@ struct pf_rl_ctx {
     double* norm_part;                          // [norm_blocks] grad-norm^2 partials
     int norm_blocks;
     void* tc;                                   // opaque state of the tensor-core path (pf_mlp_tc.cu), or NULL
+    void* wm;                                   // opaque state of the register-resident small-net path (pf_mlp_wm.cu), or NULL
     void* tc_gemm;                              // opaque state of the tensor-core training GEMM (pf_gemm_tc.cu), or NULL
 };
 
@@ -51,6 +52,14 @@ int pf_tc_mlp_forward(pf_rl_ctx* c, int net, const float* params, const float* x
 // PPO.act of both nets + Normal sample / log-prob + rollout-storage writes in ONE launch (when pf_tc_act_fusable).
 int pf_tc_act_fusable(const pf_rl_ctx* c);
 int pf_tc_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
+              int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st);
+
+// ---- register-resident warp-MMA path for small nets (pf_mlp_wm.cu); same contracts as the pf_tc_* calls above ----
+int pf_wm_create(pf_rl_ctx* c);                                   // sets c->wm when both nets qualify (else leaves it NULL, returns 0)
+void pf_wm_destroy(pf_rl_ctx* c);
+int pf_wm_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st);
+int pf_wm_mlp_forward(pf_rl_ctx* c, int net, const float* x, long long ldx, int rows, float* out, float* copy_to, cudaStream_t st);
+int pf_wm_act(pf_rl_ctx* c, const float* params, const float* obs, const float* critic_obs, const pf_rl_storage* storage,
               int t_row, int64_t policy_step, float* actions_out, float* values_out, float* logp_out, cudaStream_t st);
 
 // ---- GEMM contract of the fp32 kernel (pf_rl.cu) ----

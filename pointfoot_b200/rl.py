@@ -234,6 +234,8 @@ class PPO:
         with torch.cuda.device(self.device):
             capi.check(self._lib.pf_rl_create(C.byref(P), C.byref(ctx)), "pf_rl_create")
         self._ctx = ctx
+        # which kernels serve act / inference / evaluate (include/pointfoot_b200.h: pf_rl_inference_path)
+        self.inference_path = {0: "fp32", 1: "tcgen05", 2: "warp_mma"}[self._lib.pf_rl_inference_path(ctx)]
         ac.bind(self._lib, ctx)
         d = shard.dist_or_none()
         if d:                                      # every shard starts from rank 0's initial parameters
@@ -547,7 +549,11 @@ class BenchPolicy:
         self.alg.init_storage(env.num_envs, cfg["runner"]["num_steps_per_env"], [env.num_obs], [env.num_privileged_obs],
                               [env.num_actions])
         self.precision = precision
-        self.dtype_name = "bf16 (tcgen05 MLP, fp32 accumulate) + f32 env" if precision == "bf16" else "f32"
+        path = self.alg.inference_path
+        self.kernel_name = {"fp32": "pf_sgemm_kernel chain + pf_act_sample_kernel", "tcgen05": "pf_mlp_tc_kernel",
+                            "warp_mma": "pf_mlp_wm_kernel"}[path]
+        self.dtype_name = {"fp32": "f32", "tcgen05": "bf16 (tcgen05 MLP, fp32 accumulate) + f32 env",
+                           "warp_mma": "bf16 (register-resident warp-MMA MLP, fp32 accumulate) + f32 env"}[path]
         n_layers = len(self.ac.actor_dims) - 1 + len(self.ac.critic_dims) - 1
         self.launches_per_act = 1 if precision == "bf16" else n_layers + 3      # bf16: ONE fused tcgen05 launch
         self.t = 0

@@ -21,6 +21,45 @@ def test_tcgen05_mlp_act_matches_oracle_bf16(hidden, nc, n):
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
 
 
+@pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 1), ((128, 64, 32), 27, 15), ((128, 64, 32), 27, 16), ((128, 64, 32), 27, 17),
+                                         ((128, 64, 32), 27, 300), ((128, 64, 32), 27, 4097), ((128, 64, 32), 27, 50001),
+                                         ((64, 32), 27, 333), ((64, 32), 96, 1000), ((16,), 27, 77), ((32, 16, 16, 16, 16), 100, 130)])
+def test_warp_mma_small_net_act_matches_oracle_bf16(hidden, nc, n):
+    """Small nets (the flat policy) run register-resident on warp-level MMAs (pf_mlp_wm.cu): same bar as the tcgen05 path,
+    row counts around the 16-row task size, input widths that need padding, 1 to 5 hidden layers"""
+    ppo, _ = parity_rl.make_pair(8, 27, nc, list(hidden), T=2, precision="bf16")
+    try:
+        assert ppo.inference_path == "warp_mma"
+    finally:
+        ppo.close()
+    parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
+
+
+@pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 300), ((128, 64, 32), 27, 50001)])
+def test_tcgen05_path_still_serves_small_nets_when_asked(hidden, nc, n, monkeypatch):
+    """PF_RL_WM=0: the compact tcgen05 variant (two CTAs per SM) on the flat nets"""
+    monkeypatch.setenv("PF_RL_WM", "0")
+    ppo, _ = parity_rl.make_pair(8, 27, nc, list(hidden), T=2, precision="bf16")
+    try:
+        assert ppo.inference_path == "tcgen05"
+    finally:
+        ppo.close()
+    parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
+
+
+def test_path_selection():
+    for hidden, nc, want in (((512, 256, 128), 148, "tcgen05"), ((128, 64, 32), 148, "tcgen05"), ((100, 50), 27, "tcgen05"),
+                             ((128, 64, 32), 27, "warp_mma")):
+        ppo, _ = parity_rl.make_pair(8, 27, nc, list(hidden), T=2, precision="bf16")
+        try:
+            assert ppo.inference_path == want, (hidden, nc)
+        finally:
+            ppo.close()
+    ppo, _ = parity_rl.make_pair(8, 27, 27, [128, 64, 32], T=2, precision="fp32")
+    assert ppo.inference_path == "fp32"
+    ppo.close()
+
+
 def test_gae_bit_exact():
     parity_rl.run_gae_exact(num_envs=1000, T=24)
     parity_rl.run_gae_exact(num_envs=1, T=3, seed=5)
