@@ -537,6 +537,41 @@ def measure_workload(w, args, flush, barrier, peaks, device, min_seconds, e2e_st
     return out, post_r, act_r
 
 
+def runner_learn_fps(task, num_envs, device, iters=4, precision="bf16"):
+    """OnPolicyRunner.learn() -- the loop a user of legged_gym runs -- timed by ITS OWN clocks (runner.log's Perf/collection time and
+    Perf/learning_time, on_policy_runner.py:96-110): eager Python loop, one env.step + PPO.act + process_env_step per step, synthetic
+    physics.  Median of ``iters`` iterations after one warm-up iteration."""
+    from pointfoot_b200 import config, rl
+    from pointfoot_b200.env import PointFoot
+    cfg = config.PointFootFlatCfg() if task == "pointfoot_flat" else config.PointFootRoughCfg()
+    cfg.env.num_envs = num_envs
+    tcfg = config.class_to_dict(config.PointFootFlatCfgPPO() if task == "pointfoot_flat" else config.PointFootRoughCfgPPO())
+    env = PointFoot(cfg, None, None, device, True, seed=1)
+    old = os.environ.get("PF_RL_PRECISION")
+    os.environ["PF_RL_PRECISION"] = precision
+    try:
+        runner = rl.OnPolicyRunner(env, tcfg, None, device)
+    finally:
+        if old is None:
+            os.environ.pop("PF_RL_PRECISION", None)
+        else:
+            os.environ["PF_RL_PRECISION"] = old
+    times = []
+    for it in range(iters + 1):
+        runner.learn(1)
+        if it:
+            times.append(runner.last_times)
+    runner.alg.close()
+    env.close()
+    col = sorted(t[0] for t in times)[len(times) // 2]
+    lrn = sorted(t[1] for t in times)[len(times) // 2]
+    n = runner.num_steps_per_env * num_envs
+    return {"task": task, "num_envs": num_envs, "steps_per_iteration": runner.num_steps_per_env, "precision": precision,
+            "collection_s": col, "learning_s": lrn, "collection_env_steps_per_s": n / col, "total_fps": n / (col + lrn),
+            "what": "pointfoot_b200.rl.OnPolicyRunner.learn(): wall clock of the runner's own timers, eager Python loop (not the CUDA-graph "
+                    "step of `value`), synthetic physics"}
+
+
 def ppo_iteration(n_per_gpu, task, precision, device, rank, world, iters=3):
     """BASELINE.json configs[3]: 24 steps x N envs of PPO.act + process_env_step on synthetic observations (the rollout's
     RL-side bookkeeping), compute_returns (GAE), update (5 epochs x 4 minibatches), CUDA events per phase, median of
@@ -693,6 +728,11 @@ def run_b200(args):
             ppo.append(ppo_iteration(32768, "rough", "bf16", device, rank, world, iters=2))
         torch.cuda.empty_cache()
 
+    # ---- the reference's own training loop: OnPolicyRunner.learn() with its own timers ----
+    runner_learn = None
+    if not args.no_ppo and world == 1:
+        runner_learn = runner_learn_fps(args.task, args.num_envs, device)
+
     if rank == 0:
         total_envs = args.num_envs * world
         cfg = bench_config(args.task, args.num_envs, world, not args.no_policy)
@@ -705,7 +745,7 @@ def run_b200(args):
                                  if args.l2 == "flush" else "DIAGNOSTIC RUN, caches hot: not a valid bench line"},
                 "clocks": clocks, "gpu_launches": launches * args.steps * head["rounds"], "gpu_launches_per_step": launches,
                 "roofline": post_r, "roofline_act": act_r, "value_fp32": value_fp32,
-                "e2e": dict(head["e2e"], api=E2E_API), "sweep": sweep, "ppo_iteration": ppo}
+                "e2e": dict(head["e2e"], api=E2E_API), "sweep": sweep, "ppo_iteration": ppo, "runner_learn": runner_learn}
         if not args.no_eager and world == 1:
             try:
                 line["cuda_eager_baseline"] = cuda_eager_steps_per_sec(args.task, total_envs, device, flush)

@@ -479,6 +479,7 @@ class OnPolicyRunner:
             stop = time.time()
             learn_time = stop - start
             self.last_losses = (mean_value_loss, mean_surrogate_loss)
+            self.last_times = (collection_time, learn_time)          # what runner.log() calls Perf/collection time, Perf/learning_time
             if self.log_dir is not None:
                 self.log(locals())
                 if it % self.save_interval == 0:
