@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import rsl_rl_ref
+from oracle import ref_harness, rsl_rl_ref
 
 
 @pytest.mark.parametrize("n", [1, 2, 5, 64, 1000, 98304])
@@ -102,3 +102,31 @@ def test_export_policy_as_jit_from_a_reference_style_checkpoint(tmp_path):
     m = torch.jit.load(file)
     x = torch.randn(5, 27)
     assert torch.equal(m(x), ac.act_inference(x))
+
+
+def test_logger_records_like_the_reference(tmp_path, capsys):
+    """legged_gym/utils/logger.py:36-133, data side: same keys, the rewards weighted by the episode count, the headless plot"""
+    import numpy as np
+    import torch
+    from pointfoot_b200.logger import Logger
+    lg = Logger(0.02)
+    for i in range(5):
+        lg.log_states({"dof_pos": 0.1 * i, "base_vel_x": torch.tensor(float(i)), "contact_forces_z": np.array([1.0 * i, 2.0])})
+    lg.log_rewards({"rew_tracking_lin_vel": torch.tensor(0.5), "terrain_level": torch.tensor(3.0)}, 2)
+    lg.log_rewards({"rew_tracking_lin_vel": torch.tensor(0.25)}, 2)
+    assert lg.num_episodes == 4 and list(lg.rew_log) == ["rew_tracking_lin_vel"] and lg.rew_log["rew_tracking_lin_vel"] == [1.0, 0.5]
+    lg.print_rewards()
+    out = capsys.readouterr().out
+    assert " - rew_tracking_lin_vel: 0.375" in out and "Total number of episodes: 4" in out
+    path = lg.plot_states(str(tmp_path / "states"))
+    z = np.load(str(tmp_path / "states.npz"))
+    assert path.startswith(str(tmp_path)) and z["contact_forces_z"].shape == (5, 2) and np.allclose(z["time"], np.linspace(0, 0.1, 5))
+    if ref_harness.reference_available():
+        # same public methods as the reference class (read from its source: matplotlib is not installed here)
+        import ast
+        src = open(ref_harness.REFERENCE_ROOT + "/legged_gym/utils/logger.py").read()
+        cls = [n for n in ast.parse(src).body if isinstance(n, ast.ClassDef) and n.name == "Logger"][0]
+        names = {f.name for f in cls.body if isinstance(f, ast.FunctionDef) and not f.name.startswith("_")}
+        assert names <= set(dir(Logger))
+    lg.reset()
+    assert not lg.state_log and not lg.rew_log
