@@ -399,7 +399,11 @@ static int wm_launch(pf_rl_ctx* c, WmArgs& a, cudaStream_t st) {
     a.stage_stride = wm_stage_stride(k0);
     const size_t smem = wm_smem(nets, a.nnets, k0);
     const int ntasks = a.nnets * a.tiles;
-    const int grid = ntasks < 2 * c->num_sms ? ntasks : 2 * c->num_sms;
+    // CTAs: full ones (8 tasks, one per warp) rather than one task per CTA -- every CTA stages both nets' weights (57 KB), and
+    // at 4,096 rows 296 CTAs doing that for 512 tasks cost more than the SMs they fill (PF_WM_SPREAD=1: the old spreading)
+    static const int spread = [] { const char* e = getenv("PF_WM_SPREAD"); return e ? atoi(e) : 0; }();
+    int grid = spread ? ntasks : (ntasks + WM_WARPS - 1) / WM_WARPS;
+    if (grid > 2 * c->num_sms) grid = 2 * c->num_sms;
     return pf_launch_pdl(pf_mlp_wm_kernel, dim3(grid), dim3(WM_WARPS * 32), smem, st, a) == cudaSuccess
                ? 0 : wm_fail(2, "pf_mlp_wm_kernel: launch failed");
 }
