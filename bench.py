@@ -89,6 +89,8 @@ def bench_config(task, n_per_gpu, world, policy=True):
             "num_envs_per_gpu": n_per_gpu, "policy": "ActorCritic [128,64,32] ELU (flat) / [512,256,128] (rough), act + evaluate + "
             "sample + log-prob" if policy else "none",
             "physics": "excluded (Isaac Gym not installable): synthetic state tensors",
+            "terrain": "rough task: int16[1300,2100] field generated on the GPU by pf_terrain_generate (reference curriculum layout, "
+                       "10 x 20 sub-terrains) before any timed region; flat task: plane",
             "parallelism": f"env-sharded x{world} (rollout: no data-path collective; PPO.update: NCCL all-reduce of the flat "
                            "gradient + loss statistics per optimizer step, see ppo_iteration)"}
 
@@ -293,6 +295,23 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+_TERRAIN = {}
+
+
+def rough_terrain(device):
+    """The height field of the rough task: generated ONCE per process on the GPU by pointfoot_b200.terrain.Terrain (the reference's
+    curriculum layout, terrain.py:85-92: 10 x 20 sub-terrains of 8 m, 25 m border -> int16[1300, 2100]) -- outside every timed region,
+    like Terrain.__init__ in the reference.  Returns (height_samples, terrain_origins fp32[10, 20, 3]) as synth.make_state expects."""
+    key = str(device)
+    if key not in _TERRAIN:
+        import torch
+        from pointfoot_b200 import config
+        from pointfoot_b200.terrain import Terrain
+        t = Terrain(config.PointFootRoughCfg.terrain(), 4096, device=device, seed=1)
+        _TERRAIN[key] = (t.heightsamples.cpu(), torch.from_numpy(t.env_origins).to(torch.float))
+    return _TERRAIN[key]
+
+
 class Workload:
     """env + policy + the CUDA-graphed step for one (task, envs per GPU, scan grid) on this rank."""
 
@@ -304,6 +323,8 @@ class Workload:
         from pointfoot_b200.env import PointFoot, GraphedStep
         self.task, self.num_envs, self.world = task, num_envs, world
         cfg, train_cfg = make_cfgs(task, num_envs, grid187)
+        if task == "pointfoot_rough" and terrain is None:
+            terrain = rough_terrain(device)
         state = synth.make_state(num_envs, task, seed=1, env_id_offset=rank * num_envs, terrain=terrain)
         if task == "pointfoot_rough":     # terrain_types is a function of the GLOBAL env id (point_foot.py:981-983)
             gid = np.arange(num_envs) + rank * num_envs
@@ -706,8 +727,7 @@ def run_b200(args):
                 sweep.append(dict(head, scaling="headline"))
                 continue
             if task == "pointfoot_rough" and terrain is None:
-                from pointfoot_b200 import synth
-                terrain = synth.make_heightfield(1)
+                terrain = rough_terrain(device)
             ws = Workload(task, n, device, rank, world, grid187=g187, terrain=terrain if task == "pointfoot_rough" else None)
             r, _, _ = measure_workload(ws, args, flush, barrier, peaks, device, min(args.min_seconds, 0.25), 30)
             if world > 1:

@@ -192,6 +192,7 @@ int pf_debug_timeline(unsigned long long* device_log);
  * capture counts once; replays are the caller's to multiply).  bench.py's `gpu_launches` is measured with it. */
 unsigned long long pf_debug_launch_count(void);
 int pf_rl_debug_timeline(unsigned long long* device_log);
+int pf_tt_debug_timeline(unsigned long long* device_log);   /* the same for the training GEMM's translation unit (tools/train_trace.py) */
 
 /* PF:590-611: random push forces into forces[N,B,3] (body 0 rows; everything else zeroed).
  * max_push_force = base_mass.mean() * max_push_vel_xy / sim_dt, evaluated by the host in double (PF:592-596). */

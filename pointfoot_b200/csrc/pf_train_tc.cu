@@ -40,7 +40,8 @@ void pf_set_error(const char* msg);
 #define TT_STAGE_BYTES (TT_A_BYTES + TT_B_BYTES)
 #define TT_STAGES 4
 #define TT_MAXPROB 4
-#define TT_EPI_WARPS 8                 // 4 TMEM lane quarters x 2 column halves
+#define TT_EPI_WARPS 16                // 4 TMEM lane quarters x 4 column groups: the epilogue (ELU + pack + store), not the MMAs, bounds a tile
+#define TT_EPI_H (TT_EPI_WARPS / 4)
 #define TT_MMA_WARP TT_EPI_WARPS
 #define TT_LOAD_WARP (TT_EPI_WARPS + 1)
 #define TT_THREADS ((TT_EPI_WARPS + 2) * 32)
@@ -124,7 +125,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pf_timeline_raw_if(blockIdx.x == 0 && tid == 0, 0x340);
     pf_grid_dep_wait();              // everything above ran under the predecessor's tail; its outputs are visible from here on
+    pf_timeline_raw_if(blockIdx.x == 0 && tid == 0, 0x341);
 
     if (warp == TT_LOAD_WARP) {
         // ================================================================ loader: the whole warp issues a stage's copies
@@ -133,6 +136,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
             const TtTile T = tt_tile(g, t);
             const TtProb& P = g.p[T.pi];
             const int mode = P.mode;
+            pf_timeline_raw_if(blockIdx.x == 0 && lane == 0, 0x300 + P.mode);          // loader: tile begins
             for (int s = 0; s < T.nst; ++s, ++it) {
                 const uint32_t slot = it % TT_STAGES, gs = T.s_beg + s;
                 const int kthis = (int)gs == P.k_stages - 1 ? P.k_last : TT_KS;
@@ -180,13 +184,16 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
             const uint64_t a_step = a_mn ? 16u : (2u * TT_TH * 16u) >> 4;            // K = 16 further, in 16-byte units
             const uint64_t b_step = b_mn ? 16u : (2u * (uint32_t)P.b_th * 16u) >> 4;
             const uint32_t acc = j & 1u, td = tmem_base + acc * 256u;
+            pf_timeline_raw_if(blockIdx.x == 0 && lane == 0, 0x310);                     // MMA: tile begins (waits for its accumulator)
             if (j >= 2) mbar_wait(acce0 + 8 * acc, ((j >> 1) - 1u) & 1u);            // the epilogue has drained this accumulator
             tc_fence_after();
+            pf_timeline_raw_if(blockIdx.x == 0 && lane == 0, 0x311);                     // MMA: accumulator free
             for (int s = 0; s < T.nst; ++s, ++it) {
                 const uint32_t slot = it % TT_STAGES;
                 const int nk16 = (T.s_beg + s == P.k_stages - 1 ? P.k_last : TT_KS) >> 4;
                 mbar_wait(full0 + 8 * slot, (it / TT_STAGES) & 1u);
                 tc_fence_after();
+                pf_timeline_raw_if(blockIdx.x == 0 && lane == 0 && (s == 0 || s == T.nst - 1), s == 0 ? 0x312 : 0x313);   // first / last stage landed
                 if (elect_one()) {
                     const uint32_t base = smem_u32(smem + slot * TT_STAGE_BYTES);
                     const uint64_t ad = make_desc(base, a_lbo, a_sbo), bd = make_desc(base + TT_A_BYTES, b_lbo, b_sbo);
@@ -207,17 +214,29 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
             const TtTile T = tt_tile(g, t);
             const TtProb& P = g.p[T.pi];
             const int mode = P.mode, mt = T.mt, w = T.w;
+            // the problem's fields used per element, ONCE per tile into registers: `P` is a run-time index into the grid constant, and
+            // the compiler re-issued a constant load per use -- ~100 dependent LDCs per group of 32 columns made the epilogue
+            // 10-13 us per tile against 2-3 us of loads + MMAs (tools/train_trace.py, profiles/r2p_train_trace_rough4096_before.txt)
+            const int n_valid = P.n_valid, out_cbs = P.out_cbs, y_cbs = P.y_cbs, n_tiles = P.n_tiles, m_tiles = P.m_tiles;
+            const int rows_valid = P.rows_valid, ld_f32 = P.ld_f32, b_th = P.b_th;
+            const bool do_elu = P.elu != 0, do_ones = P.ones != 0;
+            unsigned char* const out_pk = P.out_pk;
+            const unsigned char* const y_pk = P.y_pk;
+            float* const out_f32 = P.out_f32;
+            float* const part = P.part;
             const uint32_t acc = j & 1u;
+            pf_timeline_raw_if(blockIdx.x == 0 && tid == 0, 0x320);                      // epilogue: waits for the accumulator
             mbar_wait(accf0 + 8 * acc, (j >> 1) & 1u);
             tc_fence_after();
+            pf_timeline_raw_if(blockIdx.x == 0 && tid == 0, 0x321);                      // epilogue: accumulator complete
             const uint32_t trow = tmem_base + acc * 256u + ((uint32_t)(q * 32) << 16);
-            const int n0 = T.jn * (mode == TT_FWD ? P.b_th : 256);
+            const int n0 = T.jn * (mode == TT_FWD ? b_th : 256);
             // forward into a packed tensor: the last N tile also writes the columns behind the real ones (ones, zero padding)
-            const int cols_end = (mode == TT_FWD && P.out_pk && T.jn == P.n_tiles - 1) ? P.out_cbs * 8 - n0 : w;
+            const int cols_end = (mode == TT_FWD && out_pk && T.jn == n_tiles - 1) ? out_cbs * 8 - n0 : w;
             // this warp's column range: groups of 32 columns, alternating between the two halves
             const int ngroups = (cols_end + 31) >> 5;
             bool released = false;
-            for (int gi = h; gi < ngroups || !released; gi += 2) {
+            for (int gi = h; gi < ngroups || !released; gi += TT_EPI_H) {
                 const int c0 = gi * 32;
                 uint32_t v[32];
                 const bool real = gi < ngroups && c0 < w;
@@ -232,7 +251,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
                     for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
                 }
                 // the accumulator is free once this warp's last real group sits in registers
-                if (!released && (gi + 2) * 32 >= w) {
+                if (!released && (gi + TT_EPI_H) * 32 >= w) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acce0 + 8 * acc);
@@ -240,57 +259,80 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
                 }
                 if (gi >= ngroups) break;
                 if (mode == TT_WGRAD) {
-                    float4* dst = reinterpret_cast<float4*>(P.part + ((((size_t)T.z * P.m_tiles + mt) * P.n_tiles + T.jn) * 128 + row) * 256 + c0);
+                    float4* dst = reinterpret_cast<float4*>(part + ((((size_t)T.z * m_tiles + mt) * n_tiles + T.jn) * 128 + row) * 256 + c0);
                     const int nq = min(32, w - c0) >> 2;
 #pragma unroll
                     for (int qq = 0; qq < 8; ++qq)
                         if (qq < nq) dst[qq] = make_float4(__uint_as_float(v[4 * qq]), __uint_as_float(v[4 * qq + 1]), __uint_as_float(v[4 * qq + 2]), __uint_as_float(v[4 * qq + 3]));
-                } else if (P.out_f32) {       // forward, last layer: plain fp32 rows (mu / value)
+                } else if (out_f32) {       // forward, last layer: plain fp32 rows (mu / value)
                     const int grow = mt * TT_TH + row;
-                    if (grow < P.rows_valid) {
+                    if (grow < rows_valid) {
 #pragma unroll
                         for (int jj = 0; jj < 32; ++jj)
-                            if (n0 + c0 + jj < P.n_valid) P.out_f32[(size_t)grow * P.ld_f32 + n0 + c0 + jj] = __uint_as_float(v[jj]);
+                            if (n0 + c0 + jj < n_valid) out_f32[(size_t)grow * ld_f32 + n0 + c0 + jj] = __uint_as_float(v[jj]);
                     }
                 } else {
                     const int ncb = min(4, (cols_end - c0 + 7) >> 3);
+                    uint4 yv[4];                  // dgrad: the group's four saved-activation units, all in flight before the first use
+                    if (mode == TT_DGRAD) {
+#pragma unroll
+                        for (int qq = 0; qq < 4; ++qq) {
+                            const int cb = (n0 + c0) / 8 + qq;
+                            yv[qq] = make_uint4(0u, 0u, 0u, 0u);
+                            if (qq < ncb && cb < out_cbs)
+                                yv[qq] = __ldg(reinterpret_cast<const uint4*>(y_pk + ((size_t)mt * y_cbs + cb) * (TT_TH * 16) + row * 16));
+                        }
+                    }
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq) {
                         if (qq >= ncb) continue;
                         const int cb = (n0 + c0) / 8 + qq;
-                        if (cb >= P.out_cbs) continue;
+                        if (cb >= out_cbs) continue;
                         float x[8];
 #pragma unroll
                         for (int i = 0; i < 8; ++i) x[i] = __uint_as_float(v[8 * qq + i]);
                         if (mode == TT_FWD) {
+                            if (cb * 8 + 8 <= n_valid) {          // (warp-uniform) a block of real columns: no per-element tests
+                                if (do_elu) {
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const int n = cb * 8 + i;
-                                x[i] = n < P.n_valid ? (P.elu ? tt_elu(x[i]) : x[i]) : ((P.ones && n < P.n_valid + 2) ? 1.0f : 0.0f);
+                                    for (int i = 0; i < 8; ++i) x[i] = tt_elu(x[i]);
+                                }
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    const int n = cb * 8 + i;
+                                    x[i] = n < n_valid ? (do_elu ? tt_elu(x[i]) : x[i]) : ((do_ones && n < n_valid + 2) ? 1.0f : 0.0f);
+                                }
                             }
                         } else {              // dgrad: times ELU'(y) recovered from the saved activation: y > 0 ? 1 : y + 1
-                            const uint4 yy = *reinterpret_cast<const uint4*>(P.y_pk + ((size_t)mt * P.y_cbs + cb) * (TT_TH * 16) + row * 16);
+                            const uint4 yy = yv[qq];
                             const uint32_t yw[4] = {yy.x, yy.y, yy.z, yy.w};
+                            const bool full = cb * 8 + 8 <= n_valid;          // (warp-uniform)
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const float y = __uint_as_float((i & 1) ? (yw[i >> 1] & 0xffff0000u) : (yw[i >> 1] << 16));
-                                const int n = cb * 8 + i;
-                                x[i] = n < P.n_valid ? x[i] * (y > 0.0f ? 1.0f : y + 1.0f) : 0.0f;
+                                const float d = x[i] * (y > 0.0f ? 1.0f : y + 1.0f);
+                                x[i] = (full || cb * 8 + i < n_valid) ? d : 0.0f;
                             }
                         }
-                        *reinterpret_cast<uint4*>(P.out_pk + ((size_t)mt * P.out_cbs + cb) * (TT_TH * 16) + row * 16) =
+                        *reinterpret_cast<uint4*>(out_pk + ((size_t)mt * out_cbs + cb) * (TT_TH * 16) + row * 16) =
                             make_uint4(tt_pack2(x[0], x[1]), tt_pack2(x[2], x[3]), tt_pack2(x[4], x[5]), tt_pack2(x[6], x[7]));
                     }
                 }
             }
         }
     }
+    pf_timeline_raw_if(blockIdx.x == 0 && (tid == 0 || tid == TT_MMA_WARP * 32 || tid == TT_LOAD_WARP * 32), 0x330 + (tid == 0 ? 0 : tid == TT_MMA_WARP * 32 ? 1 : 2));
     tc_fence_before();
     __syncthreads();
     if (warp == TT_MMA_WARP) {
         __syncwarp();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
+}
+
+extern "C" int pf_tt_debug_timeline(unsigned long long* device_log) {       // diagnostic builds only (tools/train_trace.py)
+    return pf_timeline_install(device_log) == cudaSuccess ? 0 : 1;
 }
 
 // ------------------------------------------------------------------------------------------------ small kernels

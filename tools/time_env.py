@@ -19,6 +19,9 @@ def main():
         for n in sizes:
             st = synth.make_state(n, task, seed=1, terrain=terrain)
             env = parity.EnvUnderTest(task, st, "cuda")
+            if os.environ.get("PF_KEEP_MH", "0") == "0":       # as pointfoot_b200.env.PointFoot does by default: measured_heights not materialised
+                env.t["measured_heights"] = None
+                env.b.measured_heights = None
             a = st["actions"].cuda()
             lib, ctx, b = env.lib, env.ctx, env.b
             stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
