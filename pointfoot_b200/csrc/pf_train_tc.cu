@@ -34,11 +34,13 @@
 void pf_set_error(const char* msg);
 
 #define TT_TH 128                      // rows per tile of every activation / gradient tensor (= UMMA M)
-#define TT_KS 64                       // K elements per pipeline stage
-#define TT_A_BYTES 16384               // staged A tile: 128 x 64 bf16 in either orientation
-#define TT_B_BYTES 32768               // staged B tile: up to 256 x 64 bf16
+#define TT_KS 128                      // K elements per pipeline stage = the tile height: a stage of an MN-major operand (wgrad's
+                                       // dY^T and X: batch rows are K) is then ONE contiguous bulk copy of whole col blocks; with 64 it was
+                                       // up to 48 copies of 1 KB per stage and 0.7 us per 48 KB (profiles/r2p_train_trace_*.txt)
+#define TT_A_BYTES 32768               // staged A tile: 128 x 128 bf16 in either orientation
+#define TT_B_BYTES 65536               // staged B tile: up to 256 x 128 bf16
 #define TT_STAGE_BYTES (TT_A_BYTES + TT_B_BYTES)
-#define TT_STAGES 4
+#define TT_STAGES 2
 #define TT_MAXPROB 4
 #define TT_EPI_WARPS 16                // 4 TMEM lane quarters x 4 column groups: the epilogue (ELU + pack + store), not the MMAs, bounds a tile
 #define TT_EPI_H (TT_EPI_WARPS / 4)
@@ -144,28 +146,28 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
                 const uint32_t fb = full0 + 8 * slot;
                 const uint32_t a_dst = smem_u32(smem + slot * TT_STAGE_BYTES), b_dst = a_dst + TT_A_BYTES;
                 const int a_ncb = mode == TT_WGRAD ? min(16, P.a_cbs - T.mt * 16) : kthis >> 3;
-                const uint32_t a_bytes = mode == TT_WGRAD ? (uint32_t)a_ncb * (uint32_t)kthis * 16u : (uint32_t)a_ncb * TT_TH * 16u;
-                const uint32_t b_bytes = mode == TT_FWD ? (uint32_t)(kthis >> 3) * (uint32_t)P.b_th * 16u : (uint32_t)(T.w >> 3) * (uint32_t)kthis * 16u;
+                const uint32_t a_bytes = (uint32_t)a_ncb * TT_TH * 16u;      // whole col blocks of the 128-row tile, either orientation
+                const uint32_t b_bytes = mode == TT_FWD ? (uint32_t)(kthis >> 3) * (uint32_t)P.b_th * 16u
+                                       : mode == TT_WGRAD ? (uint32_t)(T.w >> 3) * TT_TH * 16u : (uint32_t)(T.w >> 3) * (uint32_t)kthis * 16u;
                 if (lane == 0) mbar_expect_tx(fb, a_bytes + b_bytes);
                 __syncwarp();
                 // ---- A ----
                 if (mode != TT_WGRAD) {           // K-major rows of X / dY: the stage's col blocks are contiguous
-                    if (lane == 0) bulk_g2s(a_dst, P.a + ((size_t)T.mt * P.a_cbs + (size_t)gs * 8) * (TT_TH * 16), a_bytes, fb);
-                } else {                          // MN-major: 64 batch rows of each of the M tile's col blocks
-                    const int rt = gs >> 1, r0 = (gs & 1) * TT_KS;
-                    for (int cb = lane; cb < a_ncb; cb += 32)
-                        bulk_g2s(a_dst + cb * 1024, P.a + ((size_t)rt * P.a_cbs + (size_t)T.mt * 16 + cb) * (TT_TH * 16) + r0 * 16,
-                                 (uint32_t)kthis * 16u, fb);
+                    if (lane == 0) bulk_g2s(a_dst, P.a + ((size_t)T.mt * P.a_cbs + (size_t)gs * (TT_KS / 8)) * (TT_TH * 16), a_bytes, fb);
+                } else {                          // MN-major: row tile gs (a stage IS a row tile), the M tile's col blocks: contiguous
+                    if (lane == 0) bulk_g2s(a_dst, P.a + ((size_t)gs * P.a_cbs + (size_t)T.mt * 16) * (TT_TH * 16), a_bytes, fb);
                 }
                 // ---- B ----
                 if (mode == TT_FWD) {             // K-major rows of W: tile jn, the stage's col blocks
-                    if (lane == 0) bulk_g2s(b_dst, P.b + ((size_t)T.jn * P.b_cbs + (size_t)gs * 8) * ((size_t)P.b_th * 16), b_bytes, fb);
+                    if (lane == 0) bulk_g2s(b_dst, P.b + ((size_t)T.jn * P.b_cbs + (size_t)gs * (TT_KS / 8)) * ((size_t)P.b_th * 16), b_bytes, fb);
+                } else if (mode == TT_WGRAD) {    // MN-major batch rows of X: row tile gs, the N tile's col blocks: contiguous
+                    if (lane == 0) bulk_g2s(b_dst, P.b + ((size_t)gs * P.b_cbs + (size_t)T.jn * 32) * (TT_TH * 16), b_bytes, fb);
                 } else {
-                    // MN-major: rows [gs*64, +kthis) of the source (W rows for dgrad, batch rows of X for wgrad), col blocks of tile jn
-                    const int th = mode == TT_DGRAD ? P.b_th : TT_TH;
+                    // dgrad, MN-major: rows [gs*128, +kthis) of W (tile height b_th), col blocks of tile jn; a col block is TT_KS rows apart in the stage
+                    const int th = P.b_th;
                     const int row = gs * TT_KS, rt = row / th, r0 = row - rt * th;
                     for (int cb = lane; cb < (T.w >> 3); cb += 32)
-                        bulk_g2s(b_dst + cb * 1024, P.b + ((size_t)rt * P.b_cbs + (size_t)T.jn * 32 + cb) * ((size_t)th * 16) + r0 * 16,
+                        bulk_g2s(b_dst + cb * (TT_KS * 16), P.b + ((size_t)rt * P.b_cbs + (size_t)T.jn * 32 + cb) * ((size_t)th * 16) + r0 * 16,
                                  (uint32_t)kthis * 16u, fb);
                 }
             }
@@ -179,8 +181,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1) pf_train_gemm_kernel(const __gr
             const bool a_mn = P.mode == TT_WGRAD, b_mn = P.mode != TT_FWD;
             const uint32_t idesc = tt_idesc(T.w, a_mn, b_mn);
             // descriptor strides (bytes): K-major = (LBO: next 8 K columns, SBO: next 8 rows); MN-major = (LBO: next 8 K rows, SBO: next 8 MN)
-            const uint32_t a_lbo = a_mn ? 128u : TT_TH * 16u, a_sbo = a_mn ? 1024u : 128u;
-            const uint32_t b_lbo = b_mn ? 128u : (uint32_t)P.b_th * 16u, b_sbo = b_mn ? 1024u : 128u;
+            const uint32_t a_lbo = a_mn ? 128u : TT_TH * 16u, a_sbo = a_mn ? TT_KS * 16u : 128u;
+            const uint32_t b_lbo = b_mn ? 128u : (uint32_t)P.b_th * 16u, b_sbo = b_mn ? TT_KS * 16u : 128u;
             const uint64_t a_step = a_mn ? 16u : (2u * TT_TH * 16u) >> 4;            // K = 16 further, in 16-byte units
             const uint64_t b_step = b_mn ? 16u : (2u * (uint32_t)P.b_th * 16u) >> 4;
             const uint32_t acc = j & 1u, td = tmem_base + acc * 256u;
@@ -491,7 +493,7 @@ int pf_tt_create(pf_rl_ctx* c) {
     if (t->row_tiles < 1) t->row_tiles = 1;          // (a storage smaller than num_mini_batches: empty minibatches, as upstream)
     t->rows_p = t->row_tiles * TT_TH;
     t->num_sms = c->num_sms;
-    const int k_stages_batch = 2 * t->row_tiles;
+    const int k_stages_batch = t->row_tiles;             // wgrad: K = the batch, one stage per 128-row tile
     // tiles of all wgrad problems of one layer index (both nets): decides the split-K factor of that launch
     int tiles_at[PF_MAX_MLP_LAYERS] = {0};
     for (int k = 0; k < 2; ++k) {
