@@ -409,10 +409,14 @@ def time_call(fn, flush, n=20, warm=3):
     return tot / n
 
 
+STEP_KERNEL_SOURCES = ("pf_env.cu", "pf_env_core.cuh", "pf_rng.cuh", "pf_ctx.h", "pf_launch.h")
+
+
 def source_hash():
+    """hash of the files that define the step kernels (scan, step, finalize): what `roofline.traffic` depends on"""
     h = hashlib.sha256()
     d = os.path.join(ROOT, "pointfoot_b200", "csrc")
-    for f in sorted(os.listdir(d)):
+    for f in STEP_KERNEL_SOURCES:
         with open(os.path.join(d, f), "rb") as fh:
             h.update(fh.read())
     return h.hexdigest()[:16]
