@@ -41,7 +41,7 @@ PF_HD void lr_pd_torque_elem(const pf_lr_params& P, const pf_lr_buffers& B, cons
 
 // ------------------------------------------------------------------------------------------------ height scan
 // LR:777-813 with the PRE-reset pose (the callback runs before reset_idx, LR:122-128): measured_heights[N,P]
-PF_HD void lr_scan_point(const pf_lr_params& P, const pf_lr_buffers& B, int e, int p, float zn, float wn, float bx, float by) {
+PF_HD float lr_scan_point(const pf_lr_params& P, const pf_lr_buffers& B, int e, int p, float zn, float wn, float bx, float by) {
     float h = 0.0f;                                                   // 'plane': zeros, LR:789-790
     if (P.terrain_kind == PF_TERRAIN_HEIGHTFIELD) {
         const float gx = B.height_points_xy[2 * p], gy = B.height_points_xy[2 * p + 1];
@@ -50,6 +50,7 @@ PF_HD void lr_scan_point(const pf_lr_params& P, const pf_lr_buffers& B, int e, i
         h = (float)lr_terrain_min3(P, B.height_samples, ox + bx, oy + by) * P.vertical_scale;
     }
     B.measured_heights[(size_t)e * P.num_height_points + p] = h;
+    return h;
 }
 
 // ------------------------------------------------------------------------------------------------ rewards
@@ -306,17 +307,18 @@ PF_HD void lr_reset_all_env(const pf_lr_params& P, const pf_lr_buffers& B, const
 }
 
 // LR:219-224: heights = clip(root_z - 0.5 - measured_heights, -1, 1) * scale; root z AFTER reset_idx, scan from BEFORE it
-PF_HD void lr_obs_height(const pf_lr_params& P, const pf_lr_buffers& B, const long long i, const uint32_t step) {
-    const int Pn = P.num_height_points;
-    const int e = (int)(i / Pn), p = (int)(i % Pn), base = P.num_obs - Pn;
-    float v = pf_clipf((B.root_states[(size_t)e * 13 + 2] - 0.5f) - B.measured_heights[i], -1.0f, 1.0f) * P.obs_scale_height;
+// `h` = the env's measured height at point p, `root_z` its root z (post-reset for the reference's result), `nkey` the env's
+// OBS_NOISE key (computed once per env by the caller)
+PF_HD void lr_obs_height(const pf_lr_params& P, const pf_lr_buffers& B, const int e, const int p, const float h, const float root_z,
+                         const uint32_t nkey) {
+    const int base = P.num_obs - P.num_height_points;
+    float v = pf_clipf((root_z - 0.5f) - h, -1.0f, 1.0f) * P.obs_scale_height;
     if (P.add_noise) {
         const float s = B.noise_scale_vec[base + p];
-        if (s != 0.0f) {
-            const uint32_t nkey = pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
-            v = v + (2.0f * pf_rng_uniform(nkey, (uint32_t)(base + p)) - 1.0f) * s;
-        }
+        if (s != 0.0f) v = v + (2.0f * pf_rng_uniform(nkey, (uint32_t)(base + p)) - 1.0f) * s;
     }
     B.obs_buf[(size_t)e * P.num_obs + base + p] = pf_clipf(v, -P.clip_obs, P.clip_obs);
 }
-
+PF_HD uint32_t lr_noise_key(const pf_lr_params& P, const int e, const uint32_t step) {
+    return pf_rng_env_key(pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE), (uint32_t)(P.env_id_offset + e));
+}

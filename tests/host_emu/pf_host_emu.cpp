@@ -139,8 +139,12 @@ extern "C" int pf_emu_lr_post_physics_step(const pf_lr_params* Pp, const pf_lr_b
             for (int p = 0; p < P.num_height_points; ++p) lr_scan_point(P, B, e, p, zn, wn, r[0], r[1]);
         }
     for (int e = 0; e < P.num_envs; ++e) lr_step_env(P, B, e, step, push);
-    if (P.measure_heights)
-        for (long long i = 0; i < (long long)P.num_envs * P.num_height_points; ++i) lr_obs_height(P, B, i, step);
+    if (P.measure_heights)          // LR:219-224 after reset_idx: post-reset root z against the pre-reset scan
+        for (int e = 0; e < P.num_envs; ++e) {
+            const uint32_t nkey = lr_noise_key(P, e, step);
+            for (int p = 0; p < P.num_height_points; ++p)
+                lr_obs_height(P, B, e, p, B.measured_heights[(size_t)e * P.num_height_points + p], B.root_states[(size_t)e * 13 + 2], nkey);
+        }
     lr_emu_finalize(P, B);
     return 0;
 }
