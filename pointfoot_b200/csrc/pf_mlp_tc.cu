@@ -2,10 +2,10 @@
 // Normal sample / log-prob of PPO.act and the rollout-storage writes fused into ONE persistent sm_100a kernel built
 // on tcgen05.mma with accumulators in TMEM.
 //
-//   * a work item is (net, tile of 128 rows): UMMA M = 128, cta_group::1, bf16 operands, fp32 accumulate; one CTA
+//   * a work item is (net, tile of 128 rows): UMMA M = 128, cta_group::1, fp16 operands, fp32 accumulate; one CTA
 //     per SM walks the items round-robin, so weights of the next item stream in under the tail of the current one;
 //   * activations never leave the SM and are never held whole: the output of a layer is produced in chunks of
-//     <= 128 columns (TMEM -> registers -> ELU -> bf16 -> shared memory, in the K-major core-matrix layout an A
+//     <= 128 columns (TMEM -> registers -> ELU -> fp16 -> shared memory, in the K-major core-matrix layout an A
 //     descriptor reads) and every chunk is consumed at once as a K-slice of the NEXT layer, whose accumulator
 //     (<= 256 columns) sits in the other half of TMEM.  Two 32 KB chunk buffers + the staged input rows are all the
 //     activation storage there is, which leaves ~110 KB for the weight ring;
@@ -13,18 +13,19 @@
 //     them, <= 8 KB tiles, so a tile is ONE contiguous bulk async copy (cp.async.bulk / TMA engine, completion by
 //     mbarrier transaction bytes) issued by a dedicated loader thread that runs up to 14 tiles ahead;
 //   * the bias add is one extra K = 16 MMA per accumulator against a constant "ones" operand (bias split in
-//     hi + lo bf16), so the epilogue is only ELU + pack;
+//     hi + lo fp16), so the epilogue is only ELU + pack;
 //   * warp roles: warps 0-7 run the epilogues (4 TMEM lane quarters x 2 column halves), warps 8-15 stage the input
-//     rows of the NEXT item (fp32 -> bf16 operand layout + the rollout-storage copy) as soon as the current item's
+//     rows of the NEXT item (fp32 -> fp16 operand layout + the rollout-storage copy) as soon as the current item's
 //     first layer has consumed its rows, warp 16 owns TMEM and issues the MMAs, warp 17 issues the bulk copies.
 //     They only meet at mbarriers; the schedule (which group waits for / signals which barrier, with which phase)
 //     is a small static PROGRAM built on the host.
 //
 // Shared-memory operand layout (no swizzle, "interleave"): 8 rows x 16 bytes core matrices, stored contiguously
-// (128 B); for an operand with R rows: element (r, k) of bf16 at  (k/8) * (R*16) + r*16 + (k%8)*2  bytes.
+// (128 B); for an operand with R rows: element (r, k) of fp16 at  (k/8) * (R*16) + r*16 + (k%8)*2  bytes.
 // UMMA descriptor: leading byte offset = R*16 (next 8 K-columns), stride byte offset = 128 (next 8 rows).
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -37,7 +38,8 @@ void pf_set_error(const char* msg);
 #define TC_CHUNK 128                         // columns of one activation chunk
 #define TC_ACHUNK_BYTES (TC_ROWS * TC_CHUNK * 2)
 #define TC_X0_LBO (TC_ROWS * 16 + 16)        // staged input: byte distance between 8-column blocks, padded (see tc_stage_item)
-#define TC_SLOT_BYTES 16384                  // weight ring slot = largest tile (N x K x 2 B: 256x32, 128x64, 64x128 ...)
+#define TC_SLOT_BYTES 32768                  // weight ring slot = largest tile (N x K x 2 B: 256x64, 128x128 ...), one CTA per SM
+#define TC_SLOT_BYTES_COMPACT 16384          // ... and in the compact variant (two CTAs per SM)
 #define TC_MAX_STAGES 16
 #define TC_X0_KSTEP ((2 * TC_X0_LBO) / 16)    // K = 16 further along the staged input, in descriptor units
 // Warp roles are template parameters of the kernel: kEpi epilogue warps (8 = 4 TMEM lane quarters x 2 column halves; the ELU is
@@ -109,7 +111,7 @@ static inline int pad16(int x) { return (x + 15) & ~15; }
 enum { TC_OUT_PLAIN = 0, TC_OUT_SAMPLE = 1, TC_OUT_VALUE = 2 };
 
 struct TcNetArgs {
-    const unsigned char* blob;   // packed bf16 weight + bias tiles
+    const unsigned char* blob;   // packed fp16 weight + bias tiles
     const float* x; long long ldx;
     float* out;                  // TC_OUT_PLAIN: [rows, dims[layers]] fp32
     float* copy_to;              // optional [rows, dims[0]] copy of the input rows (rollout storage)
@@ -118,7 +120,7 @@ struct TcNetArgs {
 struct TcArgs {
     TcProgram prog[2];
     TcNetArgs net[2];
-    int nnets, rows, tiles, stages, x0_bytes;
+    int nnets, rows, tiles, stages, x0_bytes, slot_bytes;
     int tmem_cols;               // 512, or 256 in the compact variant (two CTAs per SM)
     // PPO.act tail (TC_OUT_SAMPLE / TC_OUT_VALUE)
     uint32_t seed, policy_step; int env_id_offset, num_actions;
@@ -160,9 +162,35 @@ __device__ __forceinline__ float elu_fast(float x) {
     return fmaxf(x, e - 1.0f);          // x > 0: e = 1 -> max(x, 0) = x;  x <= 0: exp(x) - 1 >= x
 }
 
-// ---- input rows of item w: fp32 global -> bf16 core-matrix layout (+ the rollout-storage copy); all epilogue warps.
+// ---- fp16 operands.  The tensor cores take f16 and bf16 at the same rate; f16 keeps 10 mantissa bits (bf16: 7) and lets the
+// whole ELU run on PACKED pairs (below).  Its range is what it costs: conversions saturate at +-65504 instead of
+// overflowing (observations are clipped to +-100 long before), and magnitudes under 6e-8 flush to zero.
+__device__ __forceinline__ uint32_t tc_pack_h2(float lo, float hi) {           // {lo, hi} -> f16x2 (lo in the low half)
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+__device__ __forceinline__ unsigned short tc_h(float v) { return (unsigned short)(tc_pack_h2(v, 0.0f) & 0xFFFFu); }
+// ELU of two accumulators, packed: convert first, then min / mul / 2x MUFU.EX2.F16 / sub / max on the pair -- 7 issue slots
+// for two elements (the fp32 form: 11), and the result is the operand word.  |error| <= 2^-11 (the -1 after an f16 exp).
+__device__ __forceinline__ uint32_t tc_elu_h2(uint32_t a0, uint32_t a1) {
+    const uint32_t z = tc_pack_h2(__uint_as_float(a0), __uint_as_float(a1)), zero = 0u, log2e = 0x3DC53DC5u, one = 0x3C003C00u;
+    uint32_t m, e, r;
+    asm("min.f16x2 %0, %1, %2;" : "=r"(m) : "r"(z), "r"(zero));
+    asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(m) : "r"(m), "r"(log2e));
+    asm("ex2.approx.f16x2 %0, %1;" : "=r"(e) : "r"(m));
+    asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(e) : "r"(e), "r"(one));
+    asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(z), "r"(e));
+    return r;
+}
+// instruction descriptor: D fp32, A/B f16 (format 0), both K-major, M = 128
+__device__ __forceinline__ uint32_t make_idesc_f16(int n) {
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+// ---- input rows of item w: fp32 global -> fp16 core-matrix layout (+ the rollout-storage copy); all epilogue warps.
 // The tile is one contiguous block of global memory, read (and copied to the storage row) with fully coalesced
-// 128-bit accesses, 4 loads in flight per thread.  The four bf16 of a float4 land in one core-matrix row as a 64-bit
+// 128-bit accesses, 4 loads in flight per thread.  The four fp16 of a float4 land in one core-matrix row as a 64-bit
 // shared store; consecutive lanes hold consecutive 8-column blocks, which is why the staged operand uses a PADDED
 // leading byte offset (TC_X0_LBO = 2048 + 16): with the natural 2048 every lane of the warp would hit the same
 // bank.  Out of line so that the loads in flight do not add to the epilogue's register pressure.
@@ -182,7 +210,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     const int total = nrows * K0;
     auto put = [&](int e, float v) {            // element e of the contiguous tile -> (row, column)
         const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
-        *reinterpret_cast<__nv_bfloat16*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = __float2bfloat16_rn(v);
+        *reinterpret_cast<unsigned short*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = tc_h(v);
     };
     if (N.ldx == K0 && ((reinterpret_cast<uintptr_t>(xb) | reinterpret_cast<uintptr_t>(cb)) & 15) == 0) {
         const int n4 = total >> 2;
@@ -203,9 +231,8 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                     if (c4) c4[idx] = v[u];
                     if (row4) {
                         const int e = idx * 4, r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
-                        __nv_bfloat162 p0 = __floats2bfloat162_rn(v[u].x, v[u].y), p1 = __floats2bfloat162_rn(v[u].z, v[u].w);
                         *reinterpret_cast<uint2*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) =
-                            make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
+                            make_uint2(tc_pack_h2(v[u].x, v[u].y), tc_pack_h2(v[u].z, v[u].w));
                     } else {
                         put(idx * 4, v[u].x); put(idx * 4 + 1, v[u].y); put(idx * 4 + 2, v[u].z); put(idx * 4 + 3, v[u].w);
                     }
@@ -230,7 +257,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     const int padw = Kp - K0;
     for (int i = tid; i < nrows * padw; i += TC_STG_THREADS) {
         const int r = i / padw, kx = K0 + (i - r * padw);
-        *reinterpret_cast<__nv_bfloat16*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = __float2bfloat16_rn(0.0f);
+        *reinterpret_cast<unsigned short*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = 0;
     }
     for (int i = tid; i < (TC_ROWS - nrows) * (Kp >> 3); i += TC_STG_THREADS) {
         const int r = nrows + i / (Kp >> 3), kb = i % (Kp >> 3);
@@ -287,11 +314,11 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32, TC_STG_THREADS = TC_STG_WARPS * 32;
     constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_STG_WARPS, TC_LOAD_WARP = TC_MMA_WARP + 1;
     extern __shared__ __align__(128) unsigned char smem[];
-    unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] bf16
-    unsigned char* ach = smem + a.x0_bytes;                    // 2 activation chunk buffers [128 x 128] bf16
-    unsigned char* ones = ach + 2 * TC_ACHUNK_BYTES;           // [128 x 16] bf16: columns 0,1 = 1
+    unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] fp16
+    unsigned char* ach = smem + a.x0_bytes;                    // 2 activation chunk buffers [128 x 128] fp16
+    unsigned char* ones = ach + 2 * TC_ACHUNK_BYTES;           // [128 x 16] fp16: columns 0,1 = 1
     unsigned char* ring = ones + TC_ROWS * 32;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + a.stages * TC_SLOT_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + a.stages * a.slot_bytes);
     const int S = a.stages;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_MAX_STAGES), pb0 = smem_u32(bars + 2 * TC_MAX_STAGES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + TC_NBARS);
@@ -310,7 +337,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else if (warp < TC_EPI_WARPS) {
         for (int i = tid; i < TC_ROWS * 2; i += TC_EPI_THREADS)             // ones operand: 2 column blocks x 128 rows x 16 B
-            *reinterpret_cast<uint4*>(ones + i * 16) = i < TC_ROWS ? make_uint4(0x3F803F80u, 0u, 0u, 0u) : make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(ones + i * 16) = i < TC_ROWS ? make_uint4(0x3C003C00u, 0u, 0u, 0u) : make_uint4(0u, 0u, 0u, 0u);
     }
     fence_async_smem();
     tc_fence_before();
@@ -330,29 +357,29 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
 
     if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
-        {
+        if (lane == 0) {
             uint32_t slot = 0, round = 0;           // ring position: slot index and how many times the ring wrapped
-            TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0 && lane == 0);
+            const uint32_t ring0 = smem_u32(ring), slot_bytes = (uint32_t)a.slot_bytes;
+            TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0);
             TC_ITEM_LOOP(j, w, dry) {
                 if (j == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
                 (void)dry;
                 const int k = w / a.tiles;
                 const TcProgram& P = a.prog[k];
                 const unsigned char* blob = a.net[k].blob;
-                for (int gi = 0; gi < P.ngroups; ++gi) {
-                    const TcGroup& G = P.g[gi];
+                const int ngroups = P.ngroups;
+                for (int gi = 0; gi < ngroups; ++gi) {
+                    const TcGroup G = P.g[gi];
                     tr.ev(0x100 + gi);
                     uint32_t off = G.blob_off;
                     const int nt = G.nt, kc = G.kc, kt = G.kt;
                     for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
                         const uint32_t bytes = (uint32_t)(nt * (k0 < 0 ? 16 : min(kt, kc - k0)) * 2);
                         if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
-                        if (elect_one()) {
-                            if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
-                            else {
-                                mbar_expect_tx(full0 + 8 * slot, bytes);
-                                bulk_g2s(smem_u32(ring + slot * TC_SLOT_BYTES), blob + off, bytes, full0 + 8 * slot);
-                            }
+                        if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
+                        else {
+                            mbar_expect_tx(full0 + 8 * slot, bytes);
+                            bulk_g2s(ring0 + slot * slot_bytes, blob + off, bytes, full0 + 8 * slot);
                         }
                         off += bytes;
                         if (++slot == (uint32_t)S) { slot = 0; ++round; }
@@ -362,81 +389,84 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         }
     } else if (warp == TC_MMA_WARP) {
         // ================================================================ MMA issue: one thread
-        // A lone thread retires about one instruction every 4-5 cycles (tools/umma_microbench.cu), and an N = 128
-        // MMA keeps the tensor pipe busy for only 64 cycles, so the loop below is written for instruction count:
-        // descriptors advance by 64-bit adds, ring addresses incrementally, no division, no per-MMA predicate setup.
-        {
+        // This thread is the critical resource of the kernel.  A lone thread retires about one instruction every 4-5 cycles
+        // (tools/umma_microbench.cu); traced at 262,144 rows, every weight tile cost it ~170 cycles of barrier wait + ~90 of
+        // bookkeeping + ~70-100 per MMA, against 64 cycles of tensor-pipe time for an N = 128 MMA -- with 16 KB tiles (2-4
+        // MMAs each) that was ~25k of an item's 31k cycles, with the tensor pipe busy for a quarter of them.  Hence: 32 KB
+        // tiles (4-8 MMAs per wait), ONE lane running the whole role (no election, no reconvergence), the group
+        // descriptor copied to registers once, and every common tile shape issued from a compile-time unrolled run
+        // (immediate uniform adds: three instructions per MMA).
+        if (lane == 0) {
             uint32_t slot = 0, round = 0, pbits = 0;
             uint32_t full_bar = full0, empty_bar = empty0;
             const uint64_t ring_desc0 = make_desc(smem_u32(ring), 0u, 128u);        // leading byte offset added per group
+            const uint64_t slot_step = (uint64_t)((uint32_t)a.slot_bytes >> 4);
             uint64_t ring_desc = ring_desc0;
             const uint64_t ones_desc = make_desc(smem_u32(ones), TC_ROWS * 16, 128u);
-            TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0 && lane == 0);
+            const uint32_t x0_addr = smem_u32(x0), ach_addr = smem_u32(ach);
+            const bool no_mma = (a.debug & 16) != 0;                                 // experiment: no MMAs
+            TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0);
             auto next_slot = [&]() {
-                full_bar += 8; empty_bar += 8; ring_desc += TC_SLOT_BYTES >> 4;
+                full_bar += 8; empty_bar += 8; ring_desc += slot_step;
                 if (++slot == (uint32_t)S) { slot = 0; ++round; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
             };
             TC_ITEM_LOOP(j, w, dry) {
                 if (j == 0) pf_grid_dep_wait();
                 (void)dry;
                 const TcProgram& P = a.prog[w / a.tiles];
-                for (int gi = 0; gi < P.ngroups; ++gi) {
-                    const TcGroup& G = P.g[gi];
+                const int ngroups = P.ngroups;
+                for (int gi = 0; gi < ngroups; ++gi) {
+                    const TcGroup G = P.g[gi];
                     tr.ev(0x200 + gi);
                     if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, ((pbits >> G.wait_bar) ^ (uint32_t)G.wait_k) & 1u);
                     tc_fence_after();
                     tr.ev(0x300 + gi);
                     const int nt = G.nt;
-                    const uint32_t idesc = make_idesc(nt);
+                    const bool xs = G.a_src == 0;
+                    const uint32_t idesc = make_idesc_f16(nt);
                     const uint32_t tmem_d = tmem_base + G.tmem_col;
-                    const uint32_t a_base = G.a_src == 0 ? smem_u32(x0) : smem_u32(ach) + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
-                    const uint32_t a_lbo = G.a_src == 0 ? TC_X0_LBO : TC_ROWS * 16;
+                    const uint32_t a_base = xs ? x0_addr : ach_addr + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
+                    const uint32_t a_lbo = xs ? TC_X0_LBO : TC_ROWS * 16;
                     uint64_t adesc = make_desc(a_base, a_lbo, 128u);
                     const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4);               // K = 16 further along the A operand
                     const uint64_t b_lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16;  // next 8 K-columns of a weight tile
                     const uint64_t b_step = (uint64_t)(nt * 2);                         // K = 16 further inside a tile, in 16 B units
                     if (G.bias) {
+                        tr.ev(0xA00 + gi);
                         mbar_wait(full_bar, round & 1u);
                         tc_fence_after();
-                        if (elect_one()) {
-                            umma_bf16(tmem_d, ones_desc, ring_desc + b_lbo, idesc, 0u);
-                            umma_commit(empty_bar);
-                        }
+                        tr.ev(0xB00 + gi);
+                        umma_bf16(tmem_d, ones_desc, ring_desc + b_lbo, idesc, 0u);
+                        umma_commit(empty_bar);
                         next_slot();
                     }
                     int left = G.kc >> 4;                       // K = 16 steps still to issue
                     const int per_tile = G.kt >> 4;
                     while (left > 0) {
+                        tr.ev(0xA00 + gi);
                         mbar_wait(full_bar, round & 1u);      // bulk copy -> MMA: both async proxy, the mbarrier orders them
+                        tr.ev(0xB00 + gi);
                         uint64_t bdesc = ring_desc + b_lbo;
                         const int nk = left < per_tile ? left : per_tile;
-                        if (elect_one()) {
-                            // the common tile shapes with compile-time descriptor strides (immediate uniform adds:
-                            // three instructions per MMA), anything else through the generic loop
-                            const bool xs = G.a_src == 0;
-                            if (a.debug & 16) { }                                   // experiment: no MMAs
-                            else if (nt == 128 && nk == 4) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 4>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 4>(tmem_d, adesc, bdesc, idesc); }
-                            else if (nt == 128 && nk == 2) { if (xs) issue_mmas<TC_X0_KSTEP, 256, 2>(tmem_d, adesc, bdesc, idesc); else issue_mmas<256, 256, 2>(tmem_d, adesc, bdesc, idesc); }
-                            else if (nt == 256 && nk == 2 && !xs) issue_mmas<256, 512, 2>(tmem_d, adesc, bdesc, idesc);
-                            else {
-                                uint64_t ad = adesc;
-                                for (int kk = 0; kk < nk; ++kk) {
-                                    umma_bf16_acc(tmem_d, ad, bdesc, idesc);
-                                    ad += a_step;
-                                    bdesc += b_step;
-                                }
+                        if (no_mma) { }
+                        else if (nt == 128 && xs) issue_tile<TC_X0_KSTEP, 256>(nk, tmem_d, adesc, bdesc, idesc);
+                        else if (nt == 128) issue_tile<256, 256>(nk, tmem_d, adesc, bdesc, idesc);
+                        else if (nt == 256 && !xs) issue_tile<256, 512>(nk, tmem_d, adesc, bdesc, idesc);
+                        else {
+                            uint64_t ad = adesc;
+                            for (int kk = 0; kk < nk; ++kk) {
+                                umma_bf16_acc(tmem_d, ad, bdesc, idesc);
+                                ad += a_step;
+                                bdesc += b_step;
                             }
-                            umma_commit(empty_bar);             // slot is free once these MMAs have read it
                         }
+                        umma_commit(empty_bar);             // slot is free once these MMAs have read it
                         adesc += (uint64_t)nk * a_step;
                         next_slot();
                         left -= nk;
                     }
-                    if (elect_one()) {
-                        if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
-                        if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
-                    }
-                    __syncwarp();
+                    if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
+                    if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
                     tr.ev(0x400 + gi);
                 }
                 pbits ^= P.parity_mask;
@@ -461,20 +491,14 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;          // (h == 0 for every warp when TC_EPI_WARPS == 4)
         uint32_t pbits = 0;
         TcTrace tr; tr.init(a.trace, 0, blockIdx.x == 0 && tid == 0);
-        // ELU + bf16 pack of 32 accumulator columns [g, g + 32) of this thread's row into a chunk buffer
-        auto pack32 = [&](const uint32_t (&v)[32], unsigned char* outb, int g, int wd) {
+        // ELU + fp16 pack of 16 accumulator columns [g, g + 16) of this thread's row into a chunk buffer
+        auto pack16 = [&](const uint32_t (&v)[16], unsigned char* outb, int g) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-                if (j < wd) {
-                    uint32_t pk[4];
+            for (int j = 0; j < 16; j += 8) {
+                uint32_t pk[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        __nv_bfloat162 p = __floats2bfloat162_rn(elu_fast(__uint_as_float(v[j + 2 * i])),
-                                                                 elu_fast(__uint_as_float(v[j + 2 * i + 1])));
-                        pk[i] = *reinterpret_cast<uint32_t*>(&p);
-                    }
-                    *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                }
+                for (int i = 0; i < 4; ++i) pk[i] = tc_elu_h2(v[j + 2 * i], v[j + 2 * i + 1]);
+                *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
         };
         TC_ITEM_LOOP(j, w, dry) {
@@ -497,14 +521,27 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                 const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + E.tmem_col;
                 if (E.dst >= 0) {
                     unsigned char* outb = ach + E.dst * TC_ACHUNK_BYTES;
-                    for (int g = c_lo; g < c_hi; g += 32) {
-                        uint32_t v[32];
-                        const int wd = min(32, c_hi - g);
+                    // two register sets of 16 columns: the TMEM load of the next 16 is in flight while the ELUs of the
+                    // current 16 issue (tcgen05.ld is asynchronous up to its wait); c_lo, c_hi are multiples of 16
+                    if (c_lo < c_hi) {
+                        uint32_t va[16], vb[16];
+                        int g = c_lo;
                         tr.ev(0xC00 + ei);
-                        if (wd == 32) tmem_ld32(trow + g, v); else tmem_ld16(trow + g, v);
-                        tmem_ld_wait();
+                        tmem_ld16(trow + g, va);
+                        tmem_ld_wait_on(va);
                         tr.ev(0xD00 + ei);
-                        pack32(v, outb, g, wd);
+                        for (;;) {
+                            const int g2 = g + 16;
+                            if (g2 < c_hi) tmem_ld16(trow + g2, vb);
+                            pack16(va, outb, g);
+                            if (g2 >= c_hi) break;
+                            tmem_ld_wait_on(vb);
+                            g = g2 + 16;
+                            if (g < c_hi) tmem_ld16(trow + g, va);
+                            pack16(vb, outb, g2);
+                            if (g >= c_hi) break;
+                            tmem_ld_wait_on(va);
+                        }
                     }
                     tr.ev(0x800 + ei);
                     fence_async_smem();
@@ -564,8 +601,8 @@ static const auto pf_mlp_tc_kernel_std = pf_mlp_tc_kernel<8, 8, 1>;
 static const auto pf_mlp_tc_kernel_compact = pf_mlp_tc_kernel<4, 4, 2>;
 
 // ------------------------------------------------------------------------------------------------ packing
-// fp32 nn.Linear weight [out, in] + bias -> bf16 tiles in consumption order.  Tiles of a group, contiguous: the BIAS
-// tile if the group starts an accumulation (nt x 16: column 0 = bf16(b), column 1 = bf16(b - bf16(b)), multiplied by
+// fp32 nn.Linear weight [out, in] + bias -> fp16 tiles in consumption order.  Tiles of a group, contiguous: the BIAS
+// tile if the group starts an accumulation (nt x 16: column 0 = fp16(b), column 1 = fp16(b - fp16(b)), multiplied by
 // the "ones" A operand), then the K tiles of kt columns.  blockIdx.y = group (both nets in one launch).
 struct TcPackArgs { TcProgram prog[2]; unsigned char* blob[2]; long long w_off[2][PF_MAX_MLP_LAYERS], b_off[2][PF_MAX_MLP_LAYERS]; };
 
@@ -574,7 +611,7 @@ __global__ void pf_tc_pack_kernel(const __grid_constant__ TcPackArgs a, const fl
     if (gi >= a.prog[0].ngroups) { gi -= a.prog[0].ngroups; k = 1; }
     const TcProgram& P = a.prog[k];
     const TcGroup& G = P.g[gi];
-    const int l = G.layer, nt = G.nt, kc = G.kc, kt = G.kt;
+    const int l = G.layer, nt = G.nt, kc = G.kc;
     const int K = P.dims[l], N = P.dims[l + 1];
     const float* W = params + a.w_off[k][l];
     const float* b = params + a.b_off[k][l];
@@ -582,16 +619,16 @@ __global__ void pf_tc_pack_kernel(const __grid_constant__ TcPackArgs a, const fl
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nt * kc; i += gridDim.x * blockDim.x) {
         const int nl = i / kc, kl = i - nl * kc;
         const int n = G.n_base + nl, kg = G.k_base + kl;
-        const int t = kl / kt, kk = kl - t * kt;
-        const long long off = (G.bias ? nt * 32 : 0) + (long long)t * nt * kt * 2 +
-                              ((long long)(kk >> 3) * (nt >> 3) + (nl >> 3)) * 128 + (nl & 7) * 16 + (kk & 7) * 2;
+        // K-major core matrices over the WHOLE group: any K range is contiguous, so the tile size (kt) is only the
+        // loader's chunking -- the standard and the compact programs read the same blob with different tiles
+        const long long off = (G.bias ? nt * 32 : 0) + (long long)(kl >> 3) * (nt * 16) + nl * 16 + (kl & 7) * 2;
         const float v = (n < N && kg < K) ? W[(long long)n * K + kg] : 0.0f;
-        *reinterpret_cast<__nv_bfloat16*>(blob + off) = __float2bfloat16_rn(v);
-        if (kl == 0 && G.bias) {   // bias tile: columns 0 / 1 = high / low bf16 parts of the bias, the rest stays zero
+        *reinterpret_cast<unsigned short*>(blob + off) = tc_h(v);
+        if (kl == 0 && G.bias) {   // bias tile: columns 0 / 1 = high / low fp16 parts of the bias, the rest stays zero
             const float bv = n < N ? b[n] : 0.0f;
-            const __nv_bfloat16 hi = __float2bfloat16_rn(bv);
-            const __nv_bfloat16 lo = __float2bfloat16_rn(bv - __bfloat162float(hi));
-            __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(blob + (long long)(nl >> 3) * 128 + (nl & 7) * 16);
+            const unsigned short hi = tc_h(bv);
+            const unsigned short lo = tc_h(bv - __half2float(__ushort_as_half(hi)));
+            unsigned short* d = reinterpret_cast<unsigned short*>(blob + (long long)(nl >> 3) * 128 + (nl & 7) * 16);
             d[0] = hi; d[1] = lo;
         }
     }
@@ -599,14 +636,14 @@ __global__ void pf_tc_pack_kernel(const __grid_constant__ TcPackArgs a, const fl
 
 static int tc_fail(int code, const char* msg) { pf_set_error(msg); return code; }
 
-static int pick_kt(int nt, int kc) {
-    int kt = (TC_SLOT_BYTES / 2 / nt) & ~15;
+static int pick_kt(int nt, int kc, int slot_bytes) {
+    int kt = (slot_bytes / 2 / nt) & ~15;
     if (kt > 128) kt = 128;
     return kt < kc ? kt : kc;
 }
 
 // Builds the static schedule of one net (see the header comment).  Returns non-zero if the shape does not fit.
-static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256) {
+static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int slot_bytes = TC_SLOT_BYTES) {
     memset(&P, 0, sizeof(P));
     const int L = n.layers;
     P.layers = L;
@@ -627,7 +664,7 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256) {
     long long off = 0;
     auto add_group = [&](TcGroup g) -> int {
         if (P.ngroups == TC_MAX_GROUPS) return 1;
-        g.kt = (uint16_t)pick_kt(g.nt, g.kc);
+        g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes);
         g.blob_off = (uint32_t)off;
         off += (long long)g.nt * ((g.bias ? 16 : 0) + g.kc) * 2;
         P.g[P.ngroups++] = g;
@@ -802,12 +839,12 @@ extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, in
 }
 
 // budget_kb: 227 (one CTA per SM), or 113 for the compact variant (two CTAs per SM: 2 x (113 + 1 KB reserved) = 228 KB)
-static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 3) {
+static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 2, int slot_bytes = TC_SLOT_BYTES) {
     const int fixed = x0_bytes + 2 * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
-    int S = (budget_kb * 1024 - fixed) / TC_SLOT_BYTES;
+    int S = (budget_kb * 1024 - fixed) / slot_bytes;
     if (S < min_stages) return 1;
     *stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
-    *smem_bytes = fixed + *stages * TC_SLOT_BYTES;
+    *smem_bytes = fixed + *stages * slot_bytes;
     return 0;
 }
 
@@ -831,11 +868,11 @@ int pf_tc_create(pf_rl_ctx* c) {
     // groups, tiles and blob offsets as the standard programs (only the accumulator columns differ): the packed weights are shared.
     t->compact = getenv("PF_TC_NO_COMPACT") == nullptr;
     for (int k = 0; k < 2 && t->compact; ++k)
-        if (build_program(t->progc[k], c->net[k], 128) || check_program(t->progc[k]) || t->progc[k].blob_bytes != t->prog[k].blob_bytes ||
+        if (build_program(t->progc[k], c->net[k], 128, TC_SLOT_BYTES_COMPACT) || check_program(t->progc[k]) || t->progc[k].blob_bytes != t->prog[k].blob_bytes ||
             t->progc[k].ngroups != t->prog[k].ngroups)
             t->compact = 0;
     for (int v = 0; v < 3 && t->compact; ++v)
-        if (smem_layout(t->x0_bytes[v], &t->stages_c[v], &t->smem_bytes_c[v], 113, 2)) t->compact = 0;
+        if (smem_layout(t->x0_bytes[v], &t->stages_c[v], &t->smem_bytes_c[v], 113, 2, TC_SLOT_BYTES_COMPACT)) t->compact = 0;
     if (t->compact) {
         int mc = 0;
         for (int v = 0; v < 3; ++v) mc = t->smem_bytes_c[v] > mc ? t->smem_bytes_c[v] : mc;
@@ -876,6 +913,7 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
     a.stages = t->stages[variant];
+    a.slot_bytes = TC_SLOT_BYTES;
     a.x0_bytes = t->x0_bytes[variant];
     a.trace = t->trace;
     a.rehearse = 0;
@@ -895,6 +933,7 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
             for (int k = 0; k < 2; ++k)
                 if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progc[k];
         a.stages = t->stages_c[variant];
+        a.slot_bytes = TC_SLOT_BYTES_COMPACT;
         a.tmem_cols = 256;
         const int grid = items < 2 * c->num_sms ? items : 2 * c->num_sms;
         return pf_launch_pdl(pf_mlp_tc_kernel_compact, dim3(grid), dim3(TC_THREADS_OF(4, 4)), (size_t)t->smem_bytes_c[variant], st, a) == cudaSuccess

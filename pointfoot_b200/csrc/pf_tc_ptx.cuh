@@ -78,6 +78,22 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[32]) {
         : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// 16 columns into a 16-register set, and the wait tied to the registers a tcgen05.ld filled: nothing that reads them can
+// be scheduled above it
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+        : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+          "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+        :: "memory");
+}
 
 // K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout)
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -97,5 +113,14 @@ template <int A_STEP, int B_STEP, int NK>
 __device__ __forceinline__ void issue_mmas(uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc) {
 #pragma unroll
     for (int kk = 0; kk < NK; ++kk) umma_bf16_acc(tmem_d, ad + (uint64_t)(kk * A_STEP), bd + (uint64_t)(kk * B_STEP), idesc);
+}
+// nk accumulating MMAs of one weight tile, compile-time descriptor strides; the usual counts fully unrolled
+template <int A_STEP, int B_STEP>
+__device__ __forceinline__ void issue_tile(int nk, uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc) {
+    if (nk == 8) issue_mmas<A_STEP, B_STEP, 8>(tmem_d, ad, bd, idesc);
+    else if (nk == 4) issue_mmas<A_STEP, B_STEP, 4>(tmem_d, ad, bd, idesc);
+    else if (nk == 2) issue_mmas<A_STEP, B_STEP, 2>(tmem_d, ad, bd, idesc);
+    else
+        for (int kk = 0; kk < nk; ++kk) { umma_bf16_acc(tmem_d, ad, bd, idesc); ad += A_STEP; bd += B_STEP; }
 }
 
