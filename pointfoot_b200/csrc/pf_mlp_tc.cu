@@ -52,12 +52,19 @@ void pf_set_error(const char* msg);
 #define TC_TRACE_CAP 512
 #define TC_TRACE_ROLES 4
 
-// program barriers (besides the ring's full / empty pairs)
+// program barriers (besides the ring's full / empty pairs).  A program names the ones it uses; what arrives on a barrier
+// (one tcgen05.commit, every epilogue warp, every staging warp) is the program's bar_kind[].
 enum { BAR_ACC0 = 0, BAR_ACC1 = 1, BAR_ACC2 = 2,      // accumulator complete: TMEM cols [0,128) or [0,256) / [128,256) / [256,512)
        BAR_AFREE0 = 3, BAR_AFREE1 = 4,               // MMAs that read activation chunk buffer b have completed
        BAR_E0 = 5, BAR_E1 = 6,                       // epilogue wrote chunk buffer b (and drained its accumulator)
        BAR_XFULL = 7,                                // input rows of the item are staged
-       BAR_XFREE = 8, TC_NBARS = 9 };                // the MMAs that read the staged rows have completed
+       BAR_XFREE = 8,                                // the MMAs that read the staged rows have completed
+       // two-phase programs only (build_program_pipe)
+       BAR_ACC3 = 9,                                 // last layer's accumulator complete
+       BAR_AFREE2 = 10, BAR_E2 = 11,                 // chunk buffer 2 (the second phase's)
+       BAR_ODONE = 12,                               // the final epilogue has read its accumulator
+       TC_NBARS = 13 };
+enum { TC_BK_COMMIT = 0, TC_BK_EPI = 1, TC_BK_STG = 2 };
 
 // One accumulation step: D[128 x nt] (+)= A[128 x kc] * W^T, A = staged input rows or an activation chunk.
 struct TcGroup {
@@ -70,7 +77,9 @@ struct TcGroup {
     int8_t bias;                       // starts the accumulation with the bias tile
     int8_t wait_bar, wait_k;           // barrier (+ completion index inside the item) to wait for before the first MMA
     int8_t commit_bar, commit2_bar;    // barriers the completion of the group's MMAs arrives on (-1: none)
-    int8_t pad;
+    int8_t phase;                      // two-phase programs: 0 = first half of the item, 1 = second half, run one iteration later
+    int8_t prev_bar, prev_k;           // also wait for completion prev_k of this barrier by the PREVIOUS item of the same phase (-1: none)
+    int8_t pad[2];
 };
 // One epilogue step: accumulator columns [tmem_col, tmem_col + nt) -> activation chunk buffer or the final output.
 struct TcEpi {
@@ -78,8 +87,9 @@ struct TcEpi {
     int8_t acc_bar, acc_k;             // accumulator-complete barrier + completion index
     int8_t dst;                        // -1 final output, else chunk buffer
     int8_t free_bar, free_k;           // MMAs still reading the chunk buffer (-1: none)
-    int8_t done_bar;                   // arrives here when written
-    int8_t pad[2];
+    int8_t done_bar;                   // arrives here when written (final output: when the accumulator has been read), -1: none
+    int8_t phase;
+    int8_t pad;
 };
 struct TcProgram {
     int odd_col;                         // TMEM column of the accumulators of odd layers: 256, or 128 in the compact variant
@@ -88,6 +98,9 @@ struct TcProgram {
     int pdims[PF_MAX_MLP_LAYERS + 1];    // padded to a multiple of 16
     int ngroups, nepis;
     uint32_t parity_mask;                // bit b: barrier b completes an odd number of times per item
+    int phases;                          // 1, or 2: steps of phase 1 belong to the item of the PREVIOUS iteration (software pipeline)
+    int nbuf;                            // activation chunk buffers (2, or 3 in two-phase programs)
+    int8_t bar_kind[TC_NBARS];           // TC_BK_*
     int x0_bytes;
     long long blob_bytes;
     TcGroup g[TC_MAX_GROUPS];
@@ -99,6 +112,8 @@ struct TcProgram {
 struct TcState {
     TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3];
     int compact; TcProgram progc[2]; int stages_c[3]; int smem_bytes_c[3];
+    int slot_bytes;
+    int pipe; TcProgram progp[2]; int stages_p[3]; int smem_bytes_p[3]; int slot_bytes_p;      // two-phase programs (large batches)
     unsigned long long* trace; int rehearse;
 };
 
@@ -120,7 +135,7 @@ struct TcNetArgs {
 struct TcArgs {
     TcProgram prog[2];
     TcNetArgs net[2];
-    int nnets, rows, tiles, stages, x0_bytes, slot_bytes;
+    int nnets, rows, tiles, stages, x0_bytes, slot_bytes, nbuf;
     int tmem_cols;               // 512, or 256 in the compact variant (two CTAs per SM)
     // PPO.act tail (TC_OUT_SAMPLE / TC_OUT_VALUE)
     uint32_t seed, policy_step; int env_id_offset, num_actions;
@@ -315,8 +330,8 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_STG_WARPS, TC_LOAD_WARP = TC_MMA_WARP + 1;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] fp16
-    unsigned char* ach = smem + a.x0_bytes;                    // 2 activation chunk buffers [128 x 128] fp16
-    unsigned char* ones = ach + 2 * TC_ACHUNK_BYTES;           // [128 x 16] fp16: columns 0,1 = 1
+    unsigned char* ach = smem + a.x0_bytes;                    // 2 (3) activation chunk buffers [128 x 128] fp16
+    unsigned char* ones = ach + a.nbuf * TC_ACHUNK_BYTES;      // [128 x 16] fp16: columns 0,1 = 1
     unsigned char* ring = ones + TC_ROWS * 32;
     uint64_t* bars = reinterpret_cast<uint64_t*>(ring + a.stages * a.slot_bytes);
     const int S = a.stages;
@@ -329,7 +344,10 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
 
     if (warp == TC_LOAD_WARP && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        for (int b = 0; b < TC_NBARS; ++b) mbar_init(pb0 + 8 * b, (b == BAR_E0 || b == BAR_E1) ? TC_EPI_WARPS : b == BAR_XFULL ? TC_STG_WARPS : 1);   // one arrival per warp
+        for (int b = 0; b < TC_NBARS; ++b) {                    // one arrival per warp, or one tcgen05.commit
+            const int kind = a.prog[0].bar_kind[b];
+            mbar_init(pb0 + 8 * b, kind == TC_BK_EPI ? TC_EPI_WARPS : kind == TC_BK_STG ? TC_STG_WARPS : 1);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == TC_MMA_WARP) {
@@ -345,41 +363,58 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pf_timeline(0x51);
-    // Every role below walks the items j = -reh, 0, 1, ...: with a.rehearse the first pass (j = -1) is a DRY copy of the
-    // CTA's first item -- zeros instead of the input rows, no outputs, every barrier used exactly as by a real item --
-    // executed BEFORE the dependency wait: launched as a programmatic dependent, the CTA would otherwise sit idle at
-    // that wait while its predecessor runs, and then execute every role's code for the first time (instruction
-    // fetches all the way from DRAM after an L2 flush) on the critical path.  Each role passes the wait at j = 0.
+    // Every role below walks ITERATIONS it = -reh, 0, 1, ..., and in each one the steps of the program in program order.
+    // A step of phase ph belongs to the CTA's item number m = it - ph: in a two-phase program the second half of item m
+    // (its last layers) is interleaved, step by step, with the first half of item m + 1, so that the epilogue warps and
+    // the tensor pipe always have the other item's work while one item's chain waits for a hand-off.  A single-phase
+    // program is the degenerate case (one item per iteration).
+    // With a.rehearse the first pass (it = -1) is a DRY copy of the CTA's first item -- zeros instead of the input rows,
+    // no outputs, every barrier used exactly as by a real item -- executed BEFORE the dependency wait: launched as a
+    // programmatic dependent, the CTA would otherwise sit idle at that wait while its predecessor runs, and then execute
+    // every role's code for the first time (instruction fetches all the way from DRAM after an L2 flush) on the critical
+    // path.  Each role passes the wait at it = 0.  (Single-phase programs only.)
     const int reh = a.rehearse ? 1 : 0;
-#define TC_ITEM_LOOP(j, w, dry)                                                                  \
-    for (int j = -reh, w = (int)blockIdx.x; w < items; ++j, w = (int)blockIdx.x + (j < 0 ? 0 : j) * (int)gridDim.x) \
-        if (const bool dry = j < 0; true)
+    const int n_local = (items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;      // items of this CTA (>= 1)
+    const int n_iter = n_local + a.prog[0].phases - 1;
+    // item of phase ph in iteration it: its work index, or -1 when that phase has no item in this iteration
+    auto item_of = [&](int it, int ph) -> int {
+        if (it < 0) return ph == 0 ? (int)blockIdx.x : -1;
+        const int m = it - ph;
+        return (m >= 0 && m < n_local) ? (int)blockIdx.x + m * (int)gridDim.x : -1;
+    };
+    // parity to wait for: completion k (inside the item) of barrier b, given the barrier completions of all earlier items
+    auto par_of = [](uint32_t bits, int b, int k) -> uint32_t { return ((bits >> b) ^ (uint32_t)k) & 1u; };
 
     if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
-        if (lane == 0) {
+        {   // (the whole warp walks the loop, one elected lane issues: code the compiler KNOWS to be warp-uniform keeps
+            // the copy's operands in uniform registers; a lone lane made it re-broadcast every operand per instruction)
             uint32_t slot = 0, round = 0;           // ring position: slot index and how many times the ring wrapped
             const uint32_t ring0 = smem_u32(ring), slot_bytes = (uint32_t)a.slot_bytes;
-            TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0);
-            TC_ITEM_LOOP(j, w, dry) {
-                if (j == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
-                (void)dry;
-                const int k = w / a.tiles;
-                const TcProgram& P = a.prog[k];
-                const unsigned char* blob = a.net[k].blob;
-                const int ngroups = P.ngroups;
+            TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0 && lane == 0);
+            for (int it = -reh; it < n_iter; ++it) {
+                if (it == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
+                const int w0 = item_of(it, 0), w1 = item_of(it, 1);
+                const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+                const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];          // step list (the same for both nets when two-phase)
+                const int ngroups = PR.ngroups;
                 for (int gi = 0; gi < ngroups; ++gi) {
-                    const TcGroup G = P.g[gi];
+                    const int k = PR.g[gi].phase ? k1n : k0n;
+                    if (k < 0) continue;
+                    const TcGroup G = a.prog[k].g[gi];
+                    const unsigned char* blob = a.net[k].blob;
                     tr.ev(0x100 + gi);
                     uint32_t off = G.blob_off;
                     const int nt = G.nt, kc = G.kc, kt = G.kt;
-                    for (int k0 = G.bias ? -16 : 0; k0 < kc; k0 += (k0 < 0 ? 16 : kt)) {
-                        const uint32_t bytes = (uint32_t)(nt * (k0 < 0 ? 16 : min(kt, kc - k0)) * 2);
+                    for (int kk = G.bias ? -16 : 0; kk < kc; kk += (kk < 0 ? 16 : kt)) {
+                        const uint32_t bytes = (uint32_t)(nt * (kk < 0 ? 16 : min(kt, kc - kk)) * 2);
                         if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
-                        if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
-                        else {
-                            mbar_expect_tx(full0 + 8 * slot, bytes);
-                            bulk_g2s(ring0 + slot * slot_bytes, blob + off, bytes, full0 + 8 * slot);
+                        if (elect_one()) {
+                            if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
+                            else {
+                                mbar_expect_tx(full0 + 8 * slot, bytes);
+                                bulk_g2s(ring0 + slot * slot_bytes, blob + off, bytes, full0 + 8 * slot);
+                            }
                         }
                         off += bytes;
                         if (++slot == (uint32_t)S) { slot = 0; ++round; }
@@ -389,14 +424,12 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         }
     } else if (warp == TC_MMA_WARP) {
         // ================================================================ MMA issue: one thread
-        // This thread is the critical resource of the kernel.  A lone thread retires about one instruction every 4-5 cycles
-        // (tools/umma_microbench.cu); traced at 262,144 rows, every weight tile cost it ~170 cycles of barrier wait + ~90 of
-        // bookkeeping + ~70-100 per MMA, against 64 cycles of tensor-pipe time for an N = 128 MMA -- with 16 KB tiles (2-4
-        // MMAs each) that was ~25k of an item's 31k cycles, with the tensor pipe busy for a quarter of them.  Hence: 32 KB
-        // tiles (4-8 MMAs per wait), ONE lane running the whole role (no election, no reconvergence), the group
-        // descriptor copied to registers once, and every common tile shape issued from a compile-time unrolled run
-        // (immediate uniform adds: three instructions per MMA).
-        if (lane == 0) {
+        // The issuing thread is the critical resource of the kernel: traced at 262,144 rows, every weight tile costs it a
+        // barrier wait (>= 90 cycles even when complete) + ~90 of bookkeeping + the MMAs, against 64 cycles of tensor-pipe
+        // time for an N = 128 MMA.  The whole warp walks the loop and one elected lane issues: code the compiler knows to
+        // be warp-uniform keeps descriptors in uniform registers (three instructions per MMA from the compile-time
+        // unrolled runs below); run by a lone lane, every MMA re-broadcast its seven operand registers first.
+        {
             uint32_t slot = 0, round = 0, pbits = 0;
             uint32_t full_bar = full0, empty_bar = empty0;
             const uint64_t ring_desc0 = make_desc(smem_u32(ring), 0u, 128u);        // leading byte offset added per group
@@ -405,20 +438,29 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             const uint64_t ones_desc = make_desc(smem_u32(ones), TC_ROWS * 16, 128u);
             const uint32_t x0_addr = smem_u32(x0), ach_addr = smem_u32(ach);
             const bool no_mma = (a.debug & 16) != 0;                                 // experiment: no MMAs
-            TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0);
+            const bool peek = (a.debug & 32) == 0;                                   // experiment: bit 5 = no barrier peeking
+            TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0 && lane == 0);
             auto next_slot = [&]() {
                 full_bar += 8; empty_bar += 8; ring_desc += slot_step;
                 if (++slot == (uint32_t)S) { slot = 0; ++round; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
             };
-            TC_ITEM_LOOP(j, w, dry) {
-                if (j == 0) pf_grid_dep_wait();
-                (void)dry;
-                const TcProgram& P = a.prog[w / a.tiles];
-                const int ngroups = P.ngroups;
+            uint32_t pbits1 = 0, pprev1 = 0, pprev0 = 0;  // parities before phase 1's current item; before the previous item of each phase
+            for (int it = -reh; it < n_iter; ++it) {
+                if (it == 0) pf_grid_dep_wait();
+                const int w0 = item_of(it, 0), w1 = item_of(it, 1);
+                const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+                const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];
+                const int ngroups = PR.ngroups;
                 for (int gi = 0; gi < ngroups; ++gi) {
-                    const TcGroup G = P.g[gi];
+                    const int ph = PR.g[gi].phase;
+                    const int k = ph ? k1n : k0n;
+                    if (k < 0) continue;
+                    const TcGroup G = a.prog[k].g[gi];
                     tr.ev(0x200 + gi);
-                    if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, ((pbits >> G.wait_bar) ^ (uint32_t)G.wait_k) & 1u);
+                    if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, par_of(ph ? pbits1 : pbits, G.wait_bar, G.wait_k));
+                    // (two-phase programs) a resource the previous item of this phase still held: its one completion of
+                    // prev_bar -- there is no such item in the phase's first iteration
+                    if (G.prev_bar >= 0 && it - ph >= 1) mbar_wait(pb0 + 8 * G.prev_bar, par_of(ph ? pprev1 : pprev0, G.prev_bar, G.prev_k));
                     tc_fence_after();
                     tr.ev(0x300 + gi);
                     const int nt = G.nt;
@@ -436,40 +478,54 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                         mbar_wait(full_bar, round & 1u);
                         tc_fence_after();
                         tr.ev(0xB00 + gi);
-                        umma_bf16(tmem_d, ones_desc, ring_desc + b_lbo, idesc, 0u);
-                        umma_commit(empty_bar);
+                        if (elect_one()) {
+                            umma_bf16(tmem_d, ones_desc, ring_desc + b_lbo, idesc, 0u);
+                            umma_commit(empty_bar);
+                        }
                         next_slot();
                     }
                     int left = G.kc >> 4;                       // K = 16 steps still to issue
                     const int per_tile = G.kt >> 4;
+                    uint32_t have = 0;                          // the next tile's barrier was already seen complete
                     while (left > 0) {
                         tr.ev(0xA00 + gi);
-                        mbar_wait(full_bar, round & 1u);      // bulk copy -> MMA: both async proxy, the mbarrier orders them
+                        if (!have) mbar_wait(full_bar, round & 1u);      // bulk copy -> MMA: both async proxy, the mbarrier orders them
                         tr.ev(0xB00 + gi);
-                        uint64_t bdesc = ring_desc + b_lbo;
+                        const uint64_t bdesc0 = ring_desc + b_lbo, adesc0 = adesc;
+                        const uint32_t cur_empty = empty_bar;
                         const int nk = left < per_tile ? left : per_tile;
-                        if (no_mma) { }
-                        else if (nt == 128 && xs) issue_tile<TC_X0_KSTEP, 256>(nk, tmem_d, adesc, bdesc, idesc);
-                        else if (nt == 128) issue_tile<256, 256>(nk, tmem_d, adesc, bdesc, idesc);
-                        else if (nt == 256 && !xs) issue_tile<256, 512>(nk, tmem_d, adesc, bdesc, idesc);
-                        else {
-                            uint64_t ad = adesc;
-                            for (int kk = 0; kk < nk; ++kk) {
-                                umma_bf16_acc(tmem_d, ad, bdesc, idesc);
-                                ad += a_step;
-                                bdesc += b_step;
-                            }
-                        }
-                        umma_commit(empty_bar);             // slot is free once these MMAs have read it
                         adesc += (uint64_t)nk * a_step;
                         next_slot();
                         left -= nk;
+                        // peek at the NEXT tile before this tile's MMAs go out: a barrier test costs this thread ~100-150
+                        // cycles even when the tile has long landed, and here they pass under the MMA issue
+                        have = (left > 0 && peek) ? mbar_test(full_bar, round & 1u) : 0u;
+                        if (elect_one()) {
+                            // the common tile shapes with compile-time descriptor strides, anything else through the generic loop
+                            if (no_mma) { }
+                            else if (nt == 128 && xs) issue_tile<TC_X0_KSTEP, 256>(nk, tmem_d, adesc0, bdesc0, idesc);
+                            else if (nt == 128) issue_tile<256, 256>(nk, tmem_d, adesc0, bdesc0, idesc);
+                            else if (nt == 256 && !xs) issue_tile<256, 512>(nk, tmem_d, adesc0, bdesc0, idesc);
+                            else {
+                                uint64_t ad = adesc0, bd = bdesc0;
+                                for (int kk = 0; kk < nk; ++kk) {
+                                    umma_bf16_acc(tmem_d, ad, bd, idesc);
+                                    ad += a_step;
+                                    bd += b_step;
+                                }
+                            }
+                            umma_commit(cur_empty);             // slot is free once these MMAs have read it
+                        }
                     }
-                    if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
-                    if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
+                    if (elect_one()) {
+                        if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
+                        if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
+                    }
+                    __syncwarp();
                     tr.ev(0x400 + gi);
                 }
-                pbits ^= P.parity_mask;
+                if (k0n >= 0) { pprev0 = pbits; pbits ^= a.prog[k0n].parity_mask; }
+                if (k1n >= 0) { pprev1 = pbits1; pbits1 ^= a.prog[k1n].parity_mask; }
             }
         }
     } else if (warp >= TC_EPI_WARPS) {
@@ -477,14 +533,16 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         // The staged rows of item i are dead once its last layer-0 MMAs have completed (BAR_XFREE); the rows of
         // item i + 1 are staged right then, under the MMAs and epilogues of the remaining layers.
         TcTrace tr; tr.init(a.trace, 3, blockIdx.x == 0 && tid == TC_EPI_THREADS);
-        uint32_t it = 0;
-        TC_ITEM_LOOP(j, w, dry) {
+        uint32_t cnt = 0;                            // items staged so far (the staging role has no phases: one item per pass)
+        for (int j = -reh; j < n_local; ++j) {
+            const bool dry = j < 0;
+            const int w = (int)blockIdx.x + (dry ? 0 : j) * (int)gridDim.x;
             if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(tid == TC_EPI_THREADS && blockIdx.x == 0, 0x52); }
-            if (it) mbar_wait(pb0 + 8 * BAR_XFREE, (it - 1u) & 1u);
+            if (cnt) mbar_wait(pb0 + 8 * BAR_XFREE, (cnt - 1u) & 1u);
             tr.ev(0x500);
             tc_stage_item<TC_STG_THREADS>(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr, dry);
             tr.ev(0x502);
-            ++it;
+            ++cnt;
         }
     } else {
         // ================================================================ epilogues: 8 warps
@@ -501,19 +559,29 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                 *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
         };
-        TC_ITEM_LOOP(j, w, dry) {
-            if (j == 0) pf_grid_dep_wait();
-            const int k = w / a.tiles, tile = w - k * a.tiles;
-            const TcProgram& P = a.prog[k];
-            const TcNetArgs& N = a.net[k];
-            const int row0 = tile * TC_ROWS;
-            const int nrows = dry ? 0 : min(TC_ROWS, a.rows - row0);      // dry item: no row is written
-            const int L = P.layers;
-            for (int ei = 0; ei < P.nepis; ++ei) {
+        uint32_t pbits1 = 0;
+        for (int it = -reh; it < n_iter; ++it) {
+            if (it == 0) pf_grid_dep_wait();
+            const bool dry = it < 0;
+            const int w0 = item_of(it, 0), w1 = item_of(it, 1);
+            const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+            const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];
+            const int nepis = PR.nepis;
+            for (int ei = 0; ei < nepis; ++ei) {
+                const int ph = PR.e[ei].phase;
+                const int k = ph ? k1n : k0n;
+                if (k < 0) continue;
+                const TcProgram& P = a.prog[k];
+                const TcNetArgs& N = a.net[k];
                 const TcEpi& E = P.e[ei];
+                const int tile = (ph ? w1 : w0) - k * a.tiles;
+                const int row0 = tile * TC_ROWS;
+                const int nrows = dry ? 0 : min(TC_ROWS, a.rows - row0);      // dry item: no row is written
+                const int L = P.layers;
+                const uint32_t bits = ph ? pbits1 : pbits;
                 tr.ev(0x600 + ei);
-                mbar_wait(pb0 + 8 * E.acc_bar, ((pbits >> E.acc_bar) ^ (uint32_t)E.acc_k) & 1u);
-                if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, ((pbits >> E.free_bar) ^ (uint32_t)E.free_k) & 1u);
+                mbar_wait(pb0 + 8 * E.acc_bar, par_of(bits, E.acc_bar, E.acc_k));
+                if (E.free_bar >= 0) mbar_wait(pb0 + 8 * E.free_bar, par_of(bits, E.free_bar, E.free_k));
                 tc_fence_after();
                 tr.ev(0x700 + ei);
                 const int nt = E.nt, units = nt >> 4, u0 = TC_EPI_WARPS == 4 ? units : (units + 1) >> 1;   // 16-column units over the column halves
@@ -579,14 +647,19 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                         }
                     }
                     tr.ev(0x800 + ei);
+                    if (E.done_bar >= 0) {              // two-phase programs: the accumulator has been read, its columns are free
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(pb0 + 8 * E.done_bar);
+                    }
                 }
                 tr.ev(0x900 + ei);
             }
             tc_fence_before();
-            pbits ^= P.parity_mask;
+            if (k0n >= 0) pbits ^= a.prog[k0n].parity_mask;
+            if (k1n >= 0) pbits1 ^= a.prog[k1n].parity_mask;
         }
     }
-#undef TC_ITEM_LOOP
     tc_fence_before();
     __syncthreads();
     pf_timeline(0x53);
@@ -642,6 +715,33 @@ static int pick_kt(int nt, int kc, int slot_bytes) {
     return kt < kc ? kt : kc;
 }
 
+// Last pass over a built program: blob offsets in CANONICAL order (layer, output column, K origin) -- whatever order and
+// tile size a program issues its groups in, all programs of a net read the same packed blob -- plus the per-item barrier
+// completion parities and what arrives on each barrier.
+static void finalize_program(TcProgram& P) {
+    if (P.phases == 0) { P.phases = 1; P.nbuf = 2; }
+    int order[TC_MAX_GROUPS];
+    for (int i = 0; i < P.ngroups; ++i) order[i] = i;
+    auto key = [&](int i) { const TcGroup& g = P.g[i]; return ((long long)g.layer << 40) | ((long long)g.n_base << 20) | g.k_base; };
+    for (int i = 1; i < P.ngroups; ++i) { const int x = order[i]; int j = i - 1; while (j >= 0 && key(order[j]) > key(x)) { order[j + 1] = order[j]; --j; } order[j + 1] = x; }
+    long long off = 0;
+    for (int i = 0; i < P.ngroups; ++i) {
+        TcGroup& g = P.g[order[i]];
+        g.blob_off = (uint32_t)off;
+        off += (long long)g.nt * ((g.bias ? 16 : 0) + g.kc) * 2;
+    }
+    P.blob_bytes = off;
+    int cnt[TC_NBARS] = {0};
+    for (int i = 0; i < P.ngroups; ++i) { if (P.g[i].commit_bar >= 0) cnt[P.g[i].commit_bar]++; if (P.g[i].commit2_bar >= 0) cnt[P.g[i].commit2_bar]++; }
+    for (int i = 0; i < P.nepis; ++i) if (P.e[i].done_bar >= 0) cnt[P.e[i].done_bar]++;
+    cnt[BAR_XFULL]++;
+    P.parity_mask = 0;
+    for (int b = 0; b < TC_NBARS; ++b) if (cnt[b] & 1) P.parity_mask |= 1u << b;
+    for (int b = 0; b < TC_NBARS; ++b) P.bar_kind[b] = TC_BK_COMMIT;
+    for (int i = 0; i < P.nepis; ++i) if (P.e[i].done_bar >= 0) P.bar_kind[P.e[i].done_bar] = TC_BK_EPI;
+    P.bar_kind[BAR_XFULL] = TC_BK_STG;
+}
+
 // Builds the static schedule of one net (see the header comment).  Returns non-zero if the shape does not fit.
 static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int slot_bytes = TC_SLOT_BYTES) {
     memset(&P, 0, sizeof(P));
@@ -661,12 +761,9 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
     int compl_[TC_NBARS] = {0};
     int last_free_k[2] = {-1, -1};
     int ach_next = 0;
-    long long off = 0;
     auto add_group = [&](TcGroup g) -> int {
         if (P.ngroups == TC_MAX_GROUPS) return 1;
         g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes);
-        g.blob_off = (uint32_t)off;
-        off += (long long)g.nt * ((g.bias ? 16 : 0) + g.kc) * 2;
         P.g[P.ngroups++] = g;
         return 0;
     };
@@ -685,7 +782,12 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
         g.layer = 0; g.n_base = (uint16_t)(c * TC_CHUNK); g.k_base = 0;
         g.nt = (uint16_t)((P.pdims[1] - c * TC_CHUNK) < TC_CHUNK ? (P.pdims[1] - c * TC_CHUNK) : TC_CHUNK);
         g.kc = (uint16_t)P.pdims[0]; g.a_src = 0; g.bias = 1; g.tmem_col = (uint16_t)((c & 1) * TC_CHUNK);
-        g.wait_bar = -1; g.wait_k = 0;
+        g.wait_bar = -1; g.wait_k = 0; g.prev_bar = -1;
+        // The accumulator slot may still hold what the PREVIOUS item's final epilogue reads: with an odd number of layers
+        // the last layer accumulates at column 0 (chunk 0's slot), and a single-layer net's chunks ARE the final outputs.
+        // (Even layer counts -- the three-hidden-layer nets of the reference -- end in the other half of TMEM.)
+        if (L == 1) { g.prev_bar = BAR_ODONE; g.prev_k = (int8_t)c; }
+        else if ((L & 1) && c == 0) { g.prev_bar = BAR_ODONE; g.prev_k = (int8_t)((P.pdims[L] + TC_CHUNK - 1) / TC_CHUNK - 1); }
         if (c == 0) { g.wait_bar = BAR_XFULL; g.wait_k = 0; }
         else if (c >= 2 && L > 1) { g.wait_bar = (int8_t)(BAR_E0 + e_b0[c - 2]); g.wait_k = (int8_t)e_k0[c - 2]; }   // slot drained
         g.commit_bar = (int8_t)(BAR_ACC0 + (c & 1));
@@ -699,7 +801,7 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
         g.layer = (int8_t)l; g.n_base = 0; g.k_base = (uint16_t)(j * TC_CHUNK);
         g.nt = (uint16_t)P.pdims[l + 1]; g.kc = (uint16_t)width; g.a_src = (int8_t)(1 + b); g.bias = j == 0;
         g.tmem_col = (uint16_t)region_col(l);
-        g.wait_bar = (int8_t)(BAR_E0 + b); g.wait_k = (int8_t)e_k;
+        g.wait_bar = (int8_t)(BAR_E0 + b); g.wait_k = (int8_t)e_k; g.prev_bar = -1;
         g.commit_bar = (int8_t)(BAR_AFREE0 + b);
         last_free_k[b] = compl_[BAR_AFREE0 + b]++;
         g.commit2_bar = -1;
@@ -723,7 +825,7 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
             if (add_epi(e)) return 1;
             if (consumer_group(1, c, nt, b, e_k0[c], c == nch0 - 1)) return 1;
             if (c == nch0 - 1) acc_k_prev = compl_[region_bar(1)]++;
-        } else if (add_epi(e)) return 1;
+        } else { e.done_bar = BAR_ODONE; if (add_epi(e)) return 1; }      // final output: tells the next item its accumulator is read
         if (c + 2 < nch0 && layer0_group(c + 2)) return 1;
     }
     // ---- layers >= 1: whole accumulator, epilogue in chunks, each chunk feeds layer l + 1 at once ----
@@ -745,50 +847,182 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
                 if (add_epi(e)) return 1;
                 if (consumer_group(l + 1, j, nt, b, e_k, j == nch - 1)) return 1;
                 if (j == nch - 1) acc_k_prev = compl_[region_bar(l + 1)]++;
-            } else if (add_epi(e)) return 1;
+            } else { e.done_bar = BAR_ODONE; if (add_epi(e)) return 1; }
         }
     }
-    compl_[BAR_XFULL] = 1;
-    compl_[BAR_XFREE] = 1;
-    for (int b = 0; b < TC_NBARS; ++b) if (compl_[b] & 1) P.parity_mask |= 1u << b;
-    P.blob_bytes = off;
+    (void)compl_;
+    finalize_program(P);
     return 0;
 }
 
-// Dry run of the schedule on the host: MMA issuer and epilogue as two in-order agents that only advance when the
-// barrier completion they wait for has happened.  A schedule that cannot finish two consecutive items is rejected
-// at create time instead of trapping on the device.
+// The same networks as a TWO-PHASE program (see the kernel's iteration loop): three hidden layers, the rsl_rl default.
+//   phase 0 of an item: layer 0 in chunks of 128 columns through ONE accumulator slot S = TMEM [0, 128), every chunk fed at
+//                       once to layer 1, whose accumulator is TMEM [256, 512);
+//   phase 1:            layer 1's epilogue (1-2 chunks) -> layer 2 -> its epilogue -> output layer, accumulators in
+//                       T = TMEM [128, 256); activation chunks through buffer 2.
+// Phase 1 of item m runs interleaved with phase 0 of item m + 1: the epilogue warps alternate between the two items'
+// steps, and the MMA thread issues every group right after the epilogue step it depends on, in the merged order.  The
+// hazards that program order does not already cover are explicit waits (see the comments below); check_program()
+// replays the schedule on the host.
+static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes) {
+    memset(&P, 0, sizeof(P));
+    const int L = n.layers;
+    if (L != 4) return 1;
+    P.layers = L; P.odd_col = 256; P.phases = 2; P.nbuf = 3;
+    for (int i = 0; i <= L; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
+    if (P.pdims[0] > 256 || P.pdims[2] > 256 || P.pdims[3] > 128 || P.pdims[4] > 128) return 1;
+    const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK, nch1 = (P.pdims[2] + TC_CHUNK - 1) / TC_CHUNK;
+    if (nch0 < 2 || nch0 > 8) return 1;
+    P.x0_bytes = (((P.pdims[0] >> 3) * TC_X0_LBO) + 127) & ~127;
+    auto width = [&](int l, int c) { const int w = P.pdims[l] - c * TC_CHUNK; return w < TC_CHUNK ? w : TC_CHUNK; };   // chunk c of layer l's OUTPUT is pdims[l]
+    const int S = 0, T = 128, A1 = 256;
+
+    // ---- the epilogue steps of the two phases, then merged A, B, A, B ...
+    struct Ep { TcEpi e; int pos; };
+    Ep ep0[8], ep1[4]; int n0 = 0, n1 = 0;
+    for (int c = 0; c < nch0; ++c) {                       // phase 0: chunk c of layer 0: S -> buffer c & 1
+        TcEpi e = {};
+        e.phase = 0; e.tmem_col = S; e.nt = (uint16_t)width(1, c); e.n0 = (uint16_t)(c * TC_CHUNK);
+        e.acc_bar = BAR_ACC0; e.acc_k = (int8_t)c;
+        e.dst = (int8_t)(c & 1); e.done_bar = (int8_t)(BAR_E0 + (c & 1));
+        e.free_bar = -1;
+        // buffer c & 1 was last read by layer-1 slice c - 2 of this item; slices of the PREVIOUS item completed before its
+        // layer-1 accumulator did, which phase 1's first step (earlier in the merged order) has waited for
+        if (c >= 2) { e.free_bar = (int8_t)(BAR_AFREE0 + (c & 1)); e.free_k = (int8_t)((c - 2) >> 1); }
+        ep0[n0++].e = e;
+    }
+    for (int j = 0; j < nch1; ++j) {                       // phase 1: chunk j of layer 1: A1 -> buffer 2
+        TcEpi e = {};
+        e.phase = 1; e.tmem_col = (uint16_t)(A1 + j * TC_CHUNK); e.nt = (uint16_t)width(2, j); e.n0 = (uint16_t)(j * TC_CHUNK);
+        e.acc_bar = BAR_ACC1; e.acc_k = 0;
+        e.dst = 2; e.done_bar = BAR_E2;
+        e.free_bar = -1;
+        if (j >= 1) { e.free_bar = BAR_AFREE2; e.free_k = (int8_t)(j - 1); }     // layer-2 slice j - 1 has read the buffer
+        ep1[n1++].e = e;                                   // (j = 0: the previous item's output MMAs, which its final epilogue waited for)
+    }
+    {                                                      // layer 2: T -> buffer 2 (its last reader, the last layer-2 slice, completed with ACC2)
+        TcEpi e = {};
+        e.phase = 1; e.tmem_col = T; e.nt = (uint16_t)P.pdims[3]; e.n0 = 0;
+        e.acc_bar = BAR_ACC2; e.acc_k = 0; e.dst = 2; e.done_bar = BAR_E2; e.free_bar = -1;
+        ep1[n1++].e = e;
+    }
+    {                                                      // output layer: T -> global memory; ODONE: T is free for the next item
+        TcEpi e = {};
+        e.phase = 1; e.tmem_col = T; e.nt = (uint16_t)P.pdims[4]; e.n0 = 0;
+        e.acc_bar = BAR_ACC3; e.acc_k = 0; e.dst = -1; e.done_bar = BAR_ODONE; e.free_bar = -1;
+        ep1[n1++].e = e;
+    }
+    int pos = 0, i0 = 0, i1 = 0;
+    while (i0 < n0 || i1 < n1) {
+        if (i1 < n1) { ep1[i1].pos = pos++; P.e[P.nepis++] = ep1[i1++].e; }
+        if (i0 < n0) { ep0[i0].pos = pos++; P.e[P.nepis++] = ep0[i0++].e; }
+    }
+
+    // ---- MMA groups, each placed after the last epilogue step it depends on (stable in the order created below)
+    struct Gr { TcGroup g; int pos; int seq; };
+    Gr gr[TC_MAX_GROUPS]; int ng = 0;
+    auto add = [&](TcGroup g, int at) { g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes); gr[ng].g = g; gr[ng].pos = at; gr[ng].seq = ng; ++ng; };
+    auto l0_group = [&](int c) {
+        TcGroup g = {};
+        g.phase = 0; g.layer = 0; g.n_base = (uint16_t)(c * TC_CHUNK); g.k_base = 0; g.nt = (uint16_t)width(1, c);
+        g.kc = (uint16_t)P.pdims[0]; g.a_src = 0; g.bias = 1; g.tmem_col = S;
+        if (c == 0) { g.wait_bar = BAR_XFULL; g.wait_k = 0; }     // S: drained by the previous item's last chunk, which its last layer-1 slice waited for
+        else { g.wait_bar = (int8_t)(BAR_E0 + ((c - 1) & 1)); g.wait_k = (int8_t)((c - 1) >> 1); }      // S drained by chunk c - 1
+        g.commit_bar = BAR_ACC0; g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_XFREE : -1); g.prev_bar = -1;
+        return g;
+    };
+    const int pos_l1_drained = ep1[nch1 - 1].pos;          // the previous item's last layer-1 chunk has left A1
+    add(l0_group(0), -1);
+    for (int j = 0; j < nch1; ++j) {                       // layer 2, slice j (reads buffer 2)
+        TcGroup g = {};
+        g.phase = 1; g.layer = 2; g.n_base = 0; g.k_base = (uint16_t)(j * TC_CHUNK); g.nt = (uint16_t)P.pdims[3];
+        g.kc = (uint16_t)width(2, j); g.a_src = 3; g.bias = j == 0; g.tmem_col = T;
+        g.wait_bar = BAR_E2; g.wait_k = (int8_t)j;
+        g.commit_bar = (int8_t)(j < nch1 - 1 ? BAR_AFREE2 : BAR_ACC2); g.commit2_bar = -1;
+        // T still holds the previous item's output accumulator until its final epilogue has read it
+        g.prev_bar = (int8_t)(j == 0 ? BAR_ODONE : -1);
+        add(g, ep1[j].pos);
+    }
+    for (int c = 0; c < nch0; ++c) {
+        if (c + 1 < nch0) add(l0_group(c + 1), ep0[c].pos);
+        TcGroup g = {};                                    // layer 1, slice c (reads buffer c & 1)
+        g.phase = 0; g.layer = 1; g.n_base = 0; g.k_base = (uint16_t)(c * TC_CHUNK); g.nt = (uint16_t)P.pdims[2];
+        g.kc = (uint16_t)width(1, c); g.a_src = (int8_t)(1 + (c & 1)); g.bias = c == 0; g.tmem_col = A1;
+        g.wait_bar = (int8_t)(BAR_E0 + (c & 1)); g.wait_k = (int8_t)(c >> 1);
+        g.commit_bar = (int8_t)(BAR_AFREE0 + (c & 1)); g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_ACC1 : -1); g.prev_bar = -1;
+        // slice 0 overwrites A1: it goes after the phase-1 group that waited for the previous item's last layer-1 chunk
+        add(g, c == 0 && pos_l1_drained > ep0[0].pos ? pos_l1_drained : ep0[c].pos);
+    }
+    {                                                      // output layer (reads buffer 2, written by the layer-2 epilogue)
+        TcGroup g = {};
+        g.phase = 1; g.layer = 3; g.n_base = 0; g.k_base = 0; g.nt = (uint16_t)P.pdims[4];
+        g.kc = (uint16_t)P.pdims[3]; g.a_src = 3; g.bias = 1; g.tmem_col = T;
+        g.wait_bar = BAR_E2; g.wait_k = (int8_t)nch1;
+        g.commit_bar = BAR_ACC3; g.commit2_bar = -1; g.prev_bar = -1;
+        add(g, ep1[nch1].pos);
+    }
+    // stable sort by (pos, phase 1 first, creation order)
+    for (int i = 1; i < ng; ++i) {
+        Gr x = gr[i]; int j = i - 1;
+        auto before = [](const Gr& u, const Gr& v) { return u.pos != v.pos ? u.pos < v.pos : (u.g.phase != v.g.phase ? u.g.phase > v.g.phase : u.seq < v.seq); };
+        while (j >= 0 && before(x, gr[j])) { gr[j + 1] = gr[j]; --j; }
+        gr[j + 1] = x;
+    }
+    for (int i = 0; i < ng; ++i) P.g[P.ngroups++] = gr[i].g;
+    finalize_program(P);
+    return 0;
+}
+
+// Dry run of the schedule on the host: staging, MMA issuer and epilogue as three in-order agents that only advance when
+// the barrier completion they wait for has happened, over three items (four iterations of a two-phase program: prologue,
+// two steady iterations, drain).  A schedule that cannot finish, or in which a barrier runs more than one completion ahead
+// of a waiter (the parity wait could not tell), is rejected at create time instead of trapping on the device.
 static int check_program(const TcProgram& P) {
-    int done[TC_NBARS] = {0}, per_item[TC_NBARS] = {0};
-    for (int item = 0; item < 2; ++item) {
-        int base[TC_NBARS];
-        for (int b = 0; b < TC_NBARS; ++b) base[b] = done[b];
-        int gi = 0, ei = 0;
-        bool staged = false, progress = true;
-        while ((gi < P.ngroups || ei < P.nepis) && progress) {
-            progress = false;
-            if (!staged) { done[BAR_XFULL]++; staged = true; progress = true; }
-            while (gi < P.ngroups) {
-                const TcGroup& G = P.g[gi];
-                if (G.wait_bar >= 0 && done[G.wait_bar] <= base[G.wait_bar] + G.wait_k) break;
+    const int NI = 3, n_iter = NI + P.phases - 1;
+    int per[TC_NBARS] = {0};
+    for (int i = 0; i < P.ngroups; ++i) { if (P.g[i].commit_bar >= 0) per[P.g[i].commit_bar]++; if (P.g[i].commit2_bar >= 0) per[P.g[i].commit2_bar]++; }
+    for (int i = 0; i < P.nepis; ++i) if (P.e[i].done_bar >= 0) per[P.e[i].done_bar]++;
+    per[BAR_XFULL] = 1;
+    for (int b = 0; b < TC_NBARS; ++b) if ((per[b] & 1) != (int)((P.parity_mask >> b) & 1u)) return 1;
+    int done[TC_NBARS] = {0};
+    int s_item = 0, g_it = 0, g_i = 0, e_it = 0, e_i = 0;
+    bool bad = false;
+    auto reached = [&](int b, int k, int m) {        // completion k of item m on barrier b
+        const int target = m * per[b] + k;
+        if (done[b] > target + 1) { bad = true; if (getenv("PF_TC_CHECK_DEBUG")) fprintf(stderr, "check_program: barrier %d at %d, waiter wants %d (item %d k %d)\n", b, done[b], target, m, k); }
+        return done[b] > target;
+    };
+    bool progress = true;
+    while (progress && !bad) {
+        progress = false;
+        while (s_item < NI && (s_item == 0 || reached(BAR_XFREE, 0, s_item - 1))) { done[BAR_XFULL]++; ++s_item; progress = true; }
+        while (g_it < n_iter) {
+            if (g_i == P.ngroups) { g_i = 0; ++g_it; progress = true; continue; }
+            const TcGroup& G = P.g[g_i];
+            const int m = g_it - G.phase;
+            if (m >= 0 && m < NI) {
+                if (G.wait_bar >= 0 && !reached(G.wait_bar, G.wait_k, m)) break;
+                if (G.prev_bar >= 0 && m >= 1 && !reached(G.prev_bar, G.prev_k, m - 1)) break;
                 if (G.commit_bar >= 0) done[G.commit_bar]++;
                 if (G.commit2_bar >= 0) done[G.commit2_bar]++;
-                ++gi; progress = true;
             }
-            while (ei < P.nepis) {
-                const TcEpi& E = P.e[ei];
-                if (done[E.acc_bar] <= base[E.acc_bar] + E.acc_k) break;
-                if (E.free_bar >= 0 && done[E.free_bar] <= base[E.free_bar] + E.free_k) break;
-                if (E.done_bar >= 0) done[E.done_bar]++;
-                ++ei; progress = true;
-            }
+            ++g_i; progress = true;
         }
-        if (gi < P.ngroups || ei < P.nepis) return 1;
-        for (int b = 0; b < TC_NBARS; ++b) {
-            if (item == 0) per_item[b] = done[b] - base[b];
-            if (done[b] - base[b] != per_item[b] || ((per_item[b] & 1) != (int)((P.parity_mask >> b) & 1u))) return 1;
+        while (e_it < n_iter) {
+            if (e_i == P.nepis) { e_i = 0; ++e_it; progress = true; continue; }
+            const TcEpi& E = P.e[e_i];
+            const int m = e_it - E.phase;
+            if (m >= 0 && m < NI) {
+                if (!reached(E.acc_bar, E.acc_k, m)) break;
+                if (E.free_bar >= 0 && !reached(E.free_bar, E.free_k, m)) break;
+                if (E.done_bar >= 0) done[E.done_bar]++;
+            }
+            ++e_i; progress = true;
         }
     }
+    if (getenv("PF_TC_CHECK_DEBUG")) fprintf(stderr, "check_program: bad=%d staged=%d mma it=%d step=%d epi it=%d step=%d\n", (int)bad, s_item, g_it, g_i, e_it, e_i);
+    if (bad || s_item < NI || g_it < n_iter || e_it < n_iter) return 1;
+    for (int b = 0; b < TC_NBARS; ++b) if (done[b] != NI * per[b]) return 1;
     return 0;
 }
 
@@ -822,25 +1056,27 @@ extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, in
     n.layers = layers;
     for (int i = 0; i <= layers; ++i) n.dims[i] = dims[i];
     TcProgram P;
-    if (build_program(P, n) || check_program(P)) return 6;
+    if (getenv("PF_TC_PLAN_PIPE")) {                 // the two-phase program of the same net (diagnostic)
+        if (build_program_pipe(P, n, 32768) || check_program(P)) return 6;
+    } else if (build_program(P, n) || check_program(P)) return 6;
     int w = 0;
     auto put = [&](const char* fmt, auto... v) { if (text && w < cap) { int r = snprintf(text + w, (size_t)(cap - w), fmt, v...); if (r > 0) w += r; } };
     put("groups=%d epilogues=%d blob_bytes=%lld x0_bytes=%d parity_mask=0x%x\n", P.ngroups, P.nepis, P.blob_bytes, P.x0_bytes, P.parity_mask);
     for (int i = 0; i < P.ngroups; ++i) {
         const TcGroup& G = P.g[i];
-        put("G%d layer=%d a_src=%d nt=%d kc=%d kt=%d col=%d bias=%d wait=%d@%d commit=%d,%d off=%u\n", i, G.layer, G.a_src, G.nt, G.kc, G.kt,
-            G.tmem_col, G.bias, G.wait_bar, G.wait_k, G.commit_bar, G.commit2_bar, G.blob_off);
+        put("G%d ph=%d layer=%d a_src=%d nt=%d kc=%d kt=%d col=%d bias=%d wait=%d@%d prev=%d commit=%d,%d off=%u\n", i, G.phase, G.layer, G.a_src, G.nt, G.kc, G.kt,
+            G.tmem_col, G.bias, G.wait_bar, G.wait_k, G.prev_bar, G.commit_bar, G.commit2_bar, G.blob_off);
     }
     for (int i = 0; i < P.nepis; ++i) {
         const TcEpi& E = P.e[i];
-        put("E%d col=%d nt=%d n0=%d acc=%d@%d dst=%d free=%d@%d done=%d\n", i, E.tmem_col, E.nt, E.n0, E.acc_bar, E.acc_k, E.dst, E.free_bar, E.free_k, E.done_bar);
+        put("E%d ph=%d col=%d nt=%d n0=%d acc=%d@%d dst=%d free=%d@%d done=%d\n", i, E.phase, E.tmem_col, E.nt, E.n0, E.acc_bar, E.acc_k, E.dst, E.free_bar, E.free_k, E.done_bar);
     }
     return 0;
 }
 
 // budget_kb: 227 (one CTA per SM), or 113 for the compact variant (two CTAs per SM: 2 x (113 + 1 KB reserved) = 228 KB)
-static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 2, int slot_bytes = TC_SLOT_BYTES) {
-    const int fixed = x0_bytes + 2 * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
+static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 2, int slot_bytes = TC_SLOT_BYTES, int nbuf = 2) {
+    const int fixed = x0_bytes + nbuf * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
     int S = (budget_kb * 1024 - fixed) / slot_bytes;
     if (S < min_stages) return 1;
     *stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
@@ -850,8 +1086,9 @@ static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb
 
 int pf_tc_create(pf_rl_ctx* c) {
     TcState* t = new TcState();
+    { const char* e = getenv("PF_TC_SLOT_KB"); t->slot_bytes = e ? atoi(e) * 1024 : TC_SLOT_BYTES; }       // experiments
     for (int k = 0; k < 2; ++k) {
-        if (build_program(t->prog[k], c->net[k]) || check_program(t->prog[k])) {
+        if (build_program(t->prog[k], c->net[k], 256, t->slot_bytes) || check_program(t->prog[k])) {
             delete t;
             return tc_fail(6, "pf_rl_create: MLP shape not supported by the fused tensor-core kernel (input <= 256 wide, "
                               "first hidden layer <= 1024, later layers <= 256)");
@@ -861,7 +1098,7 @@ int pf_tc_create(pf_rl_ctx* c) {
     for (int v = 0; v < 3; ++v) {
         const int xa = t->prog[0].x0_bytes, xc = t->prog[1].x0_bytes;
         t->x0_bytes[v] = v == 0 ? xa : v == 1 ? xc : (xa > xc ? xa : xc);
-        if (smem_layout(t->x0_bytes[v], &t->stages[v], &t->smem_bytes[v])) { delete t; return tc_fail(6, "pf_rl_create: shared memory layout does not fit"); }
+        if (smem_layout(t->x0_bytes[v], &t->stages[v], &t->smem_bytes[v], 227, 2, t->slot_bytes)) { delete t; return tc_fail(6, "pf_rl_create: shared memory layout does not fit"); }
         max_smem = t->smem_bytes[v] > max_smem ? t->smem_bytes[v] : max_smem;
     }
     // compact variant (two CTAs per SM): both nets' accumulators within 256 TMEM columns, shared memory within 113 KB.  Same
@@ -877,6 +1114,23 @@ int pf_tc_create(pf_rl_ctx* c) {
         int mc = 0;
         for (int v = 0; v < 3; ++v) mc = t->smem_bytes_c[v] > mc ? t->smem_bytes_c[v] : mc;
         if (cudaFuncSetAttribute(pf_mlp_tc_kernel_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, mc) != cudaSuccess) { cudaGetLastError(); t->compact = 0; }
+    }
+    // two-phase variant: both nets with the same step list (so that one item's second half interleaves with the other
+    // net's first half at the actor -> critic boundary), same packed weights
+    t->pipe = getenv("PF_TC_NO_PIPE") == nullptr;
+    { const char* e = getenv("PF_TC_PIPE_SLOT_KB"); t->slot_bytes_p = e ? atoi(e) * 1024 : 32768; }
+    for (int k = 0; k < 2 && t->pipe; ++k)
+        if (build_program_pipe(t->progp[k], c->net[k], t->slot_bytes_p) || check_program(t->progp[k]) || t->progp[k].blob_bytes != t->prog[k].blob_bytes)
+            t->pipe = 0;
+    if (t->pipe) {
+        const TcProgram &A = t->progp[0], &B = t->progp[1];
+        if (A.ngroups != B.ngroups || A.nepis != B.nepis) t->pipe = 0;
+        for (int i = 0; i < A.ngroups && t->pipe; ++i) if (A.g[i].phase != B.g[i].phase || A.g[i].layer != B.g[i].layer) t->pipe = 0;
+        for (int i = 0; i < A.nepis && t->pipe; ++i) if (A.e[i].phase != B.e[i].phase) t->pipe = 0;
+    }
+    for (int v = 0; v < 3 && t->pipe; ++v) {
+        if (smem_layout(t->x0_bytes[v], &t->stages_p[v], &t->smem_bytes_p[v], 227, 2, t->slot_bytes_p, 3)) t->pipe = 0;
+        else max_smem = t->smem_bytes_p[v] > max_smem ? t->smem_bytes_p[v] : max_smem;
     }
     for (int k = 0; k < 2; ++k) {
         if (cudaMalloc(&c->net[k].tc_weights, (size_t)t->prog[k].blob_bytes) != cudaSuccess) { delete t; return tc_fail(2, "pf_rl_create: cudaMalloc of the packed weights failed"); }
@@ -913,7 +1167,8 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
     a.stages = t->stages[variant];
-    a.slot_bytes = TC_SLOT_BYTES;
+    a.slot_bytes = t->slot_bytes;
+    a.nbuf = 2;
     a.x0_bytes = t->x0_bytes[variant];
     a.trace = t->trace;
     a.rehearse = 0;
@@ -941,6 +1196,21 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     }
     a.tmem_cols = TC_TMEM_COLS;
     const int grid = items < c->num_sms ? items : c->num_sms;
+    // The two-phase programs: second half of item m interleaved with the first half of item m + 1.
+    // OPT-IN (PF_TC_PIPE=1, read per launch): measured at 262,144 rows it is no faster than the single-phase program --
+    // the staged rows are single-buffered, so every iteration still waits out one staging pass
+    const char* pipe_env = getenv("PF_TC_PIPE");
+    if (t->pipe && pipe_env && atoi(pipe_env) != 0) {
+        for (int i = 0; i < a.nnets; ++i)
+            for (int k = 0; k < 2; ++k)
+                if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progp[k];
+        a.stages = t->stages_p[variant];
+        a.slot_bytes = t->slot_bytes_p;
+        a.nbuf = 3;
+        a.rehearse = 0;
+        return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes_p[variant], st, a) == cudaSuccess
+                   ? 0 : tc_fail(2, "pf_mlp_tc_kernel (two-phase): launch failed");
+    }
     return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
                ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }

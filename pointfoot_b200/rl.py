@@ -553,8 +553,8 @@ class BenchPolicy:
         path = self.alg.inference_path
         self.kernel_name = {"fp32": "pf_sgemm_kernel chain + pf_act_sample_kernel", "tcgen05": "pf_mlp_tc_kernel",
                             "warp_mma": "pf_mlp_wm_kernel"}[path]
-        self.dtype_name = {"fp32": "f32", "tcgen05": "bf16 (tcgen05 MLP, fp32 accumulate) + f32 env",
-                           "warp_mma": "bf16 (register-resident warp-MMA MLP, fp32 accumulate) + f32 env"}[path]
+        self.dtype_name = {"fp32": "f32", "tcgen05": "f16 (tcgen05 MLP, fp32 accumulate) + f32 env",
+                           "warp_mma": "f16 (register-resident warp-MMA MLP, fp32 accumulate) + f32 env"}[path]
         n_layers = len(self.ac.actor_dims) - 1 + len(self.ac.critic_dims) - 1
         self.launches_per_act = 1 if precision == "bf16" else n_layers + 3      # bf16: ONE fused tcgen05 launch
         self.t = 0

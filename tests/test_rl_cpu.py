@@ -60,11 +60,12 @@ def test_tensor_core_mlp_schedule_is_built_and_dry_run_on_the_host():
     for the PointFoot critic [148, 512, 256, 128, 1]: 4 layer-0 chunks + 4 + 2 + 1 K-slices = 11 MMA groups, 8 epilogues,
     every chunk buffer hand-over guarded by a barrier."""
     import ctypes as C
+    import os
     import re
     from pointfoot_b200 import capi
     lib = capi.load()
 
-    def plan(dims, cap=8192):
+    def plan(dims, cap=16384):
         arr = (C.c_int32 * len(dims))(*dims)
         buf = C.create_string_buffer(cap)
         return lib.pf_rl_tc_plan(arr, len(dims) - 1, buf, cap), buf.value.decode()
@@ -74,15 +75,36 @@ def test_tensor_core_mlp_schedule_is_built_and_dry_run_on_the_host():
     for bad in ([300, 64, 6], [27, 64, 512, 6], [27, 1100, 32, 1]):      # input > 256, later layer > 256, first layer > 1024
         assert plan(bad)[0] == 6, bad
     rc, text = plan([148, 512, 256, 128, 1])
-    groups = re.findall(r"^G\d+ layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+) bias=(\d+) wait=(-?\d+)@", text, re.M)
-    epis = re.findall(r"^E\d+ col=(\d+) nt=(\d+) n0=(\d+) acc=(\d+)@(\d+) dst=(-?\d+)", text, re.M)
+    groups = re.findall(r"^G\d+ ph=\d+ layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+) bias=(\d+) wait=(-?\d+)@", text, re.M)
+    epis = re.findall(r"^E\d+ ph=\d+ col=(\d+) nt=(\d+) n0=(\d+) acc=(\d+)@(\d+) dst=(-?\d+)", text, re.M)
     assert len(groups) == 11 and len(epis) == 8
     assert [g[0] for g in groups].count("0") == 4 and [g[0] for g in groups].count("1") == 4
-    assert all(int(g[2]) * int(g[4]) * 2 <= 16384 for g in groups)            # a weight tile fits a ring slot
+    assert all(int(g[2]) * int(g[4]) * 2 <= 32768 for g in groups)            # a weight tile fits a ring slot
     assert all(int(g[7]) >= 0 for g in groups if g[1] != "0")                 # chunk consumers wait for their producer
     assert [e[5] for e in epis][-1] == "-1" and all(e[5] in "01" for e in epis[:-1])
     blob = int(re.search(r"blob_bytes=(\d+)", text).group(1))
     assert blob == 2 * ((160 + 16) * 512 + (512 + 16) * 256 + (256 + 16) * 128 + (128 + 16) * 16)
+    # the TWO-PHASE program of the same net (large batches): the same 11 groups and 8 epilogues, re-ordered so that the second
+    # half of an item (phase 1: layer-1 epilogues, layers 2 and 3) interleaves with the first half of the next one; the
+    # same packed blob; replayed on the host over three items by check_program (rc 6 if it cannot finish)
+    os.environ["PF_TC_PLAN_PIPE"] = "1"
+    try:
+        rc2, text2 = plan([148, 512, 256, 128, 1])
+        assert rc2 == 0
+        g2 = re.findall(r"^G\d+ ph=(\d+) layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+)", text2, re.M)
+        e2 = re.findall(r"^E\d+ ph=(\d+) col=(\d+) nt=(\d+) n0=(\d+) acc=(\d+)@(\d+) dst=(-?\d+)", text2, re.M)
+        assert len(g2) == 11 and len(e2) == 8
+        assert [e[0] for e in e2] == ["1", "0"] * 4                               # epilogue steps alternate between the two items
+        assert sorted((g[1], g[3], g[4]) for g in g2) == sorted((g[0], g[2], g[3]) for g in groups)
+        assert int(re.search(r"blob_bytes=(\d+)", text2).group(1)) == blob
+        cols = {(g[0], g[1]): int(g[6]) for g in g2}
+        assert cols[("0", "0")] == 0 and cols[("0", "1")] == 256 and cols[("1", "2")] == 128 and cols[("1", "3")] == 128
+        for dims in ([27, 512, 256, 128, 6], [48, 256, 128, 64, 6], [48, 1024, 256, 128, 12]):
+            assert plan(dims)[0] == 0, dims
+        for dims in ([27, 128, 64, 32, 6], [48, 256, 128, 6], [27, 512, 256, 256, 6]):     # one layer-0 chunk / not 3 hidden layers / layer 3 too wide
+            assert plan(dims)[0] == 6, dims
+    finally:
+        del os.environ["PF_TC_PLAN_PIPE"]
 
 
 def test_export_policy_as_jit_from_a_reference_style_checkpoint(tmp_path):

@@ -47,6 +47,21 @@ def test_tcgen05_path_still_serves_small_nets_when_asked(hidden, nc, n, monkeypa
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
 
 
+@pytest.mark.parametrize("n", [300, 40000])
+def test_tcgen05_two_phase_program_matches_oracle(n, monkeypatch):
+    """PF_TC_PIPE=1: the software-pipelined schedule of the same kernel (second half of item m interleaved with the first
+    half of item m + 1; pf_mlp_tc.cu build_program_pipe) -- prologue + drain only at 300 rows, four to five items per CTA
+    at 40,000"""
+    monkeypatch.setenv("PF_TC_PIPE", "1")
+    parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=148, hidden=(512, 256, 128), T=3, precision="bf16")
+
+
+def test_tcgen05_odd_layer_count_many_items_per_cta():
+    """Two hidden layers: the output layer accumulates in the TMEM columns the NEXT item's first chunk uses, so the next
+    item has to wait for the final epilogue (BAR_ODONE) -- several items per CTA, ragged last tile"""
+    parity_rl.run_act_and_gae(num_envs=40001, num_critic_obs=48, hidden=(256, 128), T=2, precision="bf16")
+
+
 def test_path_selection():
     for hidden, nc, want in (((512, 256, 128), 148, "tcgen05"), ((128, 64, 32), 148, "tcgen05"), ((100, 50), 27, "tcgen05"),
                              ((128, 64, 32), 27, "warp_mma")):

@@ -1,6 +1,6 @@
 // Issue / completion cost of tcgen05.mma (kind::f16, bf16, M = 128, SS mode, K-major no-swizzle operands) from one
 // thread, with and without a tcgen05.commit after every few MMAs.  Numbers feed the tile-size choice of pf_mlp_tc.cu.
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o umma_microbench tools/umma_microbench.cu && ./umma_microbench
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o umma_microbench tools/micro/umma_microbench.cu && ./umma_microbench
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdint.h>
