@@ -63,7 +63,9 @@ enum { BAR_ACC0 = 0, BAR_ACC1 = 1, BAR_ACC2 = 2,      // accumulator complete: T
        BAR_ACC3 = 9,                                 // last layer's accumulator complete
        BAR_AFREE2 = 10, BAR_E2 = 11,                 // chunk buffer 2 (the second phase's)
        BAR_ODONE = 12,                               // the final epilogue has read its accumulator
-       TC_NBARS = 13 };
+       BAR_XFULL1 = 13, BAR_XFREE1 = 14,             // second staged-row buffer (items with odd index); = BAR_XFULL / XFREE + TC_XBAR_STEP
+       TC_NBARS = 15 };
+#define TC_XBAR_STEP 6
 enum { TC_BK_COMMIT = 0, TC_BK_EPI = 1, TC_BK_STG = 2 };
 
 // One accumulation step: D[128 x nt] (+)= A[128 x kc] * W^T, A = staged input rows or an activation chunk.
@@ -99,7 +101,8 @@ struct TcProgram {
     int ngroups, nepis;
     uint32_t parity_mask;                // bit b: barrier b completes an odd number of times per item
     int phases;                          // 1, or 2: steps of phase 1 belong to the item of the PREVIOUS iteration (software pipeline)
-    int nbuf;                            // activation chunk buffers (2, or 3 in two-phase programs)
+    int nbuf;                            // activation chunk buffers
+    int x0_nbuf;                         // staged-row buffers: 1, or 2 in two-phase programs (item m uses buffer m & 1 and barrier set m & 1)
     int8_t bar_kind[TC_NBARS];           // TC_BK_*
     int x0_bytes;
     long long blob_bytes;
@@ -135,7 +138,7 @@ struct TcNetArgs {
 struct TcArgs {
     TcProgram prog[2];
     TcNetArgs net[2];
-    int nnets, rows, tiles, stages, x0_bytes, slot_bytes, nbuf;
+    int nnets, rows, tiles, stages, x0_bytes, slot_bytes, nbuf, x0_nbuf;
     int tmem_cols;               // 512, or 256 in the compact variant (two CTAs per SM)
     // PPO.act tail (TC_OUT_SAMPLE / TC_OUT_VALUE)
     uint32_t seed, policy_step; int env_id_offset, num_actions;
@@ -227,6 +230,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
         const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
         *reinterpret_cast<unsigned short*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = tc_h(v);
     };
+    tr.ev(0x506);
     if (N.ldx == K0 && ((reinterpret_cast<uintptr_t>(xb) | reinterpret_cast<uintptr_t>(cb)) & 15) == 0) {
         const int n4 = total >> 2;
         const float4* x4 = reinterpret_cast<const float4*>(xb);
@@ -239,6 +243,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                 const int idx = base + u * TC_STG_THREADS;
                 if (idx < n4) v[u] = noload ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
             }
+            tr.ev(0x507);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int idx = base + u * TC_STG_THREADS;
@@ -253,6 +258,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                     }
                 }
             }
+            tr.ev(0x508);
         }
         for (int e = n4 * 4 + tid; e < total; e += TC_STG_THREADS) {
             const float v = noload ? 0.0f : __ldg(xb + e);
@@ -329,8 +335,8 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32, TC_STG_THREADS = TC_STG_WARPS * 32;
     constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_STG_WARPS, TC_LOAD_WARP = TC_MMA_WARP + 1;
     extern __shared__ __align__(128) unsigned char smem[];
-    unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] fp16
-    unsigned char* ach = smem + a.x0_bytes;                    // 2 (3) activation chunk buffers [128 x 128] fp16
+    unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] fp16 (x 2 in two-phase programs)
+    unsigned char* ach = smem + a.x0_nbuf * a.x0_bytes;        // activation chunk buffers [128 x 128] fp16
     unsigned char* ones = ach + a.nbuf * TC_ACHUNK_BYTES;      // [128 x 16] fp16: columns 0,1 = 1
     unsigned char* ring = ones + TC_ROWS * 32;
     uint64_t* bars = reinterpret_cast<uint64_t*>(ring + a.stages * a.slot_bytes);
@@ -457,7 +463,10 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     if (k < 0) continue;
                     const TcGroup G = a.prog[k].g[gi];
                     tr.ev(0x200 + gi);
-                    if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, par_of(ph ? pbits1 : pbits, G.wait_bar, G.wait_k));
+                    // two staged-row buffers (two-phase programs): item m of phase 0 uses buffer / barrier set m & 1, use number m >> 1
+                    const uint32_t xb = a.x0_nbuf == 2 ? (uint32_t)(it & 1) : 0u;
+                    if (G.wait_bar == BAR_XFULL && a.x0_nbuf == 2) mbar_wait(pb0 + 8 * (BAR_XFULL + xb * TC_XBAR_STEP), (uint32_t)(it >> 1) & 1u);
+                    else if (G.wait_bar >= 0) mbar_wait(pb0 + 8 * G.wait_bar, par_of(ph ? pbits1 : pbits, G.wait_bar, G.wait_k));
                     // (two-phase programs) a resource the previous item of this phase still held: its one completion of
                     // prev_bar -- there is no such item in the phase's first iteration
                     if (G.prev_bar >= 0 && it - ph >= 1) mbar_wait(pb0 + 8 * G.prev_bar, par_of(ph ? pprev1 : pprev0, G.prev_bar, G.prev_k));
@@ -467,7 +476,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     const bool xs = G.a_src == 0;
                     const uint32_t idesc = make_idesc_f16(nt);
                     const uint32_t tmem_d = tmem_base + G.tmem_col;
-                    const uint32_t a_base = xs ? x0_addr : ach_addr + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
+                    const uint32_t a_base = xs ? x0_addr + xb * (uint32_t)a.x0_bytes : ach_addr + (uint32_t)(G.a_src - 1) * TC_ACHUNK_BYTES;
                     const uint32_t a_lbo = xs ? TC_X0_LBO : TC_ROWS * 16;
                     uint64_t adesc = make_desc(a_base, a_lbo, 128u);
                     const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4);               // K = 16 further along the A operand
@@ -519,7 +528,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     }
                     if (elect_one()) {
                         if (G.commit_bar >= 0) umma_commit(pb0 + 8 * G.commit_bar);
-                        if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * G.commit2_bar);
+                        if (G.commit2_bar >= 0) umma_commit(pb0 + 8 * (G.commit2_bar + (G.commit2_bar == BAR_XFREE ? xb * TC_XBAR_STEP : 0u)));
                     }
                     __syncwarp();
                     tr.ev(0x400 + gi);
@@ -538,9 +547,11 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             const bool dry = j < 0;
             const int w = (int)blockIdx.x + (dry ? 0 : j) * (int)gridDim.x;
             if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(tid == TC_EPI_THREADS && blockIdx.x == 0, 0x52); }
-            if (cnt) mbar_wait(pb0 + 8 * BAR_XFREE, (cnt - 1u) & 1u);
+            // buffer (and barrier set) of this item; it is free once the MMAs of the item that used it last have completed
+            const uint32_t nb = (uint32_t)a.x0_nbuf, xb = nb == 2 ? (cnt & 1u) : 0u, use = nb == 2 ? (cnt >> 1) : cnt;
+            if (use) mbar_wait(pb0 + 8 * (BAR_XFREE + xb * TC_XBAR_STEP), (use - 1u) & 1u);
             tr.ev(0x500);
-            tc_stage_item<TC_STG_THREADS>(a, w, x0, pb0 + 8 * BAR_XFULL, tid - TC_EPI_THREADS, tr, dry);
+            tc_stage_item<TC_STG_THREADS>(a, w, x0 + xb * a.x0_bytes, pb0 + 8 * (BAR_XFULL + xb * TC_XBAR_STEP), tid - TC_EPI_THREADS, tr, dry);
             tr.ev(0x502);
             ++cnt;
         }
@@ -740,6 +751,8 @@ static void finalize_program(TcProgram& P) {
     for (int b = 0; b < TC_NBARS; ++b) P.bar_kind[b] = TC_BK_COMMIT;
     for (int i = 0; i < P.nepis; ++i) if (P.e[i].done_bar >= 0) P.bar_kind[P.e[i].done_bar] = TC_BK_EPI;
     P.bar_kind[BAR_XFULL] = TC_BK_STG;
+    if (P.x0_nbuf == 0) P.x0_nbuf = 1;
+    if (P.x0_nbuf == 2) P.bar_kind[BAR_XFULL1] = TC_BK_STG;
 }
 
 // Builds the static schedule of one net (see the header comment).  Returns non-zero if the shape does not fit.
@@ -856,54 +869,56 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
 }
 
 // The same networks as a TWO-PHASE program (see the kernel's iteration loop): three hidden layers, the rsl_rl default.
-//   phase 0 of an item: layer 0 in chunks of 128 columns through ONE accumulator slot S = TMEM [0, 128), every chunk fed at
-//                       once to layer 1, whose accumulator is TMEM [256, 512);
+//   phase 0 of an item: layer 0 in chunks of 128 columns through ONE accumulator slot S = TMEM [0, 128) and ONE chunk
+//                       buffer (0), every chunk fed at once to layer 1, whose accumulator is TMEM [256, 512);
 //   phase 1:            layer 1's epilogue (1-2 chunks) -> layer 2 -> its epilogue -> output layer, accumulators in
-//                       T = TMEM [128, 256); activation chunks through buffer 2.
+//                       T = TMEM [128, 256); activation chunks through buffer 1.
 // Phase 1 of item m runs interleaved with phase 0 of item m + 1: the epilogue warps alternate between the two items'
-// steps, and the MMA thread issues every group right after the epilogue step it depends on, in the merged order.  The
-// hazards that program order does not already cover are explicit waits (see the comments below); check_program()
-// replays the schedule on the host.
+// steps (so a chunk buffer's reader has a whole foreign step to finish in before its next writer asks), and the MMA
+// thread issues every group right after the epilogue step it depends on, in the merged order.  The staged input rows
+// are DOUBLE-buffered (the shared memory a third chunk buffer would take): they are held until the item's last layer-0
+// chunk, most of an iteration, and with one buffer the next item's staging pass sat on the critical loop.  The hazards
+// that program order does not already cover are explicit waits (comments below); check_program() replays the schedule.
 static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes) {
     memset(&P, 0, sizeof(P));
     const int L = n.layers;
     if (L != 4) return 1;
-    P.layers = L; P.odd_col = 256; P.phases = 2; P.nbuf = 3;
+    P.layers = L; P.odd_col = 256; P.phases = 2; P.nbuf = 2; P.x0_nbuf = 2;
     for (int i = 0; i <= L; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
     if (P.pdims[0] > 256 || P.pdims[2] > 256 || P.pdims[3] > 128 || P.pdims[4] > 128) return 1;
     const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK, nch1 = (P.pdims[2] + TC_CHUNK - 1) / TC_CHUNK;
     if (nch0 < 2 || nch0 > 8) return 1;
     P.x0_bytes = (((P.pdims[0] >> 3) * TC_X0_LBO) + 127) & ~127;
-    auto width = [&](int l, int c) { const int w = P.pdims[l] - c * TC_CHUNK; return w < TC_CHUNK ? w : TC_CHUNK; };   // chunk c of layer l's OUTPUT is pdims[l]
+    auto width = [&](int l, int c) { const int w = P.pdims[l] - c * TC_CHUNK; return w < TC_CHUNK ? w : TC_CHUNK; };   // chunk c of the layer whose OUTPUT is pdims[l]
     const int S = 0, T = 128, A1 = 256;
 
     // ---- the epilogue steps of the two phases, then merged A, B, A, B ...
     struct Ep { TcEpi e; int pos; };
     Ep ep0[8], ep1[4]; int n0 = 0, n1 = 0;
-    for (int c = 0; c < nch0; ++c) {                       // phase 0: chunk c of layer 0: S -> buffer c & 1
+    for (int c = 0; c < nch0; ++c) {                       // phase 0: chunk c of layer 0: S -> buffer 0
         TcEpi e = {};
         e.phase = 0; e.tmem_col = S; e.nt = (uint16_t)width(1, c); e.n0 = (uint16_t)(c * TC_CHUNK);
         e.acc_bar = BAR_ACC0; e.acc_k = (int8_t)c;
-        e.dst = (int8_t)(c & 1); e.done_bar = (int8_t)(BAR_E0 + (c & 1));
+        e.dst = 0; e.done_bar = BAR_E0;
         e.free_bar = -1;
-        // buffer c & 1 was last read by layer-1 slice c - 2 of this item; slices of the PREVIOUS item completed before its
-        // layer-1 accumulator did, which phase 1's first step (earlier in the merged order) has waited for
-        if (c >= 2) { e.free_bar = (int8_t)(BAR_AFREE0 + (c & 1)); e.free_k = (int8_t)((c - 2) >> 1); }
+        // buffer 0 is read by layer-1 slice c - 1 of this item (AFREE0); the last slice of the PREVIOUS item completed with
+        // its layer-1 accumulator, which phase 1's first step (earlier in the merged order) has waited for
+        if (c >= 1) { e.free_bar = BAR_AFREE0; e.free_k = (int8_t)(c - 1); }
         ep0[n0++].e = e;
     }
-    for (int j = 0; j < nch1; ++j) {                       // phase 1: chunk j of layer 1: A1 -> buffer 2
+    for (int j = 0; j < nch1; ++j) {                       // phase 1: chunk j of layer 1: A1 -> buffer 1
         TcEpi e = {};
         e.phase = 1; e.tmem_col = (uint16_t)(A1 + j * TC_CHUNK); e.nt = (uint16_t)width(2, j); e.n0 = (uint16_t)(j * TC_CHUNK);
         e.acc_bar = BAR_ACC1; e.acc_k = 0;
-        e.dst = 2; e.done_bar = BAR_E2;
+        e.dst = 1; e.done_bar = BAR_E1;
         e.free_bar = -1;
-        if (j >= 1) { e.free_bar = BAR_AFREE2; e.free_k = (int8_t)(j - 1); }     // layer-2 slice j - 1 has read the buffer
+        if (j >= 1) { e.free_bar = BAR_AFREE1; e.free_k = (int8_t)(j - 1); }     // layer-2 slice j - 1 has read the buffer
         ep1[n1++].e = e;                                   // (j = 0: the previous item's output MMAs, which its final epilogue waited for)
     }
-    {                                                      // layer 2: T -> buffer 2 (its last reader, the last layer-2 slice, completed with ACC2)
+    {                                                      // layer 2: T -> buffer 1 (its last reader, the last layer-2 slice, completed with ACC2)
         TcEpi e = {};
         e.phase = 1; e.tmem_col = T; e.nt = (uint16_t)P.pdims[3]; e.n0 = 0;
-        e.acc_bar = BAR_ACC2; e.acc_k = 0; e.dst = 2; e.done_bar = BAR_E2; e.free_bar = -1;
+        e.acc_bar = BAR_ACC2; e.acc_k = 0; e.dst = 1; e.done_bar = BAR_E1; e.free_bar = -1;
         ep1[n1++].e = e;
     }
     {                                                      // output layer: T -> global memory; ODONE: T is free for the next item
@@ -927,37 +942,37 @@ static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes) {
         g.phase = 0; g.layer = 0; g.n_base = (uint16_t)(c * TC_CHUNK); g.k_base = 0; g.nt = (uint16_t)width(1, c);
         g.kc = (uint16_t)P.pdims[0]; g.a_src = 0; g.bias = 1; g.tmem_col = S;
         if (c == 0) { g.wait_bar = BAR_XFULL; g.wait_k = 0; }     // S: drained by the previous item's last chunk, which its last layer-1 slice waited for
-        else { g.wait_bar = (int8_t)(BAR_E0 + ((c - 1) & 1)); g.wait_k = (int8_t)((c - 1) >> 1); }      // S drained by chunk c - 1
+        else { g.wait_bar = BAR_E0; g.wait_k = (int8_t)(c - 1); }   // S drained by chunk c - 1
         g.commit_bar = BAR_ACC0; g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_XFREE : -1); g.prev_bar = -1;
         return g;
     };
     const int pos_l1_drained = ep1[nch1 - 1].pos;          // the previous item's last layer-1 chunk has left A1
     add(l0_group(0), -1);
-    for (int j = 0; j < nch1; ++j) {                       // layer 2, slice j (reads buffer 2)
+    for (int j = 0; j < nch1; ++j) {                       // layer 2, slice j (reads buffer 1)
         TcGroup g = {};
         g.phase = 1; g.layer = 2; g.n_base = 0; g.k_base = (uint16_t)(j * TC_CHUNK); g.nt = (uint16_t)P.pdims[3];
-        g.kc = (uint16_t)width(2, j); g.a_src = 3; g.bias = j == 0; g.tmem_col = T;
-        g.wait_bar = BAR_E2; g.wait_k = (int8_t)j;
-        g.commit_bar = (int8_t)(j < nch1 - 1 ? BAR_AFREE2 : BAR_ACC2); g.commit2_bar = -1;
+        g.kc = (uint16_t)width(2, j); g.a_src = 2; g.bias = j == 0; g.tmem_col = T;
+        g.wait_bar = BAR_E1; g.wait_k = (int8_t)j;
+        g.commit_bar = (int8_t)(j < nch1 - 1 ? BAR_AFREE1 : BAR_ACC2); g.commit2_bar = -1;
         // T still holds the previous item's output accumulator until its final epilogue has read it
-        g.prev_bar = (int8_t)(j == 0 ? BAR_ODONE : -1);
+        g.prev_bar = (int8_t)(j == 0 ? BAR_ODONE : -1); g.prev_k = 0;
         add(g, ep1[j].pos);
     }
     for (int c = 0; c < nch0; ++c) {
         if (c + 1 < nch0) add(l0_group(c + 1), ep0[c].pos);
-        TcGroup g = {};                                    // layer 1, slice c (reads buffer c & 1)
+        TcGroup g = {};                                    // layer 1, slice c (reads buffer 0)
         g.phase = 0; g.layer = 1; g.n_base = 0; g.k_base = (uint16_t)(c * TC_CHUNK); g.nt = (uint16_t)P.pdims[2];
-        g.kc = (uint16_t)width(1, c); g.a_src = (int8_t)(1 + (c & 1)); g.bias = c == 0; g.tmem_col = A1;
-        g.wait_bar = (int8_t)(BAR_E0 + (c & 1)); g.wait_k = (int8_t)(c >> 1);
-        g.commit_bar = (int8_t)(BAR_AFREE0 + (c & 1)); g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_ACC1 : -1); g.prev_bar = -1;
+        g.kc = (uint16_t)width(1, c); g.a_src = 1; g.bias = c == 0; g.tmem_col = A1;
+        g.wait_bar = BAR_E0; g.wait_k = (int8_t)c;
+        g.commit_bar = BAR_AFREE0; g.commit2_bar = (int8_t)(c == nch0 - 1 ? BAR_ACC1 : -1); g.prev_bar = -1;
         // slice 0 overwrites A1: it goes after the phase-1 group that waited for the previous item's last layer-1 chunk
         add(g, c == 0 && pos_l1_drained > ep0[0].pos ? pos_l1_drained : ep0[c].pos);
     }
-    {                                                      // output layer (reads buffer 2, written by the layer-2 epilogue)
+    {                                                      // output layer (reads buffer 1, written by the layer-2 epilogue)
         TcGroup g = {};
         g.phase = 1; g.layer = 3; g.n_base = 0; g.k_base = 0; g.nt = (uint16_t)P.pdims[4];
-        g.kc = (uint16_t)P.pdims[3]; g.a_src = 3; g.bias = 1; g.tmem_col = T;
-        g.wait_bar = BAR_E2; g.wait_k = (int8_t)nch1;
+        g.kc = (uint16_t)P.pdims[3]; g.a_src = 2; g.bias = 1; g.tmem_col = T;
+        g.wait_bar = BAR_E1; g.wait_k = (int8_t)nch1;
         g.commit_bar = BAR_ACC3; g.commit2_bar = -1; g.prev_bar = -1;
         add(g, ep1[nch1].pos);
     }
@@ -987,15 +1002,19 @@ static int check_program(const TcProgram& P) {
     int done[TC_NBARS] = {0};
     int s_item = 0, g_it = 0, g_i = 0, e_it = 0, e_i = 0;
     bool bad = false;
+    const int nb = P.x0_nbuf;
     auto reached = [&](int b, int k, int m) {        // completion k of item m on barrier b
         const int target = m * per[b] + k;
+        if (b == BAR_XFULL && nb == 2) return done[b] > target;
         if (done[b] > target + 1) { bad = true; if (getenv("PF_TC_CHECK_DEBUG")) fprintf(stderr, "check_program: barrier %d at %d, waiter wants %d (item %d k %d)\n", b, done[b], target, m, k); }
         return done[b] > target;
     };
     bool progress = true;
     while (progress && !bad) {
         progress = false;
-        while (s_item < NI && (s_item == 0 || reached(BAR_XFREE, 0, s_item - 1))) { done[BAR_XFULL]++; ++s_item; progress = true; }
+        // staging: item s goes to buffer s % nb, free once item s - nb's layer-0 MMAs have completed (one logical XFULL /
+        // XFREE counter here; the device uses a barrier pair per buffer, so "two ahead" cannot alias there)
+        while (s_item < NI && (s_item < nb || done[BAR_XFREE] > s_item - nb)) { done[BAR_XFULL]++; ++s_item; progress = true; }
         while (g_it < n_iter) {
             if (g_i == P.ngroups) { g_i = 0; ++g_it; progress = true; continue; }
             const TcGroup& G = P.g[g_i];
@@ -1075,8 +1094,8 @@ extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, in
 }
 
 // budget_kb: 227 (one CTA per SM), or 113 for the compact variant (two CTAs per SM: 2 x (113 + 1 KB reserved) = 228 KB)
-static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 2, int slot_bytes = TC_SLOT_BYTES, int nbuf = 2) {
-    const int fixed = x0_bytes + nbuf * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
+static int smem_layout(int x0_bytes, int* stages, int* smem_bytes, int budget_kb = 227, int min_stages = 2, int slot_bytes = TC_SLOT_BYTES, int nbuf = 2, int x0_nbuf = 1) {
+    const int fixed = x0_nbuf * x0_bytes + nbuf * TC_ACHUNK_BYTES + TC_ROWS * 32 + 512;
     int S = (budget_kb * 1024 - fixed) / slot_bytes;
     if (S < min_stages) return 1;
     *stages = S > TC_MAX_STAGES ? TC_MAX_STAGES : S;
@@ -1129,7 +1148,7 @@ int pf_tc_create(pf_rl_ctx* c) {
         for (int i = 0; i < A.nepis && t->pipe; ++i) if (A.e[i].phase != B.e[i].phase) t->pipe = 0;
     }
     for (int v = 0; v < 3 && t->pipe; ++v) {
-        if (smem_layout(t->x0_bytes[v], &t->stages_p[v], &t->smem_bytes_p[v], 227, 2, t->slot_bytes_p, 3)) t->pipe = 0;
+        if (smem_layout(t->x0_bytes[v], &t->stages_p[v], &t->smem_bytes_p[v], 227, 2, t->slot_bytes_p, 2, 2)) t->pipe = 0;
         else max_smem = t->smem_bytes_p[v] > max_smem ? t->smem_bytes_p[v] : max_smem;
     }
     for (int k = 0; k < 2; ++k) {
@@ -1169,6 +1188,7 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.stages = t->stages[variant];
     a.slot_bytes = t->slot_bytes;
     a.nbuf = 2;
+    a.x0_nbuf = 1;
     a.x0_bytes = t->x0_bytes[variant];
     a.trace = t->trace;
     a.rehearse = 0;
@@ -1206,7 +1226,8 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
                 if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progp[k];
         a.stages = t->stages_p[variant];
         a.slot_bytes = t->slot_bytes_p;
-        a.nbuf = 3;
+        a.nbuf = 2;
+        a.x0_nbuf = 2;
         a.rehearse = 0;
         return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes_p[variant], st, a) == cudaSuccess
                    ? 0 : tc_fail(2, "pf_mlp_tc_kernel (two-phase): launch failed");
