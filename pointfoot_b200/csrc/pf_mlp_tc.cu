@@ -81,7 +81,7 @@ struct TcGroup {
     int8_t commit_bar, commit2_bar;    // barriers the completion of the group's MMAs arrives on (-1: none)
     int8_t phase;                      // two-phase programs: 0 = first half of the item, 1 = second half, run one iteration later
     int8_t prev_bar, prev_k;           // also wait for completion prev_k of this barrier by the PREVIOUS item of the same phase (-1: none)
-    int8_t pad[2];
+    uint16_t kt0;                      // != 0: the bias tile and the first kt0 K-columns travel as ONE weight tile (they are contiguous in the blob)
 };
 // One epilogue step: accumulator columns [tmem_col, tmem_col + nt) -> activation chunk buffer or the final output.
 struct TcEpi {
@@ -412,8 +412,10 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     tr.ev(0x100 + gi);
                     uint32_t off = G.blob_off;
                     const int nt = G.nt, kc = G.kc, kt = G.kt;
-                    for (int kk = G.bias ? -16 : 0; kk < kc; kk += (kk < 0 ? 16 : kt)) {
-                        const uint32_t bytes = (uint32_t)(nt * (kk < 0 ? 16 : min(kt, kc - kk)) * 2);
+                    // tiles: [bias] [kt] [kt] ..., or with kt0: [bias + kt0] [kt] ...
+                    for (int kk = (G.bias && !G.kt0) ? -16 : 0; kk < kc; kk += (kk < 0 ? 16 : (kk == 0 && G.kt0) ? (int)G.kt0 : kt)) {
+                        const uint32_t bytes = (kk == 0 && G.kt0) ? (uint32_t)(nt * (16 + (int)G.kt0) * 2)
+                                                                  : (uint32_t)(nt * (kk < 0 ? 16 : min(kt, kc - kk)) * 2);
                         if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
                         if (elect_one()) {
                             if (a.debug & 8) mbar_arrive(full0 + 8 * slot);          // experiment: no weight traffic
@@ -482,7 +484,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     const uint64_t a_step = (uint64_t)((2 * a_lbo) >> 4);               // K = 16 further along the A operand
                     const uint64_t b_lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16;  // next 8 K-columns of a weight tile
                     const uint64_t b_step = (uint64_t)(nt * 2);                         // K = 16 further inside a tile, in 16 B units
-                    if (G.bias) {
+                    if (G.bias && !G.kt0) {
                         tr.ev(0xA00 + gi);
                         mbar_wait(full_bar, round & 1u);
                         tc_fence_after();
@@ -496,13 +498,18 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     int left = G.kc >> 4;                       // K = 16 steps still to issue
                     const int per_tile = G.kt >> 4;
                     uint32_t have = 0;                          // the next tile's barrier was already seen complete
+                    bool first = true;
                     while (left > 0) {
                         tr.ev(0xA00 + gi);
                         if (!have) mbar_wait(full_bar, round & 1u);      // bulk copy -> MMA: both async proxy, the mbarrier orders them
                         tr.ev(0xB00 + gi);
-                        const uint64_t bdesc0 = ring_desc + b_lbo, adesc0 = adesc;
+                        uint64_t bdesc0 = ring_desc + b_lbo;
+                        const uint64_t adesc0 = adesc;
                         const uint32_t cur_empty = empty_bar;
-                        const int nk = left < per_tile ? left : per_tile;
+                        int nk = left < per_tile ? left : per_tile;
+                        const bool with_bias = first && G.kt0;         // this tile starts with the bias columns
+                        if (with_bias) { nk = G.kt0 >> 4; }
+                        first = false;
                         adesc += (uint64_t)nk * a_step;
                         next_slot();
                         left -= nk;
@@ -510,6 +517,10 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                         // cycles even when the tile has long landed, and here they pass under the MMA issue
                         have = (left > 0 && peek) ? mbar_test(full_bar, round & 1u) : 0u;
                         if (elect_one()) {
+                            if (with_bias) {
+                                if (!no_mma) umma_bf16(tmem_d, ones_desc, bdesc0, idesc, 0u);
+                                bdesc0 += (uint64_t)(nt * 2);          // past the bias columns (nt x 16 fp16 = nt * 2 sixteen-byte units)
+                            }
                             // the common tile shapes with compile-time descriptor strides, anything else through the generic loop
                             if (no_mma) { }
                             else if (nt == 128 && xs) issue_tile<TC_X0_KSTEP, 256>(nk, tmem_d, adesc0, bdesc0, idesc);
@@ -720,6 +731,16 @@ __global__ void pf_tc_pack_kernel(const __grid_constant__ TcPackArgs a, const fl
 
 static int tc_fail(int code, const char* msg) { pf_set_error(msg); return code; }
 
+// K-columns that fit a slot beside the bias tile (0: the bias travels alone -- nothing would be saved)
+static int pick_kt0(int nt, int kc, int kt, int slot_bytes, int bias) {
+    if (!bias) return 0;
+    int k0 = ((slot_bytes - nt * 32) / 2 / nt) & ~15;
+    if (k0 > 128) k0 = 128;
+    if (k0 > kc) k0 = kc;
+    if (k0 < 16) return 0;
+    const int merged = 1 + (kc - k0 + kt - 1) / kt, separate = 1 + (kc + kt - 1) / kt;
+    return merged < separate ? k0 : 0;
+}
 static int pick_kt(int nt, int kc, int slot_bytes) {
     int kt = (slot_bytes / 2 / nt) & ~15;
     if (kt > 128) kt = 128;
@@ -777,6 +798,7 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
     auto add_group = [&](TcGroup g) -> int {
         if (P.ngroups == TC_MAX_GROUPS) return 1;
         g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes);
+        g.kt0 = (uint16_t)pick_kt0(g.nt, g.kc, g.kt, slot_bytes, g.bias);
         P.g[P.ngroups++] = g;
         return 0;
     };
@@ -936,7 +958,7 @@ static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes) {
     // ---- MMA groups, each placed after the last epilogue step it depends on (stable in the order created below)
     struct Gr { TcGroup g; int pos; int seq; };
     Gr gr[TC_MAX_GROUPS]; int ng = 0;
-    auto add = [&](TcGroup g, int at) { g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes); gr[ng].g = g; gr[ng].pos = at; gr[ng].seq = ng; ++ng; };
+    auto add = [&](TcGroup g, int at) { g.kt = (uint16_t)pick_kt(g.nt, g.kc, slot_bytes); g.kt0 = (uint16_t)pick_kt0(g.nt, g.kc, g.kt, slot_bytes, g.bias); gr[ng].g = g; gr[ng].pos = at; gr[ng].seq = ng; ++ng; };
     auto l0_group = [&](int c) {
         TcGroup g = {};
         g.phase = 0; g.layer = 0; g.n_base = (uint16_t)(c * TC_CHUNK); g.k_base = 0; g.nt = (uint16_t)width(1, c);
@@ -1083,8 +1105,8 @@ extern "C" int pf_rl_tc_plan(const int32_t* dims, int32_t layers, char* text, in
     put("groups=%d epilogues=%d blob_bytes=%lld x0_bytes=%d parity_mask=0x%x\n", P.ngroups, P.nepis, P.blob_bytes, P.x0_bytes, P.parity_mask);
     for (int i = 0; i < P.ngroups; ++i) {
         const TcGroup& G = P.g[i];
-        put("G%d ph=%d layer=%d a_src=%d nt=%d kc=%d kt=%d col=%d bias=%d wait=%d@%d prev=%d commit=%d,%d off=%u\n", i, G.phase, G.layer, G.a_src, G.nt, G.kc, G.kt,
-            G.tmem_col, G.bias, G.wait_bar, G.wait_k, G.prev_bar, G.commit_bar, G.commit2_bar, G.blob_off);
+        put("G%d ph=%d layer=%d a_src=%d nt=%d kc=%d kt=%d col=%d bias=%d kt0=%d wait=%d@%d prev=%d commit=%d,%d off=%u\n", i, G.phase, G.layer, G.a_src, G.nt, G.kc, G.kt,
+            G.tmem_col, G.bias, G.kt0, G.wait_bar, G.wait_k, G.prev_bar, G.commit_bar, G.commit2_bar, G.blob_off);
     }
     for (int i = 0; i < P.nepis; ++i) {
         const TcEpi& E = P.e[i];

@@ -75,7 +75,7 @@ def test_tensor_core_mlp_schedule_is_built_and_dry_run_on_the_host():
     for bad in ([300, 64, 6], [27, 64, 512, 6], [27, 1100, 32, 1]):      # input > 256, later layer > 256, first layer > 1024
         assert plan(bad)[0] == 6, bad
     rc, text = plan([148, 512, 256, 128, 1])
-    groups = re.findall(r"^G\d+ ph=\d+ layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+) bias=(\d+) wait=(-?\d+)@", text, re.M)
+    groups = re.findall(r"^G\d+ ph=\d+ layer=(\d+) a_src=(\d+) nt=(\d+) kc=(\d+) kt=(\d+) col=(\d+) bias=(\d+) kt0=\d+ wait=(-?\d+)@", text, re.M)
     epis = re.findall(r"^E\d+ ph=\d+ col=(\d+) nt=(\d+) n0=(\d+) acc=(\d+)@(\d+) dst=(-?\d+)", text, re.M)
     assert len(groups) == 11 and len(epis) == 8
     assert [g[0] for g in groups].count("0") == 4 and [g[0] for g in groups].count("1") == 4
