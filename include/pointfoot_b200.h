@@ -245,7 +245,7 @@ int pf_step_host_join(pf_ctx* ctx, void* stream);
 
 enum pf_rl_precision {
     PF_RL_FP32 = 0,      /* hand-written fp32 SIMT kernels: the parity path (rtol 1e-4 against torch fp32) */
-    PF_RL_BF16_TC = 1    /* tcgen05 tensor-core tiles, bf16 operands, fp32 accumulation in TMEM (rtol 2e-2) */
+    PF_RL_BF16_TC = 1    /* tensor-core paths, fp32 accumulation (rtol 2e-2): 16-bit operands -- fp16 in the inference kernels, bf16 in the PPO.update GEMMs */
 };
 
 /* Hyper-parameters and shapes (PointFootRoughCfgPPO, pointfoot_rough_config.py:216-259).  POD. */
@@ -303,7 +303,7 @@ int64_t pf_rl_param_count(const pf_rl_ctx* ctx);
  * is_bias 0 = weight [out,in], 1 = bias [out] */
 int64_t pf_rl_param_offset(const pf_rl_ctx* ctx, int net, int layer, int is_bias);
 /* must be called after the caller changes `params` by other means than pf_rl_adam_step (init, load):
- * refreshes the packed bf16 copies the tensor-core path reads */
+ * refreshes the packed 16-bit copies the tensor-core path reads */
 int pf_rl_params_changed(pf_rl_ctx* ctx, const float* params, void* stream);
 /* Host-only diagnostic, no device needed: can the fused tensor-core kernel (PF_RL_BF16_TC) run an MLP of this shape
  * (dims[0..layers], the ctor args of actor_critic.py ActorCritic)?  0 yes, 6 no -- the code pf_rl_create would return.
@@ -370,7 +370,7 @@ int pf_rl_get_permutation(pf_rl_ctx* ctx, int32_t* out, void* stream);
 int pf_rl_minibatch_grad(pf_rl_ctx* ctx, const pf_rl_storage* storage, const pf_rl_learner* learner,
                          int32_t minibatch, void* stream);
 /* adaptive-KL learning-rate update (ppo.py update), clip_grad_norm_(max_grad_norm), Adam step; also refreshes
- * the packed bf16 parameter copies. */
+ * the packed 16-bit parameter copies. */
 int pf_rl_adam_step(pf_rl_ctx* ctx, const pf_rl_learner* learner, void* stream);
 
 /* ================================================================================================

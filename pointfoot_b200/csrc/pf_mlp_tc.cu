@@ -45,7 +45,11 @@ void pf_set_error(const char* msg);
 // Warp roles are template parameters of the kernel: kEpi epilogue warps (8 = 4 TMEM lane quarters x 2 column halves; the ELU is
 // MUFU-bound, more do not help; 4 in the compact variant), kStg staging warps (input rows of the NEXT item, under the tail of
 // the current one), then the MMA warp and the loader warp.
-#define TC_THREADS_OF(kEpi, kStg) (((kEpi) + (kStg) + 2) * 32)
+// Warp ids: epilogue warps 0 .. kEpi-1 (a warp reads the TMEM lane quarter `id % 4`, so they cover every scheduler); the MMA warp is
+// kEpi and the loader kEpi + 4 -- both on scheduler 0 --, the staging warps are the following ids that are NOT on scheduler 0, so the
+// issuing warp shares its scheduler with two epilogue warps and the loader only.
+constexpr int tc_last_stg_offset(int kStg) { int d = 0, n = 0; while (n < kStg) { ++d; if (d % 4) ++n; } return d; }
+#define TC_THREADS_OF(kEpi, kStg) (((kEpi) + tc_last_stg_offset(kStg) + 1) * 32)
 #define TC_MAX_GROUPS 24
 #define TC_MAX_EPIS 16
 #define TC_TMEM_COLS 512
@@ -333,7 +337,7 @@ __device__ __noinline__ void tc_sample_row(const TcArgs& a, long long er, const 
 template <int TC_EPI_WARPS, int TC_STG_WARPS, int kCtasPerSm>
 __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCtasPerSm) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
     constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32, TC_STG_THREADS = TC_STG_WARPS * 32;
-    constexpr int TC_MMA_WARP = TC_EPI_WARPS + TC_STG_WARPS, TC_LOAD_WARP = TC_MMA_WARP + 1;
+    constexpr int TC_MMA_WARP = TC_EPI_WARPS, TC_LOAD_WARP = TC_EPI_WARPS + 4;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* x0 = smem;                                  // staged input rows [128 x pdims[0]] fp16 (x 2 in two-phase programs)
     unsigned char* ach = smem + a.x0_nbuf * a.x0_bytes;        // activation chunk buffers [128 x 128] fp16
@@ -344,6 +348,8 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + TC_MAX_STAGES), pb0 = smem_u32(bars + 2 * TC_MAX_STAGES);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_MAX_STAGES + TC_NBARS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int stg_d = warp - TC_EPI_WARPS;                                          // staging warps: offsets 1, 2, 3, 5, 6, 7, 9, ...
+    const int stg_warp = (stg_d > 0 && (stg_d & 3)) ? stg_d - 1 - (stg_d >> 2) : 1 << 20, stg_tid = stg_warp * 32 + lane;
     const int items = a.nnets * a.tiles;
     pf_grid_dep_launch();       // the prologue below (barriers, TMEM, ones operand) runs under the predecessor's tail
     pf_timeline(0x50);
@@ -548,25 +554,25 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                 if (k1n >= 0) { pprev1 = pbits1; pbits1 ^= a.prog[k1n].parity_mask; }
             }
         }
-    } else if (warp >= TC_EPI_WARPS) {
+    } else if (warp > TC_EPI_WARPS && stg_warp < TC_STG_WARPS) {
         // ================================================================ staging: 8 warps, one item ahead
         // The staged rows of item i are dead once its last layer-0 MMAs have completed (BAR_XFREE); the rows of
         // item i + 1 are staged right then, under the MMAs and epilogues of the remaining layers.
-        TcTrace tr; tr.init(a.trace, 3, blockIdx.x == 0 && tid == TC_EPI_THREADS);
+        TcTrace tr; tr.init(a.trace, 3, blockIdx.x == 0 && stg_tid == 0);
         uint32_t cnt = 0;                            // items staged so far (the staging role has no phases: one item per pass)
         for (int j = -reh; j < n_local; ++j) {
             const bool dry = j < 0;
             const int w = (int)blockIdx.x + (dry ? 0 : j) * (int)gridDim.x;
-            if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(tid == TC_EPI_THREADS && blockIdx.x == 0, 0x52); }
+            if (j == 0) { pf_grid_dep_wait(); pf_timeline_raw_if(stg_tid == 0 && blockIdx.x == 0, 0x52); }
             // buffer (and barrier set) of this item; it is free once the MMAs of the item that used it last have completed
             const uint32_t nb = (uint32_t)a.x0_nbuf, xb = nb == 2 ? (cnt & 1u) : 0u, use = nb == 2 ? (cnt >> 1) : cnt;
             if (use) mbar_wait(pb0 + 8 * (BAR_XFREE + xb * TC_XBAR_STEP), (use - 1u) & 1u);
             tr.ev(0x500);
-            tc_stage_item<TC_STG_THREADS>(a, w, x0 + xb * a.x0_bytes, pb0 + 8 * (BAR_XFULL + xb * TC_XBAR_STEP), tid - TC_EPI_THREADS, tr, dry);
+            tc_stage_item<TC_STG_THREADS>(a, w, x0 + xb * a.x0_bytes, pb0 + 8 * (BAR_XFULL + xb * TC_XBAR_STEP), stg_tid, tr, dry);
             tr.ev(0x502);
             ++cnt;
         }
-    } else {
+    } else if (warp < TC_EPI_WARPS) {
         // ================================================================ epilogues: 8 warps
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;          // (h == 0 for every warp when TC_EPI_WARPS == 4)
         uint32_t pbits = 0;
