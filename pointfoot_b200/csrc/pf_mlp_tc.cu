@@ -149,8 +149,13 @@ struct TcArgs {
     const float* std;
     pf_rl_storage S; int has_storage; long long storage_row0;
     float* actions_out; float* values_out; float* logp_out;
+    // Hard-wired MMA role for the two-phase program of [*, 512, 256, 128, *] nets (tc_mma_fast3): per net, layer 0's
+    // K = 16 steps in its first (bias + K) tile and in its second tile, the output layer's UMMA N, and whether its bias
+    // travels with its one K tile.  fast3 = 0: the program interpreter.
+    int fast3, f3_first[2], f3_rest[2], f3_nto[2], f3_merged[2];
     int rehearse;                // run one DRY item (no input loads, no outputs) before the dependency wait: see pf_rl_tc_rehearse
-    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs
+    int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs,
+                                 // bit 5 no barrier peek, bit 6 epilogue steps do no work, bit 7 epilogue converts without the ELU
     unsigned long long* trace;   // optional timeline of CTA 0: TC_TRACE_ROLES x TC_TRACE_CAP (tag << 48 | clock)
 };
 
@@ -334,6 +339,144 @@ __device__ __noinline__ void tc_sample_row(const TcArgs& a, long long er, const 
     if (a.has_storage) a.S.actions_log_prob[srow] = logp;
 }
 
+// The MMA role of the two-phase program for the nets every task of the reference uses ([in, 512, 256, 128, out]), written
+// out: the eleven groups of an iteration in the order build_program_pipe gives them, every descriptor stride, tile count,
+// barrier and parity a constant of the code -- no step table, no dispatch.  The program interpreter spends ~1.3k cycles
+// per group on itself with NOTHING to issue (profiles/r2q_mlp_tc_rough_investigation.txt), 11 groups per 128 rows; this
+// role is the only one whose time a two-phase iteration cannot hide.  The loader, the epilogue and the staging warps keep
+// walking the program, so the two must agree: pf_tc launch code sets fast3 only after comparing the program's groups
+// (order, UMMA N, K extents, tile sizes, barriers) with what is written here.
+//   B = the item of this iteration's phase 0 (number mB = it), A = the item of its phase 1 (mA = it - 1).
+//   Completions per item: ACC0 4, E0 4, AFREE0 4, ACC1 1, E1 3, AFREE1 1, ACC2 1, ACC3 1, ODONE 1; XFULL / XFREE per buffer.
+__device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_iter, uint32_t x0_addr, uint32_t ach_addr, uint32_t ones_addr,
+                                          uint32_t ring_addr, uint32_t full0, uint32_t empty0, uint32_t pb0, uint32_t tmem_base) {
+    const uint32_t S = (uint32_t)a.stages;
+    uint32_t slot = 0, rpar = 0, full_bar = full0, empty_bar = empty0;
+    const uint64_t ring_desc0 = make_desc(ring_addr, 0u, 128u), slot_step = (uint64_t)((uint32_t)a.slot_bytes >> 4);
+    uint64_t ring_desc = ring_desc0;
+    const uint64_t ones_desc = make_desc(ones_addr, TC_ROWS * 16, 128u);
+    const uint64_t ach0_desc = make_desc(ach_addr, TC_ROWS * 16, 128u), ach1_desc = make_desc(ach_addr + TC_ACHUNK_BYTES, TC_ROWS * 16, 128u);
+    const uint64_t x0_desc0 = make_desc(x0_addr, TC_X0_LBO, 128u), x0_desc1 = make_desc(x0_addr + (uint32_t)a.x0_bytes, TC_X0_LBO, 128u);
+    const uint32_t idesc128 = make_idesc_f16(128), idesc256 = make_idesc_f16(256);
+    const uint64_t lbo128 = (uint64_t)(128u * 16u >> 4) << 16, lbo256 = (uint64_t)(256u * 16u >> 4) << 16;
+    const uint32_t tS = tmem_base, tT = tmem_base + 128, tA1 = tmem_base + 256;
+    auto bar = [&](int b) { return pb0 + 8u * (uint32_t)b; };
+    auto next_slot = [&]() {
+        full_bar += 8; empty_bar += 8; ring_desc += slot_step;
+        if (++slot == S) { slot = 0; rpar ^= 1u; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
+    };
+    const int gridn = (int)gridDim.x, cta = (int)blockIdx.x, tiles = a.tiles;
+    for (int it = 0; it < n_iter; ++it) {
+        if (it == 0) pf_grid_dep_wait();
+        const bool hasB = it < n_local, hasA = it >= 1;
+        const int kB = hasB ? (cta + it * gridn) / tiles : 0, kA = hasA ? (cta + (it - 1) * gridn) / tiles : 0;
+        const uint32_t mB = (uint32_t)it, mA = (uint32_t)(it - 1), xb = mB & 1u;
+        const uint64_t xdesc = xb ? x0_desc1 : x0_desc0;
+        const int nfirst = kB ? a.f3_first[1] : a.f3_first[0], nrest = kB ? a.f3_rest[1] : a.f3_rest[0];
+        // ---- layer 0, chunk c of item B: S (+)= x0 * W0[c]^T, bias + first K columns in one tile, the rest in a second
+        auto l0 = [&](int c) {
+            if (!hasB) return;
+            if (c == 0) mbar_wait(bar(BAR_XFULL) + 8u * xb * TC_XBAR_STEP, (mB >> 1) & 1u);
+            else mbar_wait(bar(BAR_E0), (uint32_t)(c - 1) & 1u);                    // S drained (and chunk c - 1 in buffer 0)
+            tc_fence_after();
+            mbar_wait(full_bar, rpar);
+            if (elect_one()) {
+                uint64_t bd = ring_desc + lbo128, ad = xdesc;
+                umma_bf16(tS, ones_desc, bd, idesc128, 0u);
+                bd += 256;
+                for (int k = 0; k < nfirst; ++k) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (nrest) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) {
+                    uint64_t bd = ring_desc + lbo128, ad = xdesc + (uint64_t)(nfirst * TC_X0_KSTEP);
+                    for (int k = 0; k < nrest; ++k) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                    umma_commit(empty_bar);
+                }
+                next_slot();
+            }
+            if (elect_one()) {
+                umma_commit(bar(BAR_ACC0));
+                if (c == 3) umma_commit(bar(BAR_XFREE) + 8u * xb * TC_XBAR_STEP);
+            }
+            __syncwarp();
+        };
+        // ---- layer 1, K-slice c of item B (chunk c from buffer 0): A1 (+)= chunk * W1[:, 128c : 128c + 128]^T, two tiles of 64
+        auto l1 = [&](int c) {
+            if (!hasB) return;
+            mbar_wait(bar(BAR_E0), (uint32_t)c & 1u);
+            tc_fence_after();
+            if (c == 0) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) { umma_bf16(tA1, ones_desc, ring_desc + lbo256, idesc256, 0u); umma_commit(empty_bar); }
+                next_slot();
+            }
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) {
+                    issue_mmas<256, 512, 4>(tA1, ach0_desc + (uint64_t)(t * 4 * 256), ring_desc + lbo256, idesc256);
+                    umma_commit(empty_bar);
+                }
+                next_slot();
+            }
+            if (elect_one()) {
+                umma_commit(bar(BAR_AFREE0));
+                if (c == 3) umma_commit(bar(BAR_ACC1));
+            }
+            __syncwarp();
+        };
+        // ---- layer 2, K-slice j of item A (layer-1 chunk j from buffer 1): T (+)= chunk * W2[:, 128j : 128j + 128]^T
+        auto l2 = [&](int j) {
+            if (!hasA) return;
+            mbar_wait(bar(BAR_E1), (mA + (uint32_t)j) & 1u);                        // completion 3 mA + j
+            if (j == 0 && mA >= 1u) mbar_wait(bar(BAR_ODONE), (mA - 1u) & 1u);        // T: the previous item's output accumulator has been read
+            tc_fence_after();
+            if (j == 0) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) { umma_bf16(tT, ones_desc, ring_desc + lbo128, idesc128, 0u); umma_commit(empty_bar); }
+                next_slot();
+            }
+            mbar_wait(full_bar, rpar);
+            if (elect_one()) {
+                issue_mmas<256, 256, 8>(tT, ach1_desc, ring_desc + lbo128, idesc128);
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (elect_one()) umma_commit(bar(j == 0 ? BAR_AFREE1 : BAR_ACC2));
+            __syncwarp();
+        };
+        // ---- output layer of item A (layer-2 activations from buffer 1): T = h3 * W3^T + b3, K = 128
+        auto l3 = [&]() {
+            if (!hasA) return;
+            mbar_wait(bar(BAR_E1), mA & 1u);                                         // completion 3 mA + 2
+            tc_fence_after();
+            const int nt = kA ? a.f3_nto[1] : a.f3_nto[0], merged = kA ? a.f3_merged[1] : a.f3_merged[0];
+            const uint32_t idesc = make_idesc_f16(nt);
+            const uint64_t lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16, bstep = (uint64_t)(nt * 2);
+            mbar_wait(full_bar, rpar);
+            if (!merged) {
+                if (elect_one()) { umma_bf16(tT, ones_desc, ring_desc + lbo, idesc, 0u); umma_commit(empty_bar); }
+                next_slot();
+                mbar_wait(full_bar, rpar);
+            }
+            if (elect_one()) {
+                uint64_t bd = ring_desc + lbo, ad = ach1_desc;
+                if (merged) { umma_bf16(tT, ones_desc, bd, idesc, 0u); bd += bstep; }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { umma_bf16_acc(tT, ad, bd, idesc); ad += 256; bd += bstep; }
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (elect_one()) umma_commit(bar(BAR_ACC3));
+            __syncwarp();
+        };
+        l0(0); l2(0); l0(1); l2(1); l1(0); l0(2); l1(1); l3(); l0(3); l1(2); l1(3);
+    }
+}
+
 template <int TC_EPI_WARPS, int TC_STG_WARPS, int kCtasPerSm>
 __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCtasPerSm) pf_mlp_tc_kernel(const __grid_constant__ TcArgs a) {
     constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32, TC_STG_THREADS = TC_STG_WARPS * 32;
@@ -436,6 +579,9 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                 }
             }
         }
+    } else if (warp == TC_MMA_WARP && a.fast3) {
+        // ================================================================ MMA issue, hard-wired (see tc_mma_fast3 below)
+        tc_mma_fast3(a, n_local, n_iter, smem_u32(x0), smem_u32(ach), smem_u32(ones), smem_u32(ring), full0, empty0, pb0, tmem_base);
     } else if (warp == TC_MMA_WARP) {
         // ================================================================ MMA issue: one thread
         // The issuing thread is the critical resource of the kernel: traced at 262,144 rows, every weight tile costs it a
@@ -577,13 +723,15 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;          // (h == 0 for every warp when TC_EPI_WARPS == 4)
         uint32_t pbits = 0;
         TcTrace tr; tr.init(a.trace, 0, blockIdx.x == 0 && tid == 0);
+        const bool raw = (a.debug & 128) != 0;          // experiment, bit 7: convert only, no ELU
         // ELU + fp16 pack of 16 accumulator columns [g, g + 16) of this thread's row into a chunk buffer
         auto pack16 = [&](const uint32_t (&v)[16], unsigned char* outb, int g) {
 #pragma unroll
             for (int j = 0; j < 16; j += 8) {
                 uint32_t pk[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) pk[i] = tc_elu_h2(v[j + 2 * i], v[j + 2 * i + 1]);
+                for (int i = 0; i < 4; ++i)
+                    pk[i] = raw ? tc_pack_h2(__uint_as_float(v[j + 2 * i]), __uint_as_float(v[j + 2 * i + 1])) : tc_elu_h2(v[j + 2 * i], v[j + 2 * i + 1]);
                 *reinterpret_cast<uint4*>(outb + (size_t)((g + j) >> 3) * (TC_ROWS * 16) + row * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
         };
@@ -619,7 +767,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                     unsigned char* outb = ach + E.dst * TC_ACHUNK_BYTES;
                     // two register sets of 16 columns: the TMEM load of the next 16 is in flight while the ELUs of the
                     // current 16 issue (tcgen05.ld is asynchronous up to its wait); c_lo, c_hi are multiples of 16
-                    if (c_lo < c_hi) {
+                    if (c_lo < c_hi && !(a.debug & 64)) {              // (experiment, bit 6: the step does no work at all)
                         uint32_t va[16], vb[16];
                         int g = c_lo;
                         tr.ev(0xC00 + ei);
@@ -1210,6 +1358,31 @@ int pf_tc_pack_weights(pf_rl_ctx* c, const float* params, cudaStream_t st) {
     return cudaGetLastError() == cudaSuccess ? 0 : tc_fail(2, "pf_tc_pack_weights: launch failed");
 }
 
+// Does this two-phase program have exactly the shape tc_mma_fast3 is written for?  Fills the per-net parameters it reads.
+static int tc_fast3_params(const TcProgram& P, int& nfirst, int& nrest, int& nto, int& merged) {
+    if (P.phases != 2 || P.layers != 4 || P.pdims[1] != 512 || P.pdims[2] != 256 || P.pdims[3] != 128 || P.ngroups != 11 || P.nepis != 8) return 0;
+    // the order the role issues in: (layer, slice) per group
+    static const int want_layer[11] = {0, 2, 0, 2, 1, 0, 1, 3, 0, 1, 1}, want_idx[11] = {0, 0, 1, 1, 0, 2, 1, 0, 3, 2, 3};
+    for (int i = 0; i < 11; ++i) {
+        const TcGroup& g = P.g[i];
+        if (g.layer != want_layer[i]) return 0;
+        const int idx = g.layer == 0 ? g.n_base / TC_CHUNK : g.k_base / TC_CHUNK;
+        if (idx != want_idx[i]) return 0;
+        if (g.layer == 0) {           // bias + first K columns in one tile, at most one more tile
+            if (g.nt != 128 || !g.bias || g.kt0 == 0 || g.kc - g.kt0 > g.kt || g.a_src != 0 || g.tmem_col != 0) return 0;
+            nfirst = g.kt0 >> 4; nrest = (g.kc - g.kt0) >> 4;
+        } else if (g.layer == 1) {    // [bias] + two tiles of 64
+            if (g.nt != 256 || g.kc != 128 || g.kt != 64 || g.kt0 != 0 || g.bias != (idx == 0) || g.a_src != 1 || g.tmem_col != 256) return 0;
+        } else if (g.layer == 2) {    // [bias] + one tile of 128
+            if (g.nt != 128 || g.kc != 128 || g.kt != 128 || g.kt0 != 0 || g.bias != (idx == 0) || g.a_src != 2 || g.tmem_col != 128) return 0;
+        } else {                      // output layer: one K tile of 128, the bias with it or in front of it
+            if (g.kc != 128 || g.kt != 128 || !g.bias || (g.kt0 != 0 && g.kt0 != 128) || g.a_src != 2 || g.tmem_col != 128 || g.nt > 128) return 0;
+            nto = g.nt; merged = g.kt0 != 0;
+        }
+    }
+    return 1;
+}
+
 static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
@@ -1257,6 +1430,10 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
         a.nbuf = 2;
         a.x0_nbuf = 2;
         a.rehearse = 0;
+        // the hard-wired MMA role, if every net of this launch has exactly the program it was written against
+        a.fast3 = getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes_p == 32768;
+        for (int i = 0; i < a.nnets && a.fast3; ++i) a.fast3 = tc_fast3_params(a.prog[i], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i]);
+        if (a.nnets == 1) { a.f3_first[1] = a.f3_first[0]; a.f3_rest[1] = a.f3_rest[0]; a.f3_nto[1] = a.f3_nto[0]; a.f3_merged[1] = a.f3_merged[0]; }
         return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes_p[variant], st, a) == cudaSuccess
                    ? 0 : tc_fail(2, "pf_mlp_tc_kernel (two-phase): launch failed");
     }
