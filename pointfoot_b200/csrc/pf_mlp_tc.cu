@@ -366,6 +366,7 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
         if (++slot == S) { slot = 0; rpar ^= 1u; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
     };
     const int gridn = (int)gridDim.x, cta = (int)blockIdx.x, tiles = a.tiles;
+    TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0 && (threadIdx.x & 31) == 0);
     for (int it = 0; it < n_iter; ++it) {
         if (it == 0) pf_grid_dep_wait();
         const bool hasB = it < n_local, hasA = it >= 1;
@@ -374,11 +375,13 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
         const uint64_t xdesc = xb ? x0_desc1 : x0_desc0;
         const int nfirst = kB ? a.f3_first[1] : a.f3_first[0], nrest = kB ? a.f3_rest[1] : a.f3_rest[0];
         // ---- layer 0, chunk c of item B: S (+)= x0 * W0[c]^T, bias + first K columns in one tile, the rest in a second
-        auto l0 = [&](int c) {
+        auto l0 = [&](int c, int gi) {
             if (!hasB) return;
+            tr.ev(0x200 + gi);
             if (c == 0) mbar_wait(bar(BAR_XFULL) + 8u * xb * TC_XBAR_STEP, (mB >> 1) & 1u);
             else mbar_wait(bar(BAR_E0), (uint32_t)(c - 1) & 1u);                    // S drained (and chunk c - 1 in buffer 0)
             tc_fence_after();
+            tr.ev(0x300 + gi);
             mbar_wait(full_bar, rpar);
             if (elect_one()) {
                 uint64_t bd = ring_desc + lbo128, ad = xdesc;
@@ -402,12 +405,15 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
                 if (c == 3) umma_commit(bar(BAR_XFREE) + 8u * xb * TC_XBAR_STEP);
             }
             __syncwarp();
+            tr.ev(0x400 + gi);
         };
         // ---- layer 1, K-slice c of item B (chunk c from buffer 0): A1 (+)= chunk * W1[:, 128c : 128c + 128]^T, two tiles of 64
-        auto l1 = [&](int c) {
+        auto l1 = [&](int c, int gi) {
             if (!hasB) return;
+            tr.ev(0x200 + gi);
             mbar_wait(bar(BAR_E0), (uint32_t)c & 1u);
             tc_fence_after();
+            tr.ev(0x300 + gi);
             if (c == 0) {
                 mbar_wait(full_bar, rpar);
                 if (elect_one()) { umma_bf16(tA1, ones_desc, ring_desc + lbo256, idesc256, 0u); umma_commit(empty_bar); }
@@ -427,13 +433,16 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
                 if (c == 3) umma_commit(bar(BAR_ACC1));
             }
             __syncwarp();
+            tr.ev(0x400 + gi);
         };
         // ---- layer 2, K-slice j of item A (layer-1 chunk j from buffer 1): T (+)= chunk * W2[:, 128j : 128j + 128]^T
-        auto l2 = [&](int j) {
+        auto l2 = [&](int j, int gi) {
             if (!hasA) return;
+            tr.ev(0x200 + gi);
             mbar_wait(bar(BAR_E1), (mA + (uint32_t)j) & 1u);                        // completion 3 mA + j
             if (j == 0 && mA >= 1u) mbar_wait(bar(BAR_ODONE), (mA - 1u) & 1u);        // T: the previous item's output accumulator has been read
             tc_fence_after();
+            tr.ev(0x300 + gi);
             if (j == 0) {
                 mbar_wait(full_bar, rpar);
                 if (elect_one()) { umma_bf16(tT, ones_desc, ring_desc + lbo128, idesc128, 0u); umma_commit(empty_bar); }
@@ -447,12 +456,15 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
             next_slot();
             if (elect_one()) umma_commit(bar(j == 0 ? BAR_AFREE1 : BAR_ACC2));
             __syncwarp();
+            tr.ev(0x400 + gi);
         };
         // ---- output layer of item A (layer-2 activations from buffer 1): T = h3 * W3^T + b3, K = 128
-        auto l3 = [&]() {
+        auto l3 = [&](int gi) {
             if (!hasA) return;
+            tr.ev(0x200 + gi);
             mbar_wait(bar(BAR_E1), mA & 1u);                                         // completion 3 mA + 2
             tc_fence_after();
+            tr.ev(0x300 + gi);
             const int nt = kA ? a.f3_nto[1] : a.f3_nto[0], merged = kA ? a.f3_merged[1] : a.f3_merged[0];
             const uint32_t idesc = make_idesc_f16(nt);
             const uint64_t lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16, bstep = (uint64_t)(nt * 2);
@@ -472,8 +484,47 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
             next_slot();
             if (elect_one()) umma_commit(bar(BAR_ACC3));
             __syncwarp();
+            tr.ev(0x400 + gi);
         };
-        l0(0); l2(0); l0(1); l2(1); l1(0); l0(2); l1(1); l3(); l0(3); l1(2); l1(3);
+        l0(0, 0); l2(0, 1); l0(1, 2); l2(1, 3); l1(0, 4); l0(2, 5); l1(1, 6); l3(7); l0(3, 8); l1(2, 9); l1(3, 10);
+    }
+}
+
+// The loader of the same program, written out the same way: the weight tiles of an iteration in the order tc_mma_fast3
+// consumes them.  With two 32 KB ring slots (what two staged-row buffers leave) a tile's round trip -- the MMAs' commit, this
+// thread's wake-up and bookkeeping, the bulk copy -- is on the MMA role's critical path, so its bookkeeping counts too.
+__device__ __noinline__ void tc_load_fast3(const TcArgs& a, int n_local, int n_iter, uint32_t ring_addr, uint32_t full0, uint32_t empty0) {
+    const uint32_t S = (uint32_t)a.stages, slot_bytes = (uint32_t)a.slot_bytes;
+    uint32_t slot = 0, round = 0;
+    const int gridn = (int)gridDim.x, cta = (int)blockIdx.x, tiles = a.tiles;
+    auto tile = [&](const unsigned char* src, uint32_t bytes) {
+        if (round) mbar_wait(empty0 + 8 * slot, (round - 1u) & 1u);
+        if (elect_one()) {
+            mbar_expect_tx(full0 + 8 * slot, bytes);
+            bulk_g2s(ring_addr + slot * slot_bytes, src, bytes, full0 + 8 * slot);
+        }
+        if (++slot == S) { slot = 0; ++round; }
+    };
+    for (int it = 0; it < n_iter; ++it) {
+        if (it == 0) pf_grid_dep_wait();
+        const bool hasB = it < n_local, hasA = it >= 1;
+        const int kB = hasB ? (cta + it * gridn) / tiles : 0, kA = hasA ? (cta + (it - 1) * gridn) / tiles : 0;
+        const unsigned char* blobB = a.net[kB].blob;
+        const unsigned char* blobA = a.net[kA].blob;
+        const TcProgram& PB = a.prog[kB];
+        const TcProgram& PA = a.prog[kA];
+        const uint32_t l0a = (uint32_t)(128 * (16 + 16 * (kB ? a.f3_first[1] : a.f3_first[0])) * 2), l0b = (uint32_t)(128 * 16 * (kB ? a.f3_rest[1] : a.f3_rest[0]) * 2);
+        auto l0 = [&](int gi) { if (!hasB) return; const unsigned char* p = blobB + PB.g[gi].blob_off; tile(p, l0a); if (l0b) tile(p + l0a, l0b); };
+        auto l1 = [&](int gi, bool bias) { if (!hasB) return; const unsigned char* p = blobB + PB.g[gi].blob_off; if (bias) { tile(p, 8192u); p += 8192; } tile(p, 32768u); tile(p + 32768, 32768u); };
+        auto l2 = [&](int gi, bool bias) { if (!hasA) return; const unsigned char* p = blobA + PA.g[gi].blob_off; if (bias) { tile(p, 4096u); p += 4096; } tile(p, 32768u); };
+        auto l3 = [&](int gi) {
+            if (!hasA) return;
+            const unsigned char* p = blobA + PA.g[gi].blob_off;
+            const uint32_t nt = (uint32_t)(kA ? a.f3_nto[1] : a.f3_nto[0]);
+            if (kA ? a.f3_merged[1] : a.f3_merged[0]) tile(p, nt * (16u + 128u) * 2u);
+            else { tile(p, nt * 32u); tile(p + nt * 32u, nt * 256u); }
+        };
+        l0(0); l2(1, true); l0(2); l2(3, false); l1(4, true); l0(5); l1(6, false); l3(7); l0(8); l1(9, false); l1(10, false);
     }
 }
 
@@ -540,7 +591,9 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     // parity to wait for: completion k (inside the item) of barrier b, given the barrier completions of all earlier items
     auto par_of = [](uint32_t bits, int b, int k) -> uint32_t { return ((bits >> b) ^ (uint32_t)k) & 1u; };
 
-    if (warp == TC_LOAD_WARP) {
+    if (warp == TC_LOAD_WARP && a.fast3 && !(a.debug & 8)) {
+        tc_load_fast3(a, n_local, n_iter, smem_u32(ring), full0, empty0);
+    } else if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
         {   // (the whole warp walks the loop, one elected lane issues: code the compiler KNOWS to be warp-uniform keeps
             // the copy's operands in uniform registers; a lone lane made it re-broadcast every operand per instruction)
@@ -1418,10 +1471,17 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.tmem_cols = TC_TMEM_COLS;
     const int grid = items < c->num_sms ? items : c->num_sms;
     // The two-phase programs: second half of item m interleaved with the first half of item m + 1.
-    // OPT-IN (PF_TC_PIPE=1, read per launch): measured at 262,144 rows it is no faster than the single-phase program --
-    // the staged rows are single-buffered, so every iteration still waits out one staging pass
+    // The two-phase program whenever the nets have one (three hidden layers, layer 0 in >= 2 chunks), except when the caller
+    // asked for the dry rehearsal item of a single-item launch (single-phase programs only).  PF_TC_PIPE=0 / 1 (read per
+    // launch) forces the choice.  Default: only with the hard-wired MMA role (fast3, the [*, 512, 256, 128, *] nets), where it is
+    // 17 % faster at 262,144 rows and never slower down to 4,096; on the program interpreter it is a wash.
     const char* pipe_env = getenv("PF_TC_PIPE");
-    if (t->pipe && pipe_env && atoi(pipe_env) != 0) {
+    bool f3ok = t->pipe && getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes_p == 32768;
+    for (int i = 0; i < a.nnets && f3ok; ++i)
+        for (int k = 0; k < 2; ++k)
+            if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights))
+                f3ok = tc_fast3_params(t->progp[k], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i]) != 0;
+    if (t->pipe && (pipe_env ? atoi(pipe_env) != 0 : (f3ok && !a.rehearse))) {
         for (int i = 0; i < a.nnets; ++i)
             for (int k = 0; k < 2; ++k)
                 if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progp[k];
@@ -1431,8 +1491,7 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
         a.x0_nbuf = 2;
         a.rehearse = 0;
         // the hard-wired MMA role, if every net of this launch has exactly the program it was written against
-        a.fast3 = getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes_p == 32768;
-        for (int i = 0; i < a.nnets && a.fast3; ++i) a.fast3 = tc_fast3_params(a.prog[i], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i]);
+        a.fast3 = f3ok ? 1 : 0;
         if (a.nnets == 1) { a.f3_first[1] = a.f3_first[0]; a.f3_rest[1] = a.f3_rest[0]; a.f3_nto[1] = a.f3_nto[0]; a.f3_merged[1] = a.f3_merged[0]; }
         return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes_p[variant], st, a) == cudaSuccess
                    ? 0 : tc_fail(2, "pf_mlp_tc_kernel (two-phase): launch failed");
