@@ -120,6 +120,7 @@ struct TcState {
     TcProgram prog[2]; int stages[3]; int smem_bytes[3]; int x0_bytes[3];
     int compact; TcProgram progc[2]; int stages_c[3]; int smem_bytes_c[3];
     int slot_bytes;
+    int x0_nbuf_p;
     int pipe; TcProgram progp[2]; int stages_p[3]; int smem_bytes_p[3]; int slot_bytes_p;      // two-phase programs (large batches)
     unsigned long long* trace; int rehearse;
 };
@@ -239,7 +240,6 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
         const int r = (int)__umulhi((uint32_t)e, magic), kx = e - r * K0;
         *reinterpret_cast<unsigned short*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = tc_h(v);
     };
-    tr.ev(0x506);
     if (N.ldx == K0 && ((reinterpret_cast<uintptr_t>(xb) | reinterpret_cast<uintptr_t>(cb)) & 15) == 0) {
         const int n4 = total >> 2;
         const float4* x4 = reinterpret_cast<const float4*>(xb);
@@ -252,7 +252,6 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                 const int idx = base + u * TC_STG_THREADS;
                 if (idx < n4) v[u] = noload ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(x4 + idx);
             }
-            tr.ev(0x507);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int idx = base + u * TC_STG_THREADS;
@@ -267,7 +266,6 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
                     }
                 }
             }
-            tr.ev(0x508);
         }
         for (int e = n4 * 4 + tid; e < total; e += TC_STG_THREADS) {
             const float v = noload ? 0.0f : __ldg(xb + e);
@@ -371,14 +369,14 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
         if (it == 0) pf_grid_dep_wait();
         const bool hasB = it < n_local, hasA = it >= 1;
         const int kB = hasB ? (cta + it * gridn) / tiles : 0, kA = hasA ? (cta + (it - 1) * gridn) / tiles : 0;
-        const uint32_t mB = (uint32_t)it, mA = (uint32_t)(it - 1), xb = mB & 1u;
+        const uint32_t mB = (uint32_t)it, mA = (uint32_t)(it - 1), xb = a.x0_nbuf == 2 ? (mB & 1u) : 0u, xuse = a.x0_nbuf == 2 ? (mB >> 1) : mB;
         const uint64_t xdesc = xb ? x0_desc1 : x0_desc0;
         const int nfirst = kB ? a.f3_first[1] : a.f3_first[0], nrest = kB ? a.f3_rest[1] : a.f3_rest[0];
         // ---- layer 0, chunk c of item B: S (+)= x0 * W0[c]^T, bias + first K columns in one tile, the rest in a second
         auto l0 = [&](int c, int gi) {
             if (!hasB) return;
             tr.ev(0x200 + gi);
-            if (c == 0) mbar_wait(bar(BAR_XFULL) + 8u * xb * TC_XBAR_STEP, (mB >> 1) & 1u);
+            if (c == 0) mbar_wait(bar(BAR_XFULL) + 8u * xb * TC_XBAR_STEP, xuse & 1u);
             else mbar_wait(bar(BAR_E0), (uint32_t)(c - 1) & 1u);                    // S drained (and chunk c - 1 in buffer 0)
             tc_fence_after();
             tr.ev(0x300 + gi);
@@ -940,7 +938,7 @@ static int tc_fail(int code, const char* msg) { pf_set_error(msg); return code; 
 
 // K-columns that fit a slot beside the bias tile (0: the bias travels alone -- nothing would be saved)
 static int pick_kt0(int nt, int kc, int kt, int slot_bytes, int bias) {
-    if (!bias) return 0;
+    if (!bias || getenv("PF_TC_NO_KT0")) return 0;          // (experiment: the bias always in its own tile)
     int k0 = ((slot_bytes - nt * 32) / 2 / nt) & ~15;
     if (k0 > 128) k0 = 128;
     if (k0 > kc) k0 = kc;
@@ -1108,11 +1106,11 @@ static int build_program(TcProgram& P, const PfNet& n, int odd_col = 256, int sl
 // are DOUBLE-buffered (the shared memory a third chunk buffer would take): they are held until the item's last layer-0
 // chunk, most of an iteration, and with one buffer the next item's staging pass sat on the critical loop.  The hazards
 // that program order does not already cover are explicit waits (comments below); check_program() replays the schedule.
-static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes) {
+static int build_program_pipe(TcProgram& P, const PfNet& n, int slot_bytes, int x0_nbuf = 2) {
     memset(&P, 0, sizeof(P));
     const int L = n.layers;
     if (L != 4) return 1;
-    P.layers = L; P.odd_col = 256; P.phases = 2; P.nbuf = 2; P.x0_nbuf = 2;
+    P.layers = L; P.odd_col = 256; P.phases = 2; P.nbuf = 2; P.x0_nbuf = x0_nbuf;
     for (int i = 0; i <= L; ++i) { P.dims[i] = n.dims[i]; P.pdims[i] = pad16(n.dims[i]); }
     if (P.pdims[0] > 256 || P.pdims[2] > 256 || P.pdims[3] > 128 || P.pdims[4] > 128) return 1;
     const int nch0 = (P.pdims[1] + TC_CHUNK - 1) / TC_CHUNK, nch1 = (P.pdims[2] + TC_CHUNK - 1) / TC_CHUNK;
@@ -1367,8 +1365,11 @@ int pf_tc_create(pf_rl_ctx* c) {
     // net's first half at the actor -> critic boundary), same packed weights
     t->pipe = getenv("PF_TC_NO_PIPE") == nullptr;
     { const char* e = getenv("PF_TC_PIPE_SLOT_KB"); t->slot_bytes_p = e ? atoi(e) * 1024 : 32768; }
+    // staged rows double-buffered if that fits beside two chunk buffers and two ring slots (inputs up to ~190 wide), else single
+    t->x0_nbuf_p = 2;
+    { int st_, sm_; const int xmax = t->x0_bytes[2]; if (smem_layout(xmax, &st_, &sm_, 227, 2, t->slot_bytes_p, 2, 2)) t->x0_nbuf_p = 1; }
     for (int k = 0; k < 2 && t->pipe; ++k)
-        if (build_program_pipe(t->progp[k], c->net[k], t->slot_bytes_p) || check_program(t->progp[k]) || t->progp[k].blob_bytes != t->prog[k].blob_bytes)
+        if (build_program_pipe(t->progp[k], c->net[k], t->slot_bytes_p, t->x0_nbuf_p) || check_program(t->progp[k]) || t->progp[k].blob_bytes != t->prog[k].blob_bytes)
             t->pipe = 0;
     if (t->pipe) {
         const TcProgram &A = t->progp[0], &B = t->progp[1];
@@ -1377,7 +1378,7 @@ int pf_tc_create(pf_rl_ctx* c) {
         for (int i = 0; i < A.nepis && t->pipe; ++i) if (A.e[i].phase != B.e[i].phase) t->pipe = 0;
     }
     for (int v = 0; v < 3 && t->pipe; ++v) {
-        if (smem_layout(t->x0_bytes[v], &t->stages_p[v], &t->smem_bytes_p[v], 227, 2, t->slot_bytes_p, 2, 2)) t->pipe = 0;
+        if (smem_layout(t->x0_bytes[v], &t->stages_p[v], &t->smem_bytes_p[v], 227, 2, t->slot_bytes_p, 2, t->x0_nbuf_p)) t->pipe = 0;
         else max_smem = t->smem_bytes_p[v] > max_smem ? t->smem_bytes_p[v] : max_smem;
     }
     for (int k = 0; k < 2; ++k) {
@@ -1471,24 +1472,25 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.tmem_cols = TC_TMEM_COLS;
     const int grid = items < c->num_sms ? items : c->num_sms;
     // The two-phase programs: second half of item m interleaved with the first half of item m + 1.
-    // The two-phase program whenever the nets have one (three hidden layers, layer 0 in >= 2 chunks), except when the caller
-    // asked for the dry rehearsal item of a single-item launch (single-phase programs only).  PF_TC_PIPE=0 / 1 (read per
-    // launch) forces the choice.  Default: only with the hard-wired MMA role (fast3, the [*, 512, 256, 128, *] nets), where it is
-    // 17 % faster at 262,144 rows and never slower down to 4,096; on the program interpreter it is a wash.
+    // The two-phase program when a CTA walks several items AND the nets are the ones its hard-wired MMA / loader roles are
+    // written for (fast3: [*, 512, 256, 128, *]) AND the staged rows fit twice (inputs up to ~190 wide): 14-17 % faster at
+    // 262,144 rows, 7 % at 65,536.  Not otherwise: on the program interpreter it is a wash, with single-buffered staged rows
+    // slower (654 vs 635 us at 214 inputs), and a single-item launch is a pure latency chain that the single-phase program
+    // walks faster inside a step (rough 4,096 envs: 70.3 vs 76.2 us per step).  PF_TC_PIPE=0 / 1 (read per launch) forces it.
     const char* pipe_env = getenv("PF_TC_PIPE");
     bool f3ok = t->pipe && getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes_p == 32768;
     for (int i = 0; i < a.nnets && f3ok; ++i)
         for (int k = 0; k < 2; ++k)
             if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights))
                 f3ok = tc_fast3_params(t->progp[k], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i]) != 0;
-    if (t->pipe && (pipe_env ? atoi(pipe_env) != 0 : (f3ok && !a.rehearse))) {
+    if (t->pipe && (pipe_env ? atoi(pipe_env) != 0 : (f3ok && t->x0_nbuf_p == 2 && items > c->num_sms))) {
         for (int i = 0; i < a.nnets; ++i)
             for (int k = 0; k < 2; ++k)
                 if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progp[k];
         a.stages = t->stages_p[variant];
         a.slot_bytes = t->slot_bytes_p;
         a.nbuf = 2;
-        a.x0_nbuf = 2;
+        a.x0_nbuf = t->x0_nbuf_p;
         a.rehearse = 0;
         // the hard-wired MMA role, if every net of this launch has exactly the program it was written against
         a.fast3 = f3ok ? 1 : 0;

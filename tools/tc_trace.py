@@ -38,7 +38,7 @@ prev = {}
 for clk, role, tag in ev[:limit]:
     d = clk - prev.get(role, t0)
     prev[role] = clk
-    sub = {0x500: "begin", 0x501: "staged", 0x502: "arrived", 0x503: "loaded", 0x504: "padded", 0x505: "signalled", 0x506: "setup", 0x507: "loads issued", 0x508: "stored"}.get(tag, str(tag & 0xFF))
+    sub = {0x500: "begin", 0x501: "staged", 0x502: "arrived", 0x503: "loaded", 0x504: "padded", 0x505: "signalled"}.get(tag, str(tag & 0xFF))
     print(f"{(clk - t0):9d} cyc  (+{d:7d})  {'  ' * role}{NAMES[tag >> 8]} {sub}")
 last = max(c for c, r, t in ev if r == 0)
 items = sum(1 for c, r, t in ev if t == 0x500)
