@@ -825,7 +825,18 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                         tmem_ld16(trow + g, va);
                         tmem_ld_wait_on(va);
                         tr.ev(0xD00 + ei);
-                        for (;;) {
+                        if (c_hi - c_lo == 64) {                 // the usual share (half of a 128-column chunk): four rounds, straight-line
+                            tmem_ld16(trow + g + 16, vb);
+                            pack16(va, outb, g);
+                            tmem_ld_wait_on(vb);
+                            tmem_ld16(trow + g + 32, va);
+                            pack16(vb, outb, g + 16);
+                            tmem_ld_wait_on(va);
+                            tmem_ld16(trow + g + 48, vb);
+                            pack16(va, outb, g + 32);
+                            tmem_ld_wait_on(vb);
+                            pack16(vb, outb, g + 48);
+                        } else for (;;) {
                             const int g2 = g + 16;
                             if (g2 < c_hi) tmem_ld16(trow + g2, vb);
                             pack16(va, outb, g);
