@@ -47,13 +47,23 @@ def test_tcgen05_path_still_serves_small_nets_when_asked(hidden, nc, n, monkeypa
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
 
 
-@pytest.mark.parametrize("n", [300, 40000])
-def test_tcgen05_two_phase_program_matches_oracle(n, monkeypatch):
-    """PF_TC_PIPE=1: the software-pipelined schedule of the same kernel (second half of item m interleaved with the first
-    half of item m + 1; pf_mlp_tc.cu build_program_pipe) -- prologue + drain only at 300 rows, four to five items per CTA
-    at 40,000"""
+@pytest.mark.parametrize("n,hardwired", [(300, True), (40000, True), (40000, False), (40001, True)])
+def test_tcgen05_two_phase_program_matches_oracle(n, hardwired, monkeypatch):
+    """The software-pipelined schedule of the same kernel (second half of item m interleaved with the first half of item
+    m + 1; pf_mlp_tc.cu build_program_pipe), forced on at every size: prologue + drain only at 300 rows, four to five
+    items per CTA at 40,000 (ragged last tile at 40,001) -- with the hard-wired MMA / loader roles of the
+    [*, 512, 256, 128, *] nets (tc_mma_fast3, the default for large batches) and on the program interpreter"""
     monkeypatch.setenv("PF_TC_PIPE", "1")
+    if not hardwired:
+        monkeypatch.setenv("PF_TC_NO_FAST3", "1")
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=148, hidden=(512, 256, 128), T=3, precision="bf16")
+
+
+def test_tcgen05_two_phase_other_shapes_on_the_interpreter(monkeypatch):
+    """A three-hidden-layer net that is NOT [*, 512, 256, 128, *]: two layer-0 chunks, one layer-1 chunk -- two-phase program
+    on the interpreter (forced; by default such nets take the single-phase program)"""
+    monkeypatch.setenv("PF_TC_PIPE", "1")
+    parity_rl.run_act_and_gae(num_envs=30000, num_critic_obs=48, hidden=(256, 128, 64), T=2, precision="bf16")
 
 
 def test_tcgen05_odd_layer_count_many_items_per_cta():
