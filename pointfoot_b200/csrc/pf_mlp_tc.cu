@@ -139,6 +139,7 @@ struct TcNetArgs {
     float* out;                  // TC_OUT_PLAIN: [rows, dims[layers]] fp32
     float* copy_to;              // optional [rows, dims[0]] copy of the input rows (rollout storage)
     int mode;
+    uint32_t magic;              // ceil(2^32 / dims[0]): element index -> row by multiply-high (filled by tc_launch)
 };
 struct TcArgs {
     TcProgram prog[2];
@@ -225,13 +226,13 @@ __device__ __forceinline__ uint32_t make_idesc_f16(int n) {
 template <int TC_STG_THREADS>
 __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char* x0, uint32_t xfull_bar, int tid, TcTrace& tr, bool dry) {
     const int lane = tid & 31;
-    const int k = w / a.tiles, tile = w - k * a.tiles;
+    const int k = w >= a.tiles ? 1 : 0, tile = w - k * a.tiles;          // (at most two nets per launch)
     const TcProgram& P = a.prog[k];
     const TcNetArgs& N = a.net[k];
     const int row0 = tile * TC_ROWS;
     const int nrows = min(TC_ROWS, a.rows - row0);
     const int K0 = P.dims[0], Kp = P.pdims[0];
-    const uint32_t magic = (uint32_t)((0x100000000ull + (uint32_t)K0 - 1) / (uint32_t)K0);
+    const uint32_t magic = N.magic;
     const float* xb = N.x + (long long)row0 * N.ldx;
     float* cb = (N.copy_to && !(a.debug & 1) && !dry) ? N.copy_to + (long long)row0 * K0 : nullptr;
     const bool noload = (a.debug & 2) || dry;       // dry item: same code, zeros instead of the rows
@@ -301,7 +302,7 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     // that traffic under a whole item of MMAs and turns the next staging pass into L2 hits.
     const int w2 = w + (int)gridDim.x;
     if (!dry && w2 < a.nnets * a.tiles) {
-        const int k2 = w2 / a.tiles, tile2 = w2 - k2 * a.tiles;
+        const int k2 = w2 >= a.tiles ? 1 : 0, tile2 = w2 - k2 * a.tiles;
         const TcNetArgs& N2 = a.net[k2];
         const int rows2 = min(TC_ROWS, a.rows - tile2 * TC_ROWS);
         const char* base = reinterpret_cast<const char*>(N2.x + (long long)tile2 * TC_ROWS * N2.ldx);
@@ -368,7 +369,7 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
     for (int it = 0; it < n_iter; ++it) {
         if (it == 0) pf_grid_dep_wait();
         const bool hasB = it < n_local, hasA = it >= 1;
-        const int kB = hasB ? (cta + it * gridn) / tiles : 0, kA = hasA ? (cta + (it - 1) * gridn) / tiles : 0;
+        const int kB = (hasB && cta + it * gridn >= tiles) ? 1 : 0, kA = (hasA && cta + (it - 1) * gridn >= tiles) ? 1 : 0;
         const uint32_t mB = (uint32_t)it, mA = (uint32_t)(it - 1), xb = a.x0_nbuf == 2 ? (mB & 1u) : 0u, xuse = a.x0_nbuf == 2 ? (mB >> 1) : mB;
         const uint64_t xdesc = xb ? x0_desc1 : x0_desc0;
         const int nfirst = kB ? a.f3_first[1] : a.f3_first[0], nrest = kB ? a.f3_rest[1] : a.f3_rest[0];
@@ -506,7 +507,7 @@ __device__ __noinline__ void tc_load_fast3(const TcArgs& a, int n_local, int n_i
     for (int it = 0; it < n_iter; ++it) {
         if (it == 0) pf_grid_dep_wait();
         const bool hasB = it < n_local, hasA = it >= 1;
-        const int kB = hasB ? (cta + it * gridn) / tiles : 0, kA = hasA ? (cta + (it - 1) * gridn) / tiles : 0;
+        const int kB = (hasB && cta + it * gridn >= tiles) ? 1 : 0, kA = (hasA && cta + (it - 1) * gridn >= tiles) ? 1 : 0;
         const unsigned char* blobB = a.net[kB].blob;
         const unsigned char* blobA = a.net[kA].blob;
         const TcProgram& PB = a.prog[kB];
@@ -601,7 +602,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             for (int it = -reh; it < n_iter; ++it) {
                 if (it == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
                 const int w0 = item_of(it, 0), w1 = item_of(it, 1);
-                const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+                const int k0n = w0 >= 0 ? (w0 >= a.tiles ? 1 : 0) : -1, k1n = w1 >= 0 ? (w1 >= a.tiles ? 1 : 0) : -1;
                 const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];          // step list (the same for both nets when two-phase)
                 const int ngroups = PR.ngroups;
                 for (int gi = 0; gi < ngroups; ++gi) {
@@ -659,7 +660,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             for (int it = -reh; it < n_iter; ++it) {
                 if (it == 0) pf_grid_dep_wait();
                 const int w0 = item_of(it, 0), w1 = item_of(it, 1);
-                const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+                const int k0n = w0 >= 0 ? (w0 >= a.tiles ? 1 : 0) : -1, k1n = w1 >= 0 ? (w1 >= a.tiles ? 1 : 0) : -1;
                 const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];
                 const int ngroups = PR.ngroups;
                 for (int gi = 0; gi < ngroups; ++gi) {
@@ -791,7 +792,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             if (it == 0) pf_grid_dep_wait();
             const bool dry = it < 0;
             const int w0 = item_of(it, 0), w1 = item_of(it, 1);
-            const int k0n = w0 >= 0 ? w0 / a.tiles : -1, k1n = w1 >= 0 ? w1 / a.tiles : -1;
+            const int k0n = w0 >= 0 ? (w0 >= a.tiles ? 1 : 0) : -1, k1n = w1 >= 0 ? (w1 >= a.tiles ? 1 : 0) : -1;
             const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];
             const int nepis = PR.nepis;
             for (int ei = 0; ei < nepis; ++ei) {
@@ -1450,6 +1451,7 @@ static int tc_fast3_params(const TcProgram& P, int& nfirst, int& nrest, int& nto
 
 static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
+    for (int i = 0; i < a.nnets; ++i) { const uint32_t K0 = (uint32_t)a.prog[i].dims[0]; a.net[i].magic = (uint32_t)((0x100000000ull + K0 - 1) / K0); }
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
     a.stages = t->stages[variant];
     a.slot_bytes = t->slot_bytes;
