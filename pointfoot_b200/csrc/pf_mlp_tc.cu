@@ -283,14 +283,17 @@ __device__ __noinline__ void tc_stage_item(const TcArgs& a, int w, unsigned char
     }
     tr.ev(0x503);
     // zero padding: columns [K0, Kp) of the valid rows, and whole rows past the end of the batch
-    const int padw = Kp - K0;
-    for (int i = tid; i < nrows * padw; i += TC_STG_THREADS) {
-        const int r = i / padw, kx = K0 + (i - r * padw);
-        *reinterpret_cast<unsigned short*>(x0 + (size_t)(kx >> 3) * TC_X0_LBO + r * 16 + (kx & 7) * 2) = 0;
-    }
-    for (int i = tid; i < (TC_ROWS - nrows) * (Kp >> 3); i += TC_STG_THREADS) {
-        const int r = nrows + i / (Kp >> 3), kb = i % (Kp >> 3);
-        *reinterpret_cast<uint4*>(x0 + (size_t)kb * TC_X0_LBO + r * 16) = make_uint4(0u, 0u, 0u, 0u);
+    // (no division: thread (row, column) pairs walk rows by TC_STG_THREADS / 16 and the <= 15 pad columns by 16)
+    {
+        const int padw = Kp - K0, pc = tid & 15;
+        if (pc < padw) {
+            const int kx = K0 + pc;
+            unsigned char* col = x0 + (size_t)(kx >> 3) * TC_X0_LBO + (kx & 7) * 2;
+            for (int r = tid >> 4; r < nrows; r += TC_STG_THREADS / 16) *reinterpret_cast<unsigned short*>(col + r * 16) = 0;
+        }
+        const int nblk = Kp >> 3;
+        for (int r = nrows + (tid >> 5); r < TC_ROWS; r += TC_STG_THREADS / 32)
+            for (int kb = lane; kb < nblk; kb += 32) *reinterpret_cast<uint4*>(x0 + (size_t)kb * TC_X0_LBO + r * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
     tr.ev(0x504);
     fence_async_smem();
