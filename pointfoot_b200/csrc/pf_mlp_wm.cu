@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(WM_WARPS * 32, 2) pf_mlp_wm_kernel(const __gri
     const int ntasks = a.nnets * a.tiles;
     // task = warp * gridDim.x + blockIdx.x: a small batch spreads over every SM before any CTA gets a second warp's worth
     for (int task = warp * gridDim.x + blockIdx.x; task < ntasks; task += gridDim.x * WM_WARPS) {
-        const int ni = task / a.tiles, tile = task - ni * a.tiles;
+        const int ni = task >= a.tiles ? 1 : 0, tile = task - ni * a.tiles;          // (at most two nets per launch)
         const WmNetArgs& N = a.n[ni];
         const WmNet& P = N.net;
         const int row0 = tile * WM_ROWS, nrows = min(WM_ROWS, a.rows - row0), K0 = P.k_true0, K0p = P.kp[0];
