@@ -492,6 +492,152 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
     }
 }
 
+// The MMA role of the SINGLE-phase program of the same nets, written out the same way (single-item launches, inputs too wide
+// for two staged-row buffers): groups in build_program's order, two layer-0 accumulator slots at TMEM [0, 128) / [128, 256),
+// layer 1 at [256, 512), layer 2 at [0, 128), the output layer at [256, ...), chunk buffers alternating.
+//   Completions per item: ACC0 3, ACC1 2, ACC2 2, AFREE0 4, AFREE1 3, E0 4, E1 3, XFULL 1, XFREE 1.
+__device__ __noinline__ void tc_mma_fast1(const TcArgs& a, int n_local, int reh, uint32_t x0_addr, uint32_t ach_addr, uint32_t ones_addr,
+                                          uint32_t ring_addr, uint32_t full0, uint32_t empty0, uint32_t pb0, uint32_t tmem_base) {
+    const uint32_t S = (uint32_t)a.stages;
+    uint32_t slot = 0, rpar = 0, full_bar = full0, empty_bar = empty0;
+    const uint64_t ring_desc0 = make_desc(ring_addr, 0u, 128u), slot_step = (uint64_t)((uint32_t)a.slot_bytes >> 4);
+    uint64_t ring_desc = ring_desc0;
+    const uint64_t ones_desc = make_desc(ones_addr, TC_ROWS * 16, 128u);
+    const uint64_t ach0_desc = make_desc(ach_addr, TC_ROWS * 16, 128u), ach1_desc = make_desc(ach_addr + TC_ACHUNK_BYTES, TC_ROWS * 16, 128u);
+    const uint64_t xdesc = make_desc(x0_addr, TC_X0_LBO, 128u);
+    const uint32_t idesc128 = make_idesc_f16(128), idesc256 = make_idesc_f16(256);
+    const uint64_t lbo128 = (uint64_t)(128u * 16u >> 4) << 16, lbo256 = (uint64_t)(256u * 16u >> 4) << 16;
+    auto bar = [&](int b) { return pb0 + 8u * (uint32_t)b; };
+    auto next_slot = [&]() {
+        full_bar += 8; empty_bar += 8; ring_desc += slot_step;
+        if (++slot == S) { slot = 0; rpar ^= 1u; full_bar = full0; empty_bar = empty0; ring_desc = ring_desc0; }
+    };
+    const int gridn = (int)gridDim.x, cta = (int)blockIdx.x, tiles = a.tiles;
+    TcTrace tr; tr.init(a.trace, 1, blockIdx.x == 0 && (threadIdx.x & 31) == 0);
+    for (int j = -reh; j < n_local; ++j) {
+        if (j == 0) pf_grid_dep_wait();
+        const uint32_t me = (uint32_t)(j + reh);                                     // items walked before this one (the dry one included)
+        const int k = (cta + (j < 0 ? 0 : j) * gridn >= tiles) ? 1 : 0;
+        const int nfirst = k ? a.f3_first[1] : a.f3_first[0], nrest = k ? a.f3_rest[1] : a.f3_rest[0];
+        auto l0 = [&](int c, int gi) {
+            tr.ev(0x200 + gi);
+            if (c == 0) mbar_wait(bar(BAR_XFULL), me & 1u);
+            else if (c == 2) mbar_wait(bar(BAR_E0), 0u);                              // slot 0 drained: E0 completion 4 me + 0
+            else if (c == 3) mbar_wait(bar(BAR_E1), me & 1u);                         // slot 1 drained: E1 completion 3 me + 0
+            tc_fence_after();
+            tr.ev(0x300 + gi);
+            const uint32_t tS = tmem_base + (uint32_t)(c & 1) * 128u;
+            mbar_wait(full_bar, rpar);
+            if (elect_one()) {
+                uint64_t bd = ring_desc + lbo128, ad = xdesc;
+                umma_bf16(tS, ones_desc, bd, idesc128, 0u);
+                bd += 256;
+                for (int kk = 0; kk < nfirst; ++kk) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (nrest) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) {
+                    uint64_t bd = ring_desc + lbo128, ad = xdesc + (uint64_t)(nfirst * TC_X0_KSTEP);
+                    for (int kk = 0; kk < nrest; ++kk) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                    umma_commit(empty_bar);
+                }
+                next_slot();
+            }
+            if (elect_one()) {
+                umma_commit(bar(BAR_ACC0 + (c & 1)));
+                if (c == 3) umma_commit(bar(BAR_XFREE));
+            }
+            __syncwarp();
+            tr.ev(0x400 + gi);
+        };
+        auto l1 = [&](int c, int gi) {
+            tr.ev(0x200 + gi);
+            // chunk c sits in buffer c & 1: E0 completions 4 me + {0, 1}, E1 completions 3 me + {0, 1}
+            if (c & 1) mbar_wait(bar(BAR_E1), (me + (uint32_t)(c >> 1)) & 1u);
+            else mbar_wait(bar(BAR_E0), (uint32_t)(c >> 1) & 1u);
+            tc_fence_after();
+            tr.ev(0x300 + gi);
+            const uint32_t tA1 = tmem_base + 256;
+            const uint64_t adesc = (c & 1) ? ach1_desc : ach0_desc;
+            if (c == 0) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) { umma_bf16(tA1, ones_desc, ring_desc + lbo256, idesc256, 0u); umma_commit(empty_bar); }
+                next_slot();
+            }
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) {
+                    issue_mmas<256, 512, 4>(tA1, adesc + (uint64_t)(t * 4 * 256), ring_desc + lbo256, idesc256);
+                    umma_commit(empty_bar);
+                }
+                next_slot();
+            }
+            if (elect_one()) {
+                umma_commit(bar(BAR_AFREE0 + (c & 1)));
+                if (c == 3) umma_commit(bar(BAR_ACC2));
+            }
+            __syncwarp();
+            tr.ev(0x400 + gi);
+        };
+        auto l2 = [&](int jj, int gi) {
+            tr.ev(0x200 + gi);
+            if (jj) mbar_wait(bar(BAR_E1), (me + 2u) & 1u);                           // layer-1 chunk 1 in buffer 1: E1 completion 3 me + 2
+            else mbar_wait(bar(BAR_E0), 0u);                                          // layer-1 chunk 0 in buffer 0: E0 completion 4 me + 2
+            tc_fence_after();
+            tr.ev(0x300 + gi);
+            const uint32_t tT = tmem_base;
+            if (jj == 0) {
+                mbar_wait(full_bar, rpar);
+                if (elect_one()) { umma_bf16(tT, ones_desc, ring_desc + lbo128, idesc128, 0u); umma_commit(empty_bar); }
+                next_slot();
+            }
+            mbar_wait(full_bar, rpar);
+            if (elect_one()) {
+                issue_mmas<256, 256, 8>(tT, jj ? ach1_desc : ach0_desc, ring_desc + lbo128, idesc128);
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (elect_one()) {
+                umma_commit(bar(BAR_AFREE0 + jj));
+                if (jj == 1) umma_commit(bar(BAR_ACC0));
+            }
+            __syncwarp();
+            tr.ev(0x400 + gi);
+        };
+        auto l3 = [&](int gi) {
+            tr.ev(0x200 + gi);
+            mbar_wait(bar(BAR_E0), 1u);                                               // layer-2 activations in buffer 0: E0 completion 4 me + 3
+            tc_fence_after();
+            tr.ev(0x300 + gi);
+            const uint32_t tO = tmem_base + 256;
+            const int nt = k ? a.f3_nto[1] : a.f3_nto[0], merged = k ? a.f3_merged[1] : a.f3_merged[0];
+            const uint32_t idesc = make_idesc_f16(nt);
+            const uint64_t lbo = (uint64_t)((uint32_t)(nt * 16) >> 4) << 16, bstep = (uint64_t)(nt * 2);
+            mbar_wait(full_bar, rpar);
+            if (!merged) {
+                if (elect_one()) { umma_bf16(tO, ones_desc, ring_desc + lbo, idesc, 0u); umma_commit(empty_bar); }
+                next_slot();
+                mbar_wait(full_bar, rpar);
+            }
+            if (elect_one()) {
+                uint64_t bd = ring_desc + lbo, ad = ach0_desc;
+                if (merged) { umma_bf16(tO, ones_desc, bd, idesc, 0u); bd += bstep; }
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) { umma_bf16_acc(tO, ad, bd, idesc); ad += 256; bd += bstep; }
+                umma_commit(empty_bar);
+            }
+            next_slot();
+            if (elect_one()) { umma_commit(bar(BAR_AFREE0)); umma_commit(bar(BAR_ACC2)); }
+            __syncwarp();
+            tr.ev(0x400 + gi);
+        };
+        l0(0, 0); l0(1, 1); l1(0, 2); l0(2, 3); l1(1, 4); l0(3, 5); l1(2, 6); l1(3, 7); l2(0, 8); l2(1, 9); l3(10);
+    }
+}
+
 // The loader of the same program, written out the same way: the weight tiles of an iteration in the order tc_mma_fast3
 // consumes them.  With two 32 KB ring slots (what two staged-row buffers leave) a tile's round trip -- the MMAs' commit, this
 // thread's wake-up and bookkeeping, the bulk copy -- is on the MMA role's critical path, so its bookkeeping counts too.
@@ -593,7 +739,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
     // parity to wait for: completion k (inside the item) of barrier b, given the barrier completions of all earlier items
     auto par_of = [](uint32_t bits, int b, int k) -> uint32_t { return ((bits >> b) ^ (uint32_t)k) & 1u; };
 
-    if (warp == TC_LOAD_WARP && a.fast3 && !(a.debug & 8)) {
+    if (warp == TC_LOAD_WARP && a.fast3 == 1 && !(a.debug & 8)) {
         tc_load_fast3(a, n_local, n_iter, smem_u32(ring), full0, empty0);
     } else if (warp == TC_LOAD_WARP) {
         // ================================================================ loader: one thread, runs ahead of the MMAs
@@ -634,6 +780,9 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
                 }
             }
         }
+    } else if (warp == TC_MMA_WARP && a.fast3 == 2) {
+        // ================================================================ MMA issue, hard-wired, single-phase program (tc_mma_fast1)
+        tc_mma_fast1(a, n_local, reh, smem_u32(x0), smem_u32(ach), smem_u32(ones), smem_u32(ring), full0, empty0, pb0, tmem_base);
     } else if (warp == TC_MMA_WARP && a.fast3) {
         // ================================================================ MMA issue, hard-wired (see tc_mma_fast3 below)
         tc_mma_fast3(a, n_local, n_iter, smem_u32(x0), smem_u32(ach), smem_u32(ones), smem_u32(ring), full0, empty0, pb0, tmem_base);
@@ -1452,6 +1601,30 @@ static int tc_fast3_params(const TcProgram& P, int& nfirst, int& nrest, int& nto
     return 1;
 }
 
+// ... and the single-phase program tc_mma_fast1 is written for.
+static int tc_fast1_params(const TcProgram& P, int& nfirst, int& nrest, int& nto, int& merged) {
+    if (P.phases != 1 || P.layers != 4 || P.pdims[1] != 512 || P.pdims[2] != 256 || P.pdims[3] != 128 || P.ngroups != 11 || P.nepis != 8 || P.odd_col != 256) return 0;
+    static const int want_layer[11] = {0, 0, 1, 0, 1, 0, 1, 1, 2, 2, 3}, want_idx[11] = {0, 1, 0, 2, 1, 3, 2, 3, 0, 1, 0};
+    for (int i = 0; i < 11; ++i) {
+        const TcGroup& g = P.g[i];
+        if (g.layer != want_layer[i]) return 0;
+        const int idx = g.layer == 0 ? g.n_base / TC_CHUNK : g.k_base / TC_CHUNK;
+        if (idx != want_idx[i]) return 0;
+        if (g.layer == 0) {
+            if (g.nt != 128 || !g.bias || g.kt0 == 0 || g.kc - g.kt0 > g.kt || g.a_src != 0 || g.tmem_col != (idx & 1) * 128) return 0;
+            nfirst = g.kt0 >> 4; nrest = (g.kc - g.kt0) >> 4;
+        } else if (g.layer == 1) {
+            if (g.nt != 256 || g.kc != 128 || g.kt != 64 || g.kt0 != 0 || g.bias != (idx == 0) || g.a_src != 1 + (idx & 1) || g.tmem_col != 256) return 0;
+        } else if (g.layer == 2) {
+            if (g.nt != 128 || g.kc != 128 || g.kt != 128 || g.kt0 != 0 || g.bias != (idx == 0) || g.a_src != 1 + idx || g.tmem_col != 0) return 0;
+        } else {
+            if (g.kc != 128 || g.kt != 128 || !g.bias || (g.kt0 != 0 && g.kt0 != 128) || g.a_src != 1 || g.tmem_col != 256 || g.nt > 128) return 0;
+            nto = g.nt; merged = g.kt0 != 0;
+        }
+    }
+    return 1;
+}
+
 static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
     for (int i = 0; i < a.nnets; ++i) { const uint32_t K0 = (uint32_t)a.prog[i].dims[0]; a.net[i].magic = (uint32_t)((0x100000000ull + K0 - 1) / K0); }
@@ -1514,6 +1687,11 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
         return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes_p[variant], st, a) == cudaSuccess
                    ? 0 : tc_fail(2, "pf_mlp_tc_kernel (two-phase): launch failed");
     }
+    // single-phase program: the hard-wired MMA role where the nets are the ones it is written for (the loader walks the program)
+    a.fast3 = (getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes == 32768) ? 2 : 0;
+    for (int i = 0; i < a.nnets && a.fast3; ++i)
+        if (!tc_fast1_params(a.prog[i], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i])) a.fast3 = 0;
+    if (a.nnets == 1) { a.f3_first[1] = a.f3_first[0]; a.f3_rest[1] = a.f3_rest[0]; a.f3_nto[1] = a.f3_nto[0]; a.f3_merged[1] = a.f3_merged[0]; }
     return pf_launch_pdl(pf_mlp_tc_kernel_std, dim3(grid), dim3(TC_THREADS_OF(8, 8)), (size_t)t->smem_bytes[variant], st, a) == cudaSuccess
                ? 0 : tc_fail(2, "pf_mlp_tc_kernel: launch failed");
 }
