@@ -1661,18 +1661,18 @@ static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     a.tmem_cols = TC_TMEM_COLS;
     const int grid = items < c->num_sms ? items : c->num_sms;
     // The two-phase programs: second half of item m interleaved with the first half of item m + 1.
-    // The two-phase program when a CTA walks several items AND the nets are the ones its hard-wired MMA / loader roles are
-    // written for (fast3: [*, 512, 256, 128, *]) AND the staged rows fit twice (inputs up to ~190 wide): 14-17 % faster at
-    // 262,144 rows, 7 % at 65,536.  Not otherwise: on the program interpreter it is a wash, with single-buffered staged rows
-    // slower (654 vs 635 us at 214 inputs), and a single-item launch is a pure latency chain that the single-phase program
-    // walks faster inside a step (rough 4,096 envs: 70.3 vs 76.2 us per step).  PF_TC_PIPE=0 / 1 (read per launch) forces it.
+    // The two-phase program is OPT-IN (PF_TC_PIPE=1, read per launch).  On the program interpreter it was a wash; with the
+    // hard-wired MMA / loader roles (fast3, the [*, 512, 256, 128, *] nets) it beat the interpreted single-phase program by
+    // 14-17 % -- and then the single-phase program got its own hard-wired role (tc_mma_fast1) and is 6-16 % faster than
+    // the two-phase one at every size (262,144 rows: 421 vs 448 us; 16,384: 41.5 vs 49.3): two accumulator slots and two
+    // chunk buffers for layer 0 are worth more than overlapping the two halves of consecutive items.  DESIGN.md 4.3.
     const char* pipe_env = getenv("PF_TC_PIPE");
     bool f3ok = t->pipe && getenv("PF_TC_NO_FAST3") == nullptr && t->slot_bytes_p == 32768;
     for (int i = 0; i < a.nnets && f3ok; ++i)
         for (int k = 0; k < 2; ++k)
             if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights))
                 f3ok = tc_fast3_params(t->progp[k], a.f3_first[i], a.f3_rest[i], a.f3_nto[i], a.f3_merged[i]) != 0;
-    if (t->pipe && (pipe_env ? atoi(pipe_env) != 0 : (f3ok && t->x0_nbuf_p == 2 && items > c->num_sms))) {
+    if (t->pipe && pipe_env && atoi(pipe_env) != 0) {
         for (int i = 0; i < a.nnets; ++i)
             for (int k = 0; k < 2; ++k)
                 if (a.net[i].blob == static_cast<const unsigned char*>(c->net[k].tc_weights)) a.prog[i] = t->progp[k];
