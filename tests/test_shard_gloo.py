@@ -99,19 +99,32 @@ def _env_worker(rank, world, port, task, N, steps, q):
         raise
 
 
-@pytest.mark.parametrize("task,N", [("pointfoot_flat", 64), ("pointfoot_rough", 51)])
-def test_two_shards_equal_one_unsharded_run(task, N):
+def _run_two_ranks(worker, extra, timeout):
+    """Two spawned gloo ranks on a fresh local port; the port is only known free at probe time, so ONE retry on a new port if the
+    ranks did not both exit cleanly (a lost rendezvous race must not look like a parity failure)."""
     ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = free_port()
-    procs = [ctx.Process(target=_env_worker, args=(r, 2, port, task, N, 3, q)) for r in range(2)]
-    [p.start() for p in procs]
-    [p.join(180) for p in procs]
-    msgs = []
-    while not q.empty():
-        msgs.append(q.get())
+    msgs, procs = [], []
+    for attempt in range(2):
+        q = ctx.Queue()
+        port = free_port()
+        procs = [ctx.Process(target=worker, args=(r, 2, port) + tuple(extra) + (q,)) for r in range(2)]
+        [p.start() for p in procs]
+        [p.join(timeout) for p in procs]
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+        msgs = []
+        while not q.empty():
+            msgs.append(q.get())
+        if all(p.exitcode == 0 for p in procs) and ("ok", True) in msgs:
+            break
     assert all(p.exitcode == 0 for p in procs), msgs
     assert ("ok", True) in msgs, msgs
+
+
+@pytest.mark.parametrize("task,N", [("pointfoot_flat", 64), ("pointfoot_rough", 51)])
+def test_two_shards_equal_one_unsharded_run(task, N):
+    _run_two_ranks(_env_worker, (task, N, 3), 180)
 
 
 def _ppo_worker(rank, world, port, q):
@@ -157,17 +170,7 @@ def _ppo_worker(rank, world, port, q):
 
 
 def test_ppo_reductions_match_oracle_on_concatenated_shards():
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = free_port()
-    procs = [ctx.Process(target=_ppo_worker, args=(r, 2, port, q)) for r in range(2)]
-    [p.start() for p in procs]
-    [p.join(120) for p in procs]
-    msgs = []
-    while not q.empty():
-        msgs.append(q.get())
-    assert all(p.exitcode == 0 for p in procs), msgs
-    assert ("ok", True) in msgs, msgs
+    _run_two_ranks(_ppo_worker, (), 120)
 
 
 def test_shard_range_partitions_every_env_once():
