@@ -341,6 +341,15 @@ __device__ __noinline__ void tc_sample_row(const TcArgs& a, long long er, const 
     if (a.has_storage) a.S.actions_log_prob[srow] = logp;
 }
 
+// A run of n accumulating N = 128 MMAs over the staged rows, the counts the usual input widths give unrolled (27 / 148 / 214
+// inputs: 2 | 7 + 3 | 7 + 7 K = 16 steps): three instructions per MMA instead of a loop's six
+__device__ __forceinline__ void tc_issue_x0_run(int n, uint32_t tmem_d, uint64_t ad, uint64_t bd, uint32_t idesc) {
+    if (n == 7) issue_mmas<TC_X0_KSTEP, 256, 7>(tmem_d, ad, bd, idesc);
+    else if (n == 3) issue_mmas<TC_X0_KSTEP, 256, 3>(tmem_d, ad, bd, idesc);
+    else if (n == 2) issue_mmas<TC_X0_KSTEP, 256, 2>(tmem_d, ad, bd, idesc);
+    else for (int k = 0; k < n; ++k) { umma_bf16_acc(tmem_d, ad, bd, idesc); ad += TC_X0_KSTEP; bd += 256; }
+}
+
 // The MMA role of the two-phase program for the nets every task of the reference uses ([in, 512, 256, 128, out]), written
 // out: the eleven groups of an iteration in the order build_program_pipe gives them, every descriptor stride, tile count,
 // barrier and parity a constant of the code -- no step table, no dispatch.  The program interpreter spends ~1.3k cycles
@@ -389,7 +398,7 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
                 uint64_t bd = ring_desc + lbo128, ad = xdesc;
                 umma_bf16(tS, ones_desc, bd, idesc128, 0u);
                 bd += 256;
-                for (int k = 0; k < nfirst; ++k) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                tc_issue_x0_run(nfirst, tS, ad, bd, idesc128);
                 umma_commit(empty_bar);
             }
             next_slot();
@@ -397,7 +406,7 @@ __device__ __noinline__ void tc_mma_fast3(const TcArgs& a, int n_local, int n_it
                 mbar_wait(full_bar, rpar);
                 if (elect_one()) {
                     uint64_t bd = ring_desc + lbo128, ad = xdesc + (uint64_t)(nfirst * TC_X0_KSTEP);
-                    for (int k = 0; k < nrest; ++k) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                    tc_issue_x0_run(nrest, tS, ad, bd, idesc128);
                     umma_commit(empty_bar);
                 }
                 next_slot();
@@ -532,7 +541,7 @@ __device__ __noinline__ void tc_mma_fast1(const TcArgs& a, int n_local, int reh,
                 uint64_t bd = ring_desc + lbo128, ad = xdesc;
                 umma_bf16(tS, ones_desc, bd, idesc128, 0u);
                 bd += 256;
-                for (int kk = 0; kk < nfirst; ++kk) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                tc_issue_x0_run(nfirst, tS, ad, bd, idesc128);
                 umma_commit(empty_bar);
             }
             next_slot();
@@ -540,7 +549,7 @@ __device__ __noinline__ void tc_mma_fast1(const TcArgs& a, int n_local, int reh,
                 mbar_wait(full_bar, rpar);
                 if (elect_one()) {
                     uint64_t bd = ring_desc + lbo128, ad = xdesc + (uint64_t)(nfirst * TC_X0_KSTEP);
-                    for (int kk = 0; kk < nrest; ++kk) { umma_bf16_acc(tS, ad, bd, idesc128); ad += TC_X0_KSTEP; bd += 256; }
+                    tc_issue_x0_run(nrest, tS, ad, bd, idesc128);
                     umma_commit(empty_bar);
                 }
                 next_slot();
