@@ -316,6 +316,18 @@ int pf_rl_tc_trace(pf_rl_ctx* ctx, unsigned long long* device_buf);
  * programmatic-dependency wait, so that the code of all its roles has been executed once while the predecessor kernel
  * (the env step) is still running.  For chains launched back to back (a CUDA-graphed step + act); off by default. */
 int pf_rl_tc_rehearse(pf_rl_ctx* ctx, int on);
+/* The inference kernels of the tensor-core paths read PACKED copies of the parameters, refreshed by a packing kernel after
+ * every optimizer step / pf_rl_params_changed.  Launched as programmatic dependents they stage those copies BEFORE their
+ * dependency wait, under the tail of the kernel in front of them -- unless that kernel may be the packing kernel itself.
+ * The context keeps track of that for what it launches; two calls cover what it cannot see:
+ *   pf_rl_weights_written  after replaying a CUDA graph that contains an optimizer step / pf_rl_params_changed
+ *                          (rl.PPO.update does): the next inference launch waits first;
+ *   pf_rl_early_weights    (ctx, 1): the caller vouches that inference launches it CAPTURES into a graph are never the
+ *                          first kernel after a repack when replayed (a step graph: env kernels, then act); without it
+ *                          captured launches always wait first.
+ * Opt-in for now: PF_RL_EARLY_WEIGHTS=1 in the environment enables the early staging; without it every launch waits first. */
+int pf_rl_weights_written(pf_rl_ctx* ctx);
+int pf_rl_early_weights(pf_rl_ctx* ctx, int on);
 /* Which kernels serve act / act_inference / evaluate of this context: 0 = fp32 SIMT chain (PF_RL_FP32), 1 = fused tcgen05
  * kernel (pf_mlp_tc.cu), 2 = register-resident warp-MMA kernel for small nets (pf_mlp_wm.cu: every hidden width a multiple of
  * 16 and <= 128, inputs <= 128, outputs <= 8 -- the pointfoot_flat policy; PF_RL_WM=0 in the environment disables it). */

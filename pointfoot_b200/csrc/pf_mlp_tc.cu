@@ -155,6 +155,7 @@ struct TcArgs {
     // K = 16 steps in its first (bias + K) tile and in its second tile, the output layer's UMMA N, and whether its bias
     // travels with its one K tile.  fast3 = 0: the program interpreter.
     int fast3, f3_first[2], f3_rest[2], f3_nto[2], f3_merged[2];
+    int weights_early;           // the loader may stream weight tiles before the dependency wait (pf_rl_weights_early)
     int rehearse;                // run one DRY item (no input loads, no outputs) before the dependency wait: see pf_rl_tc_rehearse
     int debug;                   // experiments only (PF_TC_DEBUG): bit 0 no storage copy, bit 1 no global loads, bit 3 no weight copies, bit 4 no MMAs,
                                  // bit 5 no barrier peek, bit 6 epilogue steps do no work, bit 7 epilogue converts without the ELU
@@ -663,7 +664,7 @@ __device__ __noinline__ void tc_load_fast3(const TcArgs& a, int n_local, int n_i
         if (++slot == S) { slot = 0; ++round; }
     };
     for (int it = 0; it < n_iter; ++it) {
-        if (it == 0) pf_grid_dep_wait();
+        if (it == 0 && !a.weights_early) pf_grid_dep_wait();
         const bool hasB = it < n_local, hasA = it >= 1;
         const int kB = (hasB && cta + it * gridn >= tiles) ? 1 : 0, kA = (hasA && cta + (it - 1) * gridn >= tiles) ? 1 : 0;
         const unsigned char* blobB = a.net[kB].blob;
@@ -758,7 +759,7 @@ __global__ void __launch_bounds__(TC_THREADS_OF(TC_EPI_WARPS, TC_STG_WARPS), kCt
             const uint32_t ring0 = smem_u32(ring), slot_bytes = (uint32_t)a.slot_bytes;
             TcTrace tr; tr.init(a.trace, 2, blockIdx.x == 0 && lane == 0);
             for (int it = -reh; it < n_iter; ++it) {
-                if (it == 0) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
+                if (it == 0 && !a.weights_early) pf_grid_dep_wait();      // (the dry item read the weights early: its results are discarded)
                 const int w0 = item_of(it, 0), w1 = item_of(it, 1);
                 const int k0n = w0 >= 0 ? (w0 >= a.tiles ? 1 : 0) : -1, k1n = w1 >= 0 ? (w1 >= a.tiles ? 1 : 0) : -1;
                 const TcProgram& PR = a.prog[k0n >= 0 ? k0n : k1n];          // step list (the same for both nets when two-phase)
@@ -1636,6 +1637,7 @@ static int tc_fast1_params(const TcProgram& P, int& nfirst, int& nrest, int& nto
 
 static int tc_launch(pf_rl_ctx* c, TcArgs& a, int variant, cudaStream_t st) {
     TcState* t = static_cast<TcState*>(c->tc);
+    a.weights_early = pf_rl_weights_early(c, st);
     for (int i = 0; i < a.nnets; ++i) { const uint32_t K0 = (uint32_t)a.prog[i].dims[0]; a.net[i].magic = (uint32_t)((0x100000000ull + K0 - 1) / K0); }
     a.tiles = (a.rows + TC_ROWS - 1) / TC_ROWS;
     a.stages = t->stages[variant];

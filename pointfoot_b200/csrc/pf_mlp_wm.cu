@@ -56,6 +56,7 @@ struct WmNetArgs {
 struct WmArgs {
     WmNetArgs n[2];
     int nnets, rows, tiles, stage_stride;      // stage_stride: floats of one warp's staging area
+    int weights_early;                         // the packed weights are NOT the product of the kernel right in front: stage them before the dependency wait
     uint32_t stage_off;                        // per-warp staging area offset in shared memory
     uint32_t seed, policy_step; int env_id_offset, num_actions;
     const float* std;
@@ -202,7 +203,7 @@ __global__ void __launch_bounds__(WM_WARPS * 32, 2) pf_mlp_wm_kernel(const __gri
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     pf_grid_dep_launch();
-    pf_grid_dep_wait();            // the weights may have been packed by the kernel in front of this one
+    if (!a.weights_early) pf_grid_dep_wait();            // the weights may have been packed by the kernel in front of this one
     for (int i = 0; i < a.nnets; ++i) {
         const uint4* src = reinterpret_cast<const uint4*>(a.n[i].blob);
         uint4* dst = reinterpret_cast<uint4*>(smem + a.n[i].smem_off);
@@ -215,6 +216,7 @@ __global__ void __launch_bounds__(WM_WARPS * 32, 2) pf_mlp_wm_kernel(const __gri
             for (int u = 0; u < 4; ++u) { const int k = k0 + u * WM_WARPS * 32 + tid; if (k < n16) dst[k] = v[u]; }
         }
     }
+    if (a.weights_early) pf_grid_dep_wait();             // ... or not (host-side bookkeeping): then they were staged under the predecessor's tail
     __syncthreads();
     float* stage = reinterpret_cast<float*>(smem + a.stage_off) + (size_t)warp * a.stage_stride;      // [16][K0] fp32 + [16][8] outputs
     const int ntasks = a.nnets * a.tiles;
@@ -415,6 +417,7 @@ int pf_wm_mlp_forward(pf_rl_ctx* c, int net, const float* x, long long ldx, int 
     a.n[0].net = t->net[net]; a.n[0].blob = t->blob[net];
     a.n[0].x = x; a.n[0].ldx = ldx; a.n[0].out = out; a.n[0].copy_to = copy_to; a.n[0].mode = WM_OUT_PLAIN;
     a.nnets = 1; a.rows = rows;
+    a.weights_early = pf_rl_weights_early(c, st);
     return wm_launch(c, a, st);
 }
 
@@ -438,6 +441,7 @@ int pf_wm_act(pf_rl_ctx* c, const float* params, const float* obs, const float* 
         }
     }
     a.nnets = 2; a.rows = P.num_envs;
+    a.weights_early = pf_rl_weights_early(c, st);
     a.seed = (uint32_t)P.seed; a.policy_step = (uint32_t)policy_step; a.env_id_offset = (int)P.env_id_offset; a.num_actions = P.num_actions;
     a.std = params + c->std_off;
     if (storage) { a.S = *storage; a.has_storage = 1; }

@@ -259,8 +259,33 @@ extern "C" int64_t pf_rl_param_offset(const pf_rl_ctx* c, int net, int layer, in
     return is_bias ? c->net[net].b_off[layer] : c->net[net].w_off[layer];
 }
 
+int pf_rl_weights_early(pf_rl_ctx* c, cudaStream_t st) {
+    static const bool on = [] { const char* e = getenv("PF_RL_EARLY_WEIGHTS"); return e && atoi(e) != 0; }();     // opt-in until measured
+    if (!on) return 0;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return 0; }
+    // captured: the launch will be replayed in surroundings this context cannot see -- only on the caller's word
+    if (cs != cudaStreamCaptureStatusNone) return c->early_in_graphs;
+    const int early = !c->weights_fresh;
+    c->weights_fresh = 0;
+    return early;
+}
+
+extern "C" int pf_rl_weights_written(pf_rl_ctx* c) {
+    if (!c) return rl_fail(1, "pf_rl_weights_written", "null context");
+    c->weights_fresh = 1;
+    return 0;
+}
+
+extern "C" int pf_rl_early_weights(pf_rl_ctx* c, int on) {
+    if (!c) return rl_fail(1, "pf_rl_early_weights", "null context");
+    c->early_in_graphs = on ? 1 : 0;
+    return 0;
+}
+
 extern "C" int pf_rl_params_changed(pf_rl_ctx* c, const float* params, void* stream) {
     if (!c || !params) return rl_fail(1, "pf_rl_params_changed", "null argument");
+    c->weights_fresh = 1;
     if (c->tc) { if (int rc = pf_tc_pack_weights(c, params, (cudaStream_t)stream)) return rc; }
     if (c->wm) { if (int rc = pf_wm_pack_weights(c, params, (cudaStream_t)stream)) return rc; }
     if (c->tc_gemm) return pf_tt_pack_weights(c, params, (cudaStream_t)stream);
@@ -906,6 +931,7 @@ extern "C" int pf_rl_adam_step(pf_rl_ctx* c, const pf_rl_learner* L, void* strea
     if (ublocks > c->num_sms * 8) ublocks = c->num_sms * 8;
     PF_LAUNCHED(), pf_adam_kernel<<<ublocks, 256, 0, st>>>(n, *L, sc);
     RL_CUDA(cudaGetLastError());
+    c->weights_fresh = 1;
     if (c->tc) { if (int rc = pf_tc_pack_weights(c, L->params, st)) return rc; }
     if (c->wm) { if (int rc = pf_wm_pack_weights(c, L->params, st)) return rc; }
     if (c->tc_gemm) return pf_tt_pack_weights(c, L->params, st);

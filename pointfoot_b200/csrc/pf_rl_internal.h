@@ -39,7 +39,14 @@ struct pf_rl_ctx {
     void* tc;                                   // opaque state of the tensor-core path (pf_mlp_tc.cu), or NULL
     void* wm;                                   // opaque state of the register-resident small-net path (pf_mlp_wm.cu), or NULL
     void* tc_gemm;                              // opaque state of the tensor-core training GEMM (pf_gemm_tc.cu), or NULL
+    // Packed inference weights: were they (re)written by the work most recently queued for them?  Then the next inference
+    // launch may be the packing kernel's direct successor and must not touch them before its programmatic-dependency
+    // wait; otherwise it stages / streams them under its predecessor's tail (pf_rl_weights_early()).
+    int weights_fresh;
+    int early_in_graphs;                        // pf_rl_early_weights(): the caller vouches for launches captured into graphs
 };
+// 1 if an inference launch on `st` may read the packed weights before its dependency wait (clears the fresh mark)
+int pf_rl_weights_early(pf_rl_ctx* c, cudaStream_t st);
 
 // ---- tensor-core path entry points (pf_mlp_tc.cu) ----
 int pf_tc_create(pf_rl_ctx* c);                                   // allocates packed weights, builds tile plans

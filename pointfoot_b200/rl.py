@@ -350,6 +350,8 @@ class PPO:
                 self._loss_acc.zero_()
         if use_graph:
             self._update_graph.replay()
+            # the replayed graph ends in the kernels that re-pack the inference weights: the next act must not read them early
+            self._lib.pf_rl_weights_written(self._ctx)
         else:
             n0 = self._lib.pf_debug_launch_count()
             self._update_steps()
@@ -562,6 +564,9 @@ class BenchPolicy:
         # the act kernel is launched right behind the env step's kernels (one CUDA graph): PF_RL_REHEARSE=1 lets it run a dry
         # item under their tail (pf_rl_tc_rehearse).  Off by default since the single-phase program got faster than the
         # rehearsal saves (rough 4,096 envs: 70.3 us per step without, 72.3 with; it was -5 us in round 1).
+        # the act launch is captured into the step's graph BEHIND the env step's kernels: it may stage its packed weights before
+        # its dependency wait (pf_rl_early_weights; the context cannot see what surrounds a captured launch, so it has to be told)
+        self.alg._lib.pf_rl_early_weights(self.alg._ctx, 1)
         if precision == "bf16" and os.environ.get("PF_RL_REHEARSE", "0") != "0":
             self.alg._lib.pf_rl_tc_rehearse(self.alg._ctx, 1)
 
