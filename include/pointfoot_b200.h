@@ -325,7 +325,7 @@ int pf_rl_tc_rehearse(pf_rl_ctx* ctx, int on);
  *   pf_rl_early_weights    (ctx, 1): the caller vouches that inference launches it CAPTURES into a graph are never the
  *                          first kernel after a repack when replayed (a step graph: env kernels, then act); without it
  *                          captured launches always wait first.
- * Opt-in for now: PF_RL_EARLY_WEIGHTS=1 in the environment enables the early staging; without it every launch waits first. */
+ * PF_RL_EARLY_WEIGHTS=0 in the environment disables the early staging altogether (every launch waits first). */
 int pf_rl_weights_written(pf_rl_ctx* ctx);
 int pf_rl_early_weights(pf_rl_ctx* ctx, int on);
 /* Which kernels serve act / act_inference / evaluate of this context: 0 = fp32 SIMT chain (PF_RL_FP32), 1 = fused tcgen05
