@@ -262,6 +262,7 @@ extern "C" int64_t pf_rl_param_offset(const pf_rl_ctx* c, int net, int layer, in
 int pf_rl_weights_early(pf_rl_ctx* c, cudaStream_t st) {
     static const bool off = [] { const char* e = getenv("PF_RL_EARLY_WEIGHTS"); return e && atoi(e) == 0; }();
     if (off) return 0;
+
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); return 0; }
     // captured: the launch will be replayed in surroundings this context cannot see -- only on the caller's word

@@ -1,8 +1,10 @@
 """GPU parity of the rsl_rl side (ActorCritic act/evaluate, storage writes, GAE, minibatch shuffle, PPO.update)
 through the C-ABI, against oracle/rsl_rl_ref.py.  Tolerances are stated in parity_rl.py."""
 import pytest
+import torch
 
 import parity_rl
+from pointfoot_b200 import rl
 
 pytestmark = pytest.mark.gpu
 
@@ -70,6 +72,37 @@ def test_tcgen05_odd_layer_count_many_items_per_cta():
     """Two hidden layers: the output layer accumulates in the TMEM columns the NEXT item's first chunk uses, so the next
     item has to wait for the final epilogue (BAR_ODONE) -- several items per CTA, ragged last tile"""
     parity_rl.run_act_and_gae(num_envs=40001, num_critic_obs=48, hidden=(256, 128), T=2, precision="bf16")
+
+
+@pytest.mark.parametrize("hidden,nc", [((128, 64, 32), 27), ((512, 256, 128), 148)])
+def test_inference_right_behind_a_repack_sees_the_new_weights(hidden, nc):
+    """The inference kernels stage their PACKED weights before their programmatic-dependency wait unless the packing kernel may
+    be right in front of them (pf_rl_weights_early).  Here it is: load_state_dict -> pack kernel -> act_inference, back to
+    back, six times with very different weights; then a second inference call (the early path) on the same weights.
+    (The packing kernels never trigger their dependents early, so a dependent only starts once they have exited; the wait
+    the bookkeeping adds is what makes their stores formally visible.  A forced always-early build passed this test too.)"""
+    torch.manual_seed(5)
+    ac = rl.ActorCritic(27, nc, 6, list(hidden), list(hidden), device="cuda:0")
+    ppo = rl.PPO(ac, device="cuda:0", precision="bf16")
+    ppo.init_storage(3000, 2, [27], [nc], [6])               # creates the context (and the parameter views)
+    try:
+        obs = torch.randn(3000, 27, device="cuda:0")
+        for it in range(6):
+            sd = {k: (torch.randn_like(v) * (0.02 + 0.05 * it)) for k, v in ac.state_dict().items()}
+            ac.load_state_dict(sd)                       # params_changed(): the pack kernel is now the last thing on the stream
+            got = [ac.act_inference(obs), ac.act_inference(obs)]
+            x = obs
+            n = len(hidden)
+            for l in range(n + 1):
+                x = x @ sd[f"actor.{2 * l}.weight"].t() + sd[f"actor.{2 * l}.bias"]
+                if l < n:
+                    x = torch.nn.functional.elu(x)
+            # (tolerance relative to the output scale: the point is stale weights -- errors of the size of the outputs --, and
+            # the larger weight scales make the outputs large sums with cancellation)
+            for g in got:
+                torch.testing.assert_close(g, x, rtol=2e-2, atol=2e-2 * float(x.abs().max()), msg=lambda m, it=it: f"iteration {it}: {m}")
+    finally:
+        ppo.close()
 
 
 def test_path_selection():
