@@ -52,6 +52,7 @@ struct WmNetArgs {
     const float* x; long long ldx;
     float* out; float* copy_to;
     int mode;
+    int flat3;                                 // the net is [<= 32, 128, 64, 32, <= 8]: layers called directly (set by wm_launch)
 };
 struct WmArgs {
     WmNetArgs n[2];
@@ -248,14 +249,24 @@ __global__ void __launch_bounds__(WM_WARPS * 32, 2) pf_mlp_wm_kernel(const __gri
         const unsigned char* blob = smem + N.smem_off;
         float* mrow0 = mtile + g * 8 + 2 * t;
         float* mrow8 = mrow0 + 64;
+        if (N.flat3) {
+            // the pointfoot_flat policy [<= 32, 128, 64, 32, <= 8]: the four layers called directly, no per-layer dispatch
+            auto W = [&](int l) { return reinterpret_cast<const uint2*>(blob + P.w_off[l]) + lane; };
+            auto Bv = [&](int l) { return reinterpret_cast<const float*>(blob + P.b_off[l]); };
+            wm_layer<2, 16>(af, W(0), Bv(0), t, false, mrow0, mrow8);
+            wm_layer<8, 8>(af, W(1), Bv(1), t, false, mrow0, mrow8);
+            wm_layer<4, 4>(af, W(2), Bv(2), t, false, mrow0, mrow8);
+            wm_layer<2, 1>(af, W(3), Bv(3), t, true, mrow0, mrow8);
+        } else {
 #pragma unroll 1
-        for (int l = 0; l < P.layers; ++l) {
-            const uint2* wl = reinterpret_cast<const uint2*>(blob + P.w_off[l]) + lane;
-            const float* bl = reinterpret_cast<const float*>(blob + P.b_off[l]);
-            const bool last = l + 1 == P.layers;
-            switch ((P.kp[l] >> 4) * 32 + (P.np[l] >> 3)) {          // warp-uniform: (k-steps, n-tiles) of this layer
-                WM_CASES(1) WM_CASES(2) WM_CASES(4) WM_CASES(8)
-                default: break;                                       // (pf_wm_create admits power-of-two widths only)
+            for (int l = 0; l < P.layers; ++l) {
+                const uint2* wl = reinterpret_cast<const uint2*>(blob + P.w_off[l]) + lane;
+                const float* bl = reinterpret_cast<const float*>(blob + P.b_off[l]);
+                const bool last = l + 1 == P.layers;
+                switch ((P.kp[l] >> 4) * 32 + (P.np[l] >> 3)) {          // warp-uniform: (k-steps, n-tiles) of this layer
+                    WM_CASES(1) WM_CASES(2) WM_CASES(4) WM_CASES(8)
+                    default: break;                                       // (pf_wm_create admits power-of-two widths only)
+                }
             }
         }
         __syncwarp();
@@ -394,6 +405,9 @@ static int wm_launch(pf_rl_ctx* c, WmArgs& a, cudaStream_t st) {
     WmNet nets[2];
     for (int i = 0; i < a.nnets; ++i) {
         a.n[i].smem_off = off; off += a.n[i].net.blob_bytes;
+        { const WmNet& w = a.n[i].net;
+          a.n[i].flat3 = w.layers == 4 && w.kp[0] == 32 && w.np[0] == 128 && w.kp[1] == 128 && w.np[1] == 64 && w.kp[2] == 64 && w.np[2] == 32 &&
+                         w.kp[3] == 32 && w.np[3] == 8 && getenv("PF_WM_NO_FLAT3") == nullptr; }
         if (a.n[i].net.k_true0 > k0) k0 = a.n[i].net.k_true0;
         nets[i] = a.n[i].net;
     }
