@@ -37,6 +37,28 @@ def test_warp_mma_small_net_act_matches_oracle_bf16(hidden, nc, n):
     parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=nc, hidden=hidden, T=3, precision="bf16")
 
 
+@pytest.mark.parametrize("n", [300, 50001])
+def test_warp_mma_flat_policy_through_the_layer_switch(n, monkeypatch):
+    """The flat policy's four layers are called directly (WmNetArgs.flat3); PF_WM_NO_FLAT3 sends the same nets through the
+    per-layer switch every other eligible shape uses: same parity bar, and the same bits as the direct calls"""
+    outs = []
+    for env in (None, "1"):
+        if env is None:
+            monkeypatch.delenv("PF_WM_NO_FLAT3", raising=False)
+        else:
+            monkeypatch.setenv("PF_WM_NO_FLAT3", env)
+            parity_rl.run_act_and_gae(num_envs=n, num_critic_obs=27, hidden=(128, 64, 32), T=2, precision="bf16")
+        ppo, _ = parity_rl.make_pair(n, 27, 27, [128, 64, 32], T=2, precision="bf16")
+        try:
+            assert ppo.inference_path == "warp_mma"
+            g = torch.Generator(device="cuda").manual_seed(5)
+            x = torch.randn(n, 27, device="cuda", generator=g)
+            outs.append(ppo.actor_critic.act_inference(x).clone())
+        finally:
+            ppo.close()
+    assert torch.equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("hidden,nc,n", [((128, 64, 32), 27, 300), ((128, 64, 32), 27, 50001)])
 def test_tcgen05_path_still_serves_small_nets_when_asked(hidden, nc, n, monkeypatch):
     """PF_RL_WM=0: the compact tcgen05 variant (two CTAs per SM) on the flat nets"""
