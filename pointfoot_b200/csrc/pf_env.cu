@@ -255,6 +255,98 @@ __global__ void __launch_bounds__(256, 4) pf_height_scan_kernel(const pf_params 
     pf_timeline(0x42);
 }
 
+// The same kernel for THE rough configuration of both pointfoot cfgs, everything warp-uniform decided at compile time or on
+// the host (pf_post_physics_impl): heightfield terrain, the critic's observations carry the height columns (both pointfoot cfgs:
+// 27 + 121 privileged columns) and with kActor the actor's too, noise on,
+// measured_heights not materialised, the index division of kind kDiv (1: x * RN(1/scale), 2: the checked Markstein step),
+// 32 * (kPasses - 1) < num_height_points <= 32 * kPasses so that only the last pass tests its lane.  Same arithmetic in
+// the same order as pf_scan_env (bit-identical; tests/test_env_gpu.py runs both): what goes is ~30 of ~100 issued
+// instructions per point -- pointer null tests, the division-kind dispatch, the lane's share of the noise hash.
+template <int kDiv>
+__device__ __forceinline__ int16_t pf_terrain_min3_k(const pf_params& P, const PfRewTab& T, const int16_t* __restrict__ hs, float x, float y) {
+    x = x + P.border_size;
+    y = y + P.border_size;
+    if (kDiv == 2) { x = pf_div_by(x, P.horizontal_scale, T.r_hscale); y = pf_div_by(y, P.horizontal_scale, T.r_hscale); }
+    else { x = x * T.r_hscale; y = y * T.r_hscale; }
+    const int px = (int)pf_minf(pf_maxf(x, 0.0f), T.rows_m2);
+    const int py = (int)pf_minf(pf_maxf(y, 0.0f), T.cols_m2);
+    const int16_t* r = hs + (px * P.hf_cols + py);
+    const int16_t h1 = __ldg(r), h2 = __ldg(r + P.hf_cols), h3 = __ldg(r + 1);
+    const int16_t m = h1 < h2 ? h1 : h2;
+    return m < h3 ? m : h3;
+}
+
+template <int kDiv, int kPasses, bool kActor>
+__global__ void __launch_bounds__(256, 4) pf_height_scan_std_kernel(const pf_params P, const pf_env_buffers B,
+                                                                    const PfCtxScratch S, const int epw,
+                                                                    const uint32_t step_arg) {
+    const int lane = threadIdx.x & 31;
+    const int gw = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), nw = (int)((gridDim.x * blockDim.x) >> 5);
+    pf_grid_dep_launch();
+    const int Pn = P.num_height_points, base_w = pf_obs_base_width(P);
+    float gx[kPasses], gy[kPasses], ns[kPasses];
+    uint32_t hk[kPasses];                               // the point's share of pf_rng_u32: (column) * 0x27D4EB2F
+#pragma unroll
+    for (int k = 0; k < kPasses; ++k) {
+        const int p = lane + 32 * k;
+        const bool ok = p < Pn;
+        const float2 g = ok ? reinterpret_cast<const float2*>(S.height_points)[p] : make_float2(0.f, 0.f);
+        gx[k] = g.x; gy[k] = g.y;
+        ns[k] = ok ? S.noise_vec[base_w + p] : 0.0f;
+        hk[k] = (uint32_t)(base_w + p) * 0x27D4EB2Fu;
+    }
+    const bool last_ok = lane + 32 * (kPasses - 1) < Pn;
+    pf_timeline(0x40);
+    pf_grid_dep_wait();
+    pf_timeline(0x41);
+    const uint32_t step = B.step_counter ? (uint32_t)(*B.step_counter + 1) : step_arg;
+    const uint32_t key0 = pf_rng_key(P.seed, step, PF_RNG_OBS_NOISE);
+    const double pn = (double)Pn;
+    for (int base = gw * epw; base < P.num_envs; base += nw * epw) {
+        const int nb = min(epw, P.num_envs - base);
+        float x = 0.0f, y = 0.0f, z = 0.0f, zn = 0.0f, wn = 1.0f;
+        uint32_t nkey = 0;
+        if (lane < nb) {
+            const float* g = B.root_states + (size_t)(base + lane) * 13;
+            x = g[0]; y = g[1]; z = g[2];
+            pf_yaw_quat(g + 3, zn, wn);
+            nkey = pf_rng_env_key(key0, (uint32_t)(P.env_id_offset + base + lane));
+        }
+        double hs = 0.0;
+        for (int j = 0; j < nb; ++j) {
+            const float bx = __shfl_sync(0xffffffffu, x, j), by = __shfl_sync(0xffffffffu, y, j), rz = __shfl_sync(0xffffffffu, z, j);
+            const float zj = __shfl_sync(0xffffffffu, zn, j), wj = __shfl_sync(0xffffffffu, wn, j);
+            const uint32_t kj = __shfl_sync(0xffffffffu, nkey, j);
+            float* oh = kActor ? B.obs_buf + (size_t)(base + j) * P.num_obs + base_w + lane : nullptr;
+            float* ph = B.priv_obs_buf + (size_t)(base + j) * P.num_priv_obs + base_w + lane;
+            const float zo = rz - 0.5f;
+            double acc = 0.0;
+#pragma unroll
+            for (int k = 0; k < kPasses; ++k) {
+                if (k < kPasses - 1 || last_ok) {
+                    const float t0 = -(zj * gy[k]) * 2.0f;                       // pf_scan_point
+                    const float t1 = (zj * gx[k]) * 2.0f;
+                    const float ox = (gx[k] + wj * t0) + (-(zj * t1));
+                    const float oy = (gy[k] + wj * t1) + (zj * t0);
+                    const int16_t r = pf_terrain_min3_k<kDiv>(P, S.rew, B.height_samples, ox + bx, oy + by);
+                    const float h = (float)r * P.vertical_scale;
+                    acc += (double)(rz - h);
+                    float v = pf_clipf(zo - h, -1.0f, 1.0f) * P.obs_scale_height;
+                    if (ns[k] != 0.0f)
+                        v = v + (2.0f * ((float)(pf_fmix32(kj ^ hk[k]) >> 8) * (1.0f / 16777216.0f)) - 1.0f) * ns[k];
+                    v = pf_clipf(v, -P.clip_obs, P.clip_obs);
+                    if (kActor) oh[32 * k] = v;
+                    ph[32 * k] = v;
+                }
+            }
+            const double sum = pf_warp_sum(acc);
+            if (lane == j) hs = sum;
+        }
+        if (lane < nb) S.height_mean[base + lane] = (float)(hs / pn);
+    }
+    pf_timeline(0x42);
+}
+
 // Warp partials for extras["episode"] (PF:276-288): count, terrain-level sum, per-term episode sums of the
 // warp's reset envs (read back BEFORE pf_env_reset zeroes them).  Entry index = global warp-slab index.
 __device__ __forceinline__ void pf_warp_partials(const pf_params& P, const pf_env_buffers& B, const PfCtxScratch& S,
@@ -878,7 +970,23 @@ static int pf_post_physics_impl(pf_ctx* c, const pf_env_buffers* bufs, int64_t c
         const int warps = (c->P.num_envs + sepw - 1) / sepw;
         int blocks = (warps + 7) / 8;
         if (blocks > c->num_sms * 8) blocks = c->num_sms * 8;
-        if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
+        // the specialised scan (pf_height_scan_std_kernel) where every condition it compiles in holds; PF_SCAN_NO_STD=1: never
+        const char* nse = getenv("PF_SCAN_NO_STD");
+        const int no_std = nse ? atoi(nse) : 0;
+        const int Pn = c->P.num_height_points, kind = c->S.rew.index_div_kind;
+        const bool stdcfg = !no_std && c->canonical && (kind == 1 || kind == 2) && c->P.terrain_kind == PF_TERRAIN_HEIGHTFIELD &&
+                            !bufs->measured_heights && c->P.measure_heights_critic && bufs->priv_obs_buf &&
+                            c->P.add_noise;
+        if (stdcfg && ((Pn > 96 && Pn <= 128) || (Pn > 160 && Pn <= 192))) {
+            using ScanFn = void (*)(const pf_params, const pf_env_buffers, const PfCtxScratch, const int, const uint32_t);
+            static const ScanFn fns[2][2][2] = {       // [kind - 1][passes 4 / 6][actor]
+                {{pf_height_scan_std_kernel<1, 4, false>, pf_height_scan_std_kernel<1, 4, true>},
+                 {pf_height_scan_std_kernel<1, 6, false>, pf_height_scan_std_kernel<1, 6, true>}},
+                {{pf_height_scan_std_kernel<2, 4, false>, pf_height_scan_std_kernel<2, 4, true>},
+                 {pf_height_scan_std_kernel<2, 6, false>, pf_height_scan_std_kernel<2, 6, true>}}};
+            PF_CUDA(pf_launch_pdl(fns[kind - 1][Pn > 128 ? 1 : 0][c->P.measure_heights_actor ? 1 : 0], dim3(blocks), dim3(256), 0, st,
+                                  c->P, *bufs, c->S, sepw, step32));
+        } else if (c->canonical) PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<true>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
         else PF_CUDA(pf_launch_pdl(pf_height_scan_kernel<false>, dim3(blocks), dim3(256), 0, st, c->P, *bufs, c->S, sepw, step32));
     }
     // the specialised kernels read / write pairs of the per-env state as 64-bit words: 8-byte aligned tensors only

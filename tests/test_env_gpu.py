@@ -318,26 +318,48 @@ def test_pointfoot_class_pushes_without_a_host_sync_and_inside_a_graph():
     env.close()
 
 
-def test_step_outputs_do_not_depend_on_materialising_measured_heights():
+def _actor_heights(cfg):
+    """the actor sees the height columns as well (terrain.measure_heights_actor, PF:367-369)"""
+    cfg.terrain.measure_heights_actor = True
+    cfg.env.num_propriceptive_obs = 27 + 121
+
+
+@pytest.mark.parametrize("N,grid187,actor", [(777, False, False), (777, True, False), (70001, False, False), (70001, True, False),
+                                             (5000, False, True)])
+def test_step_outputs_do_not_depend_on_materialising_measured_heights(N, grid187, actor, monkeypatch):
     """measured_heights is written only for a caller that asks (PointFoot(keep_measured_heights=True)); observations,
-    rewards and the episode sums -- its readers on the step path -- are bit-identical either way"""
+    rewards and the episode sums -- its readers on the step path -- are bit-identical either way.  Without it the rough
+    cfgs take the specialised scan kernel (pf_height_scan_std_kernel: 121 points = 4 passes, 187 = 6; one env per warp at
+    777 envs, 8 at 70,001), with it the general one; PF_SCAN_NO_STD=1 (third env) is the general one without the buffer"""
     import common
     from pointfoot_b200 import synth
     from pointfoot_b200.env import PointFoot
-    N, task = 777, "pointfoot_rough"
+    task = "pointfoot_rough"
     state = synth.make_state(N, task, seed=6, adversarial=True)
     envs = []
-    for keep in (False, True):
-        cfg = common.make_cfg(task, N)
+    for keep, no_std in ((False, False), (True, False), (False, True)):
+        cfg = common.make_cfg(task, N, common.grid187 if grid187 else (_actor_heights if actor else None))
         envs.append(PointFoot(cfg, None, None, "cuda:0", True, state=common.clone_state(state), seed=1, keep_measured_heights=keep))
+        envs[-1]._no_std = no_std
+    real_step = PointFoot.step
+
+    def step(e, a):                                    # the switch is read at every launch
+        if e._no_std:
+            monkeypatch.setenv("PF_SCAN_NO_STD", "1")
+        else:
+            monkeypatch.delenv("PF_SCAN_NO_STD", raising=False)
+        out = real_step(e, a)
+        torch.cuda.synchronize()
+        return out
     a = synth.make_state(N, task, seed=7)["actions"].cuda()
     for _ in range(3):
-        outs = [e.step(a) for e in envs]
-        torch.cuda.synchronize()
-        for x, y in zip(outs[0][:4], outs[1][:4]):
-            assert torch.equal(x, y)
-        assert torch.equal(envs[0]._episode_sums, envs[1]._episode_sums)
-    assert envs[1].measured_heights.shape == (N, 121) and float(envs[1].measured_heights.abs().sum()) > 0
+        outs = [step(e, a) for e in envs]
+        for other in (1, 2):
+            for x, y in zip(outs[0][:4], outs[other][:4]):
+                assert torch.equal(x, y)
+            assert torch.equal(envs[0]._episode_sums, envs[other]._episode_sums)
+    monkeypatch.delenv("PF_SCAN_NO_STD", raising=False)
+    assert envs[1].measured_heights.shape == (N, 187 if grid187 else 121) and float(envs[1].measured_heights.abs().sum()) > 0
     with pytest.raises(AttributeError, match="keep_measured_heights"):
         envs[0].measured_heights
     for e in envs:
