@@ -724,7 +724,8 @@ def run_b200(args):
             cases = [(t, n, g) for t, g in (("pointfoot_flat", False), ("pointfoot_rough", False), ("pointfoot_rough", True))
                      for n in (4096, 65536, 262144)]
         else:       # C5: a fixed 262,144-env job sharded over the ranks (strong) and 32,768 envs per GPU (weak)
-            cases = [(t, n, False) for t in ("pointfoot_flat", "pointfoot_rough") for n in (262144 // world, 32768)]
+            cases = [(t, n, False) for t in ("pointfoot_flat", "pointfoot_rough")
+                     for n in dict.fromkeys((262144 // world, 32768))]         # at 8 ranks the two are the same case: once
         terrain = None
         for task, n, g187 in cases:
             if world == 1 and task == args.task and n == args.num_envs and not g187:
@@ -735,7 +736,8 @@ def run_b200(args):
             ws = Workload(task, n, device, rank, world, grid187=g187, terrain=terrain if task == "pointfoot_rough" else None)
             r, _, _ = measure_workload(ws, args, flush, barrier, peaks, device, min(args.min_seconds, 0.25), 30)
             if world > 1:
-                r["scaling"] = "strong (262,144 envs in total)" if n == 262144 // world else "weak (32,768 envs per GPU)"
+                r["scaling"] = ("strong (262,144 envs in total) = weak (32,768 envs per GPU)" if 262144 // world == 32768 else
+                                "strong (262,144 envs in total)" if n == 262144 // world else "weak (32,768 envs per GPU)")
             sweep.append(r)
             ws.close()
             torch.cuda.empty_cache()
