@@ -667,6 +667,16 @@ def ppo_iteration(n_per_gpu, task, precision, device, rank, world, iters=3):
     return out
 
 
+
+def sweep_cases(world):
+    """(task, envs per GPU, 187-point grid) of the size sweep.  One GPU: both tasks at 4,096 / 65,536 / 262,144 envs plus the
+    rough task on the LeggedRobotCfg grid.  Several: C5 -- a fixed 262,144-env job sharded over the ranks (strong) and 32,768
+    envs per GPU (weak); at 8 ranks the two are the same case and run once."""
+    if world == 1:
+        return [(t, n, g) for t, g in (("pointfoot_flat", False), ("pointfoot_rough", False), ("pointfoot_rough", True))
+                for n in (4096, 65536, 262144)]
+    return [(t, n, False) for t in ("pointfoot_flat", "pointfoot_rough") for n in dict.fromkeys((262144 // world, 32768))]
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -720,12 +730,7 @@ def run_b200(args):
     # ---- sweep (1 GPU) / config C5 (N GPUs) ----
     sweep = []
     if not args.no_sweep:
-        if world == 1:
-            cases = [(t, n, g) for t, g in (("pointfoot_flat", False), ("pointfoot_rough", False), ("pointfoot_rough", True))
-                     for n in (4096, 65536, 262144)]
-        else:       # C5: a fixed 262,144-env job sharded over the ranks (strong) and 32,768 envs per GPU (weak)
-            cases = [(t, n, False) for t in ("pointfoot_flat", "pointfoot_rough")
-                     for n in dict.fromkeys((262144 // world, 32768))]         # at 8 ranks the two are the same case: once
+        cases = sweep_cases(world)
         terrain = None
         for task, n, g187 in cases:
             if world == 1 and task == args.task and n == args.num_envs and not g187:

@@ -80,3 +80,18 @@ def test_redzone_helper_detects_overruns_on_either_side():
     raw[rz.PAD - 1] = 1
     with pytest.raises(AssertionError, match="BELOW buffer t"):
         rz.check()
+
+
+def test_bench_sweep_cases_cover_c5_once_per_case():
+    """bench.py's size sweep: nine single-GPU cases; under torchrun the 262,144-env job sharded over the ranks plus 32,768
+    envs per GPU -- which coincide at 8 ranks and must then run once (host logic only: nothing is launched)"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert len(bench.sweep_cases(1)) == 9 and ("pointfoot_rough", 262144, True) in bench.sweep_cases(1)
+    for world in (2, 4, 8):
+        cases = bench.sweep_cases(world)
+        assert len(cases) == len(set(cases))
+        assert {n for _, n, _ in cases} == {262144 // world, 32768}
+        assert {t for t, _, _ in cases} == {"pointfoot_flat", "pointfoot_rough"}
